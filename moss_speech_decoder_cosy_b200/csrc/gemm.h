@@ -1,0 +1,89 @@
+// Implicit-GEMM core of the decode path (host-visible declarations).
+//
+//   out[row, n] = epilogue( sum_seg sum_c A_seg[row + shift_seg, col0_seg + c] * W[n, koff_seg + c] )
+//
+// Activations live channels-last ([rows, C], bf16) so a Conv1d / ConvTranspose1d tap is a
+// row-shifted K-slab of the same matrix ("segment").  Rows of different utterances are packed
+// back to back with zero guard rows between them, so shifted reads see the conv zero padding.
+// The kernel is a persistent, warp-specialised tcgen05 kernel: TMA producer warp -> 4-stage
+// smem ring -> single-thread tcgen05.mma issuer -> double-buffered fp32 accumulators in TMEM
+// -> 4 epilogue warps (thread == output row, so LayerNorm over channels is thread-local).
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <stdint.h>
+
+namespace mossdec {
+
+enum Act : int32_t {
+    ACT_NONE = 0,
+    ACT_MISH = 1,
+    ACT_GELU = 2,   // exact erf GELU (diffusers GELU, approximate="none")
+    ACT_ELU = 3,
+    ACT_LRELU = 4,  // slope in act_p
+    ACT_SNAKE = 5,  // x + sin^2(alpha x) / (alpha + 1e-9), alpha per channel
+    ACT_SILU = 6,
+    ACT_ABS = 7,
+};
+
+constexpr int kGemmMaxSegs = 12;
+constexpr int kGemmBM = 128;   // rows per tile == TMEM lanes
+constexpr int kGemmBK = 64;    // bf16 elements per k-block == one 128-byte swizzle span
+constexpr int kGemmStages = 4;
+
+struct GemmSeg {
+    int32_t map;        // which A tensor (0 or 1)
+    int32_t row_shift;  // added to the tile's first row (conv tap offset, may be negative)
+    int32_t col0;       // first channel of this slab inside A
+    int32_t nkb;        // number of 64-wide k-blocks
+};
+
+struct GemmEpilogue {
+    const float* bias = nullptr;       // [N]
+    const float* ln1_g = nullptr;      // LayerNorm over the full row (needs N == BN), applied to acc+bias
+    const float* ln1_b = nullptr;
+    int32_t act1 = ACT_NONE;
+    float act1_p = 0.f;
+    const float* act1_alpha = nullptr; // [N] for snake
+    const int32_t* row_seq = nullptr;  // [M] utterance id of each row, -1 for guard rows (output forced to 0)
+    const float* tbias = nullptr;      // [num_seq, tbias_ld] added after act1 (time-embedding bias)
+    int32_t tbias_ld = 0;
+    const float* resid = nullptr;      // fp32 [M, ldr] added after tbias
+    int32_t ldr = 0;
+    int32_t accum_f32 = 0;             // v += out_f32 (before scaling)
+    float out_scale = 1.f;
+    float* out_f32 = nullptr;          // fp32 [M, ldf]
+    int32_t ldf = 0;
+    __nv_bfloat16* out_bf16 = nullptr; // bf16 [M, ldo]: LN2 / act2 applied to the fp32 value
+    int32_t ldo = 0;
+    const float* ln2_g = nullptr;
+    const float* ln2_b = nullptr;
+    int32_t act2 = ACT_NONE;
+    float act2_p = 0.f;
+    const float* act2_alpha = nullptr;
+    float ln_eps = 1e-5f;
+};
+
+struct GemmOperandA {
+    const __nv_bfloat16* ptr = nullptr;
+    int64_t rows = 0;      // extent of the row dimension (reads outside are zero-filled by TMA)
+    int32_t cols = 0;      // extent of the channel dimension
+    int64_t ld = 0;        // row stride in elements (may be < cols for overlapping windows); ld*2 % 16 == 0
+};
+
+struct GemmProblem {
+    GemmOperandA a[2];
+    const __nv_bfloat16* w = nullptr;  // [N, K] K-major, K = 64 * total k-blocks
+    int32_t M = 0;                     // output rows; buffers must be padded to a multiple of 128 rows
+    int32_t N = 0;
+    int32_t BN = 0;                    // n-tile (multiple of 16, <= 256)
+    int32_t num_segs = 0;
+    GemmSeg segs[kGemmMaxSegs];
+    GemmEpilogue epi;
+};
+
+// Enqueue on `stream`.  Returns cudaSuccess or the failing CUDA error; -1 style argument errors
+// are reported as cudaErrorInvalidValue.
+cudaError_t gemm_tc_launch(const GemmProblem& p, int num_sms, cudaStream_t stream);
+
+}  // namespace mossdec
