@@ -87,7 +87,9 @@ def _get_activation(name):
 
 
 def _mod(name, **attrs):
+    import importlib.machinery
     m = types.ModuleType(name)
+    m.__spec__ = importlib.machinery.ModuleSpec(name, None)
     m.__dict__.update(attrs)
     sys.modules[name] = m
     return m
@@ -135,6 +137,16 @@ def install(with_audio_decoder: bool = True):
         mu = _mod("matcha.utils")
         mu.__path__ = [os.path.join(matcha_root, "matcha", "utils")]
         _mod("matcha.utils.pylogger", get_pylogger=lambda name=__name__: logging.getLogger(name))
+    # class_utils.py:35,38 imports the text->token LLMs and CLI front ends only to list them in a registry; they are
+    # out of scope and drag in transformers/Qwen2, so give the registry inert placeholders.
+    if "cosyvoice.llm.llm" not in sys.modules:
+        import importlib
+        importlib.import_module("cosyvoice")
+        for pkg in ("cosyvoice.llm", "cosyvoice.cli"):
+            pm = _mod(pkg)
+            pm.__path__ = [os.path.join(REF_ROOT, *pkg.split("."))]
+        _mod("cosyvoice.llm.llm", TransformerLM=_Unsupported, Qwen2LM=_Unsupported)
+        _mod("cosyvoice.cli.model", CosyVoiceModel=_Unsupported, CosyVoice2Model=_Unsupported)
     if with_audio_decoder:
         if "hyperpyyaml" not in sys.modules:
             _mod("hyperpyyaml", load_hyperpyyaml=lambda f: _HYPER["cfg"])
