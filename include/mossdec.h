@@ -1,0 +1,93 @@
+/* mossdec -- C ABI of the B200-native token->waveform decode path of MOSS-Speech-decoder-cosy.
+ *
+ * The reference is pure Python/PyTorch; the one FFI-shaped boundary it already has for this path is the TensorRT
+ * estimator contract in GLM_modules/cosyvoice/flow/flow_matching.py:129-156 (raw data_ptr()s of contiguous fp32
+ * tensors, enqueue on a CUDA stream).  Every entry point below replaces a reference call with the same tensor
+ * layouts, so a maintainer can bind it with ctypes:
+ *
+ *   mossdec_estimator   <- ConditionalCFM.forward_estimator          flow_matching.py:129-156 / decoder.py:405-494
+ *   mossdec_flow_solve  <- CausalConditionalCFM.forward + solve_euler flow_matching.py:206-230, 76-127
+ *   mossdec_hift        <- HiFTGenerator.inference                    hifigan/generator.py:570-582
+ *   mossdec_set_tensor  <- nn.Module.load_state_dict                  flow_inference.py:59-61
+ *
+ * All data pointers are DEVICE pointers owned by the caller unless stated otherwise; `stream` is a cudaStream_t
+ * passed as void*.  Calls only enqueue work (no host synchronisation except inside mossdec_set_tensor and the
+ * small layout uploads at the start of a call).  Return value: 0 = OK, negative = error (message via
+ * mossdec_last_error).  A handle must not be used from two threads at once.
+ */
+#ifndef MOSSDEC_H_
+#define MOSSDEC_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct mossdec_handle mossdec_handle;
+
+enum { MOSSDEC_F32 = 0, MOSSDEC_BF16 = 1, MOSSDEC_I32 = 2 };
+
+typedef struct mossdec_config {
+    int32_t n_feats;      /* 80   mel bins                                   flow.py:154            */
+    int32_t channels;     /* 256  estimator width (channels=[256])           decoder.py:294         */
+    int32_t heads;        /* 8                                                                    */
+    int32_t head_dim;     /* 64                                                                   */
+    int32_t n_blocks;     /* 4    transformer blocks per group                                    */
+    int32_t n_mid;        /* 12   mid groups                                                      */
+    int32_t noise_len;    /* 15000 frames of the fixed noise bank             flow_matching.py:203 */
+    int32_t hift_base;    /* 512                                              generator.py:400     */
+    int32_t n_harmonics;  /* 8 (+1 fundamental)                                                   */
+    float sample_rate;    /* 24000                                                                */
+    float nsf_alpha, nsf_sigma, voiced_threshold, lrelu_slope, audio_limit;
+} mossdec_config;
+
+/* Fill `cfg` with the pinned CosyVoice2-style configuration. */
+void mossdec_default_config(mossdec_config* cfg);
+
+int mossdec_create(const mossdec_config* cfg, mossdec_handle** out);
+void mossdec_destroy(mossdec_handle* h);
+const char* mossdec_last_error(const mossdec_handle* h);
+
+/* Upload one engine-ready tensor (HOST pointer; copied).  Names/layouts: moss_speech_decoder_cosy_b200/weights.py. */
+int mossdec_set_tensor(mossdec_handle* h, const char* name, const void* host_data, int32_t dtype, int32_t ndim,
+                       const int64_t* shape);
+/* Check that every tensor the engine needs is present. */
+int mossdec_finalize(mossdec_handle* h);
+
+/* One estimator evaluation, dense batch.  x, mu, cond, out: [B2, 80, T] fp32; mask: [B2, 1, T] (ignored: all valid);
+ * t: [B2]; spks: [B2, 80] (spks / cond may be NULL = zeros).  chunk = 0 -> full attention, > 0 -> block-causal mask
+ * with `chunk` mel frames (decoder.py:439-440, streaming=True). */
+int mossdec_estimator(mossdec_handle* h, int32_t B2, int32_t T, const float* x, const float* mask, const float* mu,
+                      const float* t, const float* spks, const float* cond, float* out, int32_t chunk, void* stream);
+
+/* n_steps Euler steps with classifier-free guidance for B utterances of lens[b] frames (HOST array).
+ * mu, cond, mel_out: ragged [80, lens[b]] blocks back to back (for equal lengths this is [B, 80, T]); spks [B, 80].
+ * noise: NULL -> the bank uploaded as tensor "flow.rand_noise" [80, noise_len]; else a device bank [80, noise_len_arg]
+ * shared by all utterances (z = bank[:, :T] * temperature, flow_matching.py:225). */
+int mossdec_flow_solve(mossdec_handle* h, int32_t B, const int32_t* lens, const float* mu, const float* spks,
+                       const float* cond, const float* noise, int32_t noise_len_arg, int32_t n_steps, float cfg_rate,
+                       float temperature, int32_t chunk, float* mel_out, void* stream);
+
+/* HiFT vocoder for B mel segments of lens[b] frames (HOST array): mel ragged [80, lens[b]] back to back ->
+ * wav_out ragged [480 * lens[b]], source_out ragged [480 * lens[b]] (may be NULL).
+ * cache_source / cache_len: optional per-utterance source prefix (generator.py:579-580); cache_source is
+ * [B, cache_stride] with cache_len[b] valid samples (HOST array) -- NULL = none.
+ * nsf_noise: optional injected N(0,1) draws, ragged [480 * lens[b], 9] (sample-major, torch.randn_like order of
+ * generator.py:334); NULL -> counter-based Philox on device seeded with `seed`. */
+int mossdec_hift(mossdec_handle* h, int32_t B, const int32_t* lens, const float* mel, const float* cache_source,
+                 int32_t cache_stride, const int32_t* cache_len, const float* nsf_noise, float* wav_out,
+                 float* source_out, uint64_t seed, void* stream);
+
+/* Streaming glue (flow_inference.py:35-43,151-156): speech[:n] = speech[:n]*w[:n] + prev_tail[:n]*w[n:], fp32, device. */
+int mossdec_fade_in_out(mossdec_handle* h, float* speech, const float* prev_tail, const float* window2n, int32_t n,
+                        void* stream);
+
+/* Number of kernels this handle has enqueued since creation / last reset (bench.py reports it as gpu_launches). */
+int64_t mossdec_launch_count(const mossdec_handle* h);
+void mossdec_reset_launch_count(mossdec_handle* h);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MOSSDEC_H_ */

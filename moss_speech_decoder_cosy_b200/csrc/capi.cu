@@ -1,0 +1,81 @@
+// extern "C" surface of libmossdec.so (include/mossdec.h).
+#include "mossdec.h"
+
+#include "engine.h"
+
+using mossdec::Engine;
+using mossdec::EngineConfig;
+
+struct mossdec_handle {
+    Engine* eng;
+    std::string create_err;
+};
+
+extern "C" {
+
+void mossdec_default_config(mossdec_config* c) {
+    c->n_feats = 80; c->channels = 256; c->heads = 8; c->head_dim = 64; c->n_blocks = 4; c->n_mid = 12;
+    c->noise_len = 15000; c->hift_base = 512; c->n_harmonics = 8; c->sample_rate = 24000.f;
+    c->nsf_alpha = 0.1f; c->nsf_sigma = 0.003f; c->voiced_threshold = 10.f; c->lrelu_slope = 0.1f;
+    c->audio_limit = 0.99f;
+}
+
+int mossdec_create(const mossdec_config* c, mossdec_handle** out) {
+    if (!c || !out) return -1;
+    if (c->head_dim != 64 || c->channels != 256 || c->n_feats != 80 || c->heads * c->head_dim != 512) return -2;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) return -3;  // no CPU fallback: fail loudly
+    EngineConfig e;
+    e.n_feats = c->n_feats; e.channels = c->channels; e.heads = c->heads; e.head_dim = c->head_dim;
+    e.n_blocks = c->n_blocks; e.n_mid = c->n_mid; e.time_dim = 4 * c->channels; e.in_channels = 4 * c->n_feats;
+    e.noise_len = c->noise_len; e.hift_base = c->hift_base; e.n_harm = c->n_harmonics + 1;
+    e.sample_rate = c->sample_rate; e.sine_amp = c->nsf_alpha; e.noise_std = c->nsf_sigma;
+    e.voiced_thr = c->voiced_threshold; e.lrelu = c->lrelu_slope; e.audio_limit = c->audio_limit;
+    mossdec_handle* h = new mossdec_handle;
+    h->eng = new Engine(e);
+    *out = h;
+    return 0;
+}
+
+void mossdec_destroy(mossdec_handle* h) {
+    if (!h) return;
+    delete h->eng;
+    delete h;
+}
+
+const char* mossdec_last_error(const mossdec_handle* h) { return h ? h->eng->last_error() : "null handle"; }
+
+int mossdec_set_tensor(mossdec_handle* h, const char* name, const void* host_data, int32_t dtype, int32_t ndim,
+                       const int64_t* shape) {
+    return h->eng->set_tensor(name, host_data, dtype, ndim, shape);
+}
+int mossdec_finalize(mossdec_handle* h) { return h->eng->finalize(); }
+
+int mossdec_estimator(mossdec_handle* h, int32_t B2, int32_t T, const float* x, const float* mask, const float* mu,
+                      const float* t, const float* spks, const float* cond, float* out, int32_t chunk, void* stream) {
+    return h->eng->estimator(B2, T, x, mask, mu, t, spks, cond, out, chunk, (cudaStream_t)stream);
+}
+
+int mossdec_flow_solve(mossdec_handle* h, int32_t B, const int32_t* lens, const float* mu, const float* spks,
+                       const float* cond, const float* noise, int32_t noise_len_arg, int32_t n_steps, float cfg_rate,
+                       float temperature, int32_t chunk, float* mel_out, void* stream) {
+    return h->eng->flow_solve(B, lens, mu, spks, cond, noise, noise_len_arg, n_steps, cfg_rate, temperature, chunk,
+                              mel_out, (cudaStream_t)stream);
+}
+
+int mossdec_hift(mossdec_handle* h, int32_t B, const int32_t* lens, const float* mel, const float* cache_source,
+                 int32_t cache_stride, const int32_t* cache_len, const float* nsf_noise, float* wav_out,
+                 float* source_out, uint64_t seed, void* stream) {
+    return h->eng->hift(B, lens, mel, cache_source, cache_stride, cache_len, nsf_noise, wav_out, source_out, seed,
+                        (cudaStream_t)stream);
+}
+
+int mossdec_fade_in_out(mossdec_handle* h, float* speech, const float* prev_tail, const float* window2n, int32_t n,
+                        void* stream) {
+    return h->eng->fade_in_out(speech, prev_tail, window2n, n, (cudaStream_t)stream);
+}
+
+int64_t mossdec_launch_count(const mossdec_handle* h) { return h->eng->launches(); }
+void mossdec_reset_launch_count(mossdec_handle* h) { h->eng->reset_launches(); }
+
+}  // extern "C"

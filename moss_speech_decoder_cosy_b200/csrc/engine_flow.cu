@@ -1,0 +1,402 @@
+// Engine: weight store, flow layout, estimator forward and the CFG Euler solver.
+#include "engine.h"
+
+#include <math.h>
+#include <stdio.h>
+#include <string.h>
+
+namespace mossdec {
+
+#define MD_CUDA(x)                                                                          \
+    do {                                                                                    \
+        cudaError_t e_ = (x);                                                               \
+        if (e_ != cudaSuccess) return fail(std::string(#x) + ": " + cudaGetErrorString(e_)); \
+    } while (0)
+
+bool DeviceBuffer::reserve(size_t bytes) {
+    if (bytes <= bytes_) return false;
+    release();
+    if (cudaMalloc(&ptr_, bytes) != cudaSuccess) {
+        ptr_ = nullptr;
+        bytes_ = 0;
+        return true;
+    }
+    cudaMemset(ptr_, 0, bytes);
+    bytes_ = bytes;
+    return true;
+}
+void DeviceBuffer::release() {
+    if (ptr_) cudaFree(ptr_);
+    ptr_ = nullptr;
+    bytes_ = 0;
+}
+
+Engine::Engine(const EngineConfig& cfg) : cfg_(cfg) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&num_sms_, cudaDevAttrMultiProcessorCount, dev);
+}
+
+Engine::~Engine() {
+    for (auto& kv : tensors_)
+        if (kv.second.ptr) cudaFree(kv.second.ptr);
+}
+
+int Engine::set_tensor(const char* name, const void* host, int dtype, int ndim, const int64_t* shape) {
+    DevTensor t;
+    t.dtype = dtype;
+    size_t n = 1;
+    for (int i = 0; i < ndim; ++i) {
+        t.shape.push_back(shape[i]);
+        n *= (size_t)shape[i];
+    }
+    t.bytes = n * (dtype == 1 ? 2 : 4);
+    auto it = tensors_.find(name);
+    if (it != tensors_.end()) {
+        cudaFree(it->second.ptr);
+        tensors_.erase(it);
+    }
+    // pad allocations so TMA boxes that start inside the tensor never touch unmapped memory
+    MD_CUDA(cudaMalloc(&t.ptr, t.bytes + 1024));
+    MD_CUDA(cudaMemset(t.ptr, 0, t.bytes + 1024));
+    MD_CUDA(cudaMemcpy(t.ptr, host, t.bytes, cudaMemcpyHostToDevice));
+    tensors_[name] = t;
+    return 0;
+}
+
+const DevTensor* Engine::find(const std::string& name) {
+    auto it = tensors_.find(name);
+    if (it == tensors_.end()) {
+        if (missing_.size() < 400) missing_ += name + " ";
+        return nullptr;
+    }
+    return &it->second;
+}
+
+int Engine::gemm(const GemmProblem& p, cudaStream_t st) {
+    cudaError_t e = gemm_tc_launch(p, num_sms_, st);
+    ++launches_;
+    if (e != cudaSuccess) return fail(std::string("gemm_tc_launch: ") + cudaGetErrorString(e));
+    return 0;
+}
+
+static std::string S(const char* fmt, int a = 0, int b = 0) {
+    char buf[128];
+    snprintf(buf, sizeof buf, fmt, a, b);
+    return buf;
+}
+
+int Engine::finalize() {
+    missing_.clear();
+    const int ngroups = cfg_.n_mid + 2;
+    const char* once[] = {"est.time.w1", "est.time.b1", "est.time.w2", "est.time.b2", "est.tbias.w", "est.tbias.b",
+                          "est.down.conv.w", "est.down.conv.b", "est.up.conv.w", "est.up.conv.b", "est.final.w",
+                          "est.final.b", "est.final.ln.g", "est.final.ln.b", "est.proj.w", "est.proj.b"};
+    for (const char* n : once) find(n);
+    const char* res[] = {"c1.w", "c1.b", "ln1.g", "ln1.b", "c2.w", "c2.b", "ln2.g", "ln2.b", "rc.w", "rc.b"};
+    const char* tf[] = {"n1.g", "n1.b", "qkv.w", "o.w", "o.b", "n3.g", "n3.b", "ff1.w", "ff1.b", "ff2.w", "ff2.b"};
+    for (int i = 0; i < ngroups; ++i) {
+        for (const char* n : res) find(S("est.res%d.", i) + n);
+        for (int j = 0; j < cfg_.n_blocks; ++j)
+            for (const char* n : tf) find(S("est.tf%d.%d.", i, j) + n);
+    }
+    if (!missing_.empty()) return fail("missing estimator tensors: " + missing_);
+    finalized_ = true;
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------------------ layout
+// Sequences are packed back to back with kGuard zero rows in front of each one; the CFG-unconditional half repeats
+// the same layout rows_half further down (sequence ids nseq_half .. 2*nseq_half-1).
+static constexpr int kGuard = 4;
+
+int Engine::build_flow_layout(int nseq_half, const int32_t* lens, bool cfg_double) {
+    int rows = 0, max_len = 0;
+    const int nseq = cfg_double ? 2 * nseq_half : nseq_half;
+    h_seq_start_.assign(nseq, 0);
+    h_seq_len_.assign(nseq, 0);
+    h_in_offset_.assign(nseq, 0);
+    int64_t off = 0;
+    for (int s = 0; s < nseq_half; ++s) {
+        if (lens[s] <= 0) return fail("sequence length must be positive");
+        rows += kGuard;
+        h_seq_start_[s] = rows;
+        h_seq_len_[s] = lens[s];
+        h_in_offset_[s] = off;
+        off += (int64_t)lens[s] * cfg_.n_feats;
+        rows += lens[s];
+        max_len = lens[s] > max_len ? lens[s] : max_len;
+    }
+    rows += kGuard;
+    const int rows_half = (rows + kGemmBM - 1) / kGemmBM * kGemmBM;
+    const int M = cfg_double ? 2 * rows_half : rows_half;
+    h_row_seq_.assign(M, -1);
+    for (int s = 0; s < nseq_half; ++s)
+        for (int t = 0; t < lens[s]; ++t) h_row_seq_[h_seq_start_[s] + t] = s;
+    if (cfg_double) {
+        for (int s = 0; s < nseq_half; ++s) {
+            h_seq_start_[nseq_half + s] = h_seq_start_[s] + rows_half;
+            h_seq_len_[nseq_half + s] = lens[s];
+            h_in_offset_[nseq_half + s] = h_in_offset_[s];
+            for (int t = 0; t < lens[s]; ++t) h_row_seq_[rows_half + h_seq_start_[s] + t] = nseq_half + s;
+        }
+    }
+    flow_M_ = M;
+    flow_rows_half_ = rows_half;
+    flow_nseq_ = nseq;
+    flow_max_len_ = max_len;
+
+    // layout arrays
+    const size_t lay_bytes = (size_t)M * 4 + (size_t)nseq * (4 + 4 + 8) + 64;
+    ws_layout_.reserve(lay_bytes + 256);
+    if (!ws_layout_.as<void>()) return fail("cudaMalloc(layout) failed");
+    uint8_t* lp = ws_layout_.as<uint8_t>();
+    int64_t* d_off = reinterpret_cast<int64_t*>(lp);
+    int32_t* d_rowseq = reinterpret_cast<int32_t*>(lp + (((size_t)nseq * 8 + 15) & ~size_t(15)));
+    int32_t* d_start = d_rowseq + M;
+    int32_t* d_len = d_start + nseq;
+    MD_CUDA(cudaMemcpy(d_off, h_in_offset_.data(), (size_t)nseq * 8, cudaMemcpyHostToDevice));
+    MD_CUDA(cudaMemcpy(d_rowseq, h_row_seq_.data(), (size_t)M * 4, cudaMemcpyHostToDevice));
+    MD_CUDA(cudaMemcpy(d_start, h_seq_start_.data(), (size_t)nseq * 4, cudaMemcpyHostToDevice));
+    MD_CUDA(cudaMemcpy(d_len, h_seq_len_.data(), (size_t)nseq * 4, cudaMemcpyHostToDevice));
+    layout_.n_feats = cfg_.n_feats;
+    layout_.rows_half = rows_half;
+    layout_.noise_cstride = cfg_.noise_len;
+    layout_.row_seq = d_rowseq;
+    layout_.seq_start = d_start;
+    layout_.seq_len = d_len;
+    layout_.in_offset = d_off;
+
+    // activation workspace (all buffers have M rows; one slack tile at the end for TMA boxes)
+    const int C = cfg_.channels, H = cfg_.heads * cfg_.head_dim;
+    const size_t Mr = (size_t)M + kGemmBM;
+    size_t need = 0;
+    auto take = [&](size_t bytes) {
+        size_t o = need;
+        need += (bytes + 1023) & ~size_t(1023);
+        return o;
+    };
+    const size_t o_xin = take(Mr * cfg_.in_channels * 2), o_xn = take(Mr * C * 2), o_h1 = take(Mr * C * 2),
+                 o_qkv = take(Mr * 3 * H * 2), o_att = take(Mr * H * 2), o_ff = take(Mr * 4 * C * 2),
+                 o_cat = take(Mr * 2 * C * 2), o_xs = take(Mr * cfg_.n_feats * 4), o_hres = take(Mr * C * 4),
+                 o_rres = take(Mr * C * 4), o_d = take(Mr * cfg_.n_feats * 4);
+    ws_flow_.reserve(need);
+    if (!ws_flow_.as<void>()) return fail("cudaMalloc(flow workspace) failed");
+    uint8_t* b = ws_flow_.as<uint8_t>();
+    xin_ = (__nv_bfloat16*)(b + o_xin);
+    xn_ = (__nv_bfloat16*)(b + o_xn);
+    h1_ = (__nv_bfloat16*)(b + o_h1);
+    qkv_ = (__nv_bfloat16*)(b + o_qkv);
+    att_ = (__nv_bfloat16*)(b + o_att);
+    ff_ = (__nv_bfloat16*)(b + o_ff);
+    cat_ = (__nv_bfloat16*)(b + o_cat);
+    xstate_ = (float*)(b + o_xs);
+    hres_ = (float*)(b + o_hres);
+    rres_ = (float*)(b + o_rres);
+    dout_ = (float*)(b + o_d);
+
+    const int ngroups = cfg_.n_mid + 2;
+    const size_t tbytes = ((size_t)nseq * cfg_.time_dim + (size_t)nseq * ngroups * C + nseq + 64) * 4;
+    ws_time_.reserve(tbytes);
+    if (!ws_time_.as<void>()) return fail("cudaMalloc(time workspace) failed");
+    temb_ = ws_time_.as<float>();
+    tbias_ = temb_ + (size_t)nseq * cfg_.time_dim;
+    tvals_ = tbias_ + (size_t)nseq * ngroups * C;
+    return 0;
+}
+
+int Engine::time_bias(const float* t_dev, int nt, cudaStream_t st) {
+    const int ngroups = cfg_.n_mid + 2;
+    launch_time_embed(t_dev, nt, cfg_.in_channels, cfg_.time_dim, W<float>("est.time.w1"), W<float>("est.time.b1"),
+                      W<float>("est.time.w2"), W<float>("est.time.b2"), temb_, st);
+    launch_time_bias(temb_, nt, cfg_.time_dim, W<float>("est.tbias.w"), W<float>("est.tbias.b"),
+                     ngroups * cfg_.channels, tbias_, st);
+    launches_ += 2;
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------------------ estimator
+// Input: xin_ [M, 320] bf16 (guard rows zero).  Output: dout_ [M, 80] fp32 (guard rows zero).
+int Engine::estimator_forward(int M, int nseq, int max_len, const float* tbias, int tbias_ld, int chunk,
+                              cudaStream_t st) {
+    const int C = cfg_.channels, H = cfg_.heads * cfg_.head_dim;
+    const int ngroups = cfg_.n_mid + 2;
+    const int32_t* row_seq = layout_.row_seq;
+
+    auto causal3 = [&](GemmProblem& p, const __nv_bfloat16* a, int cin) {
+        p.a[0].ptr = a;
+        p.a[0].rows = M;
+        p.a[0].cols = cin;
+        p.a[0].ld = cin;
+        p.num_segs = 3;
+        for (int k = 0; k < 3; ++k) p.segs[k] = {0, k - 2, 0, (cin + kGemmBK - 1) / kGemmBK};
+        p.M = M;
+    };
+    auto dense = [&](GemmProblem& p, const __nv_bfloat16* a, int cin) {
+        p.a[0].ptr = a;
+        p.a[0].rows = M;
+        p.a[0].cols = cin;
+        p.a[0].ld = cin;
+        p.num_segs = 1;
+        p.segs[0] = {0, 0, 0, (cin + kGemmBK - 1) / kGemmBK};
+        p.M = M;
+    };
+
+    const __nv_bfloat16* gin = xin_;  // input of the current group's resnet
+    int gin_c = cfg_.in_channels;
+    for (int g = 0; g < ngroups; ++g) {
+        const std::string r = S("est.res%d.", g);
+        if (g == ngroups - 1) {  // up block: cat(x, skip)
+            gin = cat_;
+            gin_c = 2 * C;
+        }
+        {   // block1: causal conv -> LN -> Mish -> mask -> + time bias            (decoder.py:65-78, matcha decoder.py:56-57)
+            GemmProblem p;
+            causal3(p, gin, gin_c);
+            p.w = W<__nv_bfloat16>(r + "c1.w");
+            p.N = C; p.BN = C;
+            p.epi.bias = W<float>(r + "c1.b");
+            p.epi.ln1_g = W<float>(r + "ln1.g"); p.epi.ln1_b = W<float>(r + "ln1.b");
+            p.epi.act1 = ACT_MISH;
+            p.epi.row_seq = row_seq;
+            p.epi.tbias = tbias + (size_t)g * C; p.epi.tbias_ld = tbias_ld;
+            p.epi.out_bf16 = h1_; p.epi.ldo = C;
+            if (gemm(p, st)) return -1;
+        }
+        {   // res_conv 1x1 on x*mask                                                 (matcha decoder.py:60)
+            GemmProblem p;
+            dense(p, gin, gin_c);
+            p.w = W<__nv_bfloat16>(r + "rc.w");
+            p.N = C; p.BN = C;
+            p.epi.bias = W<float>(r + "rc.b");
+            p.epi.out_f32 = rres_; p.epi.ldf = C;
+            if (gemm(p, st)) return -1;
+        }
+        {   // block2 + residual; also emits norm1 of the first transformer block
+            GemmProblem p;
+            causal3(p, h1_, C);
+            p.w = W<__nv_bfloat16>(r + "c2.w");
+            p.N = C; p.BN = C;
+            p.epi.bias = W<float>(r + "c2.b");
+            p.epi.ln1_g = W<float>(r + "ln2.g"); p.epi.ln1_b = W<float>(r + "ln2.b");
+            p.epi.act1 = ACT_MISH;
+            p.epi.row_seq = row_seq;
+            p.epi.resid = rres_; p.epi.ldr = C;
+            p.epi.out_f32 = hres_; p.epi.ldf = C;
+            p.epi.ln2_g = W<float>(S("est.tf%d.0.n1.g", g)); p.epi.ln2_b = W<float>(S("est.tf%d.0.n1.b", g));
+            p.epi.out_bf16 = xn_; p.epi.ldo = C;
+            if (gemm(p, st)) return -1;
+        }
+        for (int j = 0; j < cfg_.n_blocks; ++j) {
+            const std::string t = S("est.tf%d.%d.", g, j);
+            {   // q | k | v projection (q rows pre-scaled by 1/sqrt(d))
+                GemmProblem p;
+                dense(p, xn_, C);
+                p.w = W<__nv_bfloat16>(t + "qkv.w");
+                p.N = 3 * H; p.BN = 256;
+                p.epi.out_bf16 = qkv_; p.epi.ldo = 3 * H;
+                if (gemm(p, st)) return -1;
+            }
+            launch_attention(qkv_, att_, layout_.seq_start, layout_.seq_len, nseq, max_len, cfg_.heads, chunk, st);
+            ++launches_;
+            {   // out projection + residual, emits norm3
+                GemmProblem p;
+                dense(p, att_, H);
+                p.w = W<__nv_bfloat16>(t + "o.w");
+                p.N = C; p.BN = C;
+                p.epi.bias = W<float>(t + "o.b");
+                p.epi.row_seq = row_seq;
+                p.epi.resid = hres_; p.epi.ldr = C;
+                p.epi.out_f32 = hres_; p.epi.ldf = C;
+                p.epi.ln2_g = W<float>(t + "n3.g"); p.epi.ln2_b = W<float>(t + "n3.b");
+                p.epi.out_bf16 = xn_; p.epi.ldo = C;
+                if (gemm(p, st)) return -1;
+            }
+            {   // FF1 + erf-GELU
+                GemmProblem p;
+                dense(p, xn_, C);
+                p.w = W<__nv_bfloat16>(t + "ff1.w");
+                p.N = 4 * C; p.BN = 256;
+                p.epi.bias = W<float>(t + "ff1.b");
+                p.epi.act1 = ACT_GELU;
+                p.epi.out_bf16 = ff_; p.epi.ldo = 4 * C;
+                if (gemm(p, st)) return -1;
+            }
+            {   // FF2 + residual; emits either the next block's norm1 or the masked bf16 copy for the next conv
+                GemmProblem p;
+                dense(p, ff_, 4 * C);
+                p.w = W<__nv_bfloat16>(t + "ff2.w");
+                p.N = C; p.BN = C;
+                p.epi.bias = W<float>(t + "ff2.b");
+                p.epi.row_seq = row_seq;
+                p.epi.resid = hres_; p.epi.ldr = C;
+                p.epi.out_f32 = hres_; p.epi.ldf = C;
+                if (j + 1 < cfg_.n_blocks) {
+                    p.epi.ln2_g = W<float>(S("est.tf%d.%d.n1.g", g, j + 1));
+                    p.epi.ln2_b = W<float>(S("est.tf%d.%d.n1.b", g, j + 1));
+                    p.epi.out_bf16 = xn_; p.epi.ldo = C;
+                } else if (g == 0) {           // down block: skip connection -> right half of the concat buffer
+                    p.epi.out_bf16 = cat_ + C; p.epi.ldo = 2 * C;
+                } else if (g == ngroups - 2) { // last mid block -> left half of the concat buffer
+                    p.epi.out_bf16 = cat_; p.epi.ldo = 2 * C;
+                } else {                        // mid block -> next resnet input; up block -> upsample conv input
+                    p.epi.out_bf16 = xn_; p.epi.ldo = C;
+                }
+                if (gemm(p, st)) return -1;
+            }
+        }
+        if (g == 0) {  // "downsample" slot = plain causal conv when channels == [256]   (decoder.py:348-350)
+            GemmProblem p;
+            p.a[0].ptr = cat_ + C; p.a[0].rows = M; p.a[0].cols = C; p.a[0].ld = 2 * C;
+            p.num_segs = 3;
+            for (int k = 0; k < 3; ++k) p.segs[k] = {0, k - 2, 0, C / kGemmBK};
+            p.M = M;
+            p.w = W<__nv_bfloat16>("est.down.conv.w");
+            p.N = C; p.BN = C;
+            p.epi.bias = W<float>("est.down.conv.b");
+            p.epi.row_seq = row_seq;
+            p.epi.out_bf16 = xn_; p.epi.ldo = C;  // first mid resnet input
+            if (gemm(p, st)) return -1;
+            gin = xn_;
+            gin_c = C;
+        } else if (g < ngroups - 1) {
+            gin = xn_;
+            gin_c = C;
+        }
+    }
+    {   // "upsample" slot = causal conv                                                (decoder.py:395-399)
+        GemmProblem p;
+        causal3(p, xn_, C);
+        p.w = W<__nv_bfloat16>("est.up.conv.w");
+        p.N = C; p.BN = C;
+        p.epi.bias = W<float>("est.up.conv.b");
+        p.epi.row_seq = row_seq;
+        p.epi.out_bf16 = h1_; p.epi.ldo = C;
+        if (gemm(p, st)) return -1;
+    }
+    {   // final_block: conv -> LN -> Mish -> mask                                       (decoder.py:401, 492)
+        GemmProblem p;
+        causal3(p, h1_, C);
+        p.w = W<__nv_bfloat16>("est.final.w");
+        p.N = C; p.BN = C;
+        p.epi.bias = W<float>("est.final.b");
+        p.epi.ln1_g = W<float>("est.final.ln.g"); p.epi.ln1_b = W<float>("est.final.ln.b");
+        p.epi.act1 = ACT_MISH;
+        p.epi.row_seq = row_seq;
+        p.epi.out_bf16 = xn_; p.epi.ldo = C;
+        if (gemm(p, st)) return -1;
+    }
+    {   // final_proj 1x1 -> 80, masked                                                  (decoder.py:493-494)
+        GemmProblem p;
+        dense(p, xn_, C);
+        p.w = W<__nv_bfloat16>("est.proj.w");
+        p.N = cfg_.n_feats; p.BN = cfg_.n_feats;
+        p.epi.bias = W<float>("est.proj.b");
+        p.epi.row_seq = row_seq;
+        p.epi.out_f32 = dout_; p.epi.ldf = cfg_.n_feats;
+        if (gemm(p, st)) return -1;
+    }
+    return 0;
+}
+
+}  // namespace mossdec

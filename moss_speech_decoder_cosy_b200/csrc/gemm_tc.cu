@@ -268,7 +268,19 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
                 const float rstd2 = rsqrtf(fmaxf(ss / (float)p.BN - mean2 * mean2, 0.f) + e.ln_eps);
                 for (int c = 0; c < nchunks; ++c) {
                     float v[16];
-                    chunk_value(c, v);
+                    if (e.out_f32 != nullptr) {
+                        // re-read what this thread stored in pass 1 (also makes resid == out_f32 in-place safe)
+                        if (inb) {
+                            const float* o = e.out_f32 + (size_t)row * e.ldf + n0 + c * 16;
+#pragma unroll
+                            for (int i = 0; i < 16; i += 4) {
+                                float4 t = *reinterpret_cast<const float4*>(o + i);
+                                v[i] = t.x; v[i + 1] = t.y; v[i + 2] = t.z; v[i + 3] = t.w;
+                            }
+                        }
+                    } else {
+                        chunk_value(c, v);
+                    }
 #pragma unroll
                     for (int i = 0; i < 16; ++i) {
                         const int n = n0 + c * 16 + i;

@@ -1,0 +1,182 @@
+"""ctypes binding of libmossdec.so (include/mossdec.h).  No fallback: a missing library or GPU raises."""
+import ctypes
+import os
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "lib", "libmossdec.so")
+
+F32, BF16, I32 = 0, 1, 2
+
+
+class MossdecConfig(ctypes.Structure):
+    _fields_ = [("n_feats", ctypes.c_int32), ("channels", ctypes.c_int32), ("heads", ctypes.c_int32),
+                ("head_dim", ctypes.c_int32), ("n_blocks", ctypes.c_int32), ("n_mid", ctypes.c_int32),
+                ("noise_len", ctypes.c_int32), ("hift_base", ctypes.c_int32), ("n_harmonics", ctypes.c_int32),
+                ("sample_rate", ctypes.c_float), ("nsf_alpha", ctypes.c_float), ("nsf_sigma", ctypes.c_float),
+                ("voiced_threshold", ctypes.c_float), ("lrelu_slope", ctypes.c_float),
+                ("audio_limit", ctypes.c_float)]
+
+
+_lib = None
+
+
+def load_library():
+    """dlopen libmossdec.so and declare every prototype of include/mossdec.h."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(f"{LIB_PATH} not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                           "(the decode path has no CPU or PyTorch fallback)")
+    lib = ctypes.CDLL(LIB_PATH)
+    vp, i32, i64, f32 = ctypes.c_void_p, ctypes.c_int32, ctypes.c_int64, ctypes.c_float
+    lib.mossdec_default_config.argtypes = [ctypes.POINTER(MossdecConfig)]
+    lib.mossdec_default_config.restype = None
+    lib.mossdec_create.argtypes = [ctypes.POINTER(MossdecConfig), ctypes.POINTER(vp)]
+    lib.mossdec_create.restype = i32
+    lib.mossdec_destroy.argtypes = [vp]
+    lib.mossdec_destroy.restype = None
+    lib.mossdec_last_error.argtypes = [vp]
+    lib.mossdec_last_error.restype = ctypes.c_char_p
+    lib.mossdec_set_tensor.argtypes = [vp, ctypes.c_char_p, vp, i32, i32, ctypes.POINTER(i64)]
+    lib.mossdec_set_tensor.restype = i32
+    lib.mossdec_finalize.argtypes = [vp]
+    lib.mossdec_finalize.restype = i32
+    lib.mossdec_estimator.argtypes = [vp, i32, i32, vp, vp, vp, vp, vp, vp, vp, i32, vp]
+    lib.mossdec_estimator.restype = i32
+    lib.mossdec_flow_solve.argtypes = [vp, i32, ctypes.POINTER(i32), vp, vp, vp, vp, i32, i32, f32, f32, i32, vp, vp]
+    lib.mossdec_flow_solve.restype = i32
+    lib.mossdec_hift.argtypes = [vp, i32, ctypes.POINTER(i32), vp, vp, i32, ctypes.POINTER(i32), vp, vp, vp,
+                                 ctypes.c_uint64, vp]
+    lib.mossdec_hift.restype = i32
+    lib.mossdec_fade_in_out.argtypes = [vp, vp, vp, vp, i32, vp]
+    lib.mossdec_fade_in_out.restype = i32
+    lib.mossdec_launch_count.argtypes = [vp]
+    lib.mossdec_launch_count.restype = i64
+    lib.mossdec_reset_launch_count.argtypes = [vp]
+    lib.mossdec_reset_launch_count.restype = None
+    _lib = lib
+    return lib
+
+
+EXPORTED_SYMBOLS = [
+    "mossdec_default_config", "mossdec_create", "mossdec_destroy", "mossdec_last_error", "mossdec_set_tensor",
+    "mossdec_finalize", "mossdec_estimator", "mossdec_flow_solve", "mossdec_hift", "mossdec_fade_in_out",
+    "mossdec_launch_count", "mossdec_reset_launch_count",
+]
+
+
+def _ptr(t):
+    return None if t is None else ctypes.c_void_p(t.data_ptr())
+
+
+def _i32_array(values):
+    return (ctypes.c_int32 * len(values))(*[int(v) for v in values])
+
+
+class Engine:
+    """One decode engine on the current CUDA device (wraps a mossdec_handle)."""
+
+    def __init__(self, config: MossdecConfig = None):
+        if not torch.cuda.is_available():
+            raise RuntimeError("mossdec needs a CUDA device (sm_100a); there is no CPU path")
+        self.lib = load_library()
+        self.cfg = config or self.default_config()
+        h = ctypes.c_void_p()
+        rc = self.lib.mossdec_create(ctypes.byref(self.cfg), ctypes.byref(h))
+        if rc != 0:
+            raise RuntimeError(f"mossdec_create failed ({rc})")
+        self.h = h
+
+    @staticmethod
+    def default_config():
+        cfg = MossdecConfig()
+        load_library().mossdec_default_config(ctypes.byref(cfg))
+        return cfg
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.mossdec_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _check(self, rc, what):
+        if rc != 0:
+            raise RuntimeError(f"{what} failed: {self.lib.mossdec_last_error(self.h).decode()}")
+
+    def load_tensors(self, tensors):
+        for name, t in tensors.items():
+            t = t.contiguous().cpu()
+            dt = {torch.float32: F32, torch.bfloat16: BF16, torch.int32: I32}[t.dtype]
+            shape = (ctypes.c_int64 * t.ndim)(*t.shape)
+            self._check(self.lib.mossdec_set_tensor(self.h, name.encode(), ctypes.c_void_p(t.data_ptr()), dt, t.ndim,
+                                                    shape), f"set_tensor({name})")
+
+    def finalize(self):
+        self._check(self.lib.mossdec_finalize(self.h), "finalize")
+
+    @staticmethod
+    def _stream():
+        return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+    def estimator(self, x, mask, mu, t, spks, cond, chunk=0):
+        """Same contract as ConditionalCFM.forward_estimator (flow_matching.py:129): fp32 CUDA tensors [B2,80,T]."""
+        B2, _, T = x.shape
+        x, mu = x.float().contiguous(), mu.float().contiguous()
+        t = t.float().contiguous()
+        spks = None if spks is None else spks.float().contiguous()
+        cond = None if cond is None else cond.float().contiguous()
+        out = torch.empty_like(x)
+        self._check(self.lib.mossdec_estimator(self.h, B2, T, _ptr(x), _ptr(mask), _ptr(mu), _ptr(t), _ptr(spks),
+                                               _ptr(cond), _ptr(out), int(chunk), self._stream()), "estimator")
+        return out
+
+    def flow_solve(self, lens, mu, spks, cond, noise=None, n_steps=10, cfg_rate=0.7, temperature=1.0, chunk=0):
+        """mu / cond: ragged fp32 CUDA buffers ([80, T_b] blocks back to back); returns mel in the same layout."""
+        B = len(lens)
+        mu, cond, spks = mu.float().contiguous(), cond.float().contiguous(), spks.float().contiguous()
+        out = torch.empty_like(mu)
+        nlen = 0
+        if noise is not None:
+            noise = noise.float().contiguous()
+            nlen = noise.shape[-1]
+        self._check(self.lib.mossdec_flow_solve(self.h, B, _i32_array(lens), _ptr(mu), _ptr(spks), _ptr(cond),
+                                                _ptr(noise), nlen, int(n_steps), float(cfg_rate), float(temperature),
+                                                int(chunk), _ptr(out), self._stream()), "flow_solve")
+        return out
+
+    def hift(self, lens, mel, cache_source=None, cache_len=None, nsf_noise=None, seed=0, want_source=True):
+        B = len(lens)
+        mel = mel.float().contiguous()
+        total = int(sum(lens)) * 480
+        wav = torch.empty(total, dtype=torch.float32, device=mel.device)
+        src = torch.empty(total, dtype=torch.float32, device=mel.device) if want_source else None
+        cstride = 0
+        clen = None
+        if cache_source is not None:
+            cache_source = cache_source.float().contiguous()
+            cstride = cache_source.shape[-1]
+            clen = _i32_array(cache_len)
+        if nsf_noise is not None:
+            nsf_noise = nsf_noise.float().contiguous()
+        self._check(self.lib.mossdec_hift(self.h, B, _i32_array(lens), _ptr(mel), _ptr(cache_source), cstride, clen,
+                                          _ptr(nsf_noise), _ptr(wav), _ptr(src), int(seed), self._stream()), "hift")
+        return wav, src
+
+    def fade_in_out(self, speech, prev_tail, window2n):
+        n = prev_tail.numel()
+        self._check(self.lib.mossdec_fade_in_out(self.h, _ptr(speech), _ptr(prev_tail), _ptr(window2n), n,
+                                                 self._stream()), "fade_in_out")
+
+    def launch_count(self):
+        return int(self.lib.mossdec_launch_count(self.h))
+
+    def reset_launch_count(self):
+        self.lib.mossdec_reset_launch_count(self.h)

@@ -1,0 +1,121 @@
+"""Weight packer: reference state_dicts (flow.pt / hift.pt key names) -> engine-ready tensors for libmossdec.
+
+Layouts produced (all CPU tensors; bf16 for tensor-core operands, fp32 for biases / norms / small matrices):
+
+  conv k taps, Cin -> Cout     : bf16 [Cout, k * Cin_pad], K index = tap * Cin_pad + c, Cin_pad = ceil64(Cin)
+                                 (one 64-wide k-block never straddles two taps; extra columns are zero)
+  Linear                        : bf16 [out, in]
+  q|k|v                         : bf16 [3 * 512, 256], q rows pre-multiplied by 1/sqrt(head_dim) (exact: 1/8)
+  ConvTranspose1d(stride s)     : bf16 [s * Cout, 3 * Cin]: row r * Cout + co, column (d + 1) * Cin + ci holds
+                                 w[ci, co, r + p - s * d] for input offset d in {-1, 0, +1} (zero where the tap does
+                                 not exist), so out[s * q + r] = sum_d x[q + d] . W_r,d    (polyphase form)
+  weight_norm                   : folded, w = g * v / ||v|| with the norm over all dims but 0 (generator.py:26-29)
+
+Reference layer -> engine name map is spelled out next to each block below (cites are to GLM_modules/).
+"""
+import math
+
+import torch
+
+BK = 64
+
+
+def _ceil64(n):
+    return (n + BK - 1) // BK * BK
+
+
+def conv_weight_taps(w: torch.Tensor, cin_pad: int = None) -> torch.Tensor:
+    """Conv1d weight [Cout, Cin, k] -> [Cout, k * Cin_pad] (tap-major K)."""
+    cout, cin, k = w.shape
+    cp = cin_pad or _ceil64(cin)
+    out = torch.zeros(cout, k, cp, dtype=torch.float32)
+    out[:, :, :cin] = w.permute(0, 2, 1)
+    return out.reshape(cout, k * cp)
+
+
+def fold_weight_norm(sd, prefix):
+    """w = g * v / ||v||  (new-style parametrizations or old weight_g / weight_v)."""
+    if prefix + ".parametrizations.weight.original0" in sd:
+        g, v = sd[prefix + ".parametrizations.weight.original0"], sd[prefix + ".parametrizations.weight.original1"]
+    elif prefix + ".weight_g" in sd:
+        g, v = sd[prefix + ".weight_g"], sd[prefix + ".weight_v"]
+    else:
+        return sd[prefix + ".weight"].float()
+    g, v = g.float(), v.float()
+    norm = v.flatten(1).norm(dim=1).view(-1, *([1] * (v.ndim - 1)))
+    return g * v / norm
+
+
+def convtranspose_polyphase(w: torch.Tensor, stride: int, padding: int) -> torch.Tensor:
+    """ConvTranspose1d weight [Cin, Cout, k] -> [stride * Cout, 3 * Cin] (see module docstring)."""
+    cin, cout, k = w.shape
+    out = torch.zeros(stride, cout, 3, cin, dtype=torch.float32)
+    for r in range(stride):
+        for di, d in enumerate((-1, 0, 1)):
+            kk = r + padding - stride * d
+            if 0 <= kk < k:
+                out[r, :, di, :] = w[:, :, kk].t()
+    return out.reshape(stride * cout, 3 * cin)
+
+
+def _bf16(t):
+    return t.to(torch.bfloat16).contiguous()
+
+
+def _f32(t):
+    return t.float().contiguous()
+
+
+def pack_estimator(sd, prefix="decoder.estimator.", n_mid=12, n_blocks=4, head_dim=64):
+    """CausalConditionalDecoder (cosyvoice/flow/decoder.py:294-403) with channels=[256]."""
+    out = {}
+    g = lambda k: sd[prefix + k].float()
+    out["est.time.w1"] = _f32(g("time_mlp.linear_1.weight"))   # matcha decoder.py:85
+    out["est.time.b1"] = _f32(g("time_mlp.linear_1.bias"))
+    out["est.time.w2"] = _f32(g("time_mlp.linear_2.weight"))   # matcha decoder.py:98
+    out["est.time.b2"] = _f32(g("time_mlp.linear_2.bias"))
+    groups = ["down_blocks.0"] + [f"mid_blocks.{i}" for i in range(n_mid)] + ["up_blocks.0"]
+    tb_w, tb_b = [], []
+    for gi, gp in enumerate(groups):
+        r = f"{gp}.0."
+        # CausalResnetBlock1D (decoder.py:81-85): block1/block2 = CausalConv1d k3 + LayerNorm + Mish
+        out[f"est.res{gi}.c1.w"] = _bf16(conv_weight_taps(g(r + "block1.block.0.weight")))
+        out[f"est.res{gi}.c1.b"] = _f32(g(r + "block1.block.0.bias"))
+        out[f"est.res{gi}.ln1.g"] = _f32(g(r + "block1.block.2.weight"))
+        out[f"est.res{gi}.ln1.b"] = _f32(g(r + "block1.block.2.bias"))
+        out[f"est.res{gi}.c2.w"] = _bf16(conv_weight_taps(g(r + "block2.block.0.weight")))
+        out[f"est.res{gi}.c2.b"] = _f32(g(r + "block2.block.0.bias"))
+        out[f"est.res{gi}.ln2.g"] = _f32(g(r + "block2.block.2.weight"))
+        out[f"est.res{gi}.ln2.b"] = _f32(g(r + "block2.block.2.bias"))
+        out[f"est.res{gi}.rc.w"] = _bf16(conv_weight_taps(g(r + "res_conv.weight")))   # 1x1
+        out[f"est.res{gi}.rc.b"] = _f32(g(r + "res_conv.bias"))
+        tb_w.append(g(r + "mlp.1.weight"))                                              # matcha decoder.py:49
+        tb_b.append(g(r + "mlp.1.bias"))
+        for j in range(n_blocks):
+            t = f"{gp}.1.{j}."
+            o = f"est.tf{gi}.{j}."
+            out[o + "n1.g"] = _f32(g(t + "norm1.weight"))
+            out[o + "n1.b"] = _f32(g(t + "norm1.bias"))
+            q = g(t + "attn1.to_q.weight") * (1.0 / math.sqrt(head_dim))
+            out[o + "qkv.w"] = _bf16(torch.cat([q, g(t + "attn1.to_k.weight"), g(t + "attn1.to_v.weight")], 0))
+            out[o + "o.w"] = _bf16(g(t + "attn1.to_out.0.weight"))
+            out[o + "o.b"] = _f32(g(t + "attn1.to_out.0.bias"))
+            out[o + "n3.g"] = _f32(g(t + "norm3.weight"))
+            out[o + "n3.b"] = _f32(g(t + "norm3.bias"))
+            out[o + "ff1.w"] = _bf16(g(t + "ff.net.0.proj.weight"))
+            out[o + "ff1.b"] = _f32(g(t + "ff.net.0.proj.bias"))
+            out[o + "ff2.w"] = _bf16(g(t + "ff.net.2.weight"))
+            out[o + "ff2.b"] = _f32(g(t + "ff.net.2.bias"))
+    out["est.tbias.w"] = _f32(torch.cat(tb_w, 0))
+    out["est.tbias.b"] = _f32(torch.cat(tb_b, 0))
+    out["est.down.conv.w"] = _bf16(conv_weight_taps(g("down_blocks.0.2.weight")))     # decoder.py:348-350
+    out["est.down.conv.b"] = _f32(g("down_blocks.0.2.bias"))
+    out["est.up.conv.w"] = _bf16(conv_weight_taps(g("up_blocks.0.2.weight")))         # decoder.py:395-399
+    out["est.up.conv.b"] = _f32(g("up_blocks.0.2.bias"))
+    out["est.final.w"] = _bf16(conv_weight_taps(g("final_block.block.0.weight")))     # decoder.py:401
+    out["est.final.b"] = _f32(g("final_block.block.0.bias"))
+    out["est.final.ln.g"] = _f32(g("final_block.block.2.weight"))
+    out["est.final.ln.b"] = _f32(g("final_block.block.2.bias"))
+    out["est.proj.w"] = _bf16(conv_weight_taps(g("final_proj.weight")))               # decoder.py:402
+    out["est.proj.b"] = _f32(g("final_proj.bias"))
+    return out

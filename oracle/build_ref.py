@@ -5,11 +5,9 @@ Config = SURVEY.md section 8(a0): CausalMaskedDiffWithXvec (flow.py:151) with Up
 (decoder.py:294, channels=[256], 12 mid blocks, 4 transformer blocks each) and HiFTGenerator
 (generator.py:392, 24 kHz, ups [8,5,3]) with ConvRNNF0Predictor (f0_predictor.py:22).
 
-The reference ships no checkpoint or config, so weights are random (torch.manual_seed) with two documented
-calibrations that keep the fixtures meaningful:
-  * f0_predictor.classifier is rescaled so that predicted f0 crosses the 10 Hz voiced threshold on a good share
-    of frames (random-init gives f0 < 0.2 Hz => the harmonic branch would never be exercised);
-  * HiFT conv weights are init N(0, 0.01) by the reference itself (generator.py:83-84,484-485).
+The reference ships no checkpoint or config, so the modules are loaded (strict=True) with the product's deterministic
+random-init checkpoint (moss_speech_decoder_cosy_b200/synth.py), whose scales keep every layer in its non-linear
+range (voiced and unvoiced frames, no clipping).
 """
 import math
 import os
@@ -50,20 +48,13 @@ def build_flow(static_chunk_tokens: int = DEFAULT_CHUNK_TOKENS, seed: int = 0, v
         input_size=512, output_size=80, spk_embed_dim=192, output_type='mel', vocab_size=vocab_size,
         input_frame_rate=12.5, only_mask_loss=True, token_mel_ratio=4, pre_lookahead_len=3,
         encoder=encoder, decoder=cfm)
-    # kaiming/zero-bias init of the estimator leaves every LayerNorm at (1, 0) and biases at 0; perturb them so the
-    # fixtures exercise gamma/beta/bias paths (deterministic under `seed`).
-    g = torch.Generator().manual_seed(seed + 17)
-    with torch.no_grad():
-        for name, p in estimator.named_parameters():
-            if p.ndim == 1:
-                if ('norm' in name or '.block.2.' in name) and name.endswith('weight'):
-                    p.copy_(1.0 + 0.1 * torch.randn(p.shape, generator=g))
-                else:
-                    p.copy_(0.05 * torch.randn(p.shape, generator=g))
+    # weights: the product's deterministic random-init checkpoint (strict load also pins the key/shape schema)
+    from moss_speech_decoder_cosy_b200 import synth
+    flow.load_state_dict(synth.synth_flow_state_dict(seed), strict=True)
     return flow.eval()
 
 
-def build_hift(seed: int = 0, calibrate_f0: bool = True):
+def build_hift(seed: int = 0):
     ref_shims.install()
     from cosyvoice.hifigan.generator import HiFTGenerator
     from cosyvoice.hifigan.f0_predictor import ConvRNNF0Predictor
@@ -77,37 +68,8 @@ def build_hift(seed: int = 0, calibrate_f0: bool = True):
         resblock_dilation_sizes=[[1, 3, 5], [1, 3, 5], [1, 3, 5]], source_resblock_kernel_sizes=[7, 7, 11],
         source_resblock_dilation_sizes=[[1, 3, 5], [1, 3, 5], [1, 3, 5]], lrelu_slope=0.1, audio_limit=0.99,
         f0_predictor=f0p)
-    g = torch.Generator().manual_seed(seed + 23)
-    with torch.no_grad():
-        # Snake alphas default to exactly 1; spread them so per-channel alpha indexing is tested.
-        for name, p in hift.named_parameters():
-            if name.endswith('.alpha'):
-                p.copy_(1.0 + 0.3 * torch.rand(p.shape, generator=g))
-        # N(0, 0.01) conv weights make every activation ~1e-3 and the waveform ~0.  Every weight-normed layer has
-        # w = g * v / |v|, so setting the gain g directly fixes each layer's signal gain regardless of fan-in and keeps
-        # O(1) signals through Snake / exp / sin (deterministic; no clipping at the +-0.99 limiter).
-        params = dict(hift.named_parameters())
-        for name, p in params.items():
-            if not name.endswith('parametrizations.weight.original0') or name.startswith('f0_predictor'):
-                continue
-            if name.startswith('ups.'):
-                stride = (8, 5, 3)[int(name.split('.')[1])]
-                p.fill_(math.sqrt(stride / 2.0))
-            elif name.startswith('conv_pre'):
-                p.fill_(1.0)
-            elif name.startswith('conv_post'):
-                p.fill_(0.5)
-            else:
-                p.fill_(0.7)
-        for name, p in params.items():
-            if name.startswith('source_downs') and name.endswith('weight'):
-                p.mul_(4.0 / p.flatten(1).norm(dim=1).view(-1, 1, 1))
-            if name.endswith('.bias') and not name.startswith('f0_predictor'):
-                p.copy_(0.05 * torch.randn(p.shape, generator=g))
-        if calibrate_f0:
-            # shift/scale the classifier so |f0| spans roughly 0..400 Hz on N(−5, 2) log-mel-like inputs
-            hift.f0_predictor.classifier.weight.mul_(1500.0)
-            hift.f0_predictor.classifier.bias.fill_(12.0)
+    from moss_speech_decoder_cosy_b200 import synth
+    hift.load_state_dict(synth.synth_hift_state_dict(seed), strict=True)
     return hift.eval()
 
 
