@@ -80,6 +80,7 @@ class Engine {
     const char* last_error() const { return err_.c_str(); }
     long launches() const { return launches_; }
     void reset_launches() { launches_ = 0; }
+    void set_hift_group_frames(int64_t f) { hift_group_frames_ = f > 0 ? f : 8192; }
     int num_sms() const { return num_sms_; }
 
    private:
@@ -102,6 +103,10 @@ class Engine {
     int build_flow_layout(int nseq_half, const int32_t* lens, bool cfg_double);
     int estimator_forward(int M, int nseq, int max_len, const float* tbias, int tbias_ld, int chunk, cudaStream_t st);
     int time_bias(const float* t_dev, int nt, cudaStream_t st);
+    int finalize_hift();
+    int hift_group(int b0, int b1, const int32_t* lens, int64_t mel_off0, int64_t wav_off0, const float* mel,
+                   const float* cache_source, int cache_stride, const int32_t* cache_len, const float* nsf_noise,
+                   float* wav_out, float* source_out, uint64_t seed, cudaStream_t st);
 
     EngineConfig cfg_;
     int num_sms_ = 148;
@@ -124,6 +129,8 @@ class Engine {
 
     // ---- hift workspace
     DeviceBuffer ws_hift_, ws_hift_layout_;
+    bool has_hift_ = false;
+    int64_t hift_group_frames_ = 8192;  // frames per HiFT group (bounds the stage-2 working set)
 };
 
 }  // namespace mossdec

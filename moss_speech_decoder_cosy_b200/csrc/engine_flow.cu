@@ -102,6 +102,7 @@ int Engine::finalize() {
     }
     if (!missing_.empty()) return fail("missing estimator tensors: " + missing_);
     finalized_ = true;
+    finalize_hift();  // HiFT tensors are optional at load time; mossdec_hift fails loudly if they are absent
     return 0;
 }
 

@@ -37,4 +37,36 @@ void launch_est_pack(const FlowLayout& L, int nrows, const float* x, const float
 void launch_attention(const __nv_bfloat16* qkv, __nv_bfloat16* out, const int32_t* seq_start, const int32_t* seq_len,
                       int nseq, int max_len, int heads, int chunk, cudaStream_t st);
 
+// ------------------------------------------------------------------------------------------------ HiFT
+// Packed layout of one group of mel segments: sequence b owns frame rows [seq_start[b], seq_start[b] + seq_len[b]);
+// at least 4 zero guard frames separate sequences.  Stage rows are frame rows x 8 / 40 / 120 (the last stage has one
+// extra row per sequence: ReflectionPad1d((1, 0)), generator.py:529-530).
+struct HiftLayout {
+    int32_t nseq;
+    int32_t rows_f;            // frame rows incl. guards, multiple of 128
+    const int32_t* seq_start;  // [nseq]
+    const int32_t* seq_len;    // [nseq]
+    const int64_t* mel_off;    // [nseq] element offset inside the ragged [80, T_b] input
+    const int64_t* wav_off;    // [nseq] sample offset inside the ragged [480 T_b] output
+};
+
+void hift_init_constants();
+void launch_hift_row_seq(const HiftLayout& L, int scale, int extra, int rows, int32_t* out, cudaStream_t st);
+void launch_hift_pack_mel(const HiftLayout& L, const int32_t* row_seq, const float* mel, __nv_bfloat16* out,
+                          cudaStream_t st);
+void launch_hift_phase(const HiftLayout& L, const float* f0, int f0_ld, float sample_rate, float upsample, int n_harm,
+                       float* p480, cudaStream_t st);
+void launch_hift_source(const HiftLayout& L, int max_len, const float* f0, int f0_ld, const float* p480,
+                        const float* noise, const float* lin_w, const float* lin_b, const float* cache,
+                        int cache_stride, const int32_t* cache_len, int n_harm, float sine_amp, float noise_std,
+                        float voiced_thr, int up, uint64_t seed, float* src_out, cudaStream_t st);
+void launch_hift_stft(const HiftLayout& L, const int32_t* row_seq2, int rows2, const float* src, __nv_bfloat16* out,
+                      cudaStream_t st);
+void launch_hift_fuse_snake(const HiftLayout& L, const int32_t* row_seq, int scale, int reflect, int64_t rows, int C,
+                            const float* u, const float* si, const float* a0, const float* a1, const float* a2,
+                            float* x, __nv_bfloat16* o0, __nv_bfloat16* o1, __nv_bfloat16* o2, cudaStream_t st);
+void launch_hift_istft(const HiftLayout& L, int max_len, const float* post, int post_ld, float limit, float* wav,
+                       cudaStream_t st);
+void launch_fade(float* speech, const float* prev, const float* w, int n, cudaStream_t st);
+
 }  // namespace mossdec

@@ -119,3 +119,66 @@ def pack_estimator(sd, prefix="decoder.estimator.", n_mid=12, n_blocks=4, head_d
     out["est.proj.w"] = _bf16(conv_weight_taps(g("final_proj.weight")))               # decoder.py:402
     out["est.proj.b"] = _f32(g("final_proj.bias"))
     return out
+
+
+HIFT_UPS = ((8, 16), (5, 11), (3, 7))          # (stride, kernel) of HiFTGenerator.ups, generator.py:437-451
+HIFT_RES_K = (3, 7, 11)                        # resblock_kernel_sizes
+HIFT_SRC_RES_K = (7, 7, 11)                    # source_resblock_kernel_sizes
+HIFT_DIL = (1, 3, 5)
+STFT_LD = 24                                   # 18 STFT channels padded to 24 (48-byte rows, TMA stride rule)
+
+
+def _pad_k(w2d):
+    n, k = w2d.shape
+    kp = _ceil64(k)
+    if kp == k:
+        return w2d
+    out = torch.zeros(n, kp, dtype=w2d.dtype)
+    out[:, :k] = w2d
+    return out
+
+
+def source_down_weight(w: torch.Tensor) -> torch.Tensor:
+    """Conv1d(18 -> C, k, stride) weight [C, 18, k] -> [C, ceil64(k * 24)], K index = tap * 24 + channel: the strided
+    conv reads a window of k consecutive 24-wide STFT rows, i.e. one contiguous K-slab per output row."""
+    c, cin, k = w.shape
+    out = torch.zeros(c, k, STFT_LD, dtype=torch.float32)
+    out[:, :, :cin] = w.permute(0, 2, 1)
+    return _pad_k(out.reshape(c, k * STFT_LD))
+
+
+def _pack_resblock(out, sd, src, dst, n_layers=3):
+    """ResBlock (generator.py:46-101): convs1[l] (dilated), convs2[l], Snake alphas."""
+    for l in range(n_layers):
+        out[f"{dst}.c1.{l}.w"] = _bf16(conv_weight_taps(fold_weight_norm(sd, f"{src}.convs1.{l}")))
+        out[f"{dst}.c1.{l}.b"] = _f32(sd[f"{src}.convs1.{l}.bias"])
+        out[f"{dst}.c2.{l}.w"] = _bf16(conv_weight_taps(fold_weight_norm(sd, f"{src}.convs2.{l}")))
+        out[f"{dst}.c2.{l}.b"] = _f32(sd[f"{src}.convs2.{l}.bias"])
+        out[f"{dst}.a1.{l}"] = _f32(sd[f"{src}.activations1.{l}.alpha"])
+        out[f"{dst}.a2.{l}"] = _f32(sd[f"{src}.activations2.{l}.alpha"])
+
+
+def pack_hift(sd):
+    """HiFTGenerator + ConvRNNF0Predictor (hifigan/generator.py:392-502, f0_predictor.py:22-53)."""
+    out = {}
+    for i, idx in enumerate((0, 2, 4, 6, 8)):                                     # f0_predictor.condnet
+        out[f"hift.f0.c{i}.w"] = _bf16(conv_weight_taps(fold_weight_norm(sd, f"f0_predictor.condnet.{idx}")))
+        out[f"hift.f0.c{i}.b"] = _f32(sd[f"f0_predictor.condnet.{idx}.bias"])
+    out["hift.f0.cls.w"] = _bf16(sd["f0_predictor.classifier.weight"].float())    # [1, 512]
+    out["hift.f0.cls.b"] = _f32(sd["f0_predictor.classifier.bias"])
+    out["hift.src.w"] = _f32(sd["m_source.l_linear.weight"].reshape(-1))          # generator.py:380
+    out["hift.src.b"] = _f32(sd["m_source.l_linear.bias"])
+    out["hift.pre.w"] = _bf16(conv_weight_taps(fold_weight_norm(sd, "conv_pre")))  # [512, 7 * 128]
+    out["hift.pre.b"] = _f32(sd["conv_pre.bias"])
+    for i, (s, k) in enumerate(HIFT_UPS):
+        w = fold_weight_norm(sd, f"ups.{i}")                                       # [Cin, Cout, k], norm over dim 0 = Cin
+        out[f"hift.up{i}.w"] = _bf16(convtranspose_polyphase(w, s, (k - s) // 2))
+        out[f"hift.up{i}.b"] = _f32(sd[f"ups.{i}.bias"].float().repeat(s))
+        out[f"hift.sd{i}.w"] = _bf16(source_down_weight(sd[f"source_downs.{i}.weight"].float()))
+        out[f"hift.sd{i}.b"] = _f32(sd[f"source_downs.{i}.bias"])
+        _pack_resblock(out, sd, f"source_resblocks.{i}", f"hift.srb{i}")
+        for r in range(3):
+            _pack_resblock(out, sd, f"resblocks.{3 * i + r}", f"hift.rb{i}.{r}")
+    out["hift.post.w"] = _bf16(conv_weight_taps(fold_weight_norm(sd, "conv_post")))  # [18, 7 * 64]
+    out["hift.post.b"] = _f32(sd["conv_post.bias"])
+    return out

@@ -66,7 +66,7 @@ def gen_solve(flow):
 
 def main(argv):
     what = set(argv) or {"estimator", "solve", "hift", "e2e", "stream"}
-    flow = build_ref.build_flow()
+    flow = build_ref.build_flow() if what & {"estimator", "solve", "e2e", "stream"} else None
     if "estimator" in what:
         gen_estimator(flow)
     if "solve" in what:
