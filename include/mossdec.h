@@ -83,6 +83,10 @@ int mossdec_hift(mossdec_handle* h, int32_t B, const int32_t* lens, const float*
 int mossdec_fade_in_out(mossdec_handle* h, float* speech, const float* prev_tail, const float* window2n, int32_t n,
                         void* stream);
 
+/* Test hook: copy up to max_floats of a named fp32 intermediate of the last call ("hift.f0", "hift.p480",
+ * "hift.post", "hift.x") to HOST memory; synchronises the device.  Returns floats copied, negative on error. */
+int mossdec_debug_read(mossdec_handle* h, const char* name, float* host_dst, int64_t max_floats);
+
 /* Number of kernels this handle has enqueued since creation / last reset (bench.py reports it as gpu_launches). */
 int64_t mossdec_launch_count(const mossdec_handle* h);
 void mossdec_reset_launch_count(mossdec_handle* h);

@@ -75,6 +75,10 @@ int mossdec_fade_in_out(mossdec_handle* h, float* speech, const float* prev_tail
     return h->eng->fade_in_out(speech, prev_tail, window2n, n, (cudaStream_t)stream);
 }
 
+int mossdec_debug_read(mossdec_handle* h, const char* name, float* host_dst, int64_t max_floats) {
+    return h->eng->debug_read(name, host_dst, (size_t)max_floats * 4);
+}
+
 int64_t mossdec_launch_count(const mossdec_handle* h) { return h->eng->launches(); }
 void mossdec_reset_launch_count(mossdec_handle* h) { h->eng->reset_launches(); }
 

@@ -75,6 +75,8 @@ class Engine {
     int hift(int B, const int32_t* lens, const float* mel, const float* cache_source, int cache_stride,
              const int32_t* cache_len, const float* nsf_noise, float* wav_out, float* source_out, uint64_t seed,
              cudaStream_t st);
+    // test hook: copy a named intermediate of the last call to the host; returns floats copied or -1
+    int debug_read(const char* name, void* host_dst, size_t bytes);
     int fade_in_out(float* speech, const float* prev_tail, const float* window2n, int n, cudaStream_t st);
 
     const char* last_error() const { return err_.c_str(); }
@@ -130,6 +132,7 @@ class Engine {
     // ---- hift workspace
     DeviceBuffer ws_hift_, ws_hift_layout_;
     bool has_hift_ = false;
+    std::map<std::string, std::pair<const void*, size_t>> taps_;
     int64_t hift_group_frames_ = 8192;  // frames per HiFT group (bounds the stage-2 working set)
 };
 

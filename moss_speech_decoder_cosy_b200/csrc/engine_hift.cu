@@ -46,7 +46,8 @@ struct HiftRunner {
     int64_t M[3] = {0, 0, 0};
     int32_t *rs_f = nullptr, *rs[3] = {nullptr, nullptr, nullptr};
     // frame level
-    __nv_bfloat16 *melb = nullptr, *fa = nullptr, *fb = nullptr, *stft = nullptr;
+    __nv_bfloat16 *melb = nullptr, *melb_lo = nullptr, *fa = nullptr, *fb = nullptr, *fa_lo = nullptr, *fb_lo = nullptr,
+                  *stft = nullptr;
     float *f0 = nullptr, *p480 = nullptr, *src = nullptr, *post = nullptr;
     // stage buffers (sized for the largest stage)
     float *u = nullptr, *si = nullptr, *x = nullptr, *xr = nullptr, *xs = nullptr;
@@ -247,7 +248,8 @@ int Engine::hift_group(int b0, int b1, const int32_t* lens, int64_t mel_off0, in
     const size_t slack = 256;  // rows of slack after every matrix (TMA boxes / shifted windows stay inside)
     const size_t Fr = (size_t)rows_f + slack;
     const size_t S = ((size_t)R.M[2] + slack) * 64;  // elements of one stage matrix (largest: stage 2; M0*256 and M1*128 are smaller)
-    const size_t o_melb = take(Fr * 128 * 2), o_fa = take(Fr * base * 2), o_fb = take(Fr * base * 2),
+    const size_t o_melb = take(Fr * 128 * 2), o_melb_lo = take(Fr * 128 * 2), o_fa = take(Fr * base * 2),
+                 o_fb = take(Fr * base * 2), o_fa_lo = take(Fr * base * 2), o_fb_lo = take(Fr * base * 2),
                  o_f0 = take(Fr * 4 * 4), o_p480 = take(Fr * 16 * 4), o_src = take(((size_t)rows_f * 480 + 1024) * 4),
                  o_stft = take(((size_t)R.M[2] + 2 * slack) * kStftLd * 2), o_post = take(((size_t)R.M[2] + slack) * 32 * 4),
                  o_u = take(S * 4), o_si = take(S * 4), o_x = take(S * 4), o_xr = take(S * 4), o_xs = take(S * 4),
@@ -258,8 +260,11 @@ int Engine::hift_group(int b0, int b1, const int32_t* lens, int64_t mel_off0, in
     if (!ws_hift_.as<void>()) return fail("cudaMalloc(hift workspace) failed");
     uint8_t* wb = ws_hift_.as<uint8_t>();
     R.melb = (__nv_bfloat16*)(wb + o_melb);
+    R.melb_lo = (__nv_bfloat16*)(wb + o_melb_lo);
     R.fa = (__nv_bfloat16*)(wb + o_fa);
     R.fb = (__nv_bfloat16*)(wb + o_fb);
+    R.fa_lo = (__nv_bfloat16*)(wb + o_fa_lo);
+    R.fb_lo = (__nv_bfloat16*)(wb + o_fb_lo);
     R.f0 = (float*)(wb + o_f0);
     R.p480 = (float*)(wb + o_p480);
     R.src = (float*)(wb + o_src);
@@ -271,27 +276,39 @@ int Engine::hift_group(int b0, int b1, const int32_t* lens, int64_t mel_off0, in
     R.h = (__nv_bfloat16*)(wb + o_h); R.lr = (__nv_bfloat16*)(wb + o_lr); R.sb = (__nv_bfloat16*)(wb + o_sb);
 
     // ---------------------------------------------------------------- f0 predictor (f0_predictor.py:55-60)
-    launch_hift_pack_mel(L, R.rs_f, mel, R.melb, st);
+    launch_hift_pack_mel(L, R.rs_f, mel, R.melb, R.melb_lo, st);
     ++launches_;
-    {
-        const __nv_bfloat16* in = R.melb;
+    {   // split-bf16: segments [a_hi taps | a_hi taps | a_lo taps] against weights [w_hi | w_lo | w_hi]
+        auto split_taps = [&](GemmProblem& p, const __nv_bfloat16* hi, const __nv_bfloat16* lo, int cin_pad, int k) {
+            p.a[0].ptr = hi; p.a[0].rows = rows_f; p.a[0].cols = cin_pad; p.a[0].ld = cin_pad;
+            p.a[1].ptr = lo; p.a[1].rows = rows_f; p.a[1].cols = cin_pad; p.a[1].ld = cin_pad;
+            p.num_segs = 3 * k;
+            for (int part = 0; part < 3; ++part)
+                for (int j = 0; j < k; ++j)
+                    p.segs[part * k + j] = {part == 2 ? 1 : 0, j - (k - 1) / 2, 0, cin_pad / kGemmBK};
+            p.M = rows_f;
+        };
+        const __nv_bfloat16 *in_hi = R.melb, *in_lo = R.melb_lo;
         int cin = 128;
         __nv_bfloat16* outs[2] = {R.fa, R.fb};
+        __nv_bfloat16* outs_lo[2] = {R.fa_lo, R.fb_lo};
         for (int i = 0; i < 5; ++i) {
             GemmProblem p;
-            R.conv_taps(p, in, rows_f, cin, 3, 1);
+            split_taps(p, in_hi, in_lo, cin, 3);
             p.w = W<__nv_bfloat16>(N("hift.f0.c%d.w", i));
             p.N = base; p.BN = 256;
             p.epi.bias = W<float>(N("hift.f0.c%d.b", i));
             p.epi.act1 = ACT_ELU;
             p.epi.row_seq = R.rs_f;
             p.epi.out_bf16 = outs[i & 1]; p.epi.ldo = base;
+            p.epi.out_bf16_lo = outs_lo[i & 1];
             if (gemm(p, st)) return -1;
-            in = outs[i & 1];
+            in_hi = outs[i & 1];
+            in_lo = outs_lo[i & 1];
             cin = base;
         }
         GemmProblem p;  // classifier Linear(512 -> 1) + abs
-        R.conv_taps(p, in, rows_f, base, 1, 1);
+        split_taps(p, in_hi, in_lo, base, 1);
         p.w = W<__nv_bfloat16>("hift.f0.cls.w");
         p.N = 1; p.BN = 16;
         p.epi.bias = W<float>("hift.f0.cls.b");
@@ -400,7 +417,20 @@ int Engine::hift_group(int b0, int b1, const int32_t* lens, int64_t mel_off0, in
     }
     launch_hift_istft(L, max_len, R.post, 32, cfg_.audio_limit, wav_out, st);
     ++launches_;
+    taps_["hift.f0"] = {R.f0, (size_t)rows_f * 4 * 4};          // [rows_f, 4] fp32, column 0; first sequence at row 4
+    taps_["hift.p480"] = {R.p480, (size_t)rows_f * 16 * 4};
+    taps_["hift.post"] = {R.post, (size_t)R.M[2] * 32 * 4};
+    taps_["hift.x"] = {R.xs, (size_t)R.M[2] * 64 * 4};
     return 0;
+}
+
+int Engine::debug_read(const char* name, void* host_dst, size_t bytes) {
+    auto it = taps_.find(name);
+    if (it == taps_.end()) return fail(std::string("no such tap: ") + name);
+    if (bytes > it->second.second) bytes = it->second.second;
+    MD_CUDA(cudaDeviceSynchronize());
+    MD_CUDA(cudaMemcpy(host_dst, it->second.first, bytes, cudaMemcpyDeviceToHost));
+    return (int)(bytes >> 2);
 }
 
 int Engine::fade_in_out(float* speech, const float* prev_tail, const float* window2n, int n, cudaStream_t st) {

@@ -56,6 +56,7 @@ struct GemmEpilogue {
     int32_t ldf = 0;
     __nv_bfloat16* out_bf16 = nullptr; // bf16 [M, ldo]: LN2 / act2 applied to the fp32 value
     int32_t ldo = 0;
+    __nv_bfloat16* out_bf16_lo = nullptr;  // optional bf16 [M, ldo] remainder v - bf16(v) (split-bf16 operands)
     const float* ln2_g = nullptr;
     const float* ln2_b = nullptr;
     int32_t act2 = ACT_NONE;

@@ -247,6 +247,17 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
                             t.z = pack_bf16x2(v[i + 4], v[i + 5]);
                             t.w = pack_bf16x2(v[i + 6], v[i + 7]);
                             *reinterpret_cast<uint4*>(o + i) = t;
+                            if (e.out_bf16_lo != nullptr) {
+                                float r[8];
+#pragma unroll
+                                for (int j = 0; j < 8; ++j) r[j] = v[i + j] - __bfloat162float(__float2bfloat16(v[i + j]));
+                                uint4 u;
+                                u.x = pack_bf16x2(r[0], r[1]);
+                                u.y = pack_bf16x2(r[2], r[3]);
+                                u.z = pack_bf16x2(r[4], r[5]);
+                                u.w = pack_bf16x2(r[6], r[7]);
+                                *reinterpret_cast<uint4*>(e.out_bf16_lo + (size_t)row * e.ldo + n0 + c * 16 + i) = u;
+                            }
                         }
                 }
             };

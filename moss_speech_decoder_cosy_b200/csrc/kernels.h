@@ -53,7 +53,7 @@ struct HiftLayout {
 void hift_init_constants();
 void launch_hift_row_seq(const HiftLayout& L, int scale, int extra, int rows, int32_t* out, cudaStream_t st);
 void launch_hift_pack_mel(const HiftLayout& L, const int32_t* row_seq, const float* mel, __nv_bfloat16* out,
-                          cudaStream_t st);
+                          __nv_bfloat16* out_lo, cudaStream_t st);
 void launch_hift_phase(const HiftLayout& L, const float* f0, int f0_ld, float sample_rate, float upsample, int n_harm,
                        float* p480, cudaStream_t st);
 void launch_hift_source(const HiftLayout& L, int max_len, const float* f0, int f0_ld, const float* p480,

@@ -53,6 +53,8 @@ def load_library():
     lib.mossdec_hift.restype = i32
     lib.mossdec_fade_in_out.argtypes = [vp, vp, vp, vp, i32, vp]
     lib.mossdec_fade_in_out.restype = i32
+    lib.mossdec_debug_read.argtypes = [vp, ctypes.c_char_p, vp, i64]
+    lib.mossdec_debug_read.restype = i32
     lib.mossdec_launch_count.argtypes = [vp]
     lib.mossdec_launch_count.restype = i64
     lib.mossdec_reset_launch_count.argtypes = [vp]
@@ -64,7 +66,7 @@ def load_library():
 EXPORTED_SYMBOLS = [
     "mossdec_default_config", "mossdec_create", "mossdec_destroy", "mossdec_last_error", "mossdec_set_tensor",
     "mossdec_finalize", "mossdec_estimator", "mossdec_flow_solve", "mossdec_hift", "mossdec_fade_in_out",
-    "mossdec_launch_count", "mossdec_reset_launch_count",
+    "mossdec_launch_count", "mossdec_reset_launch_count", "mossdec_debug_read",
 ]
 
 
@@ -174,6 +176,13 @@ class Engine:
         n = prev_tail.numel()
         self._check(self.lib.mossdec_fade_in_out(self.h, _ptr(speech), _ptr(prev_tail), _ptr(window2n), n,
                                                  self._stream()), "fade_in_out")
+
+    def debug_read(self, name, max_floats):
+        buf = torch.empty(int(max_floats), dtype=torch.float32)
+        n = self.lib.mossdec_debug_read(self.h, name.encode(), ctypes.c_void_p(buf.data_ptr()), int(max_floats))
+        if n < 0:
+            raise RuntimeError(f"debug_read({name}) failed: {self.lib.mossdec_last_error(self.h).decode()}")
+        return buf[:n]
 
     def launch_count(self):
         return int(self.lib.mossdec_launch_count(self.h))

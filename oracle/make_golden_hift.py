@@ -11,11 +11,15 @@ from . import build_ref
 
 
 def nsf_draws(seed, L):
-    """The draws SineGen2 consumes for one utterance of L samples, in the reference's order."""
+    """The draws SineGen2 consumes for one utterance of L samples, in the reference's order.
+
+    `sine_waves` is a transposed view ([1, L, 9] with strides (9L, 1, L), generator.py:281), so
+    `torch.randn_like(sine_waves)` (generator.py:334) fills a non-contiguous tensor: torch's CPU generator then takes
+    its scalar path, whose stream differs from `torch.randn(1, L, 9)`.  Reproduce it with the same strides."""
     torch.manual_seed(seed)
     rand_ini = torch.rand(1, 9)          # generator.py:270 (provably unused: only sample 0 of the phase is touched)
-    noise = torch.randn(1, L, 9)         # generator.py:334
-    return rand_ini, noise
+    noise = torch.randn_like(torch.empty(1, 9, L).transpose(1, 2))
+    return rand_ini, noise.contiguous()
 
 
 def hift_case(hift, name, T, seed, cache_len=0):
