@@ -61,13 +61,17 @@ int mossdec_finalize(mossdec_handle* h);
 int mossdec_estimator(mossdec_handle* h, int32_t B2, int32_t T, const float* x, const float* mask, const float* mu,
                       const float* t, const float* spks, const float* cond, float* out, int32_t chunk, void* stream);
 
+/* flags bit 0 (MOSSDEC_TIME_MAJOR): the ragged mel-like tensors (mu, cond, mel_out of mossdec_flow_solve; mel of
+ * mossdec_hift) are [lens[b], 80] blocks instead of the reference's channel-first [80, lens[b]]. */
+enum { MOSSDEC_TIME_MAJOR = 1 };
+
 /* n_steps Euler steps with classifier-free guidance for B utterances of lens[b] frames (HOST array).
  * mu, cond, mel_out: ragged [80, lens[b]] blocks back to back (for equal lengths this is [B, 80, T]); spks [B, 80].
  * noise: NULL -> the bank uploaded as tensor "flow.rand_noise" [80, noise_len]; else a device bank [80, noise_len_arg]
  * shared by all utterances (z = bank[:, :T] * temperature, flow_matching.py:225). */
 int mossdec_flow_solve(mossdec_handle* h, int32_t B, const int32_t* lens, const float* mu, const float* spks,
                        const float* cond, const float* noise, int32_t noise_len_arg, int32_t n_steps, float cfg_rate,
-                       float temperature, int32_t chunk, float* mel_out, void* stream);
+                       float temperature, int32_t chunk, float* mel_out, int32_t flags, void* stream);
 
 /* HiFT vocoder for B mel segments of lens[b] frames (HOST array): mel ragged [80, lens[b]] back to back ->
  * wav_out ragged [480 * lens[b]], source_out ragged [480 * lens[b]] (may be NULL).
@@ -77,7 +81,7 @@ int mossdec_flow_solve(mossdec_handle* h, int32_t B, const int32_t* lens, const 
  * generator.py:334); NULL -> counter-based Philox on device seeded with `seed`. */
 int mossdec_hift(mossdec_handle* h, int32_t B, const int32_t* lens, const float* mel, const float* cache_source,
                  int32_t cache_stride, const int32_t* cache_len, const float* nsf_noise, float* wav_out,
-                 float* source_out, uint64_t seed, void* stream);
+                 float* source_out, uint64_t seed, int32_t flags, void* stream);
 
 /* Streaming glue (flow_inference.py:35-43,151-156): speech[:n] = speech[:n]*w[:n] + prev_tail[:n]*w[n:], fp32, device. */
 int mossdec_fade_in_out(mossdec_handle* h, float* speech, const float* prev_tail, const float* window2n, int32_t n,

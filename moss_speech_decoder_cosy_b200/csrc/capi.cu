@@ -58,15 +58,15 @@ int mossdec_estimator(mossdec_handle* h, int32_t B2, int32_t T, const float* x, 
 
 int mossdec_flow_solve(mossdec_handle* h, int32_t B, const int32_t* lens, const float* mu, const float* spks,
                        const float* cond, const float* noise, int32_t noise_len_arg, int32_t n_steps, float cfg_rate,
-                       float temperature, int32_t chunk, float* mel_out, void* stream) {
+                       float temperature, int32_t chunk, float* mel_out, int32_t flags, void* stream) {
     return h->eng->flow_solve(B, lens, mu, spks, cond, noise, noise_len_arg, n_steps, cfg_rate, temperature, chunk,
-                              mel_out, (cudaStream_t)stream);
+                              mel_out, flags, (cudaStream_t)stream);
 }
 
 int mossdec_hift(mossdec_handle* h, int32_t B, const int32_t* lens, const float* mel, const float* cache_source,
                  int32_t cache_stride, const int32_t* cache_len, const float* nsf_noise, float* wav_out,
-                 float* source_out, uint64_t seed, void* stream) {
-    return h->eng->hift(B, lens, mel, cache_source, cache_stride, cache_len, nsf_noise, wav_out, source_out, seed,
+                 float* source_out, uint64_t seed, int32_t flags, void* stream) {
+    return h->eng->hift(B, lens, mel, cache_source, cache_stride, cache_len, nsf_noise, wav_out, source_out, seed, flags,
                         (cudaStream_t)stream);
 }
 

@@ -70,11 +70,11 @@ class Engine {
     // to back).  noise == nullptr -> built-in bank uploaded as tensor "flow.rand_noise".
     int flow_solve(int B, const int32_t* lens, const float* mu, const float* spks, const float* cond,
                    const float* noise, int noise_len_arg, int n_steps, float cfg_rate, float temperature, int chunk, float* mel_out,
-                   cudaStream_t st);
+                   int flags, cudaStream_t st);
     // HiFT vocoder for B ragged mel segments ([80, T_b] back to back) -> wav [480 T_b] back to back.
     int hift(int B, const int32_t* lens, const float* mel, const float* cache_source, int cache_stride,
              const int32_t* cache_len, const float* nsf_noise, float* wav_out, float* source_out, uint64_t seed,
-             cudaStream_t st);
+             int flags, cudaStream_t st);
     // test hook: copy a named intermediate of the last call to the host; returns floats copied or -1
     int debug_read(const char* name, void* host_dst, size_t bytes);
     int fade_in_out(float* speech, const float* prev_tail, const float* window2n, int n, cudaStream_t st);
@@ -108,7 +108,7 @@ class Engine {
     int finalize_hift();
     int hift_group(int b0, int b1, const int32_t* lens, int64_t mel_off0, int64_t wav_off0, const float* mel,
                    const float* cache_source, int cache_stride, const int32_t* cache_len, const float* nsf_noise,
-                   float* wav_out, float* source_out, uint64_t seed, cudaStream_t st);
+                   float* wav_out, float* source_out, uint64_t seed, int flags, cudaStream_t st);
 
     EngineConfig cfg_;
     int num_sms_ = 148;

@@ -148,7 +148,7 @@ int Engine::finalize_hift() {
 
 int Engine::hift(int B, const int32_t* lens, const float* mel, const float* cache_source, int cache_stride,
                  const int32_t* cache_len, const float* nsf_noise, float* wav_out, float* source_out, uint64_t seed,
-                 cudaStream_t st) {
+                 int flags, cudaStream_t st) {
     if (!finalized_) return fail("weights not finalized");
     if (!has_hift_) return fail("HiFT tensors missing: " + missing_);
     if (B <= 0) return fail("hift: bad batch");
@@ -164,7 +164,7 @@ int Engine::hift(int B, const int32_t* lens, const float* mel, const float* cach
         int64_t frames = 0;
         while (b1 < B && (b1 == b0 || frames + lens[b1] <= hift_group_frames_)) frames += lens[b1++];
         if (hift_group(b0, b1, lens, mel_off, wav_off, mel, cache_source, cache_stride, cache_len, nsf_noise, wav_out,
-                       source_out, seed, st))
+                       source_out, seed, flags, st))
             return -1;
         for (int b = b0; b < b1; ++b) {
             mel_off += (int64_t)lens[b] * cfg_.n_feats;
@@ -178,7 +178,7 @@ int Engine::hift(int B, const int32_t* lens, const float* mel, const float* cach
 
 int Engine::hift_group(int b0, int b1, const int32_t* lens, int64_t mel_off0, int64_t wav_off0, const float* mel,
                        const float* cache_source, int cache_stride, const int32_t* cache_len, const float* nsf_noise,
-                       float* wav_out, float* source_out, uint64_t seed, cudaStream_t st) {
+                       float* wav_out, float* source_out, uint64_t seed, int flags, cudaStream_t st) {
     const int nseq = b1 - b0;
     HiftRunner R(*this, st);
     // ---------------------------------------------------------------- host layout
@@ -225,6 +225,7 @@ int Engine::hift_group(int b0, int b1, const int32_t* lens, int64_t mel_off0, in
     HiftLayout& L = R.L;
     L.nseq = nseq;
     L.rows_f = rows_f;
+    L.time_major = flags & 1;
     L.seq_start = d_start;
     L.seq_len = d_len;
     L.mel_off = d_mel;

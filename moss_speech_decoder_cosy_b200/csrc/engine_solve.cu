@@ -18,6 +18,7 @@ int Engine::estimator(int B2, int T, const float* x, const float* mask, const fl
     if (B2 <= 0 || T <= 0) return fail("estimator: bad shape");
     std::vector<int32_t> lens(B2, T);
     if (build_flow_layout(B2, lens.data(), /*cfg_double=*/false)) return -1;
+    layout_.time_major = 0;
     const int M = flow_M_;
     launch_est_pack(layout_, M, x, mu, spks, cond, mask, xin_, st);
     ++launches_;
@@ -43,8 +44,7 @@ static void cosine_t_span(int n, std::vector<float>& ts) {
 
 int Engine::flow_solve(int B, const int32_t* lens, const float* mu, const float* spks, const float* cond,
                        const float* noise, int noise_len_arg, int n_steps, float cfg_rate, float temperature, int chunk,
-                       float* mel_out,
-                       cudaStream_t st) {
+                       float* mel_out, int flags, cudaStream_t st) {
     if (!finalized_) return fail("weights not finalized");
     if (B <= 0 || n_steps <= 0) return fail("flow_solve: bad arguments");
     const int noise_bstride = 0;  // one bank shared by all utterances, like the reference
@@ -58,6 +58,7 @@ int Engine::flow_solve(int B, const int32_t* lens, const float* mu, const float*
         if (lens[b] > noise_len) return fail("sequence longer than the noise bank");
     if (build_flow_layout(B, lens, /*cfg_double=*/true)) return -1;
     layout_.noise_cstride = noise_len;
+    layout_.time_major = flags & 1;
     const int M = flow_M_;
     launch_flow_prepare(layout_, mu, spks, cond, noise, noise_bstride, temperature, xin_, xstate_, st);
     ++launches_;

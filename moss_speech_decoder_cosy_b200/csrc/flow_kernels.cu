@@ -90,7 +90,7 @@ __global__ void flow_prepare_kernel(FlowLayout L, const float* __restrict__ mu, 
     }
     const int t = row - L.seq_start[s];
     const int T = L.seq_len[s];
-    const size_t off = L.in_offset[s] + (size_t)c * T + t;        // [B, C, T] (ragged: per-utterance offset)
+    const size_t off = L.in_offset[s] + (L.time_major ? (size_t)t * C + c : (size_t)c * T + t);  // ragged [C, T] or [T, C]
     xc[C + c] = __float2bfloat16(mu[off]);
     xc[2 * C + c] = __float2bfloat16(spks[(size_t)s * C + c]);
     xc[3 * C + c] = __float2bfloat16(cond[off]);
@@ -135,7 +135,7 @@ __global__ void rows_to_bct_kernel(FlowLayout L, const float* __restrict__ rows,
     const int s = L.row_seq[row];
     if (s < 0) return;
     const int t = row - L.seq_start[s];
-    out[L.in_offset[s] + (size_t)c * L.seq_len[s] + t] = rows[(size_t)(row + row_offset) * C + c];
+    out[L.in_offset[s] + (L.time_major ? (size_t)t * C + c : (size_t)c * L.seq_len[s] + t)] = rows[(size_t)(row + row_offset) * C + c];
 }
 
 // generic estimator entry: x/mu/cond [nseq, C, T] + spks [nseq, C] -> bf16 rows [M, 4C] (all sequences explicit)
@@ -155,7 +155,7 @@ __global__ void est_pack_kernel(FlowLayout L, int nseq_rows, const float* __rest
     }
     const int t = row - L.seq_start[s];
     const int T = L.seq_len[s];
-    const size_t off = L.in_offset[s] + (size_t)c * T + t;
+    const size_t off = L.in_offset[s] + (L.time_major ? (size_t)t * C + c : (size_t)c * T + t);
     (void)mask;
     xr[c] = __float2bfloat16(x[off]);
     xr[C + c] = __float2bfloat16(mu[off]);

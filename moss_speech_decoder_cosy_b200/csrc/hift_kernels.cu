@@ -53,7 +53,7 @@ __global__ void hift_pack_mel_kernel(HiftLayout L, const int32_t* __restrict__ r
     float v = 0.f;
     if (s >= 0 && c < 80) {
         const int t = row - L.seq_start[s];
-        v = mel[L.mel_off[s] + (int64_t)c * L.seq_len[s] + t];
+        v = mel[L.mel_off[s] + (L.time_major ? (int64_t)t * 80 + c : (int64_t)c * L.seq_len[s] + t)];
     }
     const __nv_bfloat16 hi = __float2bfloat16(v);
     out[idx] = hi;

@@ -12,6 +12,7 @@ struct FlowLayout {
     int32_t n_feats;          // 80
     int32_t rows_half;        // rows of one CFG half (multiple of 128)
     int32_t noise_cstride;    // channel stride of the noise bank
+    int32_t time_major;       // ragged tensors are [T_b, C] (1) instead of the reference's [C, T_b] (0)
     const int32_t* row_seq;   // [2 * rows_half] sequence id or -1
     const int32_t* seq_start; // [nseq] first row
     const int32_t* seq_len;   // [nseq] frames
@@ -44,6 +45,7 @@ void launch_attention(const __nv_bfloat16* qkv, __nv_bfloat16* out, const int32_
 struct HiftLayout {
     int32_t nseq;
     int32_t rows_f;            // frame rows incl. guards, multiple of 128
+    int32_t time_major;        // mel input is ragged [T_b, 80] (1) instead of [80, T_b] (0)
     const int32_t* seq_start;  // [nseq]
     const int32_t* seq_len;    // [nseq]
     const int64_t* mel_off;    // [nseq] element offset inside the ragged [80, T_b] input

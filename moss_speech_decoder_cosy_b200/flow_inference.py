@@ -1,0 +1,260 @@
+"""Drop-in mirror of the reference's `GLM_modules/flow_inference.py` (AudioDecoder) on top of libmossdec.
+
+Same constructor and method signatures, argument meaning, return shapes and per-uuid cache behaviour as the reference
+(`AudioDecoder.__init__` flow_inference.py:49-92, `token2wav` :94-123, `token2wav_streaming` :130-164,
+`stream_inference` :166-243), so `GLM4Encoder.decode / decode_streaming` (whisper_encoder_decoder.py:240-264,302-309)
+run unchanged.  New capability on top of it: `token2wav_batch` / `decode_batch` run a ragged batch of independent
+utterances through ONE flow solve and ONE vocoder pass (the reference asserts batch 1, flow.py:248), and
+`streaming.StreamScheduler` steps many concurrent streams together.
+
+There is no CPU or PyTorch fallback: constructing the decoder without a CUDA device or without the built
+libmossdec.so raises.
+"""
+import os
+import re
+import uuid as _uuid
+from collections import defaultdict
+
+import numpy as np
+import torch
+
+from . import frontend, lib, synth, weights
+
+TOKEN_MEL_RATIO = 4
+PRE_LOOKAHEAD = 3
+
+
+def _read_config(config_path):
+    """The reference instantiates its models from a hyperpyyaml object graph (flow_inference.py:53-55).  Only scalar
+    hyper-parameters matter here; they are picked out of the yaml text when present, else the pinned defaults of
+    SURVEY.md 8(a0) apply."""
+    cfg = {"static_chunk_size": 25, "inference_cfg_rate": 0.7, "sample_rate": 24000, "n_timesteps": 10}
+    if config_path and os.path.exists(config_path):
+        text = open(config_path).read()
+        for key, cast in (("static_chunk_size", int), ("inference_cfg_rate", float), ("sample_rate", int)):
+            m = re.search(rf"^\s*{key}\s*:\s*([0-9.eE+-]+)\s*$", text, re.M)
+            if m:
+                cfg[key] = cast(float(m.group(1)))
+    return cfg
+
+
+class _FlowFacade:
+    """What callers read from `decoder.flow` (flow_inference.py:77,141,191) + an `inference` with the reference's
+    signature (flow.py:237-283)."""
+    token_mel_ratio = TOKEN_MEL_RATIO
+    pre_lookahead_len = PRE_LOOKAHEAD
+    input_frame_rate = 12.5
+
+    def __init__(self, dec):
+        self._dec = dec
+
+    @torch.inference_mode()
+    def inference(self, token, token_len, prompt_token, prompt_token_len, prompt_feat, prompt_feat_len, embedding,
+                  streaming, finalize):
+        assert token.shape[0] == 1
+        r = self._dec.flow_batch([token], [prompt_token], [prompt_feat], embedding, streaming, finalize)
+        full = r["mel"].t().unsqueeze(0).contiguous()             # [1, 80, T]
+        mel_len1 = int(r["prompt_frames"][0])
+        feat_return = full[:, :, mel_len1:]
+        assert feat_return.shape[2] == full.shape[2] - mel_len1
+        return feat_return.float(), full.float()
+
+
+class _HiftFacade:
+    """`decoder.hift.inference(speech_feat=, cache_source=)` (generator.py:570-582)."""
+
+    def __init__(self, dec):
+        self._dec = dec
+
+    @torch.inference_mode()
+    def inference(self, speech_feat, cache_source=torch.zeros(1, 1, 0), nsf_noise=None):
+        assert speech_feat.shape[0] == 1
+        dev = self._dec.device
+        T = speech_feat.shape[2]
+        mel = speech_feat[0].to(dev).float().contiguous()
+        kw = {}
+        if cache_source.shape[2] != 0:
+            kw = dict(cache_source=cache_source.to(dev).reshape(1, -1).float(), cache_len=[cache_source.shape[2]])
+        wav, src = self._dec.engine.hift([T], mel.reshape(-1), nsf_noise=self._dec._noise_for([T], nsf_noise),
+                                         seed=self._dec._next_seed(), **kw)
+        return wav.view(1, -1), src.view(1, 1, -1)
+
+
+class AudioDecoder(torch.nn.Module):
+    def __init__(self, config_path=None, flow_ckpt_path=None, hift_ckpt_path=None, campplus_model=None,
+                 mel_cache_len=8, device="cuda", flow_state_dict=None, hift_state_dict=None, seed=0):
+        super().__init__()
+        if not torch.cuda.is_available():
+            raise RuntimeError("AudioDecoder (mossdec) needs a CUDA device: there is no CPU path")
+        self.device = torch.device(device if device != "cuda" else f"cuda:{torch.cuda.current_device()}")
+        torch.cuda.set_device(self.device)
+        self.scratch_configs = _read_config(config_path)
+        # checkpoints in the reference's state_dict format (flow_inference.py:59-61); random-init when absent
+        if flow_state_dict is None:
+            flow_state_dict = (torch.load(flow_ckpt_path, map_location="cpu") if flow_ckpt_path and
+                               os.path.exists(flow_ckpt_path) else synth.synth_flow_state_dict(seed))
+        if hift_state_dict is None:
+            hift_state_dict = (torch.load(hift_ckpt_path, map_location="cpu") if hift_ckpt_path and
+                               os.path.exists(hift_ckpt_path) else synth.synth_hift_state_dict(seed))
+        self.engine = lib.Engine()
+        tensors = weights.pack_estimator(flow_state_dict)
+        tensors["flow.rand_noise"] = synth.synth_noise_bank()[0].contiguous()   # flow_matching.py:202-203
+        tensors.update(weights.pack_hift(hift_state_dict))
+        self.engine.load_tensors(tensors)
+        self.engine.finalize()
+        self.enc_weights = frontend.EncoderWeights(flow_state_dict, self.device)
+        self.flow = _FlowFacade(self)
+        self.hift = _HiftFacade(self)
+        self.sample_rate = self.scratch_configs["sample_rate"]
+        self.feat_extractor = None      # prompt mel extractor (matcha mel_spectrogram) -- SURVEY 8(f) N2
+        self.campplus_session = None    # x-vector ONNX session stays with the caller (CPU, out of scope)
+        self.static_chunk_size = int(self.scratch_configs["static_chunk_size"])   # tokens
+        self.n_timesteps = int(self.scratch_configs["n_timesteps"])
+        self.inference_cfg_rate = float(self.scratch_configs["inference_cfg_rate"])
+
+        # session state, same keys as the reference (flow_inference.py:70-74)
+        self.mel_overlap_dict = defaultdict(lambda: None)
+        self.hift_cache_dict = defaultdict(lambda: None)
+        self.llm_end_dict = defaultdict(lambda: None)
+        self.tts_speech_token_dict = defaultdict(lambda: None)
+        self.flow_cache_dict = defaultdict(lambda: None)
+
+        self.token_overlap_len = 3.5
+        self.mel_overlap_len = int(self.token_overlap_len / self.flow.input_frame_rate * 24000 / 480 / 2)  # 7
+        self.mel_window = np.hamming(2 * self.mel_overlap_len)
+        self.mel_cache_len = mel_cache_len
+        self.source_cache_len = int(self.mel_cache_len * 480)
+        self.speech_window = np.hamming(2 * self.source_cache_len)
+        self._speech_window_dev = torch.from_numpy(self.speech_window.astype(np.float32)).to(self.device)
+        self._seed = 0
+
+    def _next_seed(self):
+        self._seed += 1
+        return self._seed
+
+    # Parity tests inject the reference's NSF noise draws (generator.py:334): a callable taking the list of vocoder
+    # segment lengths (frames) and returning the ragged [sum 480 T_b, 9] noise on the device.  None -> device Philox.
+    nsf_noise_hook = None
+
+    def _noise_for(self, lens, nsf_noise=None):
+        if nsf_noise is None and self.nsf_noise_hook is not None:
+            nsf_noise = self.nsf_noise_hook(lens)
+        return nsf_noise
+
+    # ------------------------------------------------------------------------------------------ batched core
+    @torch.inference_mode()
+    def flow_batch(self, tokens, prompt_tokens, prompt_feats, embeddings, streaming, finalize):
+        """CausalMaskedDiffWithXvec.inference (flow.py:237-283) for a list of utterances.
+
+        tokens[b]: int [1, N_b]; prompt_tokens[b]: int [1, P_b]; prompt_feats[b]: float [1, F_b, 80];
+        embeddings: float [B, 192].  Returns ragged time-major mel [sum T_b, 80] (prompt frames included), the
+        per-utterance frame counts T_b and prompt frame counts F_b."""
+        dev = self.device
+        B = len(tokens)
+        ctx = 0 if finalize else PRE_LOOKAHEAD
+        rows = [torch.cat([prompt_tokens[b].reshape(-1).long().cpu(), tokens[b].reshape(-1).long().cpu()])
+                for b in range(B)]
+        lens_tok = [int(r.numel()) for r in rows]
+        if min(lens_tok) - ctx <= 0:
+            raise ValueError("every utterance needs at least one token besides the look-ahead context")
+        tok = torch.zeros(B, max(lens_tok), dtype=torch.long).pin_memory()
+        for b, r in enumerate(rows):
+            tok[b, :lens_tok[b]] = r
+        tok = tok.to(dev, non_blocking=True)
+        lens_t = torch.tensor(lens_tok, dtype=torch.long).to(dev)
+        chunk_tokens = self.static_chunk_size if streaming else 0
+        mu_pad, main = frontend.encode(self.enc_weights, tok, lens_t, ctx, chunk_tokens)
+        T = [(n - ctx) * TOKEN_MEL_RATIO for n in lens_tok]
+        Tmax = mu_pad.shape[1]
+        if all(t == Tmax for t in T):
+            mu = mu_pad.reshape(-1, 80)
+        else:
+            valid = torch.arange(Tmax, device=dev).unsqueeze(0) < (main * TOKEN_MEL_RATIO).unsqueeze(1)
+            mu = mu_pad[valid]
+        F_ = [int(pf.shape[1]) for pf in prompt_feats]
+        parts = []
+        for b in range(B):
+            if F_[b] > T[b]:
+                raise ValueError("prompt_feat longer than the decoded sequence")
+            if F_[b]:
+                parts.append(prompt_feats[b].reshape(F_[b], 80).to(dev, non_blocking=True).float())
+            parts.append(torch.zeros(T[b] - F_[b], 80, device=dev))
+        cond = torch.cat(parts, 0)                                    # flow.py:268-270
+        spks = frontend.speaker_projection(self.enc_weights, embeddings.to(dev))
+        mel = self.engine.flow_solve(T, mu.reshape(-1), spks, cond.reshape(-1), n_steps=self.n_timesteps,
+                                     cfg_rate=self.inference_cfg_rate,
+                                     chunk=self.static_chunk_size * TOKEN_MEL_RATIO if streaming else 0,
+                                     time_major=True).view(-1, 80)
+        return {"mel": mel, "frames": T, "prompt_frames": F_}
+
+    @torch.inference_mode()
+    def decode_batch(self, tokens, prompt_tokens=None, prompt_feats=None, embeddings=None, nsf_noise=None, seed=None):
+        """token2wav (flow_inference.py:94-123) for B independent utterances in one pass.
+
+        Returns {"wav": ragged fp32 [sum 1920 N_b], "wav_lens", "mel": ragged time-major [sum 4 N_b, 80], "mel_lens"}."""
+        B = len(tokens)
+        prompt_tokens = prompt_tokens or [torch.zeros(1, 0, dtype=torch.int32)] * B
+        prompt_feats = prompt_feats or [torch.zeros(1, 0, 80)] * B
+        if embeddings is None:
+            embeddings = torch.zeros(B, 192)
+        r = self.flow_batch(tokens, prompt_tokens, prompt_feats, embeddings, streaming=False, finalize=True)
+        T, F_ = r["frames"], r["prompt_frames"]
+        gen = [t - f for t, f in zip(T, F_)]
+        if any(F_):
+            idx, off = [], 0
+            for t, f in zip(T, F_):
+                idx.append(torch.arange(off + f, off + t))
+                off += t
+            mel = r["mel"].index_select(0, torch.cat(idx).to(self.device))      # strip prompt frames, flow.py:281
+        else:
+            mel = r["mel"]
+        wav, _ = self.engine.hift(gen, mel.reshape(-1), nsf_noise=self._noise_for(gen, nsf_noise),
+                                  seed=self._next_seed() if seed is None else seed, want_source=False, time_major=True)
+        return {"wav": wav, "wav_lens": [g * 480 for g in gen], "mel": mel, "mel_lens": gen}
+
+    def token2wav_batch(self, tokens, prompt_tokens=None, prompt_feats=None, embeddings=None, **kw):
+        """List-of-utterances convenience wrapper: returns [(tts_speech [1, 1920 N_b], tts_mel [1, 80, 4 N_b])]."""
+        r = self.decode_batch(tokens, prompt_tokens, prompt_feats, embeddings, **kw)
+        out, wo, mo = [], 0, 0
+        for wl, ml in zip(r["wav_lens"], r["mel_lens"]):
+            out.append((r["wav"][wo:wo + wl].view(1, -1), r["mel"][mo:mo + ml].t().unsqueeze(0)))
+            wo += wl
+            mo += ml
+        return out
+
+    # ------------------------------------------------------------------------------------------ reference API
+    def token2wav(self, token, uuid, prompt_token=torch.zeros(1, 0, dtype=torch.int32),
+                  prompt_feat=torch.zeros(1, 0, 80), embedding=torch.zeros(1, 192)):
+        """flow_inference.py:94-123 (mel_overlap / hift caches of `uuid` are honoured and then dropped)."""
+        tts_mel, _ = self.flow.inference(token=token, token_len=None, prompt_token=prompt_token, prompt_token_len=None,
+                                         prompt_feat=prompt_feat, prompt_feat_len=None, embedding=embedding,
+                                         streaming=False, finalize=True)
+        if self.mel_overlap_dict[uuid] is not None:
+            from .streaming import fade_in_out_mel
+            tts_mel = fade_in_out_mel(tts_mel, self.mel_overlap_dict[uuid], self.mel_window)
+        if self.hift_cache_dict[uuid] is not None:
+            hift_cache_mel, hift_cache_source = self.hift_cache_dict[uuid]['mel'], self.hift_cache_dict[uuid]['source']
+            tts_mel = torch.concat([hift_cache_mel, tts_mel], dim=2)
+        else:
+            hift_cache_source = torch.zeros(1, 1, 0)
+        tts_speech, _ = self.hift.inference(speech_feat=tts_mel, cache_source=hift_cache_source)
+        del self.hift_cache_dict[uuid]
+        del self.mel_overlap_dict[uuid]
+        return tts_speech, tts_mel
+
+    def offline_inference(self, token):
+        """flow_inference.py:125-128 (the reference passes a stale `finalize=` kwarg there and raises; this works)."""
+        tts_speech, _ = self.token2wav(token, uuid=str(_uuid.uuid1()))
+        return tts_speech.cpu()
+
+    def token2wav_streaming(self, token, prompt_token, prompt_feat, token_offset, uuid, embedding=torch.zeros(1, 192),
+                            finalize=False, stream=False, speed=1.0):
+        from .streaming import token2wav_streaming
+        return token2wav_streaming(self, token, prompt_token, prompt_feat, token_offset, uuid, embedding, finalize,
+                                   stream, speed)
+
+    def stream_inference(self, token, prompt_token=torch.zeros(1, 0, dtype=torch.int32),
+                         prompt_feat=torch.zeros(1, 0, 80), embedding=torch.zeros(0, 192), block_size=8,
+                         max_token_len=None):
+        from .streaming import stream_inference
+        return stream_inference(self, token, prompt_token, prompt_feat, embedding, block_size, max_token_len)

@@ -46,10 +46,10 @@ def load_library():
     lib.mossdec_finalize.restype = i32
     lib.mossdec_estimator.argtypes = [vp, i32, i32, vp, vp, vp, vp, vp, vp, vp, i32, vp]
     lib.mossdec_estimator.restype = i32
-    lib.mossdec_flow_solve.argtypes = [vp, i32, ctypes.POINTER(i32), vp, vp, vp, vp, i32, i32, f32, f32, i32, vp, vp]
+    lib.mossdec_flow_solve.argtypes = [vp, i32, ctypes.POINTER(i32), vp, vp, vp, vp, i32, i32, f32, f32, i32, vp, i32, vp]
     lib.mossdec_flow_solve.restype = i32
     lib.mossdec_hift.argtypes = [vp, i32, ctypes.POINTER(i32), vp, vp, i32, ctypes.POINTER(i32), vp, vp, vp,
-                                 ctypes.c_uint64, vp]
+                                 ctypes.c_uint64, i32, vp]
     lib.mossdec_hift.restype = i32
     lib.mossdec_fade_in_out.argtypes = [vp, vp, vp, vp, i32, vp]
     lib.mossdec_fade_in_out.restype = i32
@@ -140,7 +140,8 @@ class Engine:
                                                _ptr(cond), _ptr(out), int(chunk), self._stream()), "estimator")
         return out
 
-    def flow_solve(self, lens, mu, spks, cond, noise=None, n_steps=10, cfg_rate=0.7, temperature=1.0, chunk=0):
+    def flow_solve(self, lens, mu, spks, cond, noise=None, n_steps=10, cfg_rate=0.7, temperature=1.0, chunk=0,
+                   time_major=False):
         """mu / cond: ragged fp32 CUDA buffers ([80, T_b] blocks back to back); returns mel in the same layout."""
         B = len(lens)
         mu, cond, spks = mu.float().contiguous(), cond.float().contiguous(), spks.float().contiguous()
@@ -151,10 +152,11 @@ class Engine:
             nlen = noise.shape[-1]
         self._check(self.lib.mossdec_flow_solve(self.h, B, _i32_array(lens), _ptr(mu), _ptr(spks), _ptr(cond),
                                                 _ptr(noise), nlen, int(n_steps), float(cfg_rate), float(temperature),
-                                                int(chunk), _ptr(out), self._stream()), "flow_solve")
+                                                int(chunk), _ptr(out), int(bool(time_major)), self._stream()), "flow_solve")
         return out
 
-    def hift(self, lens, mel, cache_source=None, cache_len=None, nsf_noise=None, seed=0, want_source=True):
+    def hift(self, lens, mel, cache_source=None, cache_len=None, nsf_noise=None, seed=0, want_source=True,
+             time_major=False):
         B = len(lens)
         mel = mel.float().contiguous()
         total = int(sum(lens)) * 480
@@ -169,7 +171,8 @@ class Engine:
         if nsf_noise is not None:
             nsf_noise = nsf_noise.float().contiguous()
         self._check(self.lib.mossdec_hift(self.h, B, _i32_array(lens), _ptr(mel), _ptr(cache_source), cstride, clen,
-                                          _ptr(nsf_noise), _ptr(wav), _ptr(src), int(seed), self._stream()), "hift")
+                                          _ptr(nsf_noise), _ptr(wav), _ptr(src), int(seed), int(bool(time_major)),
+                                          self._stream()), "hift")
         return wav, src
 
     def fade_in_out(self, speech, prev_tail, window2n):

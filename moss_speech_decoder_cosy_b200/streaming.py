@@ -1,0 +1,205 @@
+"""Streaming half of the AudioDecoder mirror: `token2wav_streaming` (flow_inference.py:130-164), the chunk loop of
+`stream_inference` (:166-243), and a batched scheduler that steps many concurrent streams through one flow solve and
+one vocoder pass per chunk (BASELINE.json config 3; the reference serves one stream at a time).
+
+Semantics kept from the reference: every chunk RECOMPUTES the flow over prompt + window tokens with block-causal
+masks (`stream=True`), crops `token_offset * 4` frames, prepends the cached `mel_cache_len` mel frames, feeds the
+cached source samples to HiFT (generator.py:579-580), cross-fades the first `source_cache_len` samples with the cached
+speech tail under a Hamming window (flow_inference.py:35-43) and holds back the new tail.  The fade runs on the device
+(the reference round-trips through the CPU and a float64 numpy window, flow_inference.py:37-43).
+"""
+import uuid as _uuid
+
+import numpy as np
+import torch
+
+TOKEN_MEL_RATIO = 4
+PRE_LOOKAHEAD = 3
+
+
+def fade_in_out_mel(fade_in_mel, fade_out_mel, window):
+    """flow_inference.py:35-43 for mel tensors (only reachable when a caller fills mel_overlap_dict)."""
+    n = int(window.shape[0] / 2)
+    w = torch.from_numpy(np.asarray(window, dtype=np.float32)).to(fade_in_mel.device)
+    out = fade_in_mel.clone()
+    out[..., :n] = fade_in_mel[..., :n] * w[:n] + fade_out_mel[..., -n:].to(out.device) * w[n:]
+    return out
+
+
+def _hift_chunks(dec, mels, caches, finalize, nsf_noise=None):
+    """Shared tail of token2wav_streaming for a list of streams.
+
+    mels[b]: time-major [T_b, 80] new mel frames (already cropped by token_offset); caches[b]: None or the dict
+    {'mel' [1,80,8], 'source' [1,1,3840], 'speech' [1,3840]}.  Returns (speech list [1, n_b], new caches)."""
+    dev = dec.device
+    B = len(mels)
+    full, lens, clen = [], [], []
+    S = dec.source_cache_len
+    cache_src = torch.zeros(B, S, device=dev)
+    for b in range(B):
+        m = mels[b]
+        if caches[b] is not None:
+            m = torch.cat([caches[b]['mel'][0].t().to(dev), m], 0)
+            cs = caches[b]['source'].reshape(-1)
+            cache_src[b, :cs.numel()] = cs
+            clen.append(int(cs.numel()))
+        else:
+            clen.append(0)
+        full.append(m)
+        lens.append(int(m.shape[0]))
+    mel_cat = torch.cat(full, 0)
+    wav, src = dec.engine.hift(lens, mel_cat.reshape(-1), cache_source=cache_src, cache_len=clen,
+                               nsf_noise=dec._noise_for(lens, nsf_noise),
+                               seed=dec._next_seed(), time_major=True)
+    out, new_caches, off = [], [], 0
+    for b in range(B):
+        n = lens[b] * 480
+        speech, source = wav[off:off + n], src[off:off + n]
+        off += n
+        if caches[b] is not None:
+            prev = caches[b]['speech'].reshape(-1)
+            k = min(int(prev.numel()), S, n)
+            # speech[:k] = speech[:k] * w[:k] + prev[-k:] * w[k:]   (window of 2 * source_cache_len)
+            dec.engine.fade_in_out(speech, prev[-k:].contiguous(), dec._speech_window_dev)
+        if not finalize:
+            new_caches.append({'mel': full[b][-dec.mel_cache_len:].t().unsqueeze(0).contiguous(),
+                               'source': source[-S:].clone().view(1, 1, -1), 'speech': speech[-S:].clone().view(1, -1)})
+            out.append(speech[:-S].view(1, -1))
+        else:
+            new_caches.append(caches[b])
+            out.append(speech.view(1, -1))
+    return out, new_caches
+
+
+@torch.inference_mode()
+def token2wav_streaming(dec, token, prompt_token, prompt_feat, token_offset, uuid, embedding, finalize=False,
+                        stream=False, speed=1.0):
+    """flow_inference.py:130-164."""
+    if embedding.shape[0] == 0:
+        embedding = torch.zeros(1, 192)
+    r = dec.flow_batch([token], [prompt_token], [prompt_feat], embedding, streaming=stream, finalize=finalize)
+    mel = r["mel"][r["prompt_frames"][0]:]                       # feat_return, time-major
+    mel = mel[token_offset * TOKEN_MEL_RATIO:]
+    cache = dec.hift_cache_dict[uuid]
+    if finalize and speed != 1.0:
+        assert cache is None, 'speed change only support non-stream inference mode'
+        m = torch.nn.functional.interpolate(mel.t().unsqueeze(0), size=int(mel.shape[0] / speed), mode='linear')
+        mel = m[0].t().contiguous()
+    out, caches = _hift_chunks(dec, [mel], [cache], finalize)
+    if not finalize:
+        dec.hift_cache_dict[uuid] = caches[0]
+    return out[0]
+
+
+def chunk_plan(n_tokens, n_prompt, block_size, max_token_len, pre_lookahead=PRE_LOOKAHEAD):
+    """The chunk schedule of stream_inference (flow_inference.py:186-232) as a pure function:
+    [(start, end, actual_token_offset, finalize)] over the token list.  Shared by the single-stream loop, the batched
+    scheduler and the CPU tests."""
+    plan = []
+    token_offset = 0
+    hop = block_size
+    pad = int(np.ceil(n_prompt / hop) * hop - n_prompt)
+    while True:
+        this_hop = hop + pad if token_offset == 0 else hop
+        if n_tokens - token_offset >= this_hop + pre_lookahead:
+            end = token_offset + this_hop + pre_lookahead
+            if max_token_len is not None:
+                start = max(0, end - max_token_len)
+                actual = token_offset - start if start > 0 else token_offset
+            else:
+                start, actual = 0, token_offset
+            plan.append((start, end, actual, False))
+            token_offset += this_hop
+        else:
+            break
+    if max_token_len is not None:
+        start = max(0, n_tokens - max_token_len)
+        plan.append((start, n_tokens, token_offset - start, True))
+    else:
+        plan.append((0, n_tokens, token_offset, True))
+    return plan
+
+
+@torch.inference_mode()
+def stream_inference(dec, token, prompt_token, prompt_feat, embedding, block_size=8, max_token_len=None):
+    """flow_inference.py:166-243: chunked decode of one utterance; returns the concatenated waveform on the CPU."""
+    this_uuid = str(_uuid.uuid1())
+    toks = token.reshape(-1).cpu().tolist()
+    dec.tts_speech_token_dict[this_uuid], dec.llm_end_dict[this_uuid] = toks, True
+    dec.hift_cache_dict[this_uuid] = None
+    speechs = []
+    for start, end, actual, fin in chunk_plan(len(toks), prompt_token.shape[1], block_size, max_token_len):
+        chunk = torch.tensor(toks[start:end]).unsqueeze(0)
+        sp = token2wav_streaming(dec, chunk, prompt_token, prompt_feat, actual, this_uuid, embedding,
+                                 finalize=fin, stream=not fin)
+        speechs.append(sp.cpu())
+    del dec.hift_cache_dict[this_uuid]
+    del dec.tts_speech_token_dict[this_uuid]
+    del dec.llm_end_dict[this_uuid]
+    return torch.cat(speechs, dim=-1).cpu()
+
+
+class Stream:
+    """One concurrent session of the batched scheduler."""
+
+    def __init__(self, tokens, prompt_token, prompt_feat, embedding, block_size, max_token_len):
+        self.tokens = [int(t) for t in tokens]
+        self.prompt_token, self.prompt_feat, self.embedding = prompt_token, prompt_feat, embedding
+        self.plan = chunk_plan(len(self.tokens), prompt_token.shape[1], block_size, max_token_len)
+        self.step = 0
+        self.cache = None
+        self.out = []
+
+    @property
+    def done(self):
+        return self.step >= len(self.plan)
+
+
+class StreamScheduler:
+    """Steps many streams together: every `step()` takes the next chunk of each unfinished stream, runs ONE batched
+    flow solve (block-causal for non-final chunks, full attention for final ones, like the reference's per-call flags)
+    and ONE batched vocoder pass, and returns {stream index: speech chunk [1, n]} on the device."""
+
+    def __init__(self, dec, block_size=5, max_token_len=40):
+        self.dec, self.block_size, self.max_token_len = dec, block_size, max_token_len
+        self.streams = []
+
+    def add(self, tokens, prompt_token, prompt_feat, embedding):
+        self.streams.append(Stream(tokens, prompt_token, prompt_feat, embedding, self.block_size, self.max_token_len))
+        return len(self.streams) - 1
+
+    @torch.inference_mode()
+    def step(self):
+        dec = self.dec
+        emitted = {}
+        for fin in (False, True):
+            ids = [i for i, s in enumerate(self.streams) if not s.done and s.plan[s.step][3] == fin]
+            if not ids:
+                continue
+            toks, offs = [], []
+            for i in ids:
+                s = self.streams[i]
+                start, end, actual, _ = s.plan[s.step]
+                toks.append(torch.tensor(s.tokens[start:end]).unsqueeze(0))
+                offs.append(actual)
+            emb = torch.cat([self.streams[i].embedding.reshape(1, -1) for i in ids], 0)
+            r = dec.flow_batch(toks, [self.streams[i].prompt_token for i in ids],
+                               [self.streams[i].prompt_feat for i in ids], emb, streaming=not fin, finalize=fin)
+            mels, off = [], 0
+            for k in range(len(ids)):
+                T, F_ = r["frames"][k], r["prompt_frames"][k]
+                mels.append(r["mel"][off + F_ + offs[k] * TOKEN_MEL_RATIO: off + T])
+                off += T
+            out, caches = _hift_chunks(dec, mels, [self.streams[i].cache for i in ids], fin)
+            for k, i in enumerate(ids):
+                s = self.streams[i]
+                s.cache = caches[k]
+                s.step += 1
+                s.out.append(out[k])
+                emitted[i] = out[k]
+        return emitted
+
+    def run(self):
+        while any(not s.done for s in self.streams):
+            self.step()
+        return [torch.cat(s.out, dim=-1) for s in self.streams]

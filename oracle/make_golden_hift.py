@@ -39,7 +39,59 @@ def hift_case(hift, name, T, seed, cache_len=0):
 
 
 def run(what, flow):
+    hift = build_ref.build_hift()
+    if what & {"e2e", "stream"}:
+        e2e_cases(flow, hift)
     if "hift" in what:
-        hift = build_ref.build_hift()
         hift_case(hift, "hift_T40.npz", 40, 300)
         hift_case(hift, "hift_T28_cache.npz", 28, 301, cache_len=3840)
+
+
+def _spy_hift_lengths(hift):
+    """Wrap hift.inference to record the number of mel frames of every vocoder call."""
+    calls = []
+    orig = hift.inference
+
+    def wrapped(speech_feat, cache_source=torch.zeros(1, 1, 0)):
+        calls.append(int(speech_feat.shape[2]))
+        return orig(speech_feat=speech_feat, cache_source=cache_source)
+    hift.inference = wrapped
+    return calls
+
+
+def e2e_cases(flow, hift):
+    """token2wav (flow_inference.py:94-123) and stream_inference (:166-243) through the reference's REAL AudioDecoder."""
+    from .make_golden import _save, _logmel_like
+    from . import rng_replay
+    dec = build_ref.make_audio_decoder(flow, hift)
+    calls = _spy_hift_lengths(dec.hift)
+    # ---- non-streaming, with prompt
+    g = torch.Generator().manual_seed(400)
+    N, P = 30, 10
+    token = torch.randint(0, 16384, (1, N), generator=g)
+    prompt_token = torch.randint(0, 16384, (1, P), generator=g).to(torch.int32)
+    prompt_feat = _logmel_like(g, 4 * P)
+    emb = torch.randn(1, 192, generator=g)
+    seed = 401
+    torch.manual_seed(seed)
+    calls.clear()
+    wav, mel = dec.token2wav(token, "golden-e2e", prompt_token=prompt_token, prompt_feat=prompt_feat, embedding=emb)
+    noise = rng_replay.replay(seed, [480 * t for t in calls])
+    _save("e2e_N30_P10.npz", token=token, prompt_token=prompt_token, prompt_feat=prompt_feat, embedding=emb, wav=wav[0],
+          mel=mel[0], seed=np.int64(seed), hift_frames=np.array(calls), noise_fp=np.array(rng_replay.fingerprint(noise[0])))
+    # ---- streaming: 33 tokens, P = 7, block 5, window 20 (the window slides), chunked flow masks of 25 tokens
+    g = torch.Generator().manual_seed(410)
+    N, P = 33, 7
+    token = torch.randint(0, 16384, (1, N), generator=g)
+    prompt_token = torch.randint(0, 16384, (1, P), generator=g).to(torch.int32)
+    prompt_feat = _logmel_like(g, 4 * P)
+    emb = torch.randn(1, 192, generator=g)
+    seed = 411
+    torch.manual_seed(seed)
+    calls.clear()
+    wav = dec.stream_inference(token, prompt_token=prompt_token, prompt_feat=prompt_feat, embedding=emb, block_size=5,
+                               max_token_len=20)
+    noise = rng_replay.replay(seed, [480 * t for t in calls])
+    _save("stream_N33_P7.npz", token=token, prompt_token=prompt_token, prompt_feat=prompt_feat, embedding=emb,
+          wav=wav[0], seed=np.int64(seed), hift_frames=np.array(calls), block_size=np.int64(5), max_token_len=np.int64(20),
+          noise_fp=np.array([rng_replay.fingerprint(n) for n in noise]))
