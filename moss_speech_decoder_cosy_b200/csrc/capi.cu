@@ -79,6 +79,10 @@ int mossdec_debug_read(mossdec_handle* h, const char* name, float* host_dst, int
     return h->eng->debug_read(name, host_dst, (size_t)max_floats * 4);
 }
 
+void mossdec_profile(mossdec_handle* h, int32_t on) { h->eng->set_profile(on != 0); }
+int mossdec_profile_read(mossdec_handle* h, double* out6) { return h->eng->profile_read(out6); }
+void mossdec_set_hift_group_frames(mossdec_handle* h, int64_t frames) { h->eng->set_hift_group_frames(frames); }
+
 int64_t mossdec_launch_count(const mossdec_handle* h) { return h->eng->launches(); }
 void mossdec_reset_launch_count(mossdec_handle* h) { h->eng->reset_launches(); }
 

@@ -75,6 +75,9 @@ class Engine {
     int hift(int B, const int32_t* lens, const float* mel, const float* cache_source, int cache_stride,
              const int32_t* cache_len, const float* nsf_noise, float* wav_out, float* source_out, uint64_t seed,
              int flags, cudaStream_t st);
+    // per-launch device timing of the GEMM-class (0) and attention (1) kernels with CUDA events on the launch stream
+    void set_profile(bool on) { profile_ = on; }
+    int profile_read(double* out6);
     // test hook: copy a named intermediate of the last call to the host; returns floats copied or -1
     int debug_read(const char* name, void* host_dst, size_t bytes);
     int fade_in_out(float* speech, const float* prev_tail, const float* window2n, int n, cudaStream_t st);
@@ -133,6 +136,13 @@ class Engine {
     DeviceBuffer ws_hift_, ws_hift_layout_;
     bool has_hift_ = false;
     std::map<std::string, std::pair<const void*, size_t>> taps_;
+    struct ProfRec { cudaEvent_t a, b; int cls; double flops; };
+    bool profile_ = false;
+    std::vector<ProfRec> prof_;
+    std::vector<cudaEvent_t> prof_pool_;
+    cudaEvent_t prof_event();
+    void prof_begin(int cls, double flops, cudaStream_t st);
+    void prof_end(cudaStream_t st);
     int64_t hift_group_frames_ = 8192;  // frames per HiFT group (bounds the stage-2 working set)
 };
 

@@ -73,8 +73,47 @@ const DevTensor* Engine::find(const std::string& name) {
     return &it->second;
 }
 
+cudaEvent_t Engine::prof_event() {
+    if (!prof_pool_.empty()) {
+        cudaEvent_t e = prof_pool_.back();
+        prof_pool_.pop_back();
+        return e;
+    }
+    cudaEvent_t e;
+    cudaEventCreate(&e);
+    return e;
+}
+void Engine::prof_begin(int cls, double flops, cudaStream_t st) {
+    ProfRec r{prof_event(), prof_event(), cls, flops};
+    cudaEventRecord(r.a, st);
+    prof_.push_back(r);
+}
+void Engine::prof_end(cudaStream_t st) { cudaEventRecord(prof_.back().b, st); }
+
+int Engine::profile_read(double* out) {
+    for (int i = 0; i < 6; ++i) out[i] = 0.0;
+    if (cudaDeviceSynchronize() != cudaSuccess) return fail("profile_read: sync failed");
+    for (auto& r : prof_) {
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, r.a, r.b);
+        out[r.cls * 3 + 0] += ms;
+        out[r.cls * 3 + 1] += 1.0;
+        out[r.cls * 3 + 2] += r.flops;
+        prof_pool_.push_back(r.a);
+        prof_pool_.push_back(r.b);
+    }
+    prof_.clear();
+    return 0;
+}
+
 int Engine::gemm(const GemmProblem& p, cudaStream_t st) {
+    if (profile_) {
+        int kb = 0;
+        for (int s = 0; s < p.num_segs; ++s) kb += p.segs[s].nkb;
+        prof_begin(0, 2.0 * p.M * p.N * kb * kGemmBK, st);
+    }
     cudaError_t e = gemm_tc_launch(p, num_sms_, st);
+    if (profile_) prof_end(st);
     ++launches_;
     if (e != cudaSuccess) return fail(std::string("gemm_tc_launch: ") + cudaGetErrorString(e));
     return 0;
@@ -298,7 +337,9 @@ int Engine::estimator_forward(int M, int nseq, int max_len, const float* tbias, 
                 p.epi.out_bf16 = qkv_; p.epi.ldo = 3 * H;
                 if (gemm(p, st)) return -1;
             }
+            if (profile_) prof_begin(1, 0.0, st);
             launch_attention(qkv_, att_, layout_.seq_start, layout_.seq_len, nseq, max_len, cfg_.heads, chunk, st);
+            if (profile_) prof_end(st);
             ++launches_;
             {   // out projection + residual, emits norm3
                 GemmProblem p;

@@ -151,41 +151,71 @@ class AudioDecoder(torch.nn.Module):
         per-utterance frame counts T_b and prompt frame counts F_b."""
         dev = self.device
         B = len(tokens)
-        ctx = 0 if finalize else PRE_LOOKAHEAD
         rows = [torch.cat([prompt_tokens[b].reshape(-1).long().cpu(), tokens[b].reshape(-1).long().cpu()])
                 for b in range(B)]
         lens_tok = [int(r.numel()) for r in rows]
-        if min(lens_tok) - ctx <= 0:
-            raise ValueError("every utterance needs at least one token besides the look-ahead context")
         tok = torch.zeros(B, max(lens_tok), dtype=torch.long).pin_memory()
         for b, r in enumerate(rows):
             tok[b, :lens_tok[b]] = r
-        tok = tok.to(dev, non_blocking=True)
-        lens_t = torch.tensor(lens_tok, dtype=torch.long).to(dev)
+        F_ = [int(pf.shape[1]) for pf in prompt_feats]
+        feats = [pf.reshape(-1, 80) for pf in prompt_feats if pf.shape[1]]
+        feat_cat = torch.cat(feats, 0).float() if feats else torch.zeros(0, 80)
+        return self.flow_device(tok.to(dev, non_blocking=True), lens_tok, feat_cat.to(dev, non_blocking=True), F_,
+                                embeddings.to(dev, non_blocking=True), streaming, finalize)
+
+    @torch.inference_mode()
+    def flow_device(self, tok, lens_tok, prompt_feat_cat, prompt_frames, embeddings, streaming, finalize):
+        """Device-resident core of flow_batch: tok int64 [B, Lmax] (prompt + new tokens, right padded), lens_tok host
+        list, prompt_feat_cat [sum F_b, 80] (prompt mels back to back), prompt_frames host list F_b, embeddings
+        [B, 192] -- all tensors already on the device."""
+        dev = self.device
+        B = len(lens_tok)
+        ctx = 0 if finalize else PRE_LOOKAHEAD
+        if min(lens_tok) - ctx <= 0:
+            raise ValueError("every utterance needs at least one token besides the look-ahead context")
+        lens_t = torch.tensor(lens_tok, dtype=torch.long).to(dev, non_blocking=True)
         chunk_tokens = self.static_chunk_size if streaming else 0
         mu_pad, main = frontend.encode(self.enc_weights, tok, lens_t, ctx, chunk_tokens)
         T = [(n - ctx) * TOKEN_MEL_RATIO for n in lens_tok]
+        F_ = list(prompt_frames)
         Tmax = mu_pad.shape[1]
         if all(t == Tmax for t in T):
             mu = mu_pad.reshape(-1, 80)
         else:
             valid = torch.arange(Tmax, device=dev).unsqueeze(0) < (main * TOKEN_MEL_RATIO).unsqueeze(1)
             mu = mu_pad[valid]
-        F_ = [int(pf.shape[1]) for pf in prompt_feats]
-        parts = []
-        for b in range(B):
-            if F_[b] > T[b]:
-                raise ValueError("prompt_feat longer than the decoded sequence")
-            if F_[b]:
-                parts.append(prompt_feats[b].reshape(F_[b], 80).to(dev, non_blocking=True).float())
-            parts.append(torch.zeros(T[b] - F_[b], 80, device=dev))
-        cond = torch.cat(parts, 0)                                    # flow.py:268-270
-        spks = frontend.speaker_projection(self.enc_weights, embeddings.to(dev))
+        if any(f > t for f, t in zip(F_, T)):
+            raise ValueError("prompt_feat longer than the decoded sequence")
+        cond = torch.zeros(sum(T), 80, device=dev)                    # flow.py:268-270
+        if sum(F_):
+            dst, off = [], 0
+            for t, f in zip(T, F_):
+                dst.append(torch.arange(off, off + f))
+                off += t
+            cond.index_copy_(0, torch.cat(dst).to(dev, non_blocking=True), prompt_feat_cat.float())
+        spks = frontend.speaker_projection(self.enc_weights, embeddings)
         mel = self.engine.flow_solve(T, mu.reshape(-1), spks, cond.reshape(-1), n_steps=self.n_timesteps,
                                      cfg_rate=self.inference_cfg_rate,
                                      chunk=self.static_chunk_size * TOKEN_MEL_RATIO if streaming else 0,
                                      time_major=True).view(-1, 80)
         return {"mel": mel, "frames": T, "prompt_frames": F_}
+
+    @torch.inference_mode()
+    def vocode_generated(self, r, nsf_noise=None, seed=None):
+        """Strip the prompt frames of a flow result (flow.py:281) and run the vocoder on the generated part."""
+        T, F_ = r["frames"], r["prompt_frames"]
+        gen = [t - f for t, f in zip(T, F_)]
+        if any(F_):
+            idx, off = [], 0
+            for t, f in zip(T, F_):
+                idx.append(torch.arange(off + f, off + t))
+                off += t
+            mel = r["mel"].index_select(0, torch.cat(idx).to(self.device, non_blocking=True))
+        else:
+            mel = r["mel"]
+        wav, _ = self.engine.hift(gen, mel.reshape(-1), nsf_noise=self._noise_for(gen, nsf_noise),
+                                  seed=self._next_seed() if seed is None else seed, want_source=False, time_major=True)
+        return {"wav": wav, "wav_lens": [g * 480 for g in gen], "mel": mel, "mel_lens": gen}
 
     @torch.inference_mode()
     def decode_batch(self, tokens, prompt_tokens=None, prompt_feats=None, embeddings=None, nsf_noise=None, seed=None):
@@ -198,19 +228,7 @@ class AudioDecoder(torch.nn.Module):
         if embeddings is None:
             embeddings = torch.zeros(B, 192)
         r = self.flow_batch(tokens, prompt_tokens, prompt_feats, embeddings, streaming=False, finalize=True)
-        T, F_ = r["frames"], r["prompt_frames"]
-        gen = [t - f for t, f in zip(T, F_)]
-        if any(F_):
-            idx, off = [], 0
-            for t, f in zip(T, F_):
-                idx.append(torch.arange(off + f, off + t))
-                off += t
-            mel = r["mel"].index_select(0, torch.cat(idx).to(self.device))      # strip prompt frames, flow.py:281
-        else:
-            mel = r["mel"]
-        wav, _ = self.engine.hift(gen, mel.reshape(-1), nsf_noise=self._noise_for(gen, nsf_noise),
-                                  seed=self._next_seed() if seed is None else seed, want_source=False, time_major=True)
-        return {"wav": wav, "wav_lens": [g * 480 for g in gen], "mel": mel, "mel_lens": gen}
+        return self.vocode_generated(r, nsf_noise, seed)
 
     def token2wav_batch(self, tokens, prompt_tokens=None, prompt_feats=None, embeddings=None, **kw):
         """List-of-utterances convenience wrapper: returns [(tts_speech [1, 1920 N_b], tts_mel [1, 80, 4 N_b])]."""

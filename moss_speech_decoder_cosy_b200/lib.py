@@ -55,6 +55,12 @@ def load_library():
     lib.mossdec_fade_in_out.restype = i32
     lib.mossdec_debug_read.argtypes = [vp, ctypes.c_char_p, vp, i64]
     lib.mossdec_debug_read.restype = i32
+    lib.mossdec_profile.argtypes = [vp, i32]
+    lib.mossdec_profile.restype = None
+    lib.mossdec_profile_read.argtypes = [vp, ctypes.POINTER(ctypes.c_double)]
+    lib.mossdec_profile_read.restype = i32
+    lib.mossdec_set_hift_group_frames.argtypes = [vp, i64]
+    lib.mossdec_set_hift_group_frames.restype = None
     lib.mossdec_launch_count.argtypes = [vp]
     lib.mossdec_launch_count.restype = i64
     lib.mossdec_reset_launch_count.argtypes = [vp]
@@ -66,7 +72,8 @@ def load_library():
 EXPORTED_SYMBOLS = [
     "mossdec_default_config", "mossdec_create", "mossdec_destroy", "mossdec_last_error", "mossdec_set_tensor",
     "mossdec_finalize", "mossdec_estimator", "mossdec_flow_solve", "mossdec_hift", "mossdec_fade_in_out",
-    "mossdec_launch_count", "mossdec_reset_launch_count", "mossdec_debug_read",
+    "mossdec_launch_count", "mossdec_reset_launch_count", "mossdec_debug_read", "mossdec_profile",
+    "mossdec_profile_read", "mossdec_set_hift_group_frames",
 ]
 
 
@@ -186,6 +193,18 @@ class Engine:
         if n < 0:
             raise RuntimeError(f"debug_read({name}) failed: {self.lib.mossdec_last_error(self.h).decode()}")
         return buf[:n]
+
+    def profile(self, on=True):
+        self.lib.mossdec_profile(self.h, int(bool(on)))
+
+    def profile_read(self):
+        out = (ctypes.c_double * 6)()
+        self._check(self.lib.mossdec_profile_read(self.h, out), "profile_read")
+        return {"gemm_ms": out[0], "gemm_launches": int(out[1]), "gemm_hw_flops": out[2], "attn_ms": out[3],
+                "attn_launches": int(out[4])}
+
+    def set_hift_group_frames(self, frames):
+        self.lib.mossdec_set_hift_group_frames(self.h, int(frames))
 
     def launch_count(self):
         return int(self.lib.mossdec_launch_count(self.h))

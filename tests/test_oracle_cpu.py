@@ -1,0 +1,69 @@
+"""CPU: the oracle restatement (oracle/port.py) against golden outputs of the UNMODIFIED reference (tests/golden,
+produced from /root/reference by oracle/make_golden*.py).  This pins the oracle that the GPU box uses as checker and as
+timed CPU baseline.  fp32 on both sides: tolerances are round-off level."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from conftest import GOLDEN
+from moss_speech_decoder_cosy_b200 import synth
+from oracle import port, rng_replay
+
+
+@pytest.fixture(scope="module")
+def sds():
+    return synth.synth_flow_state_dict(0), synth.synth_hift_state_dict(0)
+
+
+def _rel(a, b):
+    return float(torch.linalg.norm(a.double() - b.double()) / torch.linalg.norm(b.double()))
+
+
+@pytest.mark.parametrize("mode", ["full", "chunk"])
+def test_estimator_restatement(sds, mode):
+    z = np.load(os.path.join(GOLDEN, "estimator_T36.npz"))
+    t = {k: torch.from_numpy(z[k]) for k in ("x", "mu", "cond", "spks", "t")}
+    with torch.inference_mode():
+        out = port.estimator(sds[0], t["x"], torch.ones(2, 1, 36), t["mu"], t["t"], t["spks"], t["cond"],
+                             chunk=int(z["chunk"]) if mode == "chunk" else 0)
+    ref = torch.from_numpy(z["out_full" if mode == "full" else "out_chunk"])
+    torch.testing.assert_close(out, ref, rtol=1e-2, atol=1e-4)   # the reference's own bar, export_onnx.py:105
+    assert _rel(out, ref) < 1e-5
+
+
+def test_euler_solve_restatement(sds):
+    z = np.load(os.path.join(GOLDEN, "solve_T64.npz"))
+    with torch.inference_mode():
+        mel = port.solve_euler(sds[0], torch.from_numpy(z["mu"]), torch.from_numpy(z["spks"]),
+                               torch.from_numpy(z["cond"]), torch.from_numpy(z["noise"]))
+    assert _rel(mel, torch.from_numpy(z["mel"])) < 1e-4
+    assert torch.equal(port.noise_bank()[:, :64], torch.from_numpy(z["noise"]))
+
+
+@pytest.mark.parametrize("name", ["hift_T40", "hift_T28_cache"])
+def test_hift_restatement(sds, name):
+    z = np.load(os.path.join(GOLDEN, name + ".npz"))
+    mel, noise = torch.from_numpy(z["mel"]), torch.from_numpy(z["noise"])
+    with torch.inference_mode():
+        f0 = port.f0_predictor(sds[1], mel.unsqueeze(0))[0]
+        wav, src = port.hift_inference(sds[1], mel, noise, torch.from_numpy(z["cache"]))
+    torch.testing.assert_close(f0, torch.from_numpy(z["f0"]), rtol=1e-5, atol=1e-4)
+    ref_w, ref_s = torch.from_numpy(z["wav"]), torch.from_numpy(z["source"])
+    snr = lambda x, r: float(10 * torch.log10(r.pow(2).sum() / (x - r).pow(2).sum().clamp_min(1e-30)))
+    assert snr(src, ref_s) > 80.0
+    assert snr(wav, ref_w) > 60.0
+
+
+def test_token2wav_restatement(sds):
+    z = np.load(os.path.join(GOLDEN, "e2e_N30_P10.npz"))
+    noise = rng_replay.replay(int(z["seed"]), [480 * int(z["hift_frames"][0])])[0]
+    if not np.allclose(rng_replay.fingerprint(noise), z["noise_fp"], rtol=1e-6):
+        pytest.skip("torch CPU generator differs from the build that produced the fixture")
+    dec = port.PortDecoder(*sds)
+    wav, mel = dec.token2wav(torch.from_numpy(z["token"]), torch.from_numpy(z["prompt_token"]),
+                             torch.from_numpy(z["prompt_feat"]), torch.from_numpy(z["embedding"]), noise=noise)
+    assert _rel(mel[0], torch.from_numpy(z["mel"])) < 1e-4
+    ref = torch.from_numpy(z["wav"])
+    assert float(10 * torch.log10(ref.pow(2).sum() / (wav[0] - ref).pow(2).sum())) > 40.0
