@@ -14,10 +14,15 @@ namespace mossdec {
 
 namespace {
 
-constexpr int kThreads = 192;  // warp0 = TMA, warp1 = MMA (+TMEM alloc), warps 2..5 = epilogue
+// warp 0 = TMA producer, warp 1 = MMA issuer (+ TMEM alloc), warps 2..9 = epilogue.
+// A warp may only touch TMEM lanes [32 * (warp % 4), +32), so the 8 epilogue warps form 4 pairs: both warps of a
+// pair own the same 32 rows of the tile and split its columns in two halves.
+constexpr int kEpiWarps = 8;
+constexpr int kThreads = 64 + 32 * kEpiWarps;
 constexpr int kABytes = kGemmBM * kGemmBK * 2;  // 16 KB
 constexpr int kBBytesMax = 256 * kGemmBK * 2;   // 32 KB
-constexpr int kSmemBytes = kGemmStages * (kABytes + kBBytesMax) + 1024 /*align slack*/ + 256 /*barriers*/;
+constexpr int kStageBytes = 4096;               // per-epilogue-warp staging tile: 32 rows x 128 B
+constexpr int kSmemBytes = kGemmStages * (kABytes + kBBytesMax) + kEpiWarps * kStageBytes + 1024 /*align*/ + 256 /*barriers*/;
 constexpr uint32_t kTmemCols = 512;
 
 struct KParams {
@@ -27,20 +32,281 @@ struct KParams {
     GemmEpilogue epi;
 };
 
-__device__ __forceinline__ float apply_act(float x, int act, float p, const float* alpha, int n) {
+__device__ __forceinline__ float4 ldg4(const float* p) { return __ldg(reinterpret_cast<const float4*>(p)); }
+
+__device__ __forceinline__ float fast_mish(float x) {
+    // x * tanh(softplus(x)) with u = e^x: tanh(log(1 + u)) = (u^2 + 2u) / (u^2 + 2u + 2)
+    const float u = __expf(fminf(x, 20.f));
+    const float n = u * (u + 2.f);
+    return x > 20.f ? x : x * __fdividef(n, n + 2.f);
+}
+__device__ __forceinline__ float fast_sin(float x) {
+    // two-term Cody-Waite reduction to [-pi, pi], then the SFU sine (abs error ~1e-6 for |x| < 1e4)
+    const float k = rintf(x * 0.15915494309189535f);
+    float r = fmaf(k, -6.2831854820251465f, x);
+    r = fmaf(k, 1.7484555e-7f, r);
+    return __sinf(r);
+}
+
+// activation over a register vector (the switch is evaluated once per vector, not per element)
+template <int NV>
+__device__ __forceinline__ void apply_act_vec(float* v, int act, float p, const float* alpha) {
     switch (act) {
-        case ACT_MISH: return mish_f(x);
-        case ACT_GELU: return gelu_erf_f(x);
-        case ACT_ELU: return elu_f(x);
-        case ACT_LRELU: return x > 0.f ? x : x * p;
-        case ACT_SNAKE: {
-            float a = __ldg(alpha + n);
-            float s = sinf(x * a);
-            return x + s * s / (a + 1e-9f);
+        case ACT_MISH:
+#pragma unroll
+            for (int i = 0; i < NV; ++i) v[i] = fast_mish(v[i]);
+            break;
+        case ACT_GELU:
+#pragma unroll
+            for (int i = 0; i < NV; ++i) v[i] = gelu_erf_f(v[i]);
+            break;
+        case ACT_ELU:
+#pragma unroll
+            for (int i = 0; i < NV; ++i) v[i] = v[i] > 0.f ? v[i] : expm1f(v[i]);
+            break;
+        case ACT_LRELU:
+#pragma unroll
+            for (int i = 0; i < NV; ++i) v[i] = v[i] > 0.f ? v[i] : v[i] * p;
+            break;
+        case ACT_SNAKE:
+#pragma unroll
+            for (int i = 0; i < NV; i += 4) {
+                const float4 a = ldg4(alpha + i);
+                const float aa[4] = {a.x, a.y, a.z, a.w};
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const float s = fast_sin(v[i + j] * aa[j]);
+                    v[i + j] = fmaf(__fdividef(1.f, aa[j] + 1e-9f), s * s, v[i + j]);
+                }
+            }
+            break;
+        case ACT_SILU:
+#pragma unroll
+            for (int i = 0; i < NV; ++i) v[i] = silu_f(v[i]);
+            break;
+        case ACT_ABS:
+#pragma unroll
+            for (int i = 0; i < NV; ++i) v[i] = fabsf(v[i]);
+            break;
+        default: break;
+    }
+}
+
+// ---- per-warp staging tile: 32 rows x RB bytes (RB = 128 or 64) held as 128-byte lines with the 16-byte units of a
+// line XOR-swizzled by the line index, so both the thread==row side and the coalesced side are bank-conflict free.
+template <int RB>
+__device__ __forceinline__ uint32_t stage_off(int r, int u) {  // logical (row, 16-byte unit) -> byte offset
+    if (RB == 128) return (uint32_t)(r * 128 + ((u ^ (r & 7)) << 4));
+    const int line = r >> 1;
+    return (uint32_t)(line * 128 + (((((r & 1) << 2) | u) ^ (line & 7)) << 4));
+}
+// coalesced side: pass k (0 .. RB/16 - 1), lane -> logical (row, unit); the 32 lanes of a pass cover 4 whole lines
+template <int RB>
+__device__ __forceinline__ void stage_coalesced(int k, int lane, int& r, int& u) {
+    const int line = k * 4 + (lane >> 3);
+    if (RB == 128) {
+        r = line;
+        u = (lane & 7) ^ (line & 7);
+    } else {
+        const int pos = (lane & 7) ^ (line & 7);
+        r = line * 2 + (pos >> 2);
+        u = pos & 3;
+    }
+}
+
+struct EpiCtx {
+    const KParams* p;
+    uint8_t* stg;       // this warp's staging tile
+    uint8_t* stg_peer;  // staging tile of the warp that owns the other column half of the same rows
+    uint32_t taddr;     // TMEM address of (lane quarter, accumulator)
+    int lane, quarter, row0, n0, seq;
+    bool valid;         // this thread's row exists and belongs to a sequence
+};
+
+__device__ __forceinline__ void pair_sync(int quarter) {
+    asm volatile("bar.sync %0, 64;" ::"r"(quarter + 1) : "memory");
+}
+// exchange one float2 per row with the peer warp (row statistics over the full tile width)
+__device__ __forceinline__ float2 pair_exchange(const EpiCtx& c, float2 mine) {
+    reinterpret_cast<float2*>(c.stg)[c.lane] = mine;
+    pair_sync(c.quarter);
+    const float2 other = reinterpret_cast<const float2*>(c.stg_peer)[c.lane];
+    pair_sync(c.quarter);
+    return make_float2(mine.x + other.x, mine.y + other.y);
+}
+
+// coalesced global -> registers (thread == row) through the staging tile; fp32, 32 columns starting at column nb
+__device__ __forceinline__ void load_rows_f32(const EpiCtx& c, const float* base, int ld, int nb, int nlim, float* out32) {
+    const KParams& p = *c.p;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        int r, u;
+        stage_coalesced<128>(k, c.lane, r, u);
+        const int grow = c.row0 + r, col = nb + u * 4;
+        float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (grow < p.M && col < nlim) t = *reinterpret_cast<const float4*>(base + (size_t)grow * ld + col);
+        *reinterpret_cast<float4*>(c.stg + k * 512 + c.lane * 16) = t;
+    }
+    __syncwarp();
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+        const float4 t = *reinterpret_cast<const float4*>(c.stg + stage_off<128>(c.lane, u));
+        out32[u * 4] = t.x; out32[u * 4 + 1] = t.y; out32[u * 4 + 2] = t.z; out32[u * 4 + 3] = t.w;
+    }
+    __syncwarp();
+}
+__device__ __forceinline__ void store_rows_f32(const EpiCtx& c, float* base, int ld, int nb, int nlim, const float* v32) {
+    const KParams& p = *c.p;
+#pragma unroll
+    for (int u = 0; u < 8; ++u)
+        *reinterpret_cast<float4*>(c.stg + stage_off<128>(c.lane, u)) =
+            make_float4(v32[u * 4], v32[u * 4 + 1], v32[u * 4 + 2], v32[u * 4 + 3]);
+    __syncwarp();
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        int r, u;
+        stage_coalesced<128>(k, c.lane, r, u);
+        const int grow = c.row0 + r, col = nb + u * 4;
+        const float4 t = *reinterpret_cast<const float4*>(c.stg + k * 512 + c.lane * 16);
+        if (grow < p.M && col < nlim) *reinterpret_cast<float4*>(base + (size_t)grow * ld + col) = t;
+    }
+    __syncwarp();
+}
+// registers (thread == row, NV values) -> bf16 global, coalesced; RB = NV * 2 bytes per row
+template <int NV>
+__device__ __forceinline__ void store_rows_bf16(const EpiCtx& c, __nv_bfloat16* base, int ld, int nb, int nlim,
+                                                const float* v) {
+    constexpr int RB = NV * 2;
+    const KParams& p = *c.p;
+#pragma unroll
+    for (int u = 0; u < NV / 8; ++u) {
+        uint4 t;
+        t.x = pack_bf16x2(v[u * 8], v[u * 8 + 1]);
+        t.y = pack_bf16x2(v[u * 8 + 2], v[u * 8 + 3]);
+        t.z = pack_bf16x2(v[u * 8 + 4], v[u * 8 + 5]);
+        t.w = pack_bf16x2(v[u * 8 + 6], v[u * 8 + 7]);
+        *reinterpret_cast<uint4*>(c.stg + stage_off<RB>(c.lane, u)) = t;
+    }
+    __syncwarp();
+#pragma unroll
+    for (int k = 0; k < RB / 16; ++k) {
+        int r, u;
+        stage_coalesced<RB>(k, c.lane, r, u);
+        const int grow = c.row0 + r, col = nb + u * 8;
+        const uint4 t = *reinterpret_cast<const uint4*>(c.stg + k * 512 + c.lane * 16);
+        if (grow < p.M && col < nlim) *reinterpret_cast<uint4*>(base + (size_t)grow * ld + col) = t;
+    }
+    __syncwarp();
+}
+
+// One pass over this warp's column range [cbeg, cend) (16-column chunks of the tile), W16 chunks at a time.
+// W16 == 4 is the bf16-only fast path (no fp32 input / output); W16 == 2 handles everything.
+template <int W16>
+__device__ __forceinline__ void epi_main(const EpiCtx& c, int cbeg, int cend, float mean1, float rstd1, float& s2,
+                                         float& ss2) {
+    constexpr int NV = W16 * 16;
+    const KParams& p = *c.p;
+    const GemmEpilogue& e = p.epi;
+    for (int cc = cbeg; cc < cend; cc += W16) {
+        const int nch = min(W16, cend - cc);
+        const int nb = c.n0 + cc * 16;
+        const int nlim = min(p.N, nb + nch * 16);  // columns of this super-chunk that exist and are ours
+        float v[NV];
+#pragma unroll
+        for (int j = 0; j < W16; ++j) {
+            if (j < nch) {
+                tmem_ld16(c.taddr + (uint32_t)((cc + j) * 16), v + j * 16);
+            } else {
+#pragma unroll
+                for (int i = 0; i < 16; ++i) v[j * 16 + i] = 0.f;
+            }
         }
-        case ACT_SILU: return silu_f(x);
-        case ACT_ABS: return fabsf(x);
-        default: return x;
+        tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < W16; ++j) {
+            if (j < nch) {
+                float* w = v + j * 16;
+                const int n = nb + j * 16;
+                if (e.bias) {
+#pragma unroll
+                    for (int i = 0; i < 16; i += 4) {
+                        const float4 b = ldg4(e.bias + n + i);
+                        w[i] += b.x; w[i + 1] += b.y; w[i + 2] += b.z; w[i + 3] += b.w;
+                    }
+                }
+                if (e.ln1_g) {
+#pragma unroll
+                    for (int i = 0; i < 16; i += 4) {
+                        const float4 g = ldg4(e.ln1_g + n + i), b = ldg4(e.ln1_b + n + i);
+                        w[i] = (w[i] - mean1) * rstd1 * g.x + b.x;
+                        w[i + 1] = (w[i + 1] - mean1) * rstd1 * g.y + b.y;
+                        w[i + 2] = (w[i + 2] - mean1) * rstd1 * g.z + b.z;
+                        w[i + 3] = (w[i + 3] - mean1) * rstd1 * g.w + b.w;
+                    }
+                }
+                apply_act_vec<16>(w, e.act1, e.act1_p, e.act1_alpha ? e.act1_alpha + n : nullptr);
+                if (e.tbias) {
+                    const float* tb = e.tbias + (size_t)(c.seq < 0 ? 0 : c.seq) * e.tbias_ld + n;
+#pragma unroll
+                    for (int i = 0; i < 16; i += 4) {
+                        const float4 b = ldg4(tb + i);
+                        w[i] += b.x; w[i + 1] += b.y; w[i + 2] += b.z; w[i + 3] += b.w;
+                    }
+                }
+            }
+        }
+        if (W16 == 2) {
+            if (e.resid) {
+                float r[32];
+                load_rows_f32(c, e.resid, e.ldr, nb, nlim, r);
+#pragma unroll
+                for (int i = 0; i < 32; ++i) v[i] += r[i];
+            }
+            if (e.accum_f32) {
+                float r[32];
+                load_rows_f32(c, e.out_f32, e.ldf, nb, nlim, r);
+#pragma unroll
+                for (int i = 0; i < 32; ++i) v[i] += r[i];
+            }
+        }
+        if (c.valid) {
+            if (e.out_scale != 1.f) {
+#pragma unroll
+                for (int i = 0; i < NV; ++i) v[i] *= e.out_scale;
+            }
+        } else {
+#pragma unroll
+            for (int i = 0; i < NV; ++i) v[i] = 0.f;
+        }
+        if (W16 == 2) {
+            if (e.out_f32) store_rows_f32(c, e.out_f32, e.ldf, nb, nlim, v);
+            if (e.ln2_g) {
+#pragma unroll
+                for (int i = 0; i < NV; ++i) {
+                    s2 += v[i];
+                    ss2 += v[i] * v[i];
+                }
+                continue;  // bf16 side is produced by the second pass
+            }
+        }
+        if (e.out_bf16) {
+            if (e.act2 != ACT_NONE) {
+#pragma unroll
+                for (int j = 0; j < W16; ++j)
+                    if (j < nch)
+                        apply_act_vec<16>(v + j * 16, e.act2, e.act2_p, e.act2_alpha ? e.act2_alpha + nb + j * 16 : nullptr);
+                if (!c.valid) {
+#pragma unroll
+                    for (int i = 0; i < NV; ++i) v[i] = 0.f;
+                }
+            }
+            store_rows_bf16<NV>(c, e.out_bf16, e.ldo, nb, nlim, v);
+            if (e.out_bf16_lo) {
+#pragma unroll
+                for (int i = 0; i < NV; ++i) v[i] -= __bfloat162float(__float2bfloat16(v[i]));
+                store_rows_bf16<NV>(c, e.out_bf16_lo, e.ldo, nb, nlim, v);
+            }
+        }
     }
 }
 
@@ -51,7 +317,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* sA = smem;
     uint8_t* sB = smem + kGemmStages * kABytes;
-    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kGemmStages * (kABytes + kBBytesMax));
+    uint8_t* sStage = smem + kGemmStages * (kABytes + kBBytesMax);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(sStage + kEpiWarps * kStageBytes);
     uint64_t* full = bars;                     // [stages]
     uint64_t* empty = bars + kGemmStages;      // [stages]
     uint64_t* tfull = bars + 2 * kGemmStages;  // [2]
@@ -71,7 +338,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
         }
         for (int i = 0; i < 2; ++i) {
             mbar_init(&tfull[i], 1);
-            mbar_init(&tempty[i], 4);
+            mbar_init(&tempty[i], kEpiWarps);
         }
         mbar_fence_init();
     }
@@ -143,183 +410,89 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
             }
         }
     } else {
-        // ------------------------------------------------------------ epilogue (thread == row)
+        // ------------------------------------------------------------ epilogue (thread == row, 2 warps per row group)
         const GemmEpilogue& e = p.epi;
-        const int quarter = warp & 3;  // TMEM lane quarter this warp may access
+        const int ew = warp - 2;
+        const int half = ew >> 2;
+        EpiCtx c;
+        c.p = &p;
+        c.lane = lane;
+        c.quarter = warp & 3;  // TMEM lane quarter this warp may access
+        c.stg = sStage + ew * kStageBytes;
+        c.stg_peer = sStage + (ew ^ 4) * kStageBytes;
         const int nchunks = p.BN / 16;
+        const int csplit = (nchunks + 1) / 2;
+        const int cbeg = half ? csplit : 0, cend = half ? nchunks : csplit;
+        const bool fast_bf16 = !e.resid && !e.accum_f32 && !e.out_f32 && !e.ln2_g;
         int acc = 0;
         uint32_t accphase = 0;
         for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
             const int m0 = (tile / p.tiles_n) * kGemmBM;
-            const int n0 = (tile % p.tiles_n) * p.BN;
-            const int row = m0 + quarter * 32 + lane;
+            c.n0 = (tile % p.tiles_n) * p.BN;
+            c.row0 = m0 + c.quarter * 32;
+            const int row = c.row0 + lane;
             const bool inb = row < p.M;
-            int seq = 0;
-            if (e.row_seq != nullptr && inb) seq = __ldg(e.row_seq + row);
-            const bool valid = inb && seq >= 0;
-            const int ncols = min(p.BN, p.N - n0);  // columns of this tile that exist in the output
+            c.seq = 0;
+            if (e.row_seq != nullptr && inb) c.seq = __ldg(e.row_seq + row);
+            c.valid = inb && c.seq >= 0;
 
             mbar_wait(&tfull[acc], accphase);
             tc_fence_after();
-            const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)acc * 256u;
+            c.taddr = tmem_base + ((uint32_t)(c.quarter * 32) << 16) + (uint32_t)acc * 256u;
 
             float mean1 = 0.f, rstd1 = 1.f;
-            if (e.ln1_g != nullptr) {
+            if (e.ln1_g != nullptr) {  // LayerNorm over the whole row (N == BN): statistics of acc + bias
                 float s = 0.f, ss = 0.f;
-                for (int c = 0; c < nchunks; ++c) {
+                for (int cc = cbeg; cc < cend; ++cc) {
                     float v[16];
-                    tmem_ld16(taddr + c * 16, v);
+                    tmem_ld16(c.taddr + (uint32_t)(cc * 16), v);
                     tmem_ld_wait();
 #pragma unroll
-                    for (int i = 0; i < 16; ++i) {
-                        float x = v[i] + (e.bias ? __ldg(e.bias + n0 + c * 16 + i) : 0.f);
-                        s += x;
-                        ss += x * x;
+                    for (int i = 0; i < 16; i += 4) {
+                        float4 b = make_float4(0.f, 0.f, 0.f, 0.f);
+                        if (e.bias) b = ldg4(e.bias + c.n0 + cc * 16 + i);
+                        const float x0 = v[i] + b.x, x1 = v[i + 1] + b.y, x2 = v[i + 2] + b.z, x3 = v[i + 3] + b.w;
+                        s += (x0 + x1) + (x2 + x3);
+                        ss += (x0 * x0 + x1 * x1) + (x2 * x2 + x3 * x3);
                     }
                 }
-                mean1 = s / (float)p.BN;
-                float var = fmaxf(ss / (float)p.BN - mean1 * mean1, 0.f);
-                rstd1 = rsqrtf(var + e.ln_eps);
+                const float2 t = pair_exchange(c, make_float2(s, ss));
+                mean1 = t.x / (float)p.BN;
+                rstd1 = rsqrtf(fmaxf(t.y / (float)p.BN - mean1 * mean1, 0.f) + e.ln_eps);
             }
+            float s2 = 0.f, ss2 = 0.f;
+            if (fast_bf16)
+                epi_main<4>(c, cbeg, cend, mean1, rstd1, s2, ss2);
+            else
+                epi_main<2>(c, cbeg, cend, mean1, rstd1, s2, ss2);
 
-            // value of columns [c*16, c*16+16) of this thread's row, before the bf16-side LN2/act2
-            auto chunk_value = [&](int c, float* v) {
-                tmem_ld16(taddr + c * 16, v);
-                tmem_ld_wait();
-                const int nb = n0 + c * 16;
-#pragma unroll
-                for (int i = 0; i < 16; ++i) {
-                    const int n = nb + i;
-                    float x = v[i];
-                    if (n < p.N) {
-                        if (e.bias) x += __ldg(e.bias + n);
-                        if (e.ln1_g) x = (x - mean1) * rstd1 * __ldg(e.ln1_g + n) + __ldg(e.ln1_b + n);
-                        x = apply_act(x, e.act1, e.act1_p, e.act1_alpha, n);
-                        if (e.tbias) x += __ldg(e.tbias + (size_t)(seq < 0 ? 0 : seq) * e.tbias_ld + n);
-                    }
-                    v[i] = x;
-                }
-                if (valid) {
-                    if (e.resid) {
-                        const float* r = e.resid + (size_t)row * e.ldr + nb;
-#pragma unroll
-                        for (int i = 0; i < 16; i += 4) {
-                            if (nb + i < p.N) {
-                                float4 t = *reinterpret_cast<const float4*>(r + i);
-                                v[i] += t.x; v[i + 1] += t.y; v[i + 2] += t.z; v[i + 3] += t.w;
-                            }
-                        }
-                    }
-                    if (e.accum_f32) {
-                        const float* r = e.out_f32 + (size_t)row * e.ldf + nb;
-#pragma unroll
-                        for (int i = 0; i < 16; i += 4) {
-                            if (nb + i < p.N) {
-                                float4 t = *reinterpret_cast<const float4*>(r + i);
-                                v[i] += t.x; v[i + 1] += t.y; v[i + 2] += t.z; v[i + 3] += t.w;
-                            }
-                        }
-                    }
-#pragma unroll
-                    for (int i = 0; i < 16; ++i) v[i] *= e.out_scale;
-                } else {
-#pragma unroll
-                    for (int i = 0; i < 16; ++i) v[i] = 0.f;
-                }
-            };
-            auto store_f32 = [&](int c, const float* v) {
-                if (e.out_f32 != nullptr && inb) {
-                    float* o = e.out_f32 + (size_t)row * e.ldf + n0 + c * 16;
-#pragma unroll
-                    for (int i = 0; i < 16; i += 4)
-                        if (c * 16 + i < ncols) *reinterpret_cast<float4*>(o + i) = make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]);
-                }
-            };
-            auto store_bf16 = [&](int c, const float* v) {
-                if (e.out_bf16 != nullptr && inb) {
-                    __nv_bfloat16* o = e.out_bf16 + (size_t)row * e.ldo + n0 + c * 16;
-#pragma unroll
-                    for (int i = 0; i < 16; i += 8)
-                        if (c * 16 + i < ncols) {
-                            uint4 t;
-                            t.x = pack_bf16x2(v[i], v[i + 1]);
-                            t.y = pack_bf16x2(v[i + 2], v[i + 3]);
-                            t.z = pack_bf16x2(v[i + 4], v[i + 5]);
-                            t.w = pack_bf16x2(v[i + 6], v[i + 7]);
-                            *reinterpret_cast<uint4*>(o + i) = t;
-                            if (e.out_bf16_lo != nullptr) {
-                                float r[8];
-#pragma unroll
-                                for (int j = 0; j < 8; ++j) r[j] = v[i + j] - __bfloat162float(__float2bfloat16(v[i + j]));
-                                uint4 u;
-                                u.x = pack_bf16x2(r[0], r[1]);
-                                u.y = pack_bf16x2(r[2], r[3]);
-                                u.z = pack_bf16x2(r[4], r[5]);
-                                u.w = pack_bf16x2(r[6], r[7]);
-                                *reinterpret_cast<uint4*>(e.out_bf16_lo + (size_t)row * e.ldo + n0 + c * 16 + i) = u;
-                            }
-                        }
-                }
-            };
-
-            if (e.ln2_g != nullptr) {
-                // pass 1: fp32 value, statistics, fp32 store; pass 2: recompute + LN2 -> bf16
-                float s = 0.f, ss = 0.f;
-                for (int c = 0; c < nchunks; ++c) {
-                    float v[16];
-                    chunk_value(c, v);
-#pragma unroll
-                    for (int i = 0; i < 16; ++i) {
-                        s += v[i];
-                        ss += v[i] * v[i];
-                    }
-                    store_f32(c, v);
-                }
-                const float mean2 = s / (float)p.BN;
-                const float rstd2 = rsqrtf(fmaxf(ss / (float)p.BN - mean2 * mean2, 0.f) + e.ln_eps);
-                for (int c = 0; c < nchunks; ++c) {
-                    float v[16];
-                    if (e.out_f32 != nullptr) {
-                        // re-read what this thread stored in pass 1 (also makes resid == out_f32 in-place safe)
-                        if (inb) {
-                            const float* o = e.out_f32 + (size_t)row * e.ldf + n0 + c * 16;
-#pragma unroll
-                            for (int i = 0; i < 16; i += 4) {
-                                float4 t = *reinterpret_cast<const float4*>(o + i);
-                                v[i] = t.x; v[i + 1] = t.y; v[i + 2] = t.z; v[i + 3] = t.w;
-                            }
-                        }
-                    } else {
-                        chunk_value(c, v);
-                    }
-#pragma unroll
-                    for (int i = 0; i < 16; ++i) {
-                        const int n = n0 + c * 16 + i;
-                        v[i] = valid ? (v[i] - mean2) * rstd2 * __ldg(e.ln2_g + n) + __ldg(e.ln2_b + n) : 0.f;
-                    }
-                    store_bf16(c, v);
-                }
-            } else {
-                for (int c = 0; c < nchunks; ++c) {
-                    float v[16];
-                    chunk_value(c, v);
-                    store_f32(c, v);
-                    if (e.act2 != ACT_NONE) {
-#pragma unroll
-                        for (int i = 0; i < 16; ++i) {
-                            const int n = n0 + c * 16 + i;
-                            if (n < p.N) v[i] = valid ? apply_act(v[i], e.act2, e.act2_p, e.act2_alpha, n) : 0.f;
-                        }
-                    }
-                    store_bf16(c, v);
-                }
-            }
-
+            // all TMEM reads of this tile are done: hand the accumulator back before the (TMEM-free) LN2 pass
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(&tempty[acc]);
             acc ^= 1;
             if (acc == 0) accphase ^= 1;
+
+            if (e.ln2_g != nullptr) {  // second LayerNorm on the fp32 value just stored -> bf16 operand of the next GEMM
+                const float2 t = pair_exchange(c, make_float2(s2, ss2));
+                const float mean2 = t.x / (float)p.BN;
+                const float rstd2 = rsqrtf(fmaxf(t.y / (float)p.BN - mean2 * mean2, 0.f) + e.ln_eps);
+                for (int cc = cbeg; cc < cend; cc += 2) {
+                    const int nb = c.n0 + cc * 16;
+                    const int nlim = min(p.N, nb + min(2, cend - cc) * 16);
+                    float v[32];
+                    load_rows_f32(c, e.out_f32, e.ldf, nb, nlim, v);
+#pragma unroll
+                    for (int i = 0; i < 32; i += 4) {
+                        const float4 g = ldg4(e.ln2_g + nb + i), b = ldg4(e.ln2_b + nb + i);
+                        v[i] = c.valid ? (v[i] - mean2) * rstd2 * g.x + b.x : 0.f;
+                        v[i + 1] = c.valid ? (v[i + 1] - mean2) * rstd2 * g.y + b.y : 0.f;
+                        v[i + 2] = c.valid ? (v[i + 2] - mean2) * rstd2 * g.z + b.z : 0.f;
+                        v[i + 3] = c.valid ? (v[i + 3] - mean2) * rstd2 * g.w + b.w : 0.f;
+                    }
+                    store_rows_bf16<32>(c, e.out_bf16, e.ldo, nb, nlim, v);
+                }
+            }
         }
     }
 
@@ -327,6 +500,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
     __syncthreads();
     if (warp == 1) tmem_dealloc(tmem_base, kTmemCols);
 }
+
+}  // namespace
 
 // ---------------------------------------------------------------------------- host side
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
@@ -364,8 +539,6 @@ bool encode_2d(CUtensorMap* m, const void* ptr, uint64_t cols, uint64_t rows, ui
     }
     return true;
 }
-
-}  // namespace
 
 cudaError_t gemm_tc_launch(const GemmProblem& g, int num_sms, cudaStream_t stream) {
     if (g.M <= 0 || g.N <= 0 || g.BN < 16 || g.BN > 256 || (g.BN % 16) != 0 || g.num_segs < 1 ||
