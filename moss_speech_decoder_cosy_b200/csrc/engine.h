@@ -136,12 +136,13 @@ class Engine {
     DeviceBuffer ws_hift_, ws_hift_layout_;
     bool has_hift_ = false;
     std::map<std::string, std::pair<const void*, size_t>> taps_;
-    struct ProfRec { cudaEvent_t a, b; int cls; double flops; };
+    struct ProfRec { cudaEvent_t a, b; int cls; double flops; uint64_t key; };
+    std::map<uint64_t, std::pair<double, long>> prof_by_key_;
     bool profile_ = false;
     std::vector<ProfRec> prof_;
     std::vector<cudaEvent_t> prof_pool_;
     cudaEvent_t prof_event();
-    void prof_begin(int cls, double flops, cudaStream_t st);
+    void prof_begin(int cls, double flops, cudaStream_t st, uint64_t key = 0);
     void prof_end(cudaStream_t st);
     int64_t hift_group_frames_ = 8192;  // frames per HiFT group (bounds the stage-2 working set)
 };

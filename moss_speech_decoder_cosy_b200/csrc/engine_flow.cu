@@ -4,6 +4,7 @@
 #include <math.h>
 #include <stdio.h>
 #include <string.h>
+#include <stdlib.h>
 
 namespace mossdec {
 
@@ -83,8 +84,8 @@ cudaEvent_t Engine::prof_event() {
     cudaEventCreate(&e);
     return e;
 }
-void Engine::prof_begin(int cls, double flops, cudaStream_t st) {
-    ProfRec r{prof_event(), prof_event(), cls, flops};
+void Engine::prof_begin(int cls, double flops, cudaStream_t st, uint64_t key) {
+    ProfRec r{prof_event(), prof_event(), cls, flops, key};
     cudaEventRecord(r.a, st);
     prof_.push_back(r);
 }
@@ -99,10 +100,24 @@ int Engine::profile_read(double* out) {
         out[r.cls * 3 + 0] += ms;
         out[r.cls * 3 + 1] += 1.0;
         out[r.cls * 3 + 2] += r.flops;
+        auto& acc = prof_by_key_[r.key];
+        acc.first += ms;
+        acc.second += 1;
         prof_pool_.push_back(r.a);
         prof_pool_.push_back(r.b);
     }
     prof_.clear();
+    if (getenv("MOSSDEC_PROFILE_DUMP")) {  // per GEMM shape/epilogue breakdown (developer aid)
+        for (auto& kv : prof_by_key_) {
+            const uint64_t k = kv.first;
+            fprintf(stderr, "[mossdec prof] M=%-8llu N=%-5llu K=%-5llu act1=%llu ln1=%llu ln2=%llu resid=%llu f32=%llu bf16=%llu  n=%-6ld ms=%.3f\n",
+                    (unsigned long long)(k >> 40), (unsigned long long)(k & 0xfff), (unsigned long long)((k >> 12) & 0xfff) * 64,
+                    (unsigned long long)((k >> 24) & 7), (unsigned long long)((k >> 27) & 1), (unsigned long long)((k >> 28) & 1),
+                    (unsigned long long)((k >> 29) & 1), (unsigned long long)((k >> 30) & 1), (unsigned long long)((k >> 31) & 1),
+                    kv.second.second, kv.second.first);
+        }
+    }
+    prof_by_key_.clear();
     return 0;
 }
 
@@ -110,7 +125,11 @@ int Engine::gemm(const GemmProblem& p, cudaStream_t st) {
     if (profile_) {
         int kb = 0;
         for (int s = 0; s < p.num_segs; ++s) kb += p.segs[s].nkb;
-        prof_begin(0, 2.0 * p.M * p.N * kb * kGemmBK, st);
+        const uint64_t key = (uint64_t)(p.N & 0xfff) | ((uint64_t)(kb & 0xfff) << 12) | ((uint64_t)(p.epi.act1 & 7) << 24) |
+                             ((uint64_t)(p.epi.ln1_g != nullptr) << 27) | ((uint64_t)(p.epi.ln2_g != nullptr) << 28) |
+                             ((uint64_t)(p.epi.resid != nullptr) << 29) | ((uint64_t)(p.epi.out_f32 != nullptr) << 30) |
+                             ((uint64_t)(p.epi.out_bf16 != nullptr) << 31) | ((uint64_t)p.M << 40);
+        prof_begin(0, 2.0 * p.M * p.N * kb * kGemmBK, st, key);
     }
     cudaError_t e = gemm_tc_launch(p, num_sms_, st);
     if (profile_) prof_end(st);

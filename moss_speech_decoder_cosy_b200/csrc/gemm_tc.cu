@@ -40,6 +40,17 @@ __device__ __forceinline__ float fast_mish(float x) {
     const float n = u * (u + 2.f);
     return x > 20.f ? x : x * __fdividef(n, n + 2.f);
 }
+__device__ __forceinline__ float fast_gelu_erf(float x) {
+    // exact-erf GELU, erf by Abramowitz-Stegun 7.1.26 (|error| < 1.5e-7, far below the bf16 output rounding)
+    const float z = fabsf(x) * 0.70710678118654752440f;
+    const float t = __fdividef(1.f, fmaf(0.3275911f, z, 1.f));
+    float poly = fmaf(1.061405429f, t, -1.453152027f);
+    poly = fmaf(poly, t, 1.421413741f);
+    poly = fmaf(poly, t, -0.284496736f);
+    poly = fmaf(poly, t, 0.254829592f);
+    const float erf_abs = fmaf(-poly * t, __expf(-z * z), 1.f);
+    return 0.5f * x * (1.f + copysignf(erf_abs, x));
+}
 __device__ __forceinline__ float fast_sin(float x) {
     // two-term Cody-Waite reduction to [-pi, pi], then the SFU sine (abs error ~1e-6 for |x| < 1e4)
     const float k = rintf(x * 0.15915494309189535f);
@@ -58,7 +69,7 @@ __device__ __forceinline__ void apply_act_vec(float* v, int act, float p, const 
             break;
         case ACT_GELU:
 #pragma unroll
-            for (int i = 0; i < NV; ++i) v[i] = gelu_erf_f(v[i]);
+            for (int i = 0; i < NV; ++i) v[i] = fast_gelu_erf(v[i]);
             break;
         case ACT_ELU:
 #pragma unroll

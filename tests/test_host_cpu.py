@@ -1,0 +1,154 @@
+"""CPU tests of the host logic: C-ABI surface, weight packer layouts, streaming chunk schedule, sharding (incl. a
+world_size-2 gloo run)."""
+import ctypes
+import os
+import re
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+from conftest import ROOT
+from moss_speech_decoder_cosy_b200 import lib, sharding, streaming, synth, weights
+
+
+@pytest.fixture(scope="module")
+def shared_lib():
+    if not os.path.exists(lib.LIB_PATH):
+        import __graft_entry__
+        __graft_entry__.build()
+    return ctypes.CDLL(lib.LIB_PATH)
+
+
+def test_cabi_exports_every_declared_symbol(shared_lib):
+    header = open(os.path.join(ROOT, "include", "mossdec.h")).read()
+    declared = sorted(set(re.findall(r"\b(mossdec_[a-z0-9_]+)\s*\(", header)))
+    assert len(declared) >= 16
+    for name in declared:
+        assert hasattr(shared_lib, name), name
+    assert sorted(lib.EXPORTED_SYMBOLS) == declared
+
+
+def test_no_cpu_fallback():
+    if torch.cuda.is_available():
+        pytest.skip("CUDA present")
+    with pytest.raises(RuntimeError):
+        lib.Engine()
+    from moss_speech_decoder_cosy_b200.flow_inference import AudioDecoder
+    with pytest.raises(RuntimeError):
+        AudioDecoder()
+
+
+def test_conv_taps_layout_is_a_shifted_gemm():
+    g = torch.Generator().manual_seed(0)
+    w, x = torch.randn(8, 80, 3, generator=g), torch.randn(1, 80, 20, generator=g)
+    ref = F.conv1d(F.pad(x, (2, 0)), w)[0].t()                       # causal conv, [T, Cout]
+    wt = weights.conv_weight_taps(w)                                  # [Cout, 3 * 128]
+    rows = F.pad(x[0].t(), (0, 48, 2, 0))                             # channels-last, 128 wide, 2 zero guard rows
+    a = torch.cat([rows[k:k + 20] for k in range(3)], 1)              # taps -2, -1, 0 as K-slabs
+    torch.testing.assert_close(a @ wt.t(), ref, rtol=1e-4, atol=1e-4)
+
+
+@pytest.mark.parametrize("stride,k", weights.HIFT_UPS)
+def test_convtranspose_polyphase(stride, k):
+    g = torch.Generator().manual_seed(stride)
+    cin, cout, T = 16, 8, 12
+    w, x = torch.randn(cin, cout, k, generator=g), torch.randn(1, cin, T, generator=g)
+    ref = F.conv_transpose1d(x, w, stride=stride, padding=(k - stride) // 2)[0].t()      # [stride * T, cout]
+    wp = weights.convtranspose_polyphase(w, stride, (k - stride) // 2)                   # [stride * cout, 3 * cin]
+    rows = F.pad(x[0].t(), (0, 0, 1, 1))
+    a = torch.cat([rows[d:d + T] for d in range(3)], 1)                                  # input offsets -1, 0, +1
+    out = (a @ wp.t()).reshape(T * stride, cout)
+    assert ref.shape[0] == stride * T
+    torch.testing.assert_close(out, ref, rtol=1e-4, atol=1e-4)
+
+
+@pytest.mark.parametrize("k,stride,pad", [(30, 15, 7), (6, 3, 1), (1, 1, 0)])
+def test_source_down_window_weight(k, stride, pad):
+    g = torch.Generator().manual_seed(k)
+    w, x = torch.randn(4, 18, k, generator=g), torch.randn(1, 18, 121, generator=g)
+    ref = F.conv1d(x, w, stride=stride, padding=pad)[0].t()
+    wp = weights.source_down_weight(w)
+    rows = F.pad(x[0].t(), (0, weights.STFT_LD - 18, pad, pad + 64)).reshape(-1)        # 24-wide rows, flattened
+    n = ref.shape[0]
+    a = torch.stack([rows[q * stride * 24: q * stride * 24 + wp.shape[1]] for q in range(n)])
+    torch.testing.assert_close(a @ wp.t(), ref, rtol=1e-4, atol=1e-4)
+
+
+def test_weight_norm_fold_and_split_bf16():
+    conv = torch.nn.utils.parametrizations.weight_norm(torch.nn.Conv1d(6, 5, 3))
+    sd = {"c." + k: v for k, v in conv.state_dict().items()}
+    torch.testing.assert_close(weights.fold_weight_norm(sd, "c"), conv.weight.detach())
+    w = torch.randn(7, 64)
+    s = weights.split_bf16_weight(w).float()
+    assert (s[:, :64] + s[:, 64:128] - w).abs().max() < 2e-5 * w.abs().max()
+    assert torch.equal(s[:, :64], s[:, 128:])
+
+
+def test_pack_shapes_and_schema():
+    t = weights.pack_estimator(synth.synth_flow_state_dict(0))
+    assert t["est.res0.c1.w"].shape == (256, 3 * 320) and t["est.res13.c1.w"].shape == (256, 3 * 512)
+    assert t["est.tf0.0.qkv.w"].shape == (1536, 256) and t["est.tbias.w"].shape == (14 * 256, 1024)
+    h = weights.pack_hift(synth.synth_hift_state_dict(0))
+    assert h["hift.up0.w"].shape == (2048, 1536) and h["hift.sd0.w"].shape == (256, 768)
+    assert h["hift.f0.c0.w"].shape == (512, 3 * 384) and h["hift.post.w"].shape == (18, 448)
+
+
+def test_chunk_plan_matches_reference_schedule():
+    # SURVEY 3.2 probe of the reference: 60 tokens, P = 38, block 5 -> windows of 10, 15, ..., 40, 40, ... tokens,
+    # every call emits 9 600 samples, 12 calls in total
+    plan = streaming.chunk_plan(60, 38, 5, 40)
+    assert len(plan) == 12 and [p[3] for p in plan] == [False] * 11 + [True]
+    sizes = [e - s for s, e, _, _ in plan]
+    assert sizes[:7] == [10, 15, 20, 25, 30, 35, 40] and set(sizes[7:]) == {40}
+    new = [(e - s) - (0 if fin else 3) - off for (s, e, off, fin) in plan]
+    assert new == [7] + [5] * 10 + [3]
+    # emitted samples: the first call holds back 3840, the last one releases them -> 9 600 per call
+    emitted = [n * 1920 - (3840 if i == 0 else 0) + (3840 if i == len(new) - 1 else 0) for i, n in enumerate(new)]
+    assert emitted == [9600] * 12
+    assert sum(((e - s) - (0 if f else 3) - o) for s, e, o, f in plan) == 60
+    # no window: every call re-runs the prefix (flow_inference.py:199-201)
+    plan = streaming.chunk_plan(23, 0, 8, None)
+    assert [p[:3] for p in plan] == [(0, 11, 0), (0, 19, 8), (0, 23, 16)]
+
+
+def test_sharding_partitions():
+    lens = list(np.random.RandomState(0).randint(25, 376, size=512))
+    costs = [sharding.utterance_cost(n, 37) for n in lens]
+    for world in (1, 2, 4, 8):
+        shares = sharding.balanced_partition(costs, world)
+        assert sorted(i for s in shares for i in s) == list(range(512))
+        load = [sum(costs[i] for i in s) for s in shares]
+        assert max(load) / (sum(load) / world) < 1.02
+    b = sharding.length_buckets(shares[0], lens, max_frames=40000)
+    assert sorted(i for g in b for i in g) == sorted(shares[0])
+    assert all(sum(4 * lens[i] for i in g) <= 40000 or len(g) == 1 for g in b)
+    assert sharding.stride_partition(10, 1, 4) == [1, 5, 9]
+
+
+def test_sharded_decode_world2_gloo(tmp_path):
+    """Two gloo ranks shard one utterance list with no data-path collective; the optional gather returns all shares."""
+    script = tmp_path / "w.py"
+    script.write_text(
+        "import os, sys, torch, torch.distributed as dist\n"
+        f"sys.path.insert(0, {ROOT!r})\n"
+        "from moss_speech_decoder_cosy_b200 import sharding\n"
+        "dist.init_process_group('gloo')\n"
+        "r, w = dist.get_rank(), dist.get_world_size()\n"
+        "lens = [30, 200, 75, 120, 41, 333, 90]\n"
+        "mine = sharding.balanced_partition([sharding.utterance_cost(n) for n in lens], w)[r]\n"
+        "done = [(i, lens[i] * 1920) for i in mine]          # stand-in for decoded waveform lengths\n"
+        "out = [None] * w\n"
+        "dist.all_gather_object(out, done)\n"
+        "flat = sorted(x for s in out for x in s)\n"
+        "assert [i for i, _ in flat] == list(range(len(lens))), flat\n"
+        "t = torch.tensor([float(sum(n for _, n in done))]); dist.all_reduce(t, op=dist.ReduceOp.MAX)\n"
+        "if r == 0: print('OK', t.item())\n"
+        "dist.destroy_process_group()\n")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
+           "--master-port", "29533", str(script)]
+    res = subprocess.run(cmd, capture_output=True, text=True, timeout=240)
+    assert res.returncode == 0 and "OK" in res.stdout, res.stdout + res.stderr
