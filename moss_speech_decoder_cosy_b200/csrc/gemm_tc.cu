@@ -14,14 +14,16 @@ namespace mossdec {
 
 namespace {
 
-// warp 0 = TMA producer, warp 1 = MMA issuer (+ TMEM alloc), warps 2..9 = epilogue.
-// A warp may only touch TMEM lanes [32 * (warp % 4), +32), so the 8 epilogue warps form 4 pairs: both warps of a
-// pair own the same 32 rows of the tile and split its columns in two halves.
-constexpr int kEpiWarps = 8;
+// warp 0 = TMA producer, warp 1 = MMA issuer (+ TMEM alloc), warps 2..17 = epilogue.
+// A warp may only touch TMEM lanes [32 * (warp % 4), +32), so the 16 epilogue warps form 4 groups of 4: the warps of
+// a group own the same 32 rows of the tile and split its columns in four parts.  (The epilogue is ALU/latency bound
+// at one row per thread; 4 resident warps per scheduler hide that latency, 2 did not -- profiles/r01_*.)
+constexpr int kEpiWarps = 16;
+constexpr int kEpiParts = kEpiWarps / 4;
 constexpr int kThreads = 64 + 32 * kEpiWarps;
 constexpr int kABytes = kGemmBM * kGemmBK * 2;  // 16 KB
 constexpr int kBBytesMax = 256 * kGemmBK * 2;   // 32 KB
-constexpr int kStageBytes = 4096;               // per-epilogue-warp staging tile: 32 rows x 128 B
+constexpr int kStageBytes = 2048;               // per-epilogue-warp staging tile: 32 rows x 64 B
 constexpr int kSmemBytes = kGemmStages * (kABytes + kBBytesMax) + kEpiWarps * kStageBytes + 1024 /*align*/ + 256 /*barriers*/;
 constexpr uint32_t kTmemCols = 512;
 
@@ -128,60 +130,76 @@ __device__ __forceinline__ void stage_coalesced(int k, int lane, int& r, int& u)
 struct EpiCtx {
     const KParams* p;
     uint8_t* stg;       // this warp's staging tile
-    uint8_t* stg_peer;  // staging tile of the warp that owns the other column half of the same rows
+    uint8_t* stg_all;   // staging tiles of all epilogue warps
+    int ew;             // epilogue warp index
     uint32_t taddr;     // TMEM address of (lane quarter, accumulator)
     int lane, quarter, row0, n0, seq;
     bool valid;         // this thread's row exists and belongs to a sequence
 };
 
-__device__ __forceinline__ void pair_sync(int quarter) {
-    asm volatile("bar.sync %0, 64;" ::"r"(quarter + 1) : "memory");
+__device__ __forceinline__ void group_sync(int quarter) {
+    asm volatile("bar.sync %0, %1;" ::"r"(quarter + 1), "n"(32 * kEpiParts) : "memory");
 }
-// exchange one float2 per row with the peer warp (row statistics over the full tile width)
-__device__ __forceinline__ float2 pair_exchange(const EpiCtx& c, float2 mine) {
+// sum one float2 per row over the warps of a group (row statistics over the full tile width)
+__device__ __forceinline__ float2 group_exchange(const EpiCtx& c, float2 mine) {
     reinterpret_cast<float2*>(c.stg)[c.lane] = mine;
-    pair_sync(c.quarter);
-    const float2 other = reinterpret_cast<const float2*>(c.stg_peer)[c.lane];
-    pair_sync(c.quarter);
-    return make_float2(mine.x + other.x, mine.y + other.y);
+    group_sync(c.quarter);
+    float2 t = make_float2(0.f, 0.f);
+#pragma unroll
+    for (int part = 0; part < kEpiParts; ++part) {
+        const float2 o = reinterpret_cast<const float2*>(c.stg_all + ((part << 2) | (c.ew & 3)) * kStageBytes)[c.lane];
+        t.x += o.x;
+        t.y += o.y;
+    }
+    group_sync(c.quarter);
+    return t;
 }
 
 // coalesced global -> registers (thread == row) through the staging tile; fp32, 32 columns starting at column nb
+// (two rounds of 16 columns = 64-byte rows)
 __device__ __forceinline__ void load_rows_f32(const EpiCtx& c, const float* base, int ld, int nb, int nlim, float* out32) {
     const KParams& p = *c.p;
 #pragma unroll
-    for (int k = 0; k < 8; ++k) {
-        int r, u;
-        stage_coalesced<128>(k, c.lane, r, u);
-        const int grow = c.row0 + r, col = nb + u * 4;
-        float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (grow < p.M && col < nlim) t = *reinterpret_cast<const float4*>(base + (size_t)grow * ld + col);
-        *reinterpret_cast<float4*>(c.stg + k * 512 + c.lane * 16) = t;
-    }
-    __syncwarp();
+    for (int h = 0; h < 2; ++h) {
 #pragma unroll
-    for (int u = 0; u < 8; ++u) {
-        const float4 t = *reinterpret_cast<const float4*>(c.stg + stage_off<128>(c.lane, u));
-        out32[u * 4] = t.x; out32[u * 4 + 1] = t.y; out32[u * 4 + 2] = t.z; out32[u * 4 + 3] = t.w;
+        for (int k = 0; k < 4; ++k) {
+            int r, u;
+            stage_coalesced<64>(k, c.lane, r, u);
+            const int grow = c.row0 + r, col = nb + h * 16 + u * 4;
+            float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (grow < p.M && col < nlim) t = *reinterpret_cast<const float4*>(base + (size_t)grow * ld + col);
+            *reinterpret_cast<float4*>(c.stg + k * 512 + c.lane * 16) = t;
+        }
+        __syncwarp();
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const float4 t = *reinterpret_cast<const float4*>(c.stg + stage_off<64>(c.lane, u));
+            float* o = out32 + h * 16 + u * 4;
+            o[0] = t.x; o[1] = t.y; o[2] = t.z; o[3] = t.w;
+        }
+        __syncwarp();
     }
-    __syncwarp();
 }
 __device__ __forceinline__ void store_rows_f32(const EpiCtx& c, float* base, int ld, int nb, int nlim, const float* v32) {
     const KParams& p = *c.p;
 #pragma unroll
-    for (int u = 0; u < 8; ++u)
-        *reinterpret_cast<float4*>(c.stg + stage_off<128>(c.lane, u)) =
-            make_float4(v32[u * 4], v32[u * 4 + 1], v32[u * 4 + 2], v32[u * 4 + 3]);
-    __syncwarp();
+    for (int h = 0; h < 2; ++h) {
 #pragma unroll
-    for (int k = 0; k < 8; ++k) {
-        int r, u;
-        stage_coalesced<128>(k, c.lane, r, u);
-        const int grow = c.row0 + r, col = nb + u * 4;
-        const float4 t = *reinterpret_cast<const float4*>(c.stg + k * 512 + c.lane * 16);
-        if (grow < p.M && col < nlim) *reinterpret_cast<float4*>(base + (size_t)grow * ld + col) = t;
+        for (int u = 0; u < 4; ++u) {
+            const float* v = v32 + h * 16 + u * 4;
+            *reinterpret_cast<float4*>(c.stg + stage_off<64>(c.lane, u)) = make_float4(v[0], v[1], v[2], v[3]);
+        }
+        __syncwarp();
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            int r, u;
+            stage_coalesced<64>(k, c.lane, r, u);
+            const int grow = c.row0 + r, col = nb + h * 16 + u * 4;
+            const float4 t = *reinterpret_cast<const float4*>(c.stg + k * 512 + c.lane * 16);
+            if (grow < p.M && col < nlim) *reinterpret_cast<float4*>(base + (size_t)grow * ld + col) = t;
+        }
+        __syncwarp();
     }
-    __syncwarp();
 }
 // registers (thread == row, NV values) -> bf16 global, coalesced; RB = NV * 2 bytes per row
 template <int NV>
@@ -421,20 +439,21 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
             }
         }
     } else {
-        // ------------------------------------------------------------ epilogue (thread == row, 2 warps per row group)
+        // ------------------------------------------------------------ epilogue (thread == row, 4 warps per row group)
         const GemmEpilogue& e = p.epi;
         const int ew = warp - 2;
-        const int half = ew >> 2;
+        const int part = ew >> 2;
         EpiCtx c;
         c.p = &p;
         c.lane = lane;
+        c.ew = ew;
         c.quarter = warp & 3;  // TMEM lane quarter this warp may access
         c.stg = sStage + ew * kStageBytes;
-        c.stg_peer = sStage + (ew ^ 4) * kStageBytes;
+        c.stg_all = sStage;
         const int nchunks = p.BN / 16;
-        const int csplit = (nchunks + 1) / 2;
-        const int cbeg = half ? csplit : 0, cend = half ? nchunks : csplit;
-        const bool fast_bf16 = !e.resid && !e.accum_f32 && !e.out_f32 && !e.ln2_g;
+        const int cbase = nchunks / kEpiParts, crem = nchunks % kEpiParts;
+        const int cbeg = part * cbase + min(part, crem);
+        const int cend = cbeg + cbase + (part < crem ? 1 : 0);
         int acc = 0;
         uint32_t accphase = 0;
         for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
@@ -467,15 +486,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
                         ss += (x0 * x0 + x1 * x1) + (x2 * x2 + x3 * x3);
                     }
                 }
-                const float2 t = pair_exchange(c, make_float2(s, ss));
+                const float2 t = group_exchange(c, make_float2(s, ss));
                 mean1 = t.x / (float)p.BN;
                 rstd1 = rsqrtf(fmaxf(t.y / (float)p.BN - mean1 * mean1, 0.f) + e.ln_eps);
             }
             float s2 = 0.f, ss2 = 0.f;
-            if (fast_bf16)
-                epi_main<4>(c, cbeg, cend, mean1, rstd1, s2, ss2);
-            else
-                epi_main<2>(c, cbeg, cend, mean1, rstd1, s2, ss2);
+            epi_main<2>(c, cbeg, cend, mean1, rstd1, s2, ss2);
 
             // all TMEM reads of this tile are done: hand the accumulator back before the (TMEM-free) LN2 pass
             tc_fence_before();
@@ -485,7 +501,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
             if (acc == 0) accphase ^= 1;
 
             if (e.ln2_g != nullptr) {  // second LayerNorm on the fp32 value just stored -> bf16 operand of the next GEMM
-                const float2 t = pair_exchange(c, make_float2(s2, ss2));
+                const float2 t = group_exchange(c, make_float2(s2, ss2));
                 const float mean2 = t.x / (float)p.BN;
                 const float rstd2 = rsqrtf(fmaxf(t.y / (float)p.BN - mean2 * mean2, 0.f) + e.ln_eps);
                 for (int cc = cbeg; cc < cend; cc += 2) {
