@@ -116,6 +116,7 @@ class Engine {
     EngineConfig cfg_;
     int num_sms_ = 148;
     bool finalized_ = false;
+    bool attn_v1_ = false;
     std::unordered_map<std::string, DevTensor> tensors_;
     std::string err_;
     std::string missing_;

@@ -36,6 +36,8 @@ Engine::Engine(const EngineConfig& cfg) : cfg_(cfg) {
     int dev = 0;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&num_sms_, cudaDevAttrMultiProcessorCount, dev);
+    const char* av = getenv("MOSSDEC_ATTN");  // "v1" selects the mma.sync kernel (developer A/B switch)
+    attn_v1_ = av != nullptr && av[0] == 'v' && av[1] == '1';
 }
 
 Engine::~Engine() {
@@ -357,7 +359,13 @@ int Engine::estimator_forward(int M, int nseq, int max_len, const float* tbias, 
                 if (gemm(p, st)) return -1;
             }
             if (profile_) prof_begin(1, 0.0, st);
-            launch_attention(qkv_, att_, layout_.seq_start, layout_.seq_len, nseq, max_len, cfg_.heads, chunk, st);
+            if (attn_v1_) {
+                launch_attention(qkv_, att_, layout_.seq_start, layout_.seq_len, nseq, max_len, cfg_.heads, chunk, st);
+            } else {
+                cudaError_t ae = launch_attention_tc(qkv_, M, att_, layout_.seq_start, layout_.seq_len, nseq, max_len,
+                                                     cfg_.heads, chunk, st);
+                if (ae != cudaSuccess) return fail(std::string("launch_attention_tc: ") + cudaGetErrorString(ae));
+            }
             if (profile_) prof_end(st);
             ++launches_;
             {   // out projection + residual, emits norm3
