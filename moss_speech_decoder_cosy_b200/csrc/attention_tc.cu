@@ -48,7 +48,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tm, __nv_bfloat16* __res
     const int start = seq_start[s];
 
     extern __shared__ uint8_t smem_raw[];
-    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);  // stays in the shared address space (STS / LDS)
     uint8_t* sQ = smem;
     uint8_t* sK = sQ + kQBytes;           // [2][8 KB]
     uint8_t* sV = sK + 2 * kKVBytes;      // [2][8 KB]

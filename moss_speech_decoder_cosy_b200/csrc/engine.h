@@ -102,6 +102,7 @@ class Engine {
         return t ? reinterpret_cast<const T*>(t->ptr) : nullptr;
     }
     int gemm(const GemmProblem& p, cudaStream_t st);
+    int ffn(const FfnProblem& p, cudaStream_t st);
 
     // flow internals
     struct FlowPlan;

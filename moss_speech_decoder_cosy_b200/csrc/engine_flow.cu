@@ -140,6 +140,16 @@ int Engine::gemm(const GemmProblem& p, cudaStream_t st) {
     return 0;
 }
 
+int Engine::ffn(const FfnProblem& f, cudaStream_t st) {
+    if (cfg_.channels != 256) return fail("fused FFN is built for channels == 256");
+    if (profile_) prof_begin(0, 2.0 * f.M * 256.0 * 1024.0 * 2.0, st, ((uint64_t)f.M << 40) | 0xfffu);
+    cudaError_t e = ffn_tc_launch(f, num_sms_, st);
+    if (profile_) prof_end(st);
+    ++launches_;
+    if (e != cudaSuccess) return fail(std::string("ffn_tc_launch: ") + cudaGetErrorString(e));
+    return 0;
+}
+
 static std::string S(const char* fmt, int a = 0, int b = 0) {
     char buf[128];
     snprintf(buf, sizeof buf, fmt, a, b);
@@ -381,37 +391,27 @@ int Engine::estimator_forward(int M, int nseq, int max_len, const float* tbias, 
                 p.epi.out_bf16 = xn_; p.epi.ldo = C;
                 if (gemm(p, st)) return -1;
             }
-            {   // FF1 + erf-GELU
-                GemmProblem p;
-                dense(p, xn_, C);
-                p.w = W<__nv_bfloat16>(t + "ff1.w");
-                p.N = 4 * C; p.BN = 256;
-                p.epi.bias = W<float>(t + "ff1.b");
-                p.epi.act1 = ACT_GELU;
-                p.epi.out_bf16 = ff_; p.epi.ldo = 4 * C;
-                if (gemm(p, st)) return -1;
-            }
-            {   // FF2 + residual; emits either the next block's norm1 or the masked bf16 copy for the next conv
-                GemmProblem p;
-                dense(p, ff_, 4 * C);
-                p.w = W<__nv_bfloat16>(t + "ff2.w");
-                p.N = C; p.BN = C;
-                p.epi.bias = W<float>(t + "ff2.b");
-                p.epi.row_seq = row_seq;
-                p.epi.resid = hres_; p.epi.ldr = C;
-                p.epi.out_f32 = hres_; p.epi.ldf = C;
+            {   // FF1 + erf-GELU + FF2 + residual in one kernel (hidden stays on chip); emits either the next block's
+                // norm1 or the masked bf16 copy for the next conv
+                FfnProblem f;
+                f.x = xn_; f.M = M;
+                f.w1 = W<__nv_bfloat16>(t + "ff1.w"); f.b1 = W<float>(t + "ff1.b");
+                f.w2 = W<__nv_bfloat16>(t + "ff2.w"); f.b2 = W<float>(t + "ff2.b");
+                f.hres = hres_;
+                f.row_seq = row_seq;
                 if (j + 1 < cfg_.n_blocks) {
-                    p.epi.ln2_g = W<float>(S("est.tf%d.%d.n1.g", g, j + 1));
-                    p.epi.ln2_b = W<float>(S("est.tf%d.%d.n1.b", g, j + 1));
-                    p.epi.out_bf16 = xn_; p.epi.ldo = C;
+                    f.ln_g = W<float>(S("est.tf%d.%d.n1.g", g, j + 1));
+                    f.ln_b = W<float>(S("est.tf%d.%d.n1.b", g, j + 1));
+                    f.out_bf16 = xn_; f.ldo = C;
                 } else if (g == 0) {           // down block: skip connection -> right half of the concat buffer
-                    p.epi.out_bf16 = cat_ + C; p.epi.ldo = 2 * C;
+                    f.out_bf16 = cat_ + C; f.ldo = 2 * C;
                 } else if (g == ngroups - 2) { // last mid block -> left half of the concat buffer
-                    p.epi.out_bf16 = cat_; p.epi.ldo = 2 * C;
+                    f.out_bf16 = cat_; f.ldo = 2 * C;
                 } else {                        // mid block -> next resnet input; up block -> upsample conv input
-                    p.epi.out_bf16 = xn_; p.epi.ldo = C;
+                    f.out_bf16 = xn_; f.ldo = C;
                 }
-                if (gemm(p, st)) return -1;
+                f.store_f32 = j + 1 < cfg_.n_blocks;  // the resnet that follows reads only the bf16 copy
+                if (ffn(f, st)) return -1;
             }
         }
         if (g == 0) {  // "downsample" slot = plain causal conv when channels == [256]   (decoder.py:348-350)

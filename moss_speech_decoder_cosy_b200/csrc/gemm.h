@@ -83,6 +83,25 @@ struct GemmProblem {
     GemmEpilogue epi;
 };
 
+// Fused transformer feed-forward (ffn_tc.cu): hres += W2 gelu(W1 x + b1) + b2 ; out = LN(hres) or bf16(hres).
+struct FfnProblem {
+    const __nv_bfloat16* x = nullptr;   // [M, 256] bf16 (normalised input)
+    int32_t M = 0;                      // multiple of 128
+    const __nv_bfloat16* w1 = nullptr;  // [1024, 256] K-major
+    const float* b1 = nullptr;
+    const __nv_bfloat16* w2 = nullptr;  // [256, 1024] K-major
+    const float* b2 = nullptr;
+    float* hres = nullptr;              // [M, 256] fp32 residual stream, updated in place
+    const int32_t* row_seq = nullptr;   // rows with id < 0 are forced to zero
+    const float* ln_g = nullptr;        // LayerNorm of the next block (nullptr: out = bf16(hres))
+    const float* ln_b = nullptr;
+    __nv_bfloat16* out_bf16 = nullptr;  // [M, ldo]
+    int32_t ldo = 0;
+    int32_t store_f32 = 1;              // 0: the fp32 stream is not needed afterwards
+    float ln_eps = 1e-5f;
+};
+cudaError_t ffn_tc_launch(const FfnProblem& p, int num_sms, cudaStream_t stream);
+
 // Enqueue on `stream`.  Returns cudaSuccess or the failing CUDA error; -1 style argument errors
 // are reported as cudaErrorInvalidValue.
 cudaError_t gemm_tc_launch(const GemmProblem& p, int num_sms, cudaStream_t stream);

@@ -6,6 +6,7 @@
 // Conv1d / ConvTranspose1d layers (cosyvoice/hifigan/generator.py:46-101,520-552).
 #include "gemm.h"
 #include "ptx.cuh"
+#include "epilogue.cuh"
 
 #include <mutex>
 #include <stdio.h>
@@ -13,220 +14,6 @@
 namespace mossdec {
 
 namespace {
-
-// warp 0 = TMA producer, warp 1 = MMA issuer (+ TMEM alloc), warps 2..17 = epilogue.
-// A warp may only touch TMEM lanes [32 * (warp % 4), +32), so the 16 epilogue warps form 4 groups of 4: the warps of
-// a group own the same 32 rows of the tile and split its columns in four parts.  (The epilogue is ALU/latency bound
-// at one row per thread; 4 resident warps per scheduler hide that latency, 2 did not -- profiles/r01_*.)
-constexpr int kEpiWarps = 16;
-constexpr int kEpiParts = kEpiWarps / 4;
-constexpr int kThreads = 64 + 32 * kEpiWarps;
-constexpr int kABytes = kGemmBM * kGemmBK * 2;  // 16 KB
-constexpr int kBBytesMax = 256 * kGemmBK * 2;   // 32 KB
-constexpr int kStageBytes = 2048;               // per-epilogue-warp staging tile: 32 rows x 64 B
-constexpr int kSmemBytes = kGemmStages * (kABytes + kBBytesMax) + kEpiWarps * kStageBytes + 1024 /*align*/ + 256 /*barriers*/;
-constexpr uint32_t kTmemCols = 512;
-
-struct KParams {
-    int32_t M, N, BN;
-    int32_t tiles_n, num_tiles, total_kb, num_segs;
-    GemmSeg segs[kGemmMaxSegs];
-    GemmEpilogue epi;
-};
-
-__device__ __forceinline__ float4 ldg4(const float* p) { return __ldg(reinterpret_cast<const float4*>(p)); }
-
-__device__ __forceinline__ float fast_mish(float x) {
-    // x * tanh(softplus(x)) with u = e^x: tanh(log(1 + u)) = (u^2 + 2u) / (u^2 + 2u + 2)
-    const float u = __expf(fminf(x, 20.f));
-    const float n = u * (u + 2.f);
-    return x > 20.f ? x : x * __fdividef(n, n + 2.f);
-}
-__device__ __forceinline__ float fast_gelu_erf(float x) {
-    // exact-erf GELU, erf by Abramowitz-Stegun 7.1.26 (|error| < 1.5e-7, far below the bf16 output rounding)
-    const float z = fabsf(x) * 0.70710678118654752440f;
-    const float t = __fdividef(1.f, fmaf(0.3275911f, z, 1.f));
-    float poly = fmaf(1.061405429f, t, -1.453152027f);
-    poly = fmaf(poly, t, 1.421413741f);
-    poly = fmaf(poly, t, -0.284496736f);
-    poly = fmaf(poly, t, 0.254829592f);
-    const float erf_abs = fmaf(-poly * t, __expf(-z * z), 1.f);
-    return 0.5f * x * (1.f + copysignf(erf_abs, x));
-}
-__device__ __forceinline__ float fast_sin(float x) {
-    // two-term Cody-Waite reduction to [-pi, pi], then the SFU sine (abs error ~1e-6 for |x| < 1e4)
-    const float k = rintf(x * 0.15915494309189535f);
-    float r = fmaf(k, -6.2831854820251465f, x);
-    r = fmaf(k, 1.7484555e-7f, r);
-    return __sinf(r);
-}
-
-// activation over a register vector (the switch is evaluated once per vector, not per element)
-template <int NV>
-__device__ __forceinline__ void apply_act_vec(float* v, int act, float p, const float* alpha) {
-    switch (act) {
-        case ACT_MISH:
-#pragma unroll
-            for (int i = 0; i < NV; ++i) v[i] = fast_mish(v[i]);
-            break;
-        case ACT_GELU:
-#pragma unroll
-            for (int i = 0; i < NV; ++i) v[i] = fast_gelu_erf(v[i]);
-            break;
-        case ACT_ELU:
-#pragma unroll
-            for (int i = 0; i < NV; ++i) v[i] = v[i] > 0.f ? v[i] : expm1f(v[i]);
-            break;
-        case ACT_LRELU:
-#pragma unroll
-            for (int i = 0; i < NV; ++i) v[i] = v[i] > 0.f ? v[i] : v[i] * p;
-            break;
-        case ACT_SNAKE:
-#pragma unroll
-            for (int i = 0; i < NV; i += 4) {
-                const float4 a = ldg4(alpha + i);
-                const float aa[4] = {a.x, a.y, a.z, a.w};
-#pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    const float s = fast_sin(v[i + j] * aa[j]);
-                    v[i + j] = fmaf(__fdividef(1.f, aa[j] + 1e-9f), s * s, v[i + j]);
-                }
-            }
-            break;
-        case ACT_SILU:
-#pragma unroll
-            for (int i = 0; i < NV; ++i) v[i] = silu_f(v[i]);
-            break;
-        case ACT_ABS:
-#pragma unroll
-            for (int i = 0; i < NV; ++i) v[i] = fabsf(v[i]);
-            break;
-        default: break;
-    }
-}
-
-// ---- per-warp staging tile: 32 rows x RB bytes (RB = 128 or 64) held as 128-byte lines with the 16-byte units of a
-// line XOR-swizzled by the line index, so both the thread==row side and the coalesced side are bank-conflict free.
-template <int RB>
-__device__ __forceinline__ uint32_t stage_off(int r, int u) {  // logical (row, 16-byte unit) -> byte offset
-    if (RB == 128) return (uint32_t)(r * 128 + ((u ^ (r & 7)) << 4));
-    const int line = r >> 1;
-    return (uint32_t)(line * 128 + (((((r & 1) << 2) | u) ^ (line & 7)) << 4));
-}
-// coalesced side: pass k (0 .. RB/16 - 1), lane -> logical (row, unit); the 32 lanes of a pass cover 4 whole lines
-template <int RB>
-__device__ __forceinline__ void stage_coalesced(int k, int lane, int& r, int& u) {
-    const int line = k * 4 + (lane >> 3);
-    if (RB == 128) {
-        r = line;
-        u = (lane & 7) ^ (line & 7);
-    } else {
-        const int pos = (lane & 7) ^ (line & 7);
-        r = line * 2 + (pos >> 2);
-        u = pos & 3;
-    }
-}
-
-struct EpiCtx {
-    const KParams* p;
-    uint8_t* stg;       // this warp's staging tile
-    uint8_t* stg_all;   // staging tiles of all epilogue warps
-    int ew;             // epilogue warp index
-    uint32_t taddr;     // TMEM address of (lane quarter, accumulator)
-    int lane, quarter, row0, n0, seq;
-    bool valid;         // this thread's row exists and belongs to a sequence
-};
-
-__device__ __forceinline__ void group_sync(int quarter) {
-    asm volatile("bar.sync %0, %1;" ::"r"(quarter + 1), "n"(32 * kEpiParts) : "memory");
-}
-// sum one float2 per row over the warps of a group (row statistics over the full tile width)
-__device__ __forceinline__ float2 group_exchange(const EpiCtx& c, float2 mine) {
-    reinterpret_cast<float2*>(c.stg)[c.lane] = mine;
-    group_sync(c.quarter);
-    float2 t = make_float2(0.f, 0.f);
-#pragma unroll
-    for (int part = 0; part < kEpiParts; ++part) {
-        const float2 o = reinterpret_cast<const float2*>(c.stg_all + ((part << 2) | (c.ew & 3)) * kStageBytes)[c.lane];
-        t.x += o.x;
-        t.y += o.y;
-    }
-    group_sync(c.quarter);
-    return t;
-}
-
-// coalesced global -> registers (thread == row) through the staging tile; fp32, 32 columns starting at column nb
-// (two rounds of 16 columns = 64-byte rows)
-__device__ __forceinline__ void load_rows_f32(const EpiCtx& c, const float* base, int ld, int nb, int nlim, float* out32) {
-    const KParams& p = *c.p;
-#pragma unroll
-    for (int h = 0; h < 2; ++h) {
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            int r, u;
-            stage_coalesced<64>(k, c.lane, r, u);
-            const int grow = c.row0 + r, col = nb + h * 16 + u * 4;
-            float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (grow < p.M && col < nlim) t = *reinterpret_cast<const float4*>(base + (size_t)grow * ld + col);
-            *reinterpret_cast<float4*>(c.stg + k * 512 + c.lane * 16) = t;
-        }
-        __syncwarp();
-#pragma unroll
-        for (int u = 0; u < 4; ++u) {
-            const float4 t = *reinterpret_cast<const float4*>(c.stg + stage_off<64>(c.lane, u));
-            float* o = out32 + h * 16 + u * 4;
-            o[0] = t.x; o[1] = t.y; o[2] = t.z; o[3] = t.w;
-        }
-        __syncwarp();
-    }
-}
-__device__ __forceinline__ void store_rows_f32(const EpiCtx& c, float* base, int ld, int nb, int nlim, const float* v32) {
-    const KParams& p = *c.p;
-#pragma unroll
-    for (int h = 0; h < 2; ++h) {
-#pragma unroll
-        for (int u = 0; u < 4; ++u) {
-            const float* v = v32 + h * 16 + u * 4;
-            *reinterpret_cast<float4*>(c.stg + stage_off<64>(c.lane, u)) = make_float4(v[0], v[1], v[2], v[3]);
-        }
-        __syncwarp();
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            int r, u;
-            stage_coalesced<64>(k, c.lane, r, u);
-            const int grow = c.row0 + r, col = nb + h * 16 + u * 4;
-            const float4 t = *reinterpret_cast<const float4*>(c.stg + k * 512 + c.lane * 16);
-            if (grow < p.M && col < nlim) *reinterpret_cast<float4*>(base + (size_t)grow * ld + col) = t;
-        }
-        __syncwarp();
-    }
-}
-// registers (thread == row, NV values) -> bf16 global, coalesced; RB = NV * 2 bytes per row
-template <int NV>
-__device__ __forceinline__ void store_rows_bf16(const EpiCtx& c, __nv_bfloat16* base, int ld, int nb, int nlim,
-                                                const float* v) {
-    constexpr int RB = NV * 2;
-    const KParams& p = *c.p;
-#pragma unroll
-    for (int u = 0; u < NV / 8; ++u) {
-        uint4 t;
-        t.x = pack_bf16x2(v[u * 8], v[u * 8 + 1]);
-        t.y = pack_bf16x2(v[u * 8 + 2], v[u * 8 + 3]);
-        t.z = pack_bf16x2(v[u * 8 + 4], v[u * 8 + 5]);
-        t.w = pack_bf16x2(v[u * 8 + 6], v[u * 8 + 7]);
-        *reinterpret_cast<uint4*>(c.stg + stage_off<RB>(c.lane, u)) = t;
-    }
-    __syncwarp();
-#pragma unroll
-    for (int k = 0; k < RB / 16; ++k) {
-        int r, u;
-        stage_coalesced<RB>(k, c.lane, r, u);
-        const int grow = c.row0 + r, col = nb + u * 8;
-        const uint4 t = *reinterpret_cast<const uint4*>(c.stg + k * 512 + c.lane * 16);
-        if (grow < p.M && col < nlim) *reinterpret_cast<uint4*>(base + (size_t)grow * ld + col) = t;
-    }
-    __syncwarp();
-}
 
 // One pass over this warp's column range [cbeg, cend) (16-column chunks of the tile), W16 chunks at a time.
 // W16 == 4 is the bf16-only fast path (no fp32 input / output); W16 == 2 handles everything.
@@ -343,7 +130,7 @@ __global__ void __launch_bounds__(kThreads, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__ CUtensorMap tmA1,
                const __grid_constant__ CUtensorMap tmB, const __grid_constant__ KParams p) {
     extern __shared__ uint8_t smem_raw[];
-    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);  // stays in the shared address space (STS / LDS)
     uint8_t* sA = smem;
     uint8_t* sB = smem + kGemmStages * kABytes;
     uint8_t* sStage = smem + kGemmStages * (kABytes + kBBytesMax);
