@@ -128,7 +128,7 @@ int Engine::gemm(const GemmProblem& p, cudaStream_t st) {
         int kb = 0;
         for (int s = 0; s < p.num_segs; ++s) kb += p.segs[s].nkb;
         const uint64_t key = (uint64_t)(p.N & 0xfff) | ((uint64_t)(kb & 0xfff) << 12) | ((uint64_t)(p.epi.act1 & 7) << 24) |
-                             ((uint64_t)(p.epi.ln1_g != nullptr) << 27) | ((uint64_t)(p.epi.ln2_g != nullptr) << 28) |
+                             ((uint64_t)(p.epi.ln1_g != nullptr) << 27) | ((uint64_t)(p.epi.ln2_g != nullptr || p.epi.ln2_plain) << 28) |
                              ((uint64_t)(p.epi.resid != nullptr) << 29) | ((uint64_t)(p.epi.out_f32 != nullptr) << 30) |
                              ((uint64_t)(p.epi.out_bf16 != nullptr) << 31) | ((uint64_t)p.M << 40);
         prof_begin(0, 2.0 * p.M * p.N * kb * kGemmBK, st, key);
@@ -164,7 +164,7 @@ int Engine::finalize() {
                           "est.final.b", "est.final.ln.g", "est.final.ln.b", "est.proj.w", "est.proj.b"};
     for (const char* n : once) find(n);
     const char* res[] = {"c1.w", "c1.b", "ln1.g", "ln1.b", "c2.w", "c2.b", "ln2.g", "ln2.b", "rc.w", "rc.b"};
-    const char* tf[] = {"n1.g", "n1.b", "qkv.w", "o.w", "o.b", "n3.g", "n3.b", "ff1.w", "ff1.b", "ff2.w", "ff2.b"};
+    const char* tf[] = {"qkv.w", "qkv.b", "o.w", "o.b", "ff1.w", "ff1.b", "ff2.w", "ff2.b"};
     for (int i = 0; i < ngroups; ++i) {
         for (const char* n : res) find(S("est.res%d.", i) + n);
         for (int j = 0; j < cfg_.n_blocks; ++j)
@@ -340,7 +340,7 @@ int Engine::estimator_forward(int M, int nseq, int max_len, const float* tbias, 
             p.w = W<__nv_bfloat16>(r + "rc.w");
             p.N = C; p.BN = C;
             p.epi.bias = W<float>(r + "rc.b");
-            p.epi.out_f32 = rres_; p.epi.ldf = C;
+            p.epi.out_f32 = rres_; p.epi.ldf = C; p.epi.f32_tiled = 1;
             if (gemm(p, st)) return -1;
         }
         {   // block2 + residual; also emits norm1 of the first transformer block
@@ -353,8 +353,8 @@ int Engine::estimator_forward(int M, int nseq, int max_len, const float* tbias, 
             p.epi.act1 = ACT_MISH;
             p.epi.row_seq = row_seq;
             p.epi.resid = rres_; p.epi.ldr = C;
-            p.epi.out_f32 = hres_; p.epi.ldf = C;
-            p.epi.ln2_g = W<float>(S("est.tf%d.0.n1.g", g)); p.epi.ln2_b = W<float>(S("est.tf%d.0.n1.b", g));
+            p.epi.out_f32 = hres_; p.epi.ldf = C; p.epi.f32_tiled = 1;
+            p.epi.ln2_plain = 1;  // norm1 of the first transformer block (affine folded into its qkv weights)
             p.epi.out_bf16 = xn_; p.epi.ldo = C;
             if (gemm(p, st)) return -1;
         }
@@ -365,6 +365,7 @@ int Engine::estimator_forward(int M, int nseq, int max_len, const float* tbias, 
                 dense(p, xn_, C);
                 p.w = W<__nv_bfloat16>(t + "qkv.w");
                 p.N = 3 * H; p.BN = 256;
+                p.epi.bias = W<float>(t + "qkv.b");  // W . beta of the folded norm1
                 p.epi.out_bf16 = qkv_; p.epi.ldo = 3 * H;
                 if (gemm(p, st)) return -1;
             }
@@ -386,8 +387,8 @@ int Engine::estimator_forward(int M, int nseq, int max_len, const float* tbias, 
                 p.epi.bias = W<float>(t + "o.b");
                 p.epi.row_seq = row_seq;
                 p.epi.resid = hres_; p.epi.ldr = C;
-                p.epi.out_f32 = hres_; p.epi.ldf = C;
-                p.epi.ln2_g = W<float>(t + "n3.g"); p.epi.ln2_b = W<float>(t + "n3.b");
+                p.epi.out_f32 = hres_; p.epi.ldf = C; p.epi.f32_tiled = 1;
+                p.epi.ln2_plain = 1;  // norm3 (affine folded into ff1)
                 p.epi.out_bf16 = xn_; p.epi.ldo = C;
                 if (gemm(p, st)) return -1;
             }
@@ -400,8 +401,7 @@ int Engine::estimator_forward(int M, int nseq, int max_len, const float* tbias, 
                 f.hres = hres_;
                 f.row_seq = row_seq;
                 if (j + 1 < cfg_.n_blocks) {
-                    f.ln_g = W<float>(S("est.tf%d.%d.n1.g", g, j + 1));
-                    f.ln_b = W<float>(S("est.tf%d.%d.n1.b", g, j + 1));
+                    f.ln = 1;  // norm1 of the next block (affine folded into its qkv weights)
                     f.out_bf16 = xn_; f.ldo = C;
                 } else if (g == 0) {           // down block: skip connection -> right half of the concat buffer
                     f.out_bf16 = cat_ + C; f.ldo = 2 * C;

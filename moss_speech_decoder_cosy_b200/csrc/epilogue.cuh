@@ -175,6 +175,29 @@ __device__ __forceinline__ void load_rows_f32(const EpiCtx& c, const float* base
         __syncwarp();
     }
 }
+// tiled fp32 layout (gemm.h tiled_f32_offset): direct, coalesced thread == row access of 32 columns starting at nb
+__device__ __forceinline__ void add_rows_f32_tiled(const float* base, int row, int nb, float* acc32) {
+    const float* q = base + tiled_f32_offset(row, nb);
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+        const float4 t = *reinterpret_cast<const float4*>(q + (size_t)u * 512);
+        acc32[u * 4] += t.x; acc32[u * 4 + 1] += t.y; acc32[u * 4 + 2] += t.z; acc32[u * 4 + 3] += t.w;
+    }
+}
+__device__ __forceinline__ void load_rows_f32_tiled(const float* base, int row, int nb, float* out32) {
+    const float* q = base + tiled_f32_offset(row, nb);
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+        const float4 t = *reinterpret_cast<const float4*>(q + (size_t)u * 512);
+        out32[u * 4] = t.x; out32[u * 4 + 1] = t.y; out32[u * 4 + 2] = t.z; out32[u * 4 + 3] = t.w;
+    }
+}
+__device__ __forceinline__ void store_rows_f32_tiled(float* base, int row, int nb, const float* v32) {
+    float* q = base + tiled_f32_offset(row, nb);
+#pragma unroll
+    for (int u = 0; u < 8; ++u)
+        *reinterpret_cast<float4*>(q + (size_t)u * 512) = make_float4(v32[u * 4], v32[u * 4 + 1], v32[u * 4 + 2], v32[u * 4 + 3]);
+}
 // same access pattern, but accumulates into acc32 (keeps the register footprint at the accumulator itself)
 __device__ __forceinline__ void add_rows_f32(const EpiCtx& c, const float* base, int ld, int nb, int nlim, float* acc32) {
     const KParams& p = *c.p;

@@ -10,7 +10,9 @@
 //                                        E1: acc1[b] -> +b1 -> GELU -> bf16 -> P[b] in shared memory, already in the
 //                                            128B-swizzled K-major layout the tensor core reads its A operand from
 //                                        G2: acc2 += P[b] . W2[:, chunk]^T    (tcgen05.mma M128 N256, K = 128)
-//   final: acc2 -> registers (TMEM released at once) -> + b2 + hres -> hres, LayerNorm -> bf16 out.
+//   acc2 is preloaded with hres + b2 through tcgen05.st at the start of the tile, so the MMAs accumulate the residual
+//   stream themselves;  final: acc2 -> registers -> hres (coalesced stores in the tiled fp32 layout), LayerNorm ->
+//   bf16 -> swizzled smem -> TMA store.
 // acc1 is double buffered in TMEM (2 x 128 columns) next to acc2 (256 columns), P is double buffered in shared memory,
 // so the GELU epilogue of chunk h overlaps G2(h-1) / G1(h+1) on the tensor pipe.  W1 / W2 stream through a 3-stage ring
 // of 32 KB TMA stages (1 MB of weights per tile, L2 resident).
@@ -30,38 +32,44 @@ bool encode_2d(CUtensorMap* m, const void* ptr, uint64_t cols, uint64_t rows, ui
 
 namespace {
 
+#ifdef FFN_EXPERIMENT_NO_GELU   // timing experiment only (tests/): how much of E1 is the activation math
+#define fast_gelu_erf(x) (x)
+#endif
+
 constexpr int kC = 256;          // model width
 constexpr int kHid = 1024;       // hidden width
 constexpr int kChunk = 128;      // hidden columns per chunk
 constexpr int kNChunk = kHid / kChunk;
+constexpr int kCluster = 2;      // CTAs per cluster: every weight stage is fetched from L2 once and multicast to both
+constexpr uint16_t kClusterMask = (1u << kCluster) - 1;
 constexpr int kFStages = 3;
 constexpr int kFStageBytes = 32768;
 constexpr int kXBytes = kGemmBM * kC * 2;      // 64 KB
 constexpr int kPBytes = kGemmBM * kChunk * 2;  // 32 KB per buffer
 constexpr int kFfnSmem = kXBytes + 2 * kPBytes + kFStages * kFStageBytes + 1024 /*align*/ + 256 /*barriers*/;
 constexpr uint32_t kAcc2Col = 0, kAcc1Col = 256;
-static_assert(kEpiWarps * kStageBytes <= kPBytes, "final-epilogue staging tiles alias P[0]");
+constexpr int kOutStageBytes = 4096;           // per epilogue warp: 32 rows x 64 bf16, the box of the output TMA store
+static_assert(kEpiWarps * kOutStageBytes <= 2 * kPBytes, "final-epilogue staging tiles alias P[0] | P[1]");
 
 struct FfnParams {
     int32_t M, num_tiles;
     const float* b1;
     const float* b2;
-    const float* ln_g;  // nullptr: out_bf16 = bf16(hres)
-    const float* ln_b;
+    int32_t ln;         // 1: out = (hres - mean) * rstd (affine folded into the consumer's weights), 0: out = bf16(hres)
     const int32_t* row_seq;
-    float* hres;        // [M, 256] fp32, read and written
-    __nv_bfloat16* out_bf16;
-    int32_t ldo;
+    float* hres;        // [M, 256] fp32 in the lane-major tiled layout (gemm.h tiled_f32_offset), read and written
     int32_t store_f32;
     float ln_eps;
+    long long* trace;   // developer aid: clock64 stamps of CTA 0 (epilogue warp 0: slots 0..31, MMA thread: 32..47 per tile)
 };
 
 __device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 __device__ __forceinline__ void epi_sync_all() { asm volatile("bar.sync 5, %0;" ::"n"(32 * kEpiWarps) : "memory"); }
 
-__global__ void __launch_bounds__(kThreads, 1)
+__global__ void __cluster_dims__(kCluster, 1, 1) __launch_bounds__(kThreads, 1)
 ffn_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmW1,
-              const __grid_constant__ CUtensorMap tmW2, const __grid_constant__ FfnParams p) {
+              const __grid_constant__ CUtensorMap tmW2, const __grid_constant__ CUtensorMap tmOut,
+              const __grid_constant__ FfnParams p) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);  // stays in the shared address space (STS / LDS)
     uint8_t* sX = smem;
@@ -76,8 +84,7 @@ ffn_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ C
     uint64_t* p_ready = a1_full + 2;     // [2] epilogue -> MMA: P[b] written, acc1[b] drained
     uint64_t* p_free = p_ready + 2;      // [2] MMA -> epilogue: G2 finished reading P[b]
     uint64_t* acc2_full = p_free + 2;    // MMA -> epilogue
-    uint64_t* acc2_free = acc2_full + 1; // epilogue -> MMA
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc2_free + 1);
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc2_full + 1);
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -86,9 +93,10 @@ ffn_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ C
         tma_prefetch_desc(&tmX);
         tma_prefetch_desc(&tmW1);
         tma_prefetch_desc(&tmW2);
+        tma_prefetch_desc(&tmOut);
         for (int i = 0; i < kFStages; ++i) {
             mbar_init(&full[i], 1);
-            mbar_init(&empty[i], 1);
+            mbar_init(&empty[i], kCluster);   // one tcgen05.commit arrival from the MMA thread of every CTA of the cluster
         }
         mbar_init(x_full, 1);
         mbar_init(x_free, 1);
@@ -98,7 +106,6 @@ ffn_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ C
             mbar_init(&p_free[i], 1);
         }
         mbar_init(acc2_full, 1);
-        mbar_init(acc2_free, kEpiWarps);
         mbar_fence_init();
     }
     if (warp == 1) {
@@ -108,7 +115,9 @@ ffn_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ C
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
+    cluster_sync_all();   // peers' barriers are initialised before any multicast / remote arrive can reach them
     const uint32_t tmem_base = *tmem_slot;
+    const int rank = (int)cluster_ctarank();
 
     if (warp == 0) {
         // ------------------------------------------------------------ TMA producer
@@ -125,9 +134,9 @@ ffn_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ C
                 for (int j = 0; j < 2; ++j) {
                     mbar_wait(&empty[stage], phase ^ 1);
                     mbar_expect_tx(&full[stage], kFStageBytes);
-                    uint8_t* dst = sRing + stage * kFStageBytes;
-                    tma_load_2d(dst, &tmW1, (2 * j) * kGemmBK, h * kChunk, &full[stage]);
-                    tma_load_2d(dst + kFStageBytes / 2, &tmW1, (2 * j + 1) * kGemmBK, h * kChunk, &full[stage]);
+                    // this CTA fetches k-block 2j + rank and multicasts it; the peer supplies the other one
+                    uint8_t* dst = sRing + stage * kFStageBytes + rank * (kFStageBytes / 2);
+                    tma_load_2d_mc(dst, &tmW1, (2 * j + rank) * kGemmBK, h * kChunk, &full[stage], kClusterMask);
                     next_stage();
                 }
             };
@@ -135,21 +144,27 @@ ffn_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ C
                 for (int j = 0; j < 2; ++j) {
                     mbar_wait(&empty[stage], phase ^ 1);
                     mbar_expect_tx(&full[stage], kFStageBytes);
-                    tma_load_2d(sRing + stage * kFStageBytes, &tmW2, h * kChunk + j * kGemmBK, 0, &full[stage]);
+                    // rows [128 rank, +128) of the 256-row k-block (8-row swizzle atoms are contiguous: offset 16 KB)
+                    tma_load_2d_mc(sRing + stage * kFStageBytes + rank * (kFStageBytes / 2), &tmW2,
+                                   h * kChunk + j * kGemmBK, rank * (kC / 2), &full[stage], kClusterMask);
                     next_stage();
                 }
             };
             int it = 0;
-            for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
+            if ((int)blockIdx.x < p.num_tiles) l2_prefetch_bulk(p.hres + (size_t)blockIdx.x * kGemmBM * kC, kGemmBM * kC * 4);
+            for (int tile = blockIdx.x; (tile & ~(kCluster - 1)) < p.num_tiles; tile += gridDim.x, ++it) {  // cluster-uniform trip count
                 if (it > 0) mbar_wait(x_free, (uint32_t)((it - 1) & 1));
                 mbar_expect_tx(x_full, kXBytes);
                 for (int kb = 0; kb < kC / kGemmBK; ++kb)
                     tma_load_2d(sX + kb * kABytes, &tmX, kb * kGemmBK, tile * kGemmBM, x_full);
+                // the residual rows of the next tile: pulled into L2 a whole tile ahead of their use
+                if (tile + (int)gridDim.x < p.num_tiles)
+                    l2_prefetch_bulk(p.hres + (size_t)(tile + gridDim.x) * kGemmBM * kC, kGemmBM * kC * 4);
                 load_g1(0);
                 load_g1(1);
                 for (int h = 0; h < kNChunk; ++h) {
-                    load_g2(h);
                     if (h + 2 < kNChunk) load_g1(h + 2);
+                    load_g2(h);
                 }
             }
         }
@@ -166,10 +181,14 @@ ffn_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ C
                     phase ^= 1;
                 }
             };
+            const bool mtr = p.trace != nullptr && blockIdx.x == 0;
+            long long w_full = 0, w_ready = 0;
             auto g1 = [&](int b) {
                 const uint32_t d = tmem_base + kAcc1Col + (uint32_t)b * kChunk;
                 for (int j = 0; j < 2; ++j) {
+                    const long long t0 = mtr ? clock64() : 0;
                     mbar_wait(&full[stage], phase);
+                    if (mtr) w_full += clock64() - t0;
                     tc_fence_after();
 #pragma unroll
                     for (int q = 0; q < 2; ++q) {
@@ -180,7 +199,7 @@ ffn_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ C
                         for (int k = 0; k < kGemmBK / 16; ++k)
                             umma_bf16(d, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc1, (uint32_t)((kb | k) != 0));
                     }
-                    umma_commit(&empty[stage]);
+                    umma_commit_mc(&empty[stage], kClusterMask);   // the stage is refilled by both CTAs: both must see it free
                     next_stage();
                 }
                 umma_commit(&a1_full[b]);
@@ -189,36 +208,47 @@ ffn_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ C
                 const int b = h & 1;
                 const uint32_t d = tmem_base + kAcc2Col;
                 for (int j = 0; j < 2; ++j) {
+                    const long long t0 = mtr ? clock64() : 0;
                     mbar_wait(&full[stage], phase);
+                    if (mtr) w_full += clock64() - t0;
                     tc_fence_after();
                     const uint64_t da = umma_desc_sw128(smem_u32(sP + b * kPBytes + j * kABytes));
                     const uint64_t db = umma_desc_sw128(smem_u32(sRing + stage * kFStageBytes));
 #pragma unroll
                     for (int k = 0; k < kGemmBK / 16; ++k)
-                        umma_bf16(d, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc2, (uint32_t)((h | j | k) != 0));
-                    umma_commit(&empty[stage]);
+                        umma_bf16(d, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc2, 1u);  // acc2 was preloaded with hres + b2
+                    umma_commit_mc(&empty[stage], kClusterMask);   // the stage is refilled by both CTAs: both must see it free
                     next_stage();
                 }
                 umma_commit(&p_free[b]);
             };
             int it = 0;
             uint32_t pr_phase[2] = {0, 0};
-            for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
+            for (int tile = blockIdx.x; (tile & ~(kCluster - 1)) < p.num_tiles; tile += gridDim.x, ++it) {  // cluster-uniform trip count
                 mbar_wait(x_full, (uint32_t)(it & 1));
                 tc_fence_after();
+                if (p.trace != nullptr && blockIdx.x == 0) p.trace[it * 48 + 32] = clock64();
                 g1(0);
                 g1(1);
                 for (int h = 0; h < kNChunk; ++h) {
                     const int b = h & 1;
-                    mbar_wait(&p_ready[b], pr_phase[b]);
+                    const long long t0 = mtr ? clock64() : 0;
+                    mbar_wait(&p_ready[b], pr_phase[b]);   // P[b] written, acc1[b] drained (h == 0: acc2 preloaded too)
                     pr_phase[b] ^= 1;
-                    if (h == 0 && it > 0) mbar_wait(acc2_free, (uint32_t)((it - 1) & 1));
                     tc_fence_after();
-                    g2(h);
-                    if (h + 2 < kNChunk) g1(b);
+                    if (mtr) w_ready += clock64() - t0;
+                    if (p.trace != nullptr && blockIdx.x == 0) p.trace[it * 48 + 33 + h] = clock64();
+                    if (h + 2 < kNChunk) g1(b);            // G1 first: its result is what the epilogue waits for next
                     if (h + 2 == kNChunk - 1) umma_commit(x_free);  // last G1 of the tile issued: X may be reloaded
+                    g2(h);
                 }
                 umma_commit(acc2_full);
+                if (mtr) {
+                    p.trace[it * 48 + 41] = clock64();
+                    p.trace[it * 48 + 42] = w_full;
+                    p.trace[it * 48 + 43] = w_ready;
+                    w_full = w_ready = 0;
+                }
             }
         }
     } else {
@@ -227,126 +257,177 @@ ffn_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ C
         const int part = ew >> 2;
         const int quarter = warp & 3;
         const int trow = quarter * 32 + lane;  // row of the tile owned by this thread
-        KParams kp;                            // only M is read by the staging helpers
-        kp.M = p.M;
-        EpiCtx c;
-        c.p = &kp;
-        c.lane = lane;
-        c.ew = ew;
-        c.quarter = quarter;
-        c.stg = sP + ew * kStageBytes;  // aliases P[0]: only used while no G2 reads it (see the sync below)
-        c.stg_all = sP;
-        c.n0 = 0;
+        // per-warp 4 KB staging tile (32 rows x 128 B, 128B-swizzled) for the bf16 TMA store; the 16 tiles alias
+        // P[0] | P[1], which no MMA reads between acc2_full and the next tile's first E1
+        uint8_t* stg = sP + ew * kOutStageBytes;
         const uint32_t tlane = tmem_base + ((uint32_t)(quarter * 32) << 16);
         uint32_t a1_phase[2] = {0, 0};
         int it = 0;
-        for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
-            c.row0 = tile * kGemmBM + quarter * 32;
-            const int row = c.row0 + lane;
-            c.seq = (p.row_seq != nullptr && row < p.M) ? __ldg(p.row_seq + row) : 0;
-            c.valid = row < p.M && c.seq >= 0;
+        const bool tr = p.trace != nullptr && blockIdx.x == 0 && ew == 0 && lane == 0;
+#define FFN_STAMP(k) do { if (tr) p.trace[it * 48 + (k)] = clock64(); } while (0)
+        for (int tile = blockIdx.x; (tile & ~(kCluster - 1)) < p.num_tiles; tile += gridDim.x, ++it) {  // cluster-uniform trip count
+            FFN_STAMP(0);
+            const int row = tile * kGemmBM + trow;
+            const bool live = tile < p.num_tiles;   // the last cluster may carry a padding tile: it only keeps the weight ring in step
+            const bool valid = live && (p.row_seq == nullptr || __ldg(p.row_seq + row) >= 0);
 
-            // ---- E1: hidden chunks -> GELU -> P[b]
+            // ---- preload acc2 := hres + b2 (own row, own 64 columns): the MMAs then accumulate the residual stream
+            // directly, and the L2 latency of these (coalesced, tiled-layout) loads hides behind G1(0) / G1(1).  This
+            // warp drained the same TMEM lanes / columns in the previous tile; the p_ready[0] arrival of E1(0)
+            // publishes the stores to the MMA thread.
+            {
+                const float* hrow = p.hres + tiled_f32_offset(row, part * 64);  // float4 j of the row: + j * 512 floats
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    float r[16];
+#pragma unroll
+                    for (int i = 0; i < 16; i += 4) {
+                        float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
+                        if (live) t = *reinterpret_cast<const float4*>(hrow + (size_t)(q * 4 + (i >> 2)) * 512);
+                        const float4 bb = ldg4(p.b2 + part * 64 + q * 16 + i);
+                        r[i] = t.x + bb.x; r[i + 1] = t.y + bb.y; r[i + 2] = t.z + bb.z; r[i + 3] = t.w + bb.w;
+                    }
+                    tmem_st16(tlane + kAcc2Col + (uint32_t)(part * 64 + q * 16), r);
+                }
+                tmem_st_wait();
+            }
+            // the previous tile's bf16 TMA store must have finished reading the staging tiles (= P) before any warp's
+            // E1 overwrites them; its latency hid behind the preload above
+            if (it > 0) {
+                if (lane == 0) tma_store_wait_read();
+                epi_sync_all();
+            }
+            FFN_STAMP(1);
+
+            // ---- E1: hidden chunks -> GELU -> P[b].  TMEM -> register reads run at ~64 B/clk/SM (a 128 x 128 fp32 chunk
+            // takes ~1000 clk to drain), so they are software-pipelined against the math: each thread's 32 columns
+            // are read as two 16-column halves, and the load of the next half (or of the next chunk's first half)
+            // is always in flight while the current half goes through the GELU.
+            float va[16], vb[16];
+            mbar_wait(&a1_full[0], a1_phase[0]);
+            a1_phase[0] ^= 1;
+            tc_fence_after();
+            tmem_ld16(tlane + kAcc1Col + (uint32_t)(part * 32), va);
             for (int h = 0; h < kNChunk; ++h) {
                 const int b = h & 1;
-                mbar_wait(&a1_full[b], a1_phase[b]);
-                a1_phase[b] ^= 1;
-                if (h >= 2) mbar_wait(&p_free[b], (uint32_t)(((h - 2) >> 1) & 1));
-                tc_fence_after();
-                float v[32];
-                const uint32_t ta = tlane + kAcc1Col + (uint32_t)(b * kChunk + part * 32);
-                tmem_ld16(ta, v);
-                tmem_ld16(ta + 16, v + 16);
-                tmem_ld_wait();
-                const float* bias = p.b1 + h * kChunk + part * 32;
+                const float* bp = p.b1 + h * kChunk + part * 32;
+                float4 bias[4];
 #pragma unroll
-                for (int i = 0; i < 32; i += 4) {
-                    const float4 bb = ldg4(bias + i);
-                    v[i] = fast_gelu_erf(v[i] + bb.x);
-                    v[i + 1] = fast_gelu_erf(v[i + 1] + bb.y);
-                    v[i + 2] = fast_gelu_erf(v[i + 2] + bb.z);
-                    v[i + 3] = fast_gelu_erf(v[i + 3] + bb.w);
+                for (int i = 0; i < 4; ++i) bias[i] = ldg4(bp + 4 * i);
+                tmem_ld_wait();   // va of this chunk
+                FFN_STAMP(2 + 2 * h);
+                tmem_ld16(tlane + kAcc1Col + (uint32_t)(b * kChunk + part * 32 + 16), vb);
+                uint32_t pk[16];
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    pk[2 * i] = pack_bf16x2(fast_gelu_erf(va[4 * i] + bias[i].x), fast_gelu_erf(va[4 * i + 1] + bias[i].y));
+                    pk[2 * i + 1] = pack_bf16x2(fast_gelu_erf(va[4 * i + 2] + bias[i].z), fast_gelu_erf(va[4 * i + 3] + bias[i].w));
                 }
+#pragma unroll
+                for (int i = 0; i < 4; ++i) bias[i] = ldg4(bp + 16 + 4 * i);
+                tmem_ld_wait();   // vb of this chunk: acc1[b] is now fully drained by this thread
+                if (h + 1 < kNChunk) {   // first half of the next chunk (other accumulator buffer) flies during the math below
+                    mbar_wait(&a1_full[b ^ 1], a1_phase[b ^ 1]);
+                    a1_phase[b ^ 1] ^= 1;
+                    tc_fence_after();
+                    tmem_ld16(tlane + kAcc1Col + (uint32_t)((b ^ 1) * kChunk + part * 32), va);
+                }
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    pk[8 + 2 * i] = pack_bf16x2(fast_gelu_erf(vb[4 * i] + bias[i].x), fast_gelu_erf(vb[4 * i + 1] + bias[i].y));
+                    pk[8 + 2 * i + 1] = pack_bf16x2(fast_gelu_erf(vb[4 * i + 2] + bias[i].z), fast_gelu_erf(vb[4 * i + 3] + bias[i].w));
+                }
+                // P[b] is only needed now: G2(h - 2) must have finished reading it (its latency hid behind the GELU math)
+                if (h >= 2) mbar_wait(&p_free[b], (uint32_t)(((h - 2) >> 1) & 1));
                 // K-major SW128 operand layout: k-block (64 hidden) = 128 rows x 128 B, 16-byte units XOR row % 8
                 uint8_t* prow = sP + b * kPBytes + (part >> 1) * kABytes + trow * 128;
                 const int ub = (part & 1) * 4;
 #pragma unroll
-                for (int u = 0; u < 4; ++u) {
-                    uint4 t;
-                    t.x = pack_bf16x2(v[u * 8], v[u * 8 + 1]);
-                    t.y = pack_bf16x2(v[u * 8 + 2], v[u * 8 + 3]);
-                    t.z = pack_bf16x2(v[u * 8 + 4], v[u * 8 + 5]);
-                    t.w = pack_bf16x2(v[u * 8 + 6], v[u * 8 + 7]);
-                    *reinterpret_cast<uint4*>(prow + (((ub + u) ^ (trow & 7)) << 4)) = t;
-                }
+                for (int u = 0; u < 4; ++u)
+                    *reinterpret_cast<uint4*>(prow + (((ub + u) ^ (trow & 7)) << 4)) =
+                        make_uint4(pk[4 * u], pk[4 * u + 1], pk[4 * u + 2], pk[4 * u + 3]);
                 fence_proxy_async_smem();
                 tc_fence_before();
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&p_ready[b]);
+                FFN_STAMP(3 + 2 * h);
             }
 
-            // ---- final: acc2 -> registers, release TMEM, then bias + residual + LayerNorm from registers
+            // ---- final: acc2 (= hres + b2 + FFN) -> registers -> fp32 stream (tiled, coalesced) + LayerNorm -> bf16
             mbar_wait(acc2_full, (uint32_t)(it & 1));
             tc_fence_after();
+            FFN_STAMP(18);
             float v[64];
-            {
+            float s = 0.f, ss = 0.f;
+            {   // drain 16 columns at a time, the next load in flight while this one is stored / reduced
                 const uint32_t ta = tlane + kAcc2Col + (uint32_t)(part * 64);
                 tmem_ld16(ta, v);
-                tmem_ld16(ta + 16, v + 16);
-                tmem_ld16(ta + 32, v + 32);
-                tmem_ld16(ta + 48, v + 48);
-                tmem_ld_wait();
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    tmem_ld_wait();
+                    if (q < 3) tmem_ld16(ta + (q + 1) * 16, v + (q + 1) * 16);
+                    float* w = v + q * 16;
+                    if (!valid) {
+#pragma unroll
+                        for (int i = 0; i < 16; ++i) w[i] = 0.f;
+                    }
+                    if (p.store_f32 && live) {
+                        float* dst = p.hres + tiled_f32_offset(row, part * 64 + q * 16);
+#pragma unroll
+                        for (int u = 0; u < 4; ++u)
+                            *reinterpret_cast<float4*>(dst + (size_t)u * 512) = make_float4(w[4 * u], w[4 * u + 1], w[4 * u + 2], w[4 * u + 3]);
+                    }
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) {
+                        s += w[i];
+                        ss = fmaf(w[i], w[i], ss);
+                    }
+                }
             }
-            tc_fence_before();
+            if (p.ln) {   // (x - mean) * rstd; gamma / beta live in the consumer's weights
+                // row statistics over the 4 warps that share this TMEM lane quarter (slot = head of the staging tile)
+                reinterpret_cast<float2*>(stg)[lane] = make_float2(s, ss);
+                group_sync(quarter);
+                s = 0.f;
+                ss = 0.f;
+#pragma unroll
+                for (int q = 0; q < kEpiParts; ++q) {
+                    const float2 o = reinterpret_cast<const float2*>(sP + ((q << 2) | (ew & 3)) * kOutStageBytes)[lane];
+                    s += o.x;
+                    ss += o.y;
+                }
+                group_sync(quarter);
+                const float mean = s * (1.f / kC);
+                const float rstd = rsqrtf(fmaxf(ss * (1.f / kC) - mean * mean, 0.f) + p.ln_eps);
+                const float a = valid ? rstd : 0.f, bsh = valid ? -mean * rstd : 0.f;
+#pragma unroll
+                for (int i = 0; i < 64; ++i) v[i] = fmaf(v[i], a, bsh);
+            }
+            // bf16 tile of this warp (32 rows x 64 columns) -> swizzled staging -> one TMA store
+#pragma unroll
+            for (int u = 0; u < 8; ++u) {
+                uint4 t;
+                t.x = pack_bf16x2(v[u * 8], v[u * 8 + 1]);
+                t.y = pack_bf16x2(v[u * 8 + 2], v[u * 8 + 3]);
+                t.z = pack_bf16x2(v[u * 8 + 4], v[u * 8 + 5]);
+                t.w = pack_bf16x2(v[u * 8 + 6], v[u * 8 + 7]);
+                *reinterpret_cast<uint4*>(stg + lane * 128 + ((u ^ (lane & 7)) << 4)) = t;
+            }
+            fence_proxy_async_smem();
             __syncwarp();
-            if (lane == 0) mbar_arrive(acc2_free);
-
-            float s = 0.f, ss = 0.f;
-#pragma unroll
-            for (int sc = 0; sc < 2; ++sc) {
-                const int nb = part * 64 + sc * 32;
-                float* w = v + sc * 32;
-#pragma unroll
-                for (int i = 0; i < 32; i += 4) {
-                    const float4 bb = ldg4(p.b2 + nb + i);
-                    w[i] += bb.x; w[i + 1] += bb.y; w[i + 2] += bb.z; w[i + 3] += bb.w;
-                }
-                add_rows_f32(c, p.hres, kC, nb, kC, w);
-                if (!c.valid) {
-#pragma unroll
-                    for (int i = 0; i < 32; ++i) w[i] = 0.f;
-                }
-                if (p.store_f32) store_rows_f32(c, p.hres, kC, nb, kC, w);
-#pragma unroll
-                for (int i = 0; i < 32; ++i) {
-                    s += w[i];
-                    ss += w[i] * w[i];
-                }
+            if (lane == 0 && live) {
+                tma_store_2d(&tmOut, stg, part * 64, tile * kGemmBM + quarter * 32);
+                tma_store_commit();
             }
-            if (p.ln_g != nullptr) {
-                const float2 t = group_exchange(c, make_float2(s, ss));
-                const float mean = t.x * (1.f / kC);
-                const float rstd = rsqrtf(fmaxf(t.y * (1.f / kC) - mean * mean, 0.f) + p.ln_eps);
-#pragma unroll
-                for (int i = 0; i < 64; i += 4) {
-                    const int n = part * 64 + i;
-                    const float4 g = ldg4(p.ln_g + n), bb = ldg4(p.ln_b + n);
-                    v[i] = c.valid ? (v[i] - mean) * rstd * g.x + bb.x : 0.f;
-                    v[i + 1] = c.valid ? (v[i + 1] - mean) * rstd * g.y + bb.y : 0.f;
-                    v[i + 2] = c.valid ? (v[i + 2] - mean) * rstd * g.z + bb.z : 0.f;
-                    v[i + 3] = c.valid ? (v[i + 3] - mean) * rstd * g.w + bb.w : 0.f;
-                }
-            }
-            // (the per-warp staging tile holds 32 rows x 64 B: two passes of 32 columns)
-            store_rows_bf16<32>(c, p.out_bf16, p.ldo, part * 64, kC, v);
-            store_rows_bf16<32>(c, p.out_bf16, p.ldo, part * 64 + 32, kC, v + 32);
-            // the staging tiles alias P[0]: every epilogue warp must be done with them before the next tile's E1
-            epi_sync_all();
+            FFN_STAMP(19);
         }
+        if (lane == 0) tma_store_wait_all();   // the global writes must be complete before the CTA exits
+#undef FFN_STAMP
     }
 
     tc_fence_before();
     __syncthreads();
+    cluster_sync_all();   // no CTA leaves while a peer may still multicast into it or arrive on its barriers
     if (warp == 1) tmem_dealloc(tmem_base, kTmemCols);
 }
 
@@ -367,22 +448,22 @@ cudaError_t ffn_tc_launch(const FfnProblem& f, int num_sms, cudaStream_t stream)
     p.num_tiles = f.M / kGemmBM;
     p.b1 = f.b1;
     p.b2 = f.b2;
-    p.ln_g = f.ln_g;
-    p.ln_b = f.ln_b;
+    p.ln = f.ln;
     p.row_seq = f.row_seq;
     p.hres = f.hres;
-    p.out_bf16 = f.out_bf16;
-    p.ldo = f.ldo;
     p.store_f32 = f.store_f32;
     p.ln_eps = f.ln_eps;
+    p.trace = f.trace;
 
-    CUtensorMap tX, tW1, tW2;
+    CUtensorMap tX, tW1, tW2, tOut;
     if (!encode_2d(&tX, f.x, kC, (uint64_t)f.M, kC, kGemmBM)) return cudaErrorInvalidValue;
     if (!encode_2d(&tW1, f.w1, kC, kHid, kC, kChunk)) return cudaErrorInvalidValue;
-    if (!encode_2d(&tW2, f.w2, kHid, kC, kHid, kC)) return cudaErrorInvalidValue;
+    if (!encode_2d(&tW2, f.w2, kHid, kC, kHid, kC / kCluster)) return cudaErrorInvalidValue;
+    if (!encode_2d(&tOut, f.out_bf16, kC, (uint64_t)f.M, (uint64_t)f.ldo, 32)) return cudaErrorInvalidValue;
 
-    const int grid = p.num_tiles < num_sms ? p.num_tiles : num_sms;
-    ffn_tc_kernel<<<grid, kThreads, kFfnSmem, stream>>>(tX, tW1, tW2, p);
+    int grid = (p.num_tiles + kCluster - 1) / kCluster * kCluster;
+    if (grid > num_sms) grid = num_sms / kCluster * kCluster;
+    ffn_tc_kernel<<<grid, kThreads, kFfnSmem, stream>>>(tX, tW1, tW2, tOut, p);
     return cudaGetLastError();
 }
 

@@ -50,6 +50,8 @@ struct GemmEpilogue {
     int32_t tbias_ld = 0;
     const float* resid = nullptr;      // fp32 [M, ldr] added after tbias
     int32_t ldr = 0;
+    int32_t f32_tiled = 0;             // resid and out_f32 use the lane-major tiled fp32 layout (tiled_f32_offset):
+                                       // thread == row accesses are coalesced without staging; needs ld == 256
     int32_t accum_f32 = 0;             // v += out_f32 (before scaling)
     float out_scale = 1.f;
     float* out_f32 = nullptr;          // fp32 [M, ldf]
@@ -59,6 +61,7 @@ struct GemmEpilogue {
     __nv_bfloat16* out_bf16_lo = nullptr;  // optional bf16 [M, ldo] remainder v - bf16(v) (split-bf16 operands)
     const float* ln2_g = nullptr;
     const float* ln2_b = nullptr;
+    int32_t ln2_plain = 0;             // second LayerNorm without affine (gamma / beta folded into the consumer's weights)
     int32_t act2 = ACT_NONE;
     float act2_p = 0.f;
     const float* act2_alpha = nullptr;
@@ -83,6 +86,13 @@ struct GemmProblem {
     GemmEpilogue epi;
 };
 
+// Lane-major tiled layout of an fp32 [M, 256] workspace matrix (M % 128 == 0): the float4 holding columns 4j..4j+3 of the
+// 128 rows of a tile are contiguous, so a warp whose lanes own consecutive rows reads / writes 512 contiguous bytes per
+// instruction.  Used for the fp32 residual stream, which only thread == row epilogues touch.
+__host__ __device__ inline size_t tiled_f32_offset(int64_t row, int col) {
+    return ((size_t)((row >> 7) * 64 + (col >> 2)) * 128 + (size_t)(row & 127)) * 4 + (size_t)(col & 3);
+}
+
 // Fused transformer feed-forward (ffn_tc.cu): hres += W2 gelu(W1 x + b1) + b2 ; out = LN(hres) or bf16(hres).
 struct FfnProblem {
     const __nv_bfloat16* x = nullptr;   // [M, 256] bf16 (normalised input)
@@ -91,14 +101,14 @@ struct FfnProblem {
     const float* b1 = nullptr;
     const __nv_bfloat16* w2 = nullptr;  // [256, 1024] K-major
     const float* b2 = nullptr;
-    float* hres = nullptr;              // [M, 256] fp32 residual stream, updated in place
+    float* hres = nullptr;              // [M, 256] fp32 residual stream (tiled_f32_offset layout), updated in place
     const int32_t* row_seq = nullptr;   // rows with id < 0 are forced to zero
-    const float* ln_g = nullptr;        // LayerNorm of the next block (nullptr: out = bf16(hres))
-    const float* ln_b = nullptr;
+    int32_t ln = 0;                     // 1: out = (hres - mean) * rstd (affine folded into the consumer); 0: out = bf16(hres)
     __nv_bfloat16* out_bf16 = nullptr;  // [M, ldo]
     int32_t ldo = 0;
     int32_t store_f32 = 1;              // 0: the fp32 stream is not needed afterwards
     float ln_eps = 1e-5f;
+    long long* trace = nullptr;         // developer aid (tests/test_ffn.cu): clock64 stamps of CTA 0
 };
 cudaError_t ffn_tc_launch(const FfnProblem& p, int num_sms, cudaStream_t stream);
 

@@ -73,10 +73,8 @@ __device__ __forceinline__ void epi_main(const EpiCtx& c, int cbeg, int cend, fl
         }
         if (W16 == 2) {
             if (e.resid) {
-                float r[32];
-                load_rows_f32(c, e.resid, e.ldr, nb, nlim, r);
-#pragma unroll
-                for (int i = 0; i < 32; ++i) v[i] += r[i];
+                if (e.f32_tiled) add_rows_f32_tiled(e.resid, c.row0 + c.lane, nb, v);
+                else add_rows_f32(c, e.resid, e.ldr, nb, nlim, v);
             }
             if (e.accum_f32) {
                 float r[32];
@@ -95,8 +93,11 @@ __device__ __forceinline__ void epi_main(const EpiCtx& c, int cbeg, int cend, fl
             for (int i = 0; i < NV; ++i) v[i] = 0.f;
         }
         if (W16 == 2) {
-            if (e.out_f32) store_rows_f32(c, e.out_f32, e.ldf, nb, nlim, v);
-            if (e.ln2_g) {
+            if (e.out_f32) {
+                if (e.f32_tiled) store_rows_f32_tiled(e.out_f32, c.row0 + c.lane, nb, v);
+                else store_rows_f32(c, e.out_f32, e.ldf, nb, nlim, v);
+            }
+            if (e.ln2_g || e.ln2_plain) {
 #pragma unroll
                 for (int i = 0; i < NV; ++i) {
                     s2 += v[i];
@@ -287,7 +288,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
             acc ^= 1;
             if (acc == 0) accphase ^= 1;
 
-            if (e.ln2_g != nullptr) {  // second LayerNorm on the fp32 value just stored -> bf16 operand of the next GEMM
+            if (e.ln2_g != nullptr || e.ln2_plain) {  // second LayerNorm on the fp32 value just stored -> bf16 operand of the next GEMM
                 const float2 t = group_exchange(c, make_float2(s2, ss2));
                 const float mean2 = t.x / (float)p.BN;
                 const float rstd2 = rsqrtf(fmaxf(t.y / (float)p.BN - mean2 * mean2, 0.f) + e.ln_eps);
@@ -295,14 +296,21 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
                     const int nb = c.n0 + cc * 16;
                     const int nlim = min(p.N, nb + min(2, cend - cc) * 16);
                     float v[32];
-                    load_rows_f32(c, e.out_f32, e.ldf, nb, nlim, v);
+                    if (e.f32_tiled) load_rows_f32_tiled(e.out_f32, c.row0 + c.lane, nb, v);
+                    else load_rows_f32(c, e.out_f32, e.ldf, nb, nlim, v);
+                    if (e.ln2_plain) {
+                        const float a = c.valid ? rstd2 : 0.f, b = c.valid ? -mean2 * rstd2 : 0.f;
 #pragma unroll
-                    for (int i = 0; i < 32; i += 4) {
-                        const float4 g = ldg4(e.ln2_g + nb + i), b = ldg4(e.ln2_b + nb + i);
-                        v[i] = c.valid ? (v[i] - mean2) * rstd2 * g.x + b.x : 0.f;
-                        v[i + 1] = c.valid ? (v[i + 1] - mean2) * rstd2 * g.y + b.y : 0.f;
-                        v[i + 2] = c.valid ? (v[i + 2] - mean2) * rstd2 * g.z + b.z : 0.f;
-                        v[i + 3] = c.valid ? (v[i + 3] - mean2) * rstd2 * g.w + b.w : 0.f;
+                        for (int i = 0; i < 32; ++i) v[i] = fmaf(v[i], a, b);
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < 32; i += 4) {
+                            const float4 g = ldg4(e.ln2_g + nb + i), b = ldg4(e.ln2_b + nb + i);
+                            v[i] = c.valid ? (v[i] - mean2) * rstd2 * g.x + b.x : 0.f;
+                            v[i + 1] = c.valid ? (v[i + 1] - mean2) * rstd2 * g.y + b.y : 0.f;
+                            v[i + 2] = c.valid ? (v[i + 2] - mean2) * rstd2 * g.z + b.z : 0.f;
+                            v[i + 3] = c.valid ? (v[i + 3] - mean2) * rstd2 * g.w + b.w : 0.f;
+                        }
                     }
                     store_rows_bf16<32>(c, e.out_bf16, e.ldo, nb, nlim, v);
                 }
@@ -359,7 +367,10 @@ cudaError_t gemm_tc_launch(const GemmProblem& g, int num_sms, cudaStream_t strea
         g.num_segs > kGemmMaxSegs)
         return cudaErrorInvalidValue;
     if (g.epi.ln1_g && g.BN != g.N) return cudaErrorInvalidValue;
-    if (g.epi.ln2_g && (g.BN != g.N || g.epi.accum_f32)) return cudaErrorInvalidValue;
+    if ((g.epi.ln2_g || g.epi.ln2_plain) && (g.BN != g.N || g.epi.accum_f32)) return cudaErrorInvalidValue;
+    if (g.epi.f32_tiled && (g.N != 256 || g.BN != 256 || g.epi.accum_f32 || (g.epi.resid && g.epi.ldr != 256) ||
+                            (g.epi.out_f32 && g.epi.ldf != 256)))
+        return cudaErrorInvalidValue;
 
     static std::once_flag attr_once;
     static cudaError_t attr_err = cudaSuccess;

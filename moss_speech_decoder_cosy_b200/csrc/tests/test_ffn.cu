@@ -65,14 +65,23 @@ static int run(int M, bool ln, bool store_f32, int ldo, int num_sms, int grid_ca
     CK(cudaMemcpy(db2, b2.data(), C * 4, cudaMemcpyHostToDevice));
     CK(cudaMemcpy(dg, g.data(), C * 4, cudaMemcpyHostToDevice));
     CK(cudaMemcpy(dbt, bt.data(), C * 4, cudaMemcpyHostToDevice));
-    CK(cudaMemcpy(dh, hres.data(), hres.size() * 4, cudaMemcpyHostToDevice));
+    {   // the kernel keeps the residual stream in the lane-major tiled layout
+        std::vector<float> ht(hres.size());
+        for (int r = 0; r < M; ++r)
+            for (int n = 0; n < C; ++n) ht[tiled_f32_offset(r, n)] = hres[(size_t)r * C + n];
+        CK(cudaMemcpy(dh, ht.data(), ht.size() * 4, cudaMemcpyHostToDevice));
+    }
     CK(cudaMemcpy(drs, rs.data(), M * 4, cudaMemcpyHostToDevice));
     CK(cudaMemset(dout, 0xff, (size_t)M * ldo * 2));
 
     FfnProblem f;
     f.x = dx; f.M = M; f.w1 = dw1; f.b1 = db1; f.w2 = dw2; f.b2 = db2; f.hres = dh; f.row_seq = drs;
-    f.ln_g = ln ? dg : nullptr; f.ln_b = ln ? dbt : nullptr;
+    f.ln = ln ? 1 : 0;
     f.out_bf16 = dout; f.ldo = ldo; f.store_f32 = store_f32;
+    long long* dtrace = nullptr;
+    CK(cudaMalloc(&dtrace, 48 * 8 * 8));
+    CK(cudaMemset(dtrace, 0, 48 * 8 * 8));
+    if (getenv("FFN_TRACE")) f.trace = dtrace;
     cudaEvent_t e0, e1;
     cudaEventCreate(&e0);
     cudaEventCreate(&e1);
@@ -83,6 +92,20 @@ static int run(int M, bool ln, bool store_f32, int ldo, int num_sms, int grid_ca
     float ms = 0;
     cudaEventElapsedTime(&ms, e0, e1);
 
+    if (f.trace && M / 128 > 148 * 2) {
+        std::vector<long long> tr(48 * 8);
+        CK(cudaMemcpy(tr.data(), dtrace, tr.size() * 8, cudaMemcpyDeviceToHost));
+        for (int it = 1; it < 3; ++it) {
+            const long long t0 = tr[it * 48];
+            printf("  tile it=%d epilogue warp: preload_done %lld |", it, tr[it * 48 + 1] - t0);
+            for (int h = 0; h < 8; ++h) printf(" E1[%d] wake %lld done %lld |", h, tr[it * 48 + 2 + 2 * h] - t0, tr[it * 48 + 3 + 2 * h] - t0);
+            printf(" acc2_full %lld stored %lld\n", tr[it * 48 + 18] - t0, tr[it * 48 + 19] - t0);
+            printf("  tile it=%d MMA thread: x_full %lld |", it, tr[it * 48 + 32] - t0);
+            for (int h = 0; h < 8; ++h) printf(" p_ready[%d] %lld |", h, tr[it * 48 + 33 + h] - t0);
+            printf(" issued_all %lld | waited on weights %lld, on p_ready %lld\n", tr[it * 48 + 41] - t0, tr[it * 48 + 42], tr[it * 48 + 43]);
+        }
+    }
+    cudaFree(dtrace);
     std::vector<float> oh(hres.size());
     std::vector<__nv_bfloat16> ob((size_t)M * ldo);
     CK(cudaMemcpy(oh.data(), dh, oh.size() * 4, cudaMemcpyDeviceToHost));
@@ -112,8 +135,8 @@ static int run(int M, bool ln, bool store_f32, int ldo, int num_sms, int grid_ca
         for (int n = 0; n < C; ++n) var += (y[n] - mean) * (y[n] - mean);
         var /= C;
         for (int n = 0; n < C; ++n) {
-            if (store_f32) max_f = fmax(max_f, fabs(oh[(size_t)r * C + n] - y[n]));
-            double want = ln ? (valid ? (y[n] - mean) / sqrt(var + 1e-5) * g[n] + bt[n] : 0.0) : y[n];
+            if (store_f32) max_f = fmax(max_f, fabs(oh[tiled_f32_offset(r, n)] - y[n]));
+            double want = ln ? (valid ? (y[n] - mean) / sqrt(var + 1e-5) : 0.0) : y[n];
             double got = __bfloat162float(ob[(size_t)r * ldo + n]);
             max_b = fmax(max_b, fabs(got - want) / (1.0 + fabs(want)));
         }

@@ -5,7 +5,9 @@ Layouts produced (all CPU tensors; bf16 for tensor-core operands, fp32 for biase
   conv k taps, Cin -> Cout     : bf16 [Cout, k * Cin_pad], K index = tap * Cin_pad + c, Cin_pad = ceil64(Cin)
                                  (one 64-wide k-block never straddles two taps; extra columns are zero)
   Linear                        : bf16 [out, in]
-  q|k|v                         : bf16 [3 * 512, 256], q rows pre-multiplied by 1/sqrt(head_dim) (exact: 1/8)
+  q|k|v                         : bf16 [3 * 512, 256], q rows pre-multiplied by 1/sqrt(head_dim) (exact: 1/8), columns
+                                 scaled by norm1's gamma; bias = W . beta (the LayerNorm affine is folded; same for
+                                 norm3 into ff1)
   ConvTranspose1d(stride s)     : bf16 [s * Cout, 3 * Cin]: row r * Cout + co, column (d + 1) * Cin + ci holds
                                  w[ci, co, r + p - s * d] for input offset d in {-1, 0, +1} (zero where the tap does
                                  not exist), so out[s * q + r] = sum_d x[q + d] . W_r,d    (polyphase form)
@@ -94,16 +96,19 @@ def pack_estimator(sd, prefix="decoder.estimator.", n_mid=12, n_blocks=4, head_d
         for j in range(n_blocks):
             t = f"{gp}.1.{j}."
             o = f"est.tf{gi}.{j}."
-            out[o + "n1.g"] = _f32(g(t + "norm1.weight"))
-            out[o + "n1.b"] = _f32(g(t + "norm1.bias"))
+            # The affine part of norm1 / norm3 is folded into the Linear that consumes the normalised activation
+            # (W . (g * n + b) = (W diag g) . n + W . b), so the kernels' LayerNorm epilogues only normalise.
+            n1g, n1b = g(t + "norm1.weight"), g(t + "norm1.bias")
+            n3g, n3b = g(t + "norm3.weight"), g(t + "norm3.bias")
             q = g(t + "attn1.to_q.weight") * (1.0 / math.sqrt(head_dim))
-            out[o + "qkv.w"] = _bf16(torch.cat([q, g(t + "attn1.to_k.weight"), g(t + "attn1.to_v.weight")], 0))
+            wqkv = torch.cat([q, g(t + "attn1.to_k.weight"), g(t + "attn1.to_v.weight")], 0)
+            out[o + "qkv.w"] = _bf16(wqkv * n1g[None, :])
+            out[o + "qkv.b"] = _f32(wqkv @ n1b)
             out[o + "o.w"] = _bf16(g(t + "attn1.to_out.0.weight"))
             out[o + "o.b"] = _f32(g(t + "attn1.to_out.0.bias"))
-            out[o + "n3.g"] = _f32(g(t + "norm3.weight"))
-            out[o + "n3.b"] = _f32(g(t + "norm3.bias"))
-            out[o + "ff1.w"] = _bf16(g(t + "ff.net.0.proj.weight"))
-            out[o + "ff1.b"] = _f32(g(t + "ff.net.0.proj.bias"))
+            w1 = g(t + "ff.net.0.proj.weight")
+            out[o + "ff1.w"] = _bf16(w1 * n3g[None, :])
+            out[o + "ff1.b"] = _f32(g(t + "ff.net.0.proj.bias") + w1 @ n3b)
             out[o + "ff2.w"] = _bf16(g(t + "ff.net.2.weight"))
             out[o + "ff2.b"] = _f32(g(t + "ff.net.2.bias"))
     out["est.tbias.w"] = _f32(torch.cat(tb_w, 0))
