@@ -127,9 +127,74 @@ __device__ __forceinline__ void epi_main(const EpiCtx& c, int cbeg, int cend, fl
     }
 }
 
+// ---- fast path for "bias + activation + mask -> bf16" tiles (q|k|v projection, most vocoder convs): no LayerNorm, no
+// fp32 traffic.  Each epilogue warp owns 32 rows x (BN / 4) columns; the TMEM drain of the second 32-column half is in
+// flight while the first goes through the math, and the bf16 tile leaves through a 64B-swizzled 2 KB staging tile and
+// one TMA store per half (no LDS / STG / predicates; TMA clips the M / N tails).
+__device__ __forceinline__ void epi_fast_half(const EpiCtx& c, const CUtensorMap* tmOut, float* v, int n) {
+    const GemmEpilogue& e = c.p->epi;
+    if (e.bias) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const float4 b = ldg4(e.bias + n + 4 * i);
+            v[4 * i] += b.x; v[4 * i + 1] += b.y; v[4 * i + 2] += b.z; v[4 * i + 3] += b.w;
+        }
+    }
+    apply_act_vec<16>(v, e.act1, e.act1_p, e.act1_alpha ? e.act1_alpha + n : nullptr);
+    apply_act_vec<16>(v + 16, e.act1, e.act1_p, e.act1_alpha ? e.act1_alpha + n + 16 : nullptr);
+    if (!c.valid) {
+#pragma unroll
+        for (int i = 0; i < 32; ++i) v[i] = 0.f;
+    }
+    // the previous TMA store of this warp must have finished reading the staging tile
+    if (c.lane == 0) tma_store_wait_read();
+    __syncwarp();
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+        uint4 t;
+        t.x = pack_bf16x2(v[u * 8], v[u * 8 + 1]);
+        t.y = pack_bf16x2(v[u * 8 + 2], v[u * 8 + 3]);
+        t.z = pack_bf16x2(v[u * 8 + 4], v[u * 8 + 5]);
+        t.w = pack_bf16x2(v[u * 8 + 6], v[u * 8 + 7]);
+        // 64B swizzle: 16-byte unit index XOR bits [7, 9) of the byte offset (= (row >> 1) & 3)
+        *reinterpret_cast<uint4*>(c.stg + c.lane * 64 + ((u ^ ((c.lane >> 1) & 3)) << 4)) = t;
+    }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    __syncwarp();
+    if (c.lane == 0) {
+        tma_store_2d(tmOut, c.stg, n, c.row0);
+        tma_store_commit();
+    }
+}
+
+// returns after the last TMEM read of the tile; the caller hands the accumulator back to the MMA warp
+__device__ __forceinline__ void epi_fast(const EpiCtx& c, const CUtensorMap* tmOut, int part, uint64_t* tempty_bar) {
+    const KParams& p = *c.p;
+    const int wcols = p.BN >> 2;            // 64 or 32 columns per warp
+    const int col0 = part * wcols;          // inside the tile
+    const int n = c.n0 + col0;
+    float va[32], vb[32];
+    tmem_ld16(c.taddr + (uint32_t)col0, va);
+    tmem_ld16(c.taddr + (uint32_t)(col0 + 16), va + 16);
+    tmem_ld_wait();
+    if (wcols == 64) {
+        tmem_ld16(c.taddr + (uint32_t)(col0 + 32), vb);
+        tmem_ld16(c.taddr + (uint32_t)(col0 + 48), vb + 16);
+        epi_fast_half(c, tmOut, va, n);
+        tmem_ld_wait();
+    }
+    tc_fence_before();
+    __syncwarp();
+    if (c.lane == 0) mbar_arrive(tempty_bar);
+    if (wcols == 64) epi_fast_half(c, tmOut, vb, n + 32);
+    else epi_fast_half(c, tmOut, va, n);
+}
+
+template <bool kFast>
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__ CUtensorMap tmA1,
-               const __grid_constant__ CUtensorMap tmB, const __grid_constant__ KParams p) {
+               const __grid_constant__ CUtensorMap tmB, const __grid_constant__ CUtensorMap tmOut,
+               const __grid_constant__ KParams p) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);  // stays in the shared address space (STS / LDS)
     uint8_t* sA = smem;
@@ -149,6 +214,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
         tma_prefetch_desc(&tmA0);
         tma_prefetch_desc(&tmA1);
         tma_prefetch_desc(&tmB);
+        if (kFast) tma_prefetch_desc(&tmOut);
         for (int i = 0; i < kGemmStages; ++i) {
             mbar_init(&full[i], 1);
             mbar_init(&empty[i], 1);
@@ -258,6 +324,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
             tc_fence_after();
             c.taddr = tmem_base + ((uint32_t)(c.quarter * 32) << 16) + (uint32_t)acc * 256u;
 
+            if constexpr (kFast) {
+                epi_fast(c, &tmOut, part, &tempty[acc]);
+                acc ^= 1;
+                if (acc == 0) accphase ^= 1;
+                continue;
+            } else {
             float mean1 = 0.f, rstd1 = 1.f;
             if (e.ln1_g != nullptr) {  // LayerNorm over the whole row (N == BN): statistics of acc + bias
                 float s = 0.f, ss = 0.f;
@@ -315,9 +387,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
                     store_rows_bf16<32>(c, e.out_bf16, e.ldo, nb, nlim, v);
                 }
             }
+            }  // !kFast
         }
     }
 
+    if (kFast && warp >= 2 && lane == 0) tma_store_wait_all();
     tc_fence_before();
     __syncthreads();
     if (warp == 1) tmem_dealloc(tmem_base, kTmemCols);
@@ -362,6 +436,26 @@ bool encode_2d(CUtensorMap* m, const void* ptr, uint64_t cols, uint64_t rows, ui
     return true;
 }
 
+// general form: box {box_cols, box_rows}; swizzle 0 = 128B, 1 = 64B
+bool encode_2d_ex(CUtensorMap* m, const void* ptr, uint64_t cols, uint64_t rows, uint64_t ld, uint32_t box_cols,
+                  uint32_t box_rows, int swizzle64) {
+    EncodeTiledFn fn = get_encode_fn();
+    if (!fn) return false;
+    cuuint64_t dims[2] = {cols, rows};
+    cuuint64_t strides[1] = {ld * 2};
+    cuuint32_t box[2] = {box_cols, box_rows};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B,
+                    CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        fprintf(stderr, "[mossdec] cuTensorMapEncodeTiled (store map) failed: %d (ptr=%p cols=%llu rows=%llu ld=%llu)\n",
+                (int)r, ptr, (unsigned long long)cols, (unsigned long long)rows, (unsigned long long)ld);
+        return false;
+    }
+    return true;
+}
+
 cudaError_t gemm_tc_launch(const GemmProblem& g, int num_sms, cudaStream_t stream) {
     if (g.M <= 0 || g.N <= 0 || g.BN < 16 || g.BN > 256 || (g.BN % 16) != 0 || g.num_segs < 1 ||
         g.num_segs > kGemmMaxSegs)
@@ -375,7 +469,9 @@ cudaError_t gemm_tc_launch(const GemmProblem& g, int num_sms, cudaStream_t strea
     static std::once_flag attr_once;
     static cudaError_t attr_err = cudaSuccess;
     std::call_once(attr_once, [] {
-        attr_err = cudaFuncSetAttribute(gemm_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
+        attr_err = cudaFuncSetAttribute(gemm_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
+        if (attr_err == cudaSuccess)
+            attr_err = cudaFuncSetAttribute(gemm_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
     });
     if (attr_err != cudaSuccess) return attr_err;
 
@@ -406,8 +502,19 @@ cudaError_t gemm_tc_launch(const GemmProblem& g, int num_sms, cudaStream_t strea
     const uint64_t K = (uint64_t)kp.total_kb * kGemmBK;
     if (!encode_2d(&tB, g.w, K, (uint64_t)g.N, K, (uint32_t)g.BN)) return cudaErrorInvalidValue;
 
+    // "bias + activation + mask -> bf16" epilogues leave through TMA stores (epi_fast)
+    const GemmEpilogue& e = g.epi;
+    kp.fast_bf16 = e.out_bf16 != nullptr && !e.out_f32 && !e.resid && !e.ln1_g && !e.ln2_g && !e.ln2_plain && !e.tbias &&
+                   !e.out_bf16_lo && !e.accum_f32 && e.act2 == ACT_NONE && e.out_scale == 1.f &&
+                   (g.BN == 256 || g.BN == 128) && (g.N % g.BN) == 0 && (e.ldo % 8) == 0 &&
+                   (reinterpret_cast<uintptr_t>(e.out_bf16) & 15) == 0;
+    CUtensorMap tOut = tB;
+    if (kp.fast_bf16 && !encode_2d_ex(&tOut, e.out_bf16, (uint64_t)g.N, (uint64_t)g.M, (uint64_t)e.ldo, 32, 32, 1))
+        return cudaErrorInvalidValue;
+
     const int grid = kp.num_tiles < num_sms ? kp.num_tiles : num_sms;
-    gemm_tc_kernel<<<grid, kThreads, kSmemBytes, stream>>>(tA0, tA1, tB, kp);
+    if (kp.fast_bf16) gemm_tc_kernel<true><<<grid, kThreads, kSmemBytes, stream>>>(tA0, tA1, tB, tOut, kp);
+    else gemm_tc_kernel<false><<<grid, kThreads, kSmemBytes, stream>>>(tA0, tA1, tB, tOut, kp);
     return cudaGetLastError();
 }
 

@@ -296,6 +296,10 @@ int main() {
         Case c = base("n32_elu", 777, 32, 32, 64); c.act1 = ACT_ELU;
         fails += run_case(c, sms);
     }
+    {   // 13. TMA-store epilogue with two warps per 64 columns (BN = 128), snake, masked rows, ragged M
+        Case c = base("n128_snake_tma_store", 3001, 256, 128, 192); c.act1 = ACT_SNAKE; c.rowseq = true;
+        fails += run_case(c, sms);
+    }
     printf("%s (%d failing)\n", fails ? "SOME TESTS FAILED" : "ALL TESTS PASSED", fails);
     return fails ? 1 : 0;
 }
