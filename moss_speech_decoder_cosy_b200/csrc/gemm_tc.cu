@@ -190,7 +190,86 @@ __device__ __forceinline__ void epi_fast(const EpiCtx& c, const CUtensorMap* tmO
     else epi_fast_half(c, tmOut, va, n);
 }
 
-template <bool kFast>
+// ---- "bias + fp32 residual (tiled layout) -> fp32 stream + LayerNorm (affine folded away) -> bf16" tiles: the attention
+// out-projection.  N == BN == 256; each warp owns 32 rows x 64 columns.  The residual loads are issued BEFORE the wait for
+// the accumulator (they do not depend on the MMA), so their latency hides behind the tile's MMAs; the TMEM drain is
+// pipelined 16 columns at a time into the same registers; the bf16 tile leaves through two TMA stores.
+__device__ __forceinline__ void epi_resln(const EpiCtx& c, const CUtensorMap* tmOut, int part, uint32_t tmem_acc,
+                                          uint64_t* tfull_bar, uint32_t tfull_phase, uint64_t* tempty_bar) {
+    const KParams& p = *c.p;
+    const GemmEpilogue& e = p.epi;
+    const int row = c.row0 + c.lane;
+    const int n = part * 64;
+    float v[64];
+    {
+        const float* q = e.resid + tiled_f32_offset(row, n);
+#pragma unroll
+        for (int u = 0; u < 16; ++u) {
+            const float4 t = *reinterpret_cast<const float4*>(q + (size_t)u * 512);
+            const float4 b = e.bias ? ldg4(e.bias + n + 4 * u) : make_float4(0.f, 0.f, 0.f, 0.f);
+            v[4 * u] = t.x + b.x; v[4 * u + 1] = t.y + b.y; v[4 * u + 2] = t.z + b.z; v[4 * u + 3] = t.w + b.w;
+        }
+    }
+    mbar_wait(tfull_bar, tfull_phase);
+    tc_fence_after();
+    const uint32_t ta = tmem_acc + (uint32_t)n;
+    float s = 0.f, ss = 0.f;
+    float t0[16], t1[16];
+    tmem_ld16(ta, t0);
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+        float* t = (q & 1) ? t1 : t0;
+        tmem_ld_wait();
+        if (q < 3) tmem_ld16(ta + (q + 1) * 16, (q & 1) ? t0 : t1);
+        if (q == 3) {   // accumulator fully read: hand it back to the MMA warp
+            tc_fence_before();
+            __syncwarp();
+            if (c.lane == 0) mbar_arrive(tempty_bar);
+        }
+        float* w = v + q * 16;
+#pragma unroll
+        for (int i = 0; i < 16; ++i) w[i] = c.valid ? w[i] + t[i] : 0.f;
+        float* dst = e.out_f32 + tiled_f32_offset(row, n + q * 16);
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+            *reinterpret_cast<float4*>(dst + (size_t)u * 512) = make_float4(w[4 * u], w[4 * u + 1], w[4 * u + 2], w[4 * u + 3]);
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+            s += w[i];
+            ss = fmaf(w[i], w[i], ss);
+        }
+    }
+    if (c.lane == 0) tma_store_wait_read();   // the exchange slot is the head of the staging tile the last store read
+    __syncwarp();
+    const float2 tot = group_exchange(c, make_float2(s, ss));
+    const float mean = tot.x * (1.f / 256.f);
+    const float rstd = rsqrtf(fmaxf(tot.y * (1.f / 256.f) - mean * mean, 0.f) + e.ln_eps);
+    const float a = c.valid ? rstd : 0.f, bsh = c.valid ? -mean * rstd : 0.f;
+#pragma unroll
+    for (int hlf = 0; hlf < 2; ++hlf) {
+        float* w = v + hlf * 32;
+        if (c.lane == 0) tma_store_wait_read();
+        __syncwarp();
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            uint4 t;
+            t.x = pack_bf16x2(fmaf(w[u * 8], a, bsh), fmaf(w[u * 8 + 1], a, bsh));
+            t.y = pack_bf16x2(fmaf(w[u * 8 + 2], a, bsh), fmaf(w[u * 8 + 3], a, bsh));
+            t.z = pack_bf16x2(fmaf(w[u * 8 + 4], a, bsh), fmaf(w[u * 8 + 5], a, bsh));
+            t.w = pack_bf16x2(fmaf(w[u * 8 + 6], a, bsh), fmaf(w[u * 8 + 7], a, bsh));
+            *reinterpret_cast<uint4*>(c.stg + c.lane * 64 + ((u ^ ((c.lane >> 1) & 3)) << 4)) = t;
+        }
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        __syncwarp();
+        if (c.lane == 0) {
+            tma_store_2d(tmOut, c.stg, n + hlf * 32, c.row0);
+            tma_store_commit();
+        }
+    }
+}
+
+// kMode: 0 = general epilogue, 1 = epi_fast (bias + act -> bf16), 2 = epi_resln (residual + LayerNorm)
+template <int kMode>
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__ CUtensorMap tmA1,
                const __grid_constant__ CUtensorMap tmB, const __grid_constant__ CUtensorMap tmOut,
@@ -214,7 +293,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
         tma_prefetch_desc(&tmA0);
         tma_prefetch_desc(&tmA1);
         tma_prefetch_desc(&tmB);
-        if (kFast) tma_prefetch_desc(&tmOut);
+        if (kMode != 0) tma_prefetch_desc(&tmOut);
         for (int i = 0; i < kGemmStages; ++i) {
             mbar_init(&full[i], 1);
             mbar_init(&empty[i], 1);
@@ -320,11 +399,17 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
             if (e.row_seq != nullptr && inb) c.seq = __ldg(e.row_seq + row);
             c.valid = inb && c.seq >= 0;
 
+            c.taddr = tmem_base + ((uint32_t)(c.quarter * 32) << 16) + (uint32_t)acc * 256u;
+            if constexpr (kMode == 2) {
+                epi_resln(c, &tmOut, part, c.taddr, &tfull[acc], accphase, &tempty[acc]);
+                acc ^= 1;
+                if (acc == 0) accphase ^= 1;
+                continue;
+            }
             mbar_wait(&tfull[acc], accphase);
             tc_fence_after();
-            c.taddr = tmem_base + ((uint32_t)(c.quarter * 32) << 16) + (uint32_t)acc * 256u;
 
-            if constexpr (kFast) {
+            if constexpr (kMode == 1) {
                 epi_fast(c, &tmOut, part, &tempty[acc]);
                 acc ^= 1;
                 if (acc == 0) accphase ^= 1;
@@ -387,11 +472,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
                     store_rows_bf16<32>(c, e.out_bf16, e.ldo, nb, nlim, v);
                 }
             }
-            }  // !kFast
+            }  // kMode == 0
         }
     }
 
-    if (kFast && warp >= 2 && lane == 0) tma_store_wait_all();
+    if (kMode != 0 && warp >= 2 && lane == 0) tma_store_wait_all();
     tc_fence_before();
     __syncthreads();
     if (warp == 1) tmem_dealloc(tmem_base, kTmemCols);
@@ -469,9 +554,11 @@ cudaError_t gemm_tc_launch(const GemmProblem& g, int num_sms, cudaStream_t strea
     static std::once_flag attr_once;
     static cudaError_t attr_err = cudaSuccess;
     std::call_once(attr_once, [] {
-        attr_err = cudaFuncSetAttribute(gemm_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
+        attr_err = cudaFuncSetAttribute(gemm_tc_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
         if (attr_err == cudaSuccess)
-            attr_err = cudaFuncSetAttribute(gemm_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
+            attr_err = cudaFuncSetAttribute(gemm_tc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
+        if (attr_err == cudaSuccess)
+            attr_err = cudaFuncSetAttribute(gemm_tc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
     });
     if (attr_err != cudaSuccess) return attr_err;
 
@@ -508,13 +595,19 @@ cudaError_t gemm_tc_launch(const GemmProblem& g, int num_sms, cudaStream_t strea
                    !e.out_bf16_lo && !e.accum_f32 && e.act2 == ACT_NONE && e.out_scale == 1.f &&
                    (g.BN == 256 || g.BN == 128) && (g.N % g.BN) == 0 && (e.ldo % 8) == 0 &&
                    (reinterpret_cast<uintptr_t>(e.out_bf16) & 15) == 0;
+    // residual + LayerNorm epilogue of the attention out-projection (epi_resln)
+    const bool resln = e.out_bf16 != nullptr && e.out_f32 != nullptr && e.resid != nullptr && e.f32_tiled && e.ln2_plain &&
+                       !e.ln1_g && !e.ln2_g && !e.tbias && !e.out_bf16_lo && !e.accum_f32 && e.act1 == ACT_NONE &&
+                       e.act2 == ACT_NONE && e.out_scale == 1.f && g.BN == 256 && g.N == 256 && (g.M % kGemmBM) == 0 &&
+                       (e.ldo % 8) == 0 && (reinterpret_cast<uintptr_t>(e.out_bf16) & 15) == 0;
     CUtensorMap tOut = tB;
-    if (kp.fast_bf16 && !encode_2d_ex(&tOut, e.out_bf16, (uint64_t)g.N, (uint64_t)g.M, (uint64_t)e.ldo, 32, 32, 1))
+    if ((kp.fast_bf16 || resln) && !encode_2d_ex(&tOut, e.out_bf16, (uint64_t)g.N, (uint64_t)g.M, (uint64_t)e.ldo, 32, 32, 1))
         return cudaErrorInvalidValue;
 
     const int grid = kp.num_tiles < num_sms ? kp.num_tiles : num_sms;
-    if (kp.fast_bf16) gemm_tc_kernel<true><<<grid, kThreads, kSmemBytes, stream>>>(tA0, tA1, tB, tOut, kp);
-    else gemm_tc_kernel<false><<<grid, kThreads, kSmemBytes, stream>>>(tA0, tA1, tB, tOut, kp);
+    if (resln) gemm_tc_kernel<2><<<grid, kThreads, kSmemBytes, stream>>>(tA0, tA1, tB, tOut, kp);
+    else if (kp.fast_bf16) gemm_tc_kernel<1><<<grid, kThreads, kSmemBytes, stream>>>(tA0, tA1, tB, tOut, kp);
+    else gemm_tc_kernel<0><<<grid, kThreads, kSmemBytes, stream>>>(tA0, tA1, tB, tOut, kp);
     return cudaGetLastError();
 }
 
