@@ -5,10 +5,11 @@
 //
 // One CTA = 128 queries of one (sequence, head); keys/values stream through in tiles of 64:
 //   S = Q K^T      tcgen05.mma  M128 N64 K64  (Q, K tiles K-major in smem via TMA, 128B swizzle)      -> TMEM cols 0..63
-//   P = softmax    4 warps, thread == query row: tcgen05.ld, predicate mask, online max / exp2 / sum   -> smem (bf16, A operand)
-//   O_j = P V      tcgen05.mma  M128 N64 K64  (V tile as MN-major B operand: rows = keys, 64 dims contiguous) -> TMEM cols 64..127
-//   O   = O * corr + O_j in registers (fp32), normalised and stored as bf16 at the end.
-// Everything inside a CTA is sequential; 3 CTAs per SM overlap each other's TMA / MMA / softmax phases.  With head_dim
+//   P = softmax    4 warps, thread == query row: tcgen05.ld, predicate mask, online max / exp2 / sum   -> tcgen05.st over S (bf16, A operand from TMEM)
+//   O  += P V      tcgen05.mma  M128 N64 K64  (V tile as MN-major B operand: rows = keys, 64 dims contiguous) -> TMEM cols 64..127,
+//                  accumulated in TMEM over all key tiles; rescaled (tcgen05.ld / .st) only when a row maximum grows by more
+//                  than 2^8 (lazy rescaling), normalised and stored as bf16 at the end.
+// Everything inside a CTA is sequential; 4 CTAs per SM overlap each other's TMA / MMA / softmax phases.  With head_dim
 // 64 the kernel is bound by the exp2 throughput of the SFUs (16 / clk / SM), not by the tensor pipe.
 #include "kernels.h"
 #include "ptx.cuh"
@@ -23,7 +24,7 @@ constexpr int kBQ = 128, kBK = 64, kD = 64;
 constexpr int kQBytes = kBQ * kD * 2;   // 16 KB
 constexpr int kKVBytes = kBK * kD * 2;  // 8 KB
 constexpr int kPBytes = kBQ * kBK * 2;  // 16 KB
-constexpr int kSmem = kQBytes + 4 * kKVBytes + kPBytes + 1024 + 128;
+constexpr int kSmem = kQBytes + 4 * kKVBytes + 1024 + 128;
 
 // B operand stored MN-major (rows = K index, 64 N-elements = 128 bytes contiguous per row), 128B swizzle:
 // 8 K-rows form one 1024-byte swizzle atom, consecutive atoms along K are SBO = 1024 bytes apart.
@@ -38,7 +39,7 @@ __device__ __forceinline__ uint64_t umma_desc_mn_sw128(uint32_t smem_addr) {
 }
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
-__global__ void __launch_bounds__(128, 3)
+__global__ void __launch_bounds__(128, 4)
 attention_tc_kernel(const __grid_constant__ CUtensorMap tm, __nv_bfloat16* __restrict__ out,
                     const int32_t* __restrict__ seq_start, const int32_t* __restrict__ seq_len, int heads, int chunk) {
     const int s = blockIdx.z, h = blockIdx.y;
@@ -52,20 +53,22 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tm, __nv_bfloat16* __res
     uint8_t* sQ = smem;
     uint8_t* sK = sQ + kQBytes;           // [2][8 KB]
     uint8_t* sV = sK + 2 * kKVBytes;      // [2][8 KB]
-    uint8_t* sP = sV + 2 * kKVBytes;      // 16 KB
-    uint64_t* bars = reinterpret_cast<uint64_t*>(sP + kPBytes);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(sV + 2 * kKVBytes);
     uint64_t* bar_q = bars;
-    uint64_t* bar_kv = bars + 1;  // [2]
-    uint64_t* bar_s = bars + 3;
-    uint64_t* bar_o = bars + 4;
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 5);
+    uint64_t* bar_k = bars + 1;  // [2]
+    uint64_t* bar_v = bars + 3;  // [2]
+    uint64_t* bar_s = bars + 5;
+    uint64_t* bar_o = bars + 6;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 7);
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     if (tid == 0) {
         tma_prefetch_desc(&tm);
         mbar_init(bar_q, 1);
-        mbar_init(&bar_kv[0], 1);
-        mbar_init(&bar_kv[1], 1);
+        mbar_init(&bar_k[0], 1);
+        mbar_init(&bar_k[1], 1);
+        mbar_init(&bar_v[0], 1);
+        mbar_init(&bar_v[1], 1);
         mbar_init(bar_s, 1);
         mbar_init(bar_o, 1);
         mbar_fence_init();
@@ -84,14 +87,29 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tm, __nv_bfloat16* __res
     if (chunk > 0) kv_end = min(len, ((min(q0 + kBQ, len) - 1) / chunk + 1) * chunk);
     const int nkt = (kv_end + kBK - 1) / kBK;
     const int qcol = h * kD, kcol = (heads + h) * kD, vcol = (2 * heads + h) * kD;
+    const uint32_t idesc_s = umma_idesc_bf16(kBQ, kBK);
+    const uint32_t idesc_o = umma_idesc_bf16(kBQ, kD) | (1u << 16);  // B operand MN-major
 
     if (tid == 0) {
         mbar_expect_tx(bar_q, kQBytes);
         tma_load_2d(sQ, &tm, qcol, start + q0, bar_q);
         tma_load_2d(sQ + kQBytes / 2, &tm, qcol, start + q0 + 64, bar_q);
-        mbar_expect_tx(&bar_kv[0], 2 * kKVBytes);
-        tma_load_2d(sK, &tm, kcol, start, &bar_kv[0]);
-        tma_load_2d(sV, &tm, vcol, start, &bar_kv[0]);
+        mbar_expect_tx(&bar_k[0], kKVBytes);
+        tma_load_2d(sK, &tm, kcol, start, &bar_k[0]);
+        mbar_expect_tx(&bar_v[0], kKVBytes);
+        tma_load_2d(sV, &tm, vcol, start, &bar_v[0]);
+        if (nkt > 1) {
+            mbar_expect_tx(&bar_k[1], kKVBytes);
+            tma_load_2d(sK + kKVBytes, &tm, kcol, start + kBK, &bar_k[1]);
+        }
+        mbar_wait(bar_q, 0);
+        mbar_wait(&bar_k[0], 0);
+        tc_fence_after();
+        const uint64_t dq = umma_desc_sw128(smem_u32(sQ));
+        const uint64_t dk = umma_desc_sw128(smem_u32(sK));
+#pragma unroll
+        for (int k = 0; k < kD / 16; ++k) umma_bf16(tmem, dq + (uint64_t)(2 * k), dk + (uint64_t)(2 * k), idesc_s, (uint32_t)(k != 0));
+        umma_commit(bar_s);
     }
 
     const int qi = q0 + tid;  // this thread's query row
@@ -99,44 +117,28 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tm, __nv_bfloat16* __res
     if (chunk > 0) lim = min(len, (min(qi, len - 1) / chunk + 1) * chunk);
     const uint32_t t_s = tmem + ((uint32_t)(warp * 32) << 16);
     const uint32_t t_o = t_s + 64;
-    const uint32_t idesc_s = umma_idesc_bf16(kBQ, kBK);
-    const uint32_t idesc_o = umma_idesc_bf16(kBQ, kD) | (1u << 16);  // B operand MN-major
     constexpr float kLog2e = 1.4426950408889634f;
+    constexpr float kRescaleThreshold = 8.f;   // log2 units: P values stay below 2^8, sums in fp32
 
-    float o[kD];
-#pragma unroll
-    for (int i = 0; i < kD; ++i) o[i] = 0.f;
-    float m = -INFINITY, l = 0.f;
+    // Running maximum in log2 units.  O accumulates in TMEM across all key tiles (tcgen05.mma accumulate); it is only
+    // rescaled when some row's maximum grows by more than the threshold (lazy rescaling: exact, because numerator and
+    // denominator use the same stale maximum).
+    float m2 = -INFINITY, l = 0.f;
+
 
     for (int j = 0; j < nkt; ++j) {
         const int b = j & 1;
-        if (tid == 0) {
-            if (j + 1 < nkt) {  // prefetch the next K/V tile (its buffer was released by the PV MMA of tile j-1)
-                mbar_expect_tx(&bar_kv[b ^ 1], 2 * kKVBytes);
-                tma_load_2d(sK + (b ^ 1) * kKVBytes, &tm, kcol, start + (j + 1) * kBK, &bar_kv[b ^ 1]);
-                tma_load_2d(sV + (b ^ 1) * kKVBytes, &tm, vcol, start + (j + 1) * kBK, &bar_kv[b ^ 1]);
-            }
-            if (j == 0) mbar_wait(bar_q, 0);
-            mbar_wait(&bar_kv[b], (uint32_t)((j >> 1) & 1));
-            tc_fence_after();
-            const uint64_t dq = umma_desc_sw128(smem_u32(sQ));
-            const uint64_t dk = umma_desc_sw128(smem_u32(sK + b * kKVBytes));
-#pragma unroll
-            for (int k = 0; k < kD / 16; ++k) umma_bf16(tmem, dq + (uint64_t)(2 * k), dk + (uint64_t)(2 * k), idesc_s, (uint32_t)(k != 0));
-            umma_commit(bar_s);
-        }
+        const int kbase = j * kBK;
         mbar_wait(bar_s, (uint32_t)(j & 1));
         tc_fence_after();
-
-        // ---- scores of this row: 64 keys
         float sc[kBK];
         tmem_ld16(t_s, sc);
         tmem_ld16(t_s + 16, sc + 16);
         tmem_ld16(t_s + 32, sc + 32);
         tmem_ld16(t_s + 48, sc + 48);
         tmem_ld_wait();
-        const int kbase = j * kBK;
-        float mx = m;
+        tc_fence_before();   // S may be overwritten by QK(j + 1) after the block barrier below
+        float mx = -INFINITY;
         if (kbase + kBK <= lim) {
 #pragma unroll
             for (int i = 0; i < kBK; ++i) mx = fmaxf(mx, sc[i]);
@@ -147,63 +149,95 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tm, __nv_bfloat16* __res
                 mx = fmaxf(mx, sc[i]);
             }
         }
-        const float ms = mx == -INFINITY ? 0.f : mx;
-        const float corr = exp2f((m - ms) * kLog2e);
-        m = mx;
-        const float nms = -ms * kLog2e;
+        const float mx2 = mx * kLog2e;
+        const bool need = mx2 > m2 + kRescaleThreshold;   // also true for the first visible key (m2 == -inf)
+        const float m2n = need ? mx2 : m2;
+        const float factor = (m2 == -INFINITY) ? 0.f : exp2f(m2 - m2n);   // 1 when the maximum is kept
+        const bool any_rescale = __any_sync(0xffffffffu, need && j > 0);
+        const float nms = (m2n == -INFINITY) ? 0.f : -m2n;
+        m2 = m2n;
         float rs = 0.f;
-        uint8_t* prow = sP + (tid >> 3) * 1024 + (tid & 7) * 128;
+        uint32_t pk[kBK / 2];
 #pragma unroll
-        for (int u = 0; u < 8; ++u) {
-            float p[8];
-#pragma unroll
-            for (int i = 0; i < 8; ++i) {
-                p[i] = exp2f(fmaf(sc[u * 8 + i], kLog2e, nms));
-                rs += p[i];
-            }
-            uint4 t;
-            t.x = pack_bf16x2(p[0], p[1]);
-            t.y = pack_bf16x2(p[2], p[3]);
-            t.z = pack_bf16x2(p[4], p[5]);
-            t.w = pack_bf16x2(p[6], p[7]);
-            *reinterpret_cast<uint4*>(prow + ((u ^ (tid & 7)) << 4)) = t;
+        for (int i = 0; i < kBK; i += 2) {
+            const float p0 = ex2_approx(fmaf(sc[i], kLog2e, nms));
+            const float p1 = ex2_approx(fmaf(sc[i + 1], kLog2e, nms));
+            rs += p0 + p1;
+            pk[i >> 1] = pack_bf16x2(p0, p1);
         }
-        l = l * corr + rs;
-        fence_proxy_async();
+        l = fmaf(l, factor, rs);
+
+        // bar_s(j) implies that every earlier MMA, PV(j - 1) included, is complete (the tensor pipe runs in order and a
+        // commit covers all prior MMAs): V buffer b^1 (tile j - 1) and K buffer b (tile j) are free, O is stable.
+        if (tid == 0) {
+            if (j + 1 < nkt) {
+                mbar_expect_tx(&bar_v[b ^ 1], kKVBytes);
+                tma_load_2d(sV + (b ^ 1) * kKVBytes, &tm, vcol, start + (j + 1) * kBK, &bar_v[b ^ 1]);
+            }
+            if (j + 2 < nkt) {
+                mbar_expect_tx(&bar_k[b], kKVBytes);
+                tma_load_2d(sK + b * kKVBytes, &tm, kcol, start + (j + 2) * kBK, &bar_k[b]);
+            }
+        }
+        if (any_rescale) {   // warp-uniform: tcgen05.ld / .st are warp-collective; lanes that keep their maximum scale by 1
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                float t[16];
+                tmem_ld16(t_o + c * 16, t);
+                tmem_ld_wait();
+#pragma unroll
+                for (int i = 0; i < 16; ++i) t[i] *= factor;
+                tmem_st16(t_o + c * 16, t);
+            }
+            tmem_st_wait();
+        }
+        // P_j (bf16, two keys per 32-bit column) overwrites the first 32 columns of S_j in tensor memory and is the A
+        // operand of the PV MMA: no shared-memory round trip.  QK(j + 1) is issued behind PV(j), so it cannot clobber it.
+        tmem_st16(t_s, reinterpret_cast<const float*>(pk));
+        tmem_st16(t_s + 16, reinterpret_cast<const float*>(pk + 16));
+        tmem_st_wait();
         tc_fence_before();
         __syncthreads();
         if (tid == 0) {
             tc_fence_after();
-            const uint64_t dp = umma_desc_sw128(smem_u32(sP));
+            mbar_wait(&bar_v[b], (uint32_t)((j >> 1) & 1));
             const uint64_t dv = umma_desc_mn_sw128(smem_u32(sV + b * kKVBytes));
 #pragma unroll
             for (int k = 0; k < kBK / 16; ++k)
-                umma_bf16(tmem + 64, dp + (uint64_t)(2 * k), dv + (uint64_t)(k * (2048 >> 4)), idesc_o, (uint32_t)(k != 0));
-            umma_commit(bar_o);
-        }
-        mbar_wait(bar_o, (uint32_t)(j & 1));
-        tc_fence_after();
+                umma_bf16_ts(tmem + 64, tmem + (uint32_t)(k * 8), dv + (uint64_t)(k * (2048 >> 4)), idesc_o, (uint32_t)((j | k) != 0));
+            if (j + 1 == nkt) umma_commit(bar_o);
+            if (j + 1 < nkt) {   // next scores right behind it on the tensor pipe (every thread has read S_j)
+                mbar_wait(&bar_k[b ^ 1], (uint32_t)(((j + 1) >> 1) & 1));
+                const uint64_t dq = umma_desc_sw128(smem_u32(sQ));
+                const uint64_t dk = umma_desc_sw128(smem_u32(sK + (b ^ 1) * kKVBytes));
 #pragma unroll
-        for (int c = 0; c < 4; ++c) {
-            float t[16];
-            tmem_ld16(t_o + c * 16, t);
-            tmem_ld_wait();
-#pragma unroll
-            for (int i = 0; i < 16; ++i) o[c * 16 + i] = fmaf(o[c * 16 + i], corr, t[i]);
+                for (int k = 0; k < kD / 16; ++k) umma_bf16(tmem, dq + (uint64_t)(2 * k), dk + (uint64_t)(2 * k), idesc_s, (uint32_t)(k != 0));
+                umma_commit(bar_s);
+            }
         }
     }
 
-    if (qi < len) {
+    mbar_wait(bar_o, 0);
+    tc_fence_after();
+    {
         const float inv = l > 0.f ? 1.f / l : 0.f;
         __nv_bfloat16* dst = out + (size_t)(start + qi) * (heads * kD) + h * kD;
 #pragma unroll
-        for (int u = 0; u < 8; ++u) {
-            uint4 t;
-            t.x = pack_bf16x2(o[u * 8] * inv, o[u * 8 + 1] * inv);
-            t.y = pack_bf16x2(o[u * 8 + 2] * inv, o[u * 8 + 3] * inv);
-            t.z = pack_bf16x2(o[u * 8 + 4] * inv, o[u * 8 + 5] * inv);
-            t.w = pack_bf16x2(o[u * 8 + 6] * inv, o[u * 8 + 7] * inv);
-            *reinterpret_cast<uint4*>(dst + u * 8) = t;
+        for (int c = 0; c < 4; ++c) {   // (tcgen05.ld is warp-collective: every lane takes part, only the store is predicated)
+            float t[16];
+            tmem_ld16(t_o + c * 16, t);
+            tmem_ld_wait();
+            if (qi < len) {
+#pragma unroll
+                for (int u = 0; u < 2; ++u) {
+                    uint4 w;
+                    w.x = pack_bf16x2(t[u * 8] * inv, t[u * 8 + 1] * inv);
+                    w.y = pack_bf16x2(t[u * 8 + 2] * inv, t[u * 8 + 3] * inv);
+                    w.z = pack_bf16x2(t[u * 8 + 4] * inv, t[u * 8 + 5] * inv);
+                    w.w = pack_bf16x2(t[u * 8 + 6] * inv, t[u * 8 + 7] * inv);
+                    *reinterpret_cast<uint4*>(dst + c * 16 + u * 8) = w;
+                }
+            }
         }
     }
     tc_fence_before();
