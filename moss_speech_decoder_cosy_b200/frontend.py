@@ -93,14 +93,25 @@ def _conformer_layer(x, L, pe, mask, heads):
     p = F.linear(pe, L["pos_w"]).view(2 * T - 1, heads, dk).transpose(0, 1)       # [H, 2T-1, dk]
     q_u = (q + L["u"]).transpose(1, 2)                                              # [B, H, T, dk]
     q_v = (q + L["v"]).transpose(1, 2)
-    ac = torch.matmul(q_u, k.transpose(-2, -1))                                     # [B, H, T, T]
     bd = torch.matmul(q_v, p.transpose(-2, -1))                                     # [B, H, T, 2T-1]
     # rel_shift (attention.py:223-244): bd[i, j] <- raw[i, j + T - 1 - i]
     bd = F.pad(bd, (1, 0)).view(B, heads, 2 * T, T)[:, :, 1:].reshape(B, heads, T, 2 * T - 1)[..., :T]
-    scores = (ac + bd).float() / math.sqrt(dk)
-    scores = scores.masked_fill(~mask, float("-inf"))
-    attn = torch.softmax(scores, dim=-1).masked_fill(~mask, 0.0).to(x.dtype)
-    o = torch.matmul(attn, v).transpose(1, 2).reshape(B, T, D)
+    if x.is_cuda:
+        # softmax((q_u k^T + bd) / sqrt(dk)) v as ONE fused attention call: the positional term (and the -inf mask)
+        # rides in as the additive bias, so the [B, H, T, T] content scores / probabilities are never materialised
+        # (they were ~10 full passes over 0.4-0.9 GB tensors per mel-rate layer at batch 64).
+        Tp = (T + 7) // 8 * 8                                                       # bias row stride: multiple of 8
+        bias = torch.empty(B, heads, T, Tp, dtype=x.dtype, device=x.device)[..., :T]
+        torch.mul(bd, 1.0 / math.sqrt(dk), out=bias)
+        bias.masked_fill_(~mask, float("-inf"))
+        o = F.scaled_dot_product_attention(q_u, k, v, attn_mask=bias, scale=1.0 / math.sqrt(dk))
+        o = o.transpose(1, 2).reshape(B, T, D)
+    else:
+        ac = torch.matmul(q_u, k.transpose(-2, -1))                                 # [B, H, T, T]
+        scores = (ac + bd).float() / math.sqrt(dk)
+        scores = scores.masked_fill(~mask, float("-inf"))
+        attn = torch.softmax(scores, dim=-1).masked_fill(~mask, 0.0).to(x.dtype)
+        o = torch.matmul(attn, v).transpose(1, 2).reshape(B, T, D)
     x = x + F.linear(o, L["out_w"], L["out_b"])
     y = F.layer_norm(x.float(), (D,), L["n2"][0], L["n2"][1], 1e-12).to(x.dtype)
     return x + F.linear(F.silu(F.linear(y, L["w1"], L["b1"])), L["w2"], L["b2"])
