@@ -138,17 +138,21 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tm, __nv_bfloat16* __res
         tmem_ld16(t_s + 48, sc + 48);
         tmem_ld_wait();
         tc_fence_before();   // S may be overwritten by QK(j + 1) after the block barrier below
-        float mx = -INFINITY;
-        if (kbase + kBK <= lim) {
+        if (kbase + kBK > lim) {
 #pragma unroll
-            for (int i = 0; i < kBK; ++i) mx = fmaxf(mx, sc[i]);
-        } else {
-#pragma unroll
-            for (int i = 0; i < kBK; ++i) {
+            for (int i = 0; i < kBK; ++i)
                 if (kbase + i >= lim) sc[i] = -INFINITY;
-                mx = fmaxf(mx, sc[i]);
-            }
         }
+        // four independent chains (the serial 64-deep max / sum chains were a visible part of the per-tile latency)
+        float mxa = fmaxf(sc[0], sc[1]), mxb = fmaxf(sc[2], sc[3]), mxc = fmaxf(sc[4], sc[5]), mxd = fmaxf(sc[6], sc[7]);
+#pragma unroll
+        for (int i = 8; i < kBK; i += 8) {
+            mxa = fmaxf(mxa, fmaxf(sc[i], sc[i + 1]));
+            mxb = fmaxf(mxb, fmaxf(sc[i + 2], sc[i + 3]));
+            mxc = fmaxf(mxc, fmaxf(sc[i + 4], sc[i + 5]));
+            mxd = fmaxf(mxd, fmaxf(sc[i + 6], sc[i + 7]));
+        }
+        const float mx = fmaxf(fmaxf(mxa, mxb), fmaxf(mxc, mxd));
         const float mx2 = mx * kLog2e;
         const bool need = mx2 > m2 + kRescaleThreshold;   // also true for the first visible key (m2 == -inf)
         const float m2n = need ? mx2 : m2;
@@ -156,16 +160,21 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tm, __nv_bfloat16* __res
         const bool any_rescale = __any_sync(0xffffffffu, need && j > 0);
         const float nms = (m2n == -INFINITY) ? 0.f : -m2n;
         m2 = m2n;
-        float rs = 0.f;
+        float rsa = 0.f, rsb = 0.f, rsc = 0.f, rsd = 0.f;
         uint32_t pk[kBK / 2];
 #pragma unroll
-        for (int i = 0; i < kBK; i += 2) {
-            const float p0 = ex2_approx(fmaf(sc[i], kLog2e, nms));
-            const float p1 = ex2_approx(fmaf(sc[i + 1], kLog2e, nms));
-            rs += p0 + p1;
+        for (int i = 0; i < kBK; i += 8) {
+            const float p0 = ex2_approx(fmaf(sc[i], kLog2e, nms)), p1 = ex2_approx(fmaf(sc[i + 1], kLog2e, nms));
+            const float p2 = ex2_approx(fmaf(sc[i + 2], kLog2e, nms)), p3 = ex2_approx(fmaf(sc[i + 3], kLog2e, nms));
+            const float p4 = ex2_approx(fmaf(sc[i + 4], kLog2e, nms)), p5 = ex2_approx(fmaf(sc[i + 5], kLog2e, nms));
+            const float p6 = ex2_approx(fmaf(sc[i + 6], kLog2e, nms)), p7 = ex2_approx(fmaf(sc[i + 7], kLog2e, nms));
+            rsa += p0 + p1; rsb += p2 + p3; rsc += p4 + p5; rsd += p6 + p7;
             pk[i >> 1] = pack_bf16x2(p0, p1);
+            pk[(i >> 1) + 1] = pack_bf16x2(p2, p3);
+            pk[(i >> 1) + 2] = pack_bf16x2(p4, p5);
+            pk[(i >> 1) + 3] = pack_bf16x2(p6, p7);
         }
-        l = fmaf(l, factor, rs);
+        l = fmaf(l, factor, (rsa + rsb) + (rsc + rsd));
 
         // bar_s(j) implies that every earlier MMA, PV(j - 1) included, is complete (the tensor pipe runs in order and a
         // commit covers all prior MMAs): V buffer b^1 (tile j - 1) and K buffer b (tile j) are free, O is stable.
