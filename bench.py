@@ -28,6 +28,7 @@ BATCH, N_TOK, N_PROMPT = 64, 125, 37
 EST_MFLOP_PER_FRAME = 132.162e6      # estimator GEMM-class FLOPs per frame per CFG branch per step
 ATTN_MFLOP_PER_FRAME_T = 0.114688e6  # attention FLOPs per frame per branch per step, times T
 HIFT_FLOP_PER_FRAME = 612.296e6      # vocoder GEMM-class FLOPs per generated frame
+FFN_FLOP_PER_FRAME = 56 * 2 * 2 * 256 * 1024   # 56 transformer blocks x (FF1 + FF2), per frame per branch per step
 
 
 def workload(batch, seed0=2000):
@@ -228,10 +229,32 @@ def main():
     value = world * audio_s * args.steps / (ms / 1e3)
     e2e = world * audio_s * args.steps / (ms_e2e / 1e3)
     T = 4 * (N_PROMPT + N_TOK)
-    gemm_flops = B * (10 * 2 * T * EST_MFLOP_PER_FRAME + 4 * N_TOK * HIFT_FLOP_PER_FRAME)   # algorithmic, per step
     pk = peaks()
-    gemm_s = prof["gemm_ms"] / 1e3 / args.steps
-    achieved = gemm_flops / gemm_s / 1e12 if gemm_s > 0 else 0.0
+    # Algorithmic FLOPs per step of the three tensor-core kernels (SURVEY 8d figures):
+    frames_steps = B * 10 * 2 * T                                    # frame . CFG branch . Euler step
+    flops = {
+        "attention_tc_kernel": frames_steps * ATTN_MFLOP_PER_FRAME_T * T,
+        "ffn_tc_kernel": frames_steps * FFN_FLOP_PER_FRAME,
+        "gemm_tc_kernel": frames_steps * (EST_MFLOP_PER_FRAME - FFN_FLOP_PER_FRAME) + B * 4 * N_TOK * HIFT_FLOP_PER_FRAME,
+    }
+    times = {"attention_tc_kernel": (prof["attn_ms"], prof["attn_launches"]),
+             "ffn_tc_kernel": (prof["ffn_ms"], prof["ffn_launches"]),
+             "gemm_tc_kernel": (prof["gemm_ms"], prof["gemm_launches"])}
+    traffic = {}
+    tpath = os.path.join(ROOT, "profiles", "ncu_dram_traffic.json")   # bytes per launch from the committed ncu --set full capture
+    if os.path.exists(tpath):
+        traffic = json.load(open(tpath))
+    desc = {"attention_tc_kernel": "tcgen05 flash attention (QK^T and PV on the tensor cores, P in TMEM)",
+            "ffn_tc_kernel": "fused feed-forward (FF1 + GELU + FF2 + residual + LayerNorm, tcgen05, hidden on chip)",
+            "gemm_tc_kernel": "tcgen05 implicit GEMM (convs, projections, vocoder) with fused epilogues"}
+    kernels = {}
+    for k, (kms, kn) in times.items():
+        sec = kms / 1e3 / args.steps
+        ach = flops[k] / sec / 1e12 if sec > 0 else 0.0
+        kernels[k] = {"ms_per_step": kms / args.steps, "launches_per_step": kn / args.steps, "share_of_step": kms / ms if ms > 0 else None,
+                      "achieved": ach, "frac": ach / pk["tflops"], "algorithmic_tflop_per_step": flops[k] / 1e12,
+                      "traffic": traffic.get(k)}
+    dom = max(kernels, key=lambda k: kernels[k]["ms_per_step"])       # the dominant kernel of the step
     line = {
         "metric": "audio_seconds_per_second", "value": value, "unit": "audio-s/s", "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
@@ -244,12 +267,14 @@ def main():
         "e2e": {"value": e2e, "unit": "audio-s/s", "h2d_bytes_per_step": int(tok_h.nbytes + feat_h.nbytes + emb_h.nbytes),
                 "d2h_bytes_per_step": int(wav_h.nbytes), "ms_per_step": ms_e2e / args.steps, "output_ok": wav_ok},
         "gpu_launches": int(launches),
-        "roofline": {"bound": "tensor", "kernel": "gemm_tc_kernel (tcgen05 implicit GEMM: convs, projections, FFN, vocoder)",
-                     "achieved": achieved, "peak": pk["tflops"], "unit": "TFLOP/s", "frac": achieved / pk["tflops"],
-                     "traffic": None, "peak_source": pk["src"], "launches_per_step": prof["gemm_launches"] / args.steps,
-                     "kernel_ms_per_step": prof["gemm_ms"] / args.steps,
-                     "share_of_step": prof["gemm_ms"] / ms if ms > 0 else None,
-                     "attention_ms_per_step": prof["attn_ms"] / args.steps},
+        "roofline": {"bound": "tensor", "kernel": f"{dom} ({desc[dom]})", "achieved": kernels[dom]["achieved"],
+                     "peak": pk["tflops"], "unit": "TFLOP/s", "frac": kernels[dom]["frac"],
+                     "traffic": kernels[dom]["traffic"], "peak_source": pk["src"],
+                     "launches_per_step": kernels[dom]["launches_per_step"],
+                     "kernel_ms_per_step": kernels[dom]["ms_per_step"], "share_of_step": kernels[dom]["share_of_step"],
+                     "all_tensor_kernels": kernels,
+                     "tensor_kernels_total": {"ms_per_step": sum(k["ms_per_step"] for k in kernels.values()),
+                                              "achieved": sum(flops.values()) / (sum(t[0] for t in times.values()) / 1e3 / args.steps) / 1e12}},
     }
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         torch.set_num_threads(os.cpu_count() or 1)

@@ -91,11 +91,11 @@ int mossdec_fade_in_out(mossdec_handle* h, float* speech, const float* prev_tail
  * "hift.post", "hift.x") to HOST memory; synchronises the device.  Returns floats copied, negative on error. */
 int mossdec_debug_read(mossdec_handle* h, const char* name, float* host_dst, int64_t max_floats);
 
-/* Per-launch device timing (CUDA events on the launch stream) of the GEMM-class kernel and the attention kernel.
- * mossdec_profile_read synchronises and returns, since the last read: out6 = {gemm ms, gemm launches, gemm executed
- * FLOPs (2 M N K incl. tile padding), attention ms, attention launches, 0}. */
+/* Per-launch device timing (CUDA events on the launch stream) of the three tensor-core kernels.
+ * mossdec_profile_read synchronises and returns, since the last read: out9 = {gemm ms, gemm launches, gemm executed
+ * FLOPs (2 M N K incl. tile padding), attention ms, attention launches, 0, fused-FFN ms, fused-FFN launches, FFN FLOPs}. */
 void mossdec_profile(mossdec_handle* h, int32_t on);
-int mossdec_profile_read(mossdec_handle* h, double* out6);
+int mossdec_profile_read(mossdec_handle* h, double* out9);
 
 /* Frames per vocoder group (bounds the stage-2 working set; default 8192). */
 void mossdec_set_hift_group_frames(mossdec_handle* h, int64_t frames);

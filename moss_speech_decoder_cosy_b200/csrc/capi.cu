@@ -80,7 +80,7 @@ int mossdec_debug_read(mossdec_handle* h, const char* name, float* host_dst, int
 }
 
 void mossdec_profile(mossdec_handle* h, int32_t on) { h->eng->set_profile(on != 0); }
-int mossdec_profile_read(mossdec_handle* h, double* out6) { return h->eng->profile_read(out6); }
+int mossdec_profile_read(mossdec_handle* h, double* out9) { return h->eng->profile_read(out9); }
 void mossdec_set_hift_group_frames(mossdec_handle* h, int64_t frames) { h->eng->set_hift_group_frames(frames); }
 
 int64_t mossdec_launch_count(const mossdec_handle* h) { return h->eng->launches(); }

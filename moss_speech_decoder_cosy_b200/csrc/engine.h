@@ -75,9 +75,9 @@ class Engine {
     int hift(int B, const int32_t* lens, const float* mel, const float* cache_source, int cache_stride,
              const int32_t* cache_len, const float* nsf_noise, float* wav_out, float* source_out, uint64_t seed,
              int flags, cudaStream_t st);
-    // per-launch device timing of the GEMM-class (0) and attention (1) kernels with CUDA events on the launch stream
+    // per-launch device timing of the GEMM (0), attention (1) and fused-FFN (2) kernels with CUDA events on the launch stream
     void set_profile(bool on) { profile_ = on; }
-    int profile_read(double* out6);
+    int profile_read(double* out9);
     // test hook: copy a named intermediate of the last call to the host; returns floats copied or -1
     int debug_read(const char* name, void* host_dst, size_t bytes);
     int fade_in_out(float* speech, const float* prev_tail, const float* window2n, int n, cudaStream_t st);

@@ -94,7 +94,7 @@ void Engine::prof_begin(int cls, double flops, cudaStream_t st, uint64_t key) {
 void Engine::prof_end(cudaStream_t st) { cudaEventRecord(prof_.back().b, st); }
 
 int Engine::profile_read(double* out) {
-    for (int i = 0; i < 6; ++i) out[i] = 0.0;
+    for (int i = 0; i < 9; ++i) out[i] = 0.0;
     if (cudaDeviceSynchronize() != cudaSuccess) return fail("profile_read: sync failed");
     for (auto& r : prof_) {
         float ms = 0.f;
@@ -142,7 +142,7 @@ int Engine::gemm(const GemmProblem& p, cudaStream_t st) {
 
 int Engine::ffn(const FfnProblem& f, cudaStream_t st) {
     if (cfg_.channels != 256) return fail("fused FFN is built for channels == 256");
-    if (profile_) prof_begin(0, 2.0 * f.M * 256.0 * 1024.0 * 2.0, st, ((uint64_t)f.M << 40) | 0xfffu);
+    if (profile_) prof_begin(2, 2.0 * f.M * 256.0 * 1024.0 * 2.0, st, ((uint64_t)f.M << 40) | 0xfffu);
     cudaError_t e = ffn_tc_launch(f, num_sms_, st);
     if (profile_) prof_end(st);
     ++launches_;

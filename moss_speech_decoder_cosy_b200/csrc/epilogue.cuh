@@ -49,6 +49,23 @@ __device__ __forceinline__ float fast_gelu_erf(float x) {
     p = fmaf(p, a, -9.999995828e-01f);
     return fmaf(-a, ex2_approx(p), fmaxf(x, 0.f));
 }
+// Two GELUs at once, packed to bf16x2: the degree-6 Horner and the final FMA run as FFMA2 (half the FMA-pipe instructions).
+__device__ __forceinline__ uint32_t gelu2_bf16(float x0, float x1) {
+    const float a0 = fminf(fabsf(x0), 6.f), a1 = fminf(fabsf(x1), 6.f);
+    const uint64_t a = f2_pack(a0, a1);
+    uint64_t p = f2_fma(f2_pack(3.291721077e-05f, 3.291721077e-05f), a, f2_pack(-7.622798439e-04f, -7.622798439e-04f));
+    p = f2_fma(p, a, f2_pack(8.039220236e-03f, 8.039220236e-03f));
+    p = f2_fma(p, a, f2_pack(-5.331587791e-02f, -5.331587791e-02f));
+    p = f2_fma(p, a, f2_pack(-4.588711560e-01f, -4.588711560e-01f));
+    p = f2_fma(p, a, f2_pack(-1.151156902e+00f, -1.151156902e+00f));
+    p = f2_fma(p, a, f2_pack(-9.999995828e-01f, -9.999995828e-01f));
+    float p0, p1;
+    f2_unpack(p, p0, p1);
+    const uint64_t r = f2_fma(f2_pack(-a0, -a1), f2_pack(ex2_approx(p0), ex2_approx(p1)), f2_pack(fmaxf(x0, 0.f), fmaxf(x1, 0.f)));
+    float r0, r1;
+    f2_unpack(r, r0, r1);
+    return pack_bf16x2(r0, r1);
+}
 __device__ __forceinline__ float fast_sin(float x) {
     // two-term Cody-Waite reduction to [-pi, pi], then the SFU sine (abs error ~1e-6 for |x| < 1e4)
     const float k = rintf(x * 0.15915494309189535f);

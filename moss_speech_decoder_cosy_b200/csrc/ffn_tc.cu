@@ -33,7 +33,7 @@ bool encode_2d(CUtensorMap* m, const void* ptr, uint64_t cols, uint64_t rows, ui
 namespace {
 
 #ifdef FFN_EXPERIMENT_NO_GELU   // timing experiment only (tests/): how much of E1 is the activation math
-#define fast_gelu_erf(x) (x)
+#define gelu2_bf16(x, y) pack_bf16x2(x, y)
 #endif
 
 constexpr int kC = 256;          // model width
@@ -320,8 +320,8 @@ ffn_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ C
                 uint32_t pk[16];
 #pragma unroll
                 for (int i = 0; i < 4; ++i) {
-                    pk[2 * i] = pack_bf16x2(fast_gelu_erf(va[4 * i] + bias[i].x), fast_gelu_erf(va[4 * i + 1] + bias[i].y));
-                    pk[2 * i + 1] = pack_bf16x2(fast_gelu_erf(va[4 * i + 2] + bias[i].z), fast_gelu_erf(va[4 * i + 3] + bias[i].w));
+                    pk[2 * i] = gelu2_bf16(va[4 * i] + bias[i].x, va[4 * i + 1] + bias[i].y);
+                    pk[2 * i + 1] = gelu2_bf16(va[4 * i + 2] + bias[i].z, va[4 * i + 3] + bias[i].w);
                 }
 #pragma unroll
                 for (int i = 0; i < 4; ++i) bias[i] = ldg4(bp + 16 + 4 * i);
@@ -334,8 +334,8 @@ ffn_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ C
                 }
 #pragma unroll
                 for (int i = 0; i < 4; ++i) {
-                    pk[8 + 2 * i] = pack_bf16x2(fast_gelu_erf(vb[4 * i] + bias[i].x), fast_gelu_erf(vb[4 * i + 1] + bias[i].y));
-                    pk[8 + 2 * i + 1] = pack_bf16x2(fast_gelu_erf(vb[4 * i + 2] + bias[i].z), fast_gelu_erf(vb[4 * i + 3] + bias[i].w));
+                    pk[8 + 2 * i] = gelu2_bf16(vb[4 * i] + bias[i].x, vb[4 * i + 1] + bias[i].y);
+                    pk[8 + 2 * i + 1] = gelu2_bf16(vb[4 * i + 2] + bias[i].z, vb[4 * i + 3] + bias[i].w);
                 }
                 // P[b] is only needed now: G2(h - 2) must have finished reading it (its latency hid behind the GELU math)
                 if (h >= 2) mbar_wait(&p_free[b], (uint32_t)(((h - 2) >> 1) & 1));

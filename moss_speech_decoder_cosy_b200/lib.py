@@ -198,10 +198,10 @@ class Engine:
         self.lib.mossdec_profile(self.h, int(bool(on)))
 
     def profile_read(self):
-        out = (ctypes.c_double * 6)()
+        out = (ctypes.c_double * 9)()
         self._check(self.lib.mossdec_profile_read(self.h, out), "profile_read")
         return {"gemm_ms": out[0], "gemm_launches": int(out[1]), "gemm_hw_flops": out[2], "attn_ms": out[3],
-                "attn_launches": int(out[4])}
+                "attn_launches": int(out[4]), "ffn_ms": out[6], "ffn_launches": int(out[7]), "ffn_hw_flops": out[8]}
 
     def set_hift_group_frames(self, frames):
         self.lib.mossdec_set_hift_group_frames(self.h, int(frames))
