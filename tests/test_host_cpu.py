@@ -97,6 +97,42 @@ def test_pack_shapes_and_schema():
     assert h["hift.f0.c0.w"].shape == (512, 3 * 384) and h["hift.post.w"].shape == (18, 448)
 
 
+def test_layernorm_affine_folded_into_consumer_weights():
+    """pack_estimator folds norm1 into q|k|v and norm3 into ff1 (W (g n + b) = (W diag g) n + W b): with the folded
+    tensors a plain (non-affine) LayerNorm reproduces the reference's affine LayerNorm + Linear."""
+    sd = synth.synth_flow_state_dict(0)
+    p = "decoder.estimator.mid_blocks.3.1.2."
+    g = torch.Generator().manual_seed(5)
+    sd = dict(sd)
+    for n in ("norm1", "norm3"):   # random-init LayerNorms are the identity affine: perturb them so the fold is exercised
+        sd[p + n + ".weight"] = 1 + 0.3 * torch.randn(256, generator=g)
+        sd[p + n + ".bias"] = 0.2 * torch.randn(256, generator=g)
+    t = weights.pack_estimator(sd)
+    x = torch.randn(9, 256, generator=g) * 3 + 1
+    plain = torch.nn.functional.layer_norm(x, (256,))
+    ref1 = torch.nn.functional.layer_norm(x, (256,), sd[p + "norm1.weight"], sd[p + "norm1.bias"])
+    want = torch.cat([ref1 @ sd[p + "attn1.to_q.weight"].t() / 8.0, ref1 @ sd[p + "attn1.to_k.weight"].t(),
+                      ref1 @ sd[p + "attn1.to_v.weight"].t()], 1)
+    got = plain @ t["est.tf4.2.qkv.w"].float().t() + t["est.tf4.2.qkv.b"]
+    assert (got - want).abs().max() < 2e-2 * want.abs().max()            # bf16 weight rounding only
+    ref3 = torch.nn.functional.layer_norm(x, (256,), sd[p + "norm3.weight"], sd[p + "norm3.bias"])
+    want = ref3 @ sd[p + "ff.net.0.proj.weight"].t() + sd[p + "ff.net.0.proj.bias"]
+    got = plain @ t["est.tf4.2.ff1.w"].float().t() + t["est.tf4.2.ff1.b"]
+    assert (got - want).abs().max() < 2e-2 * want.abs().max()
+    assert "est.tf4.2.n1.g" not in t and "est.tf4.2.n3.b" not in t
+
+
+def test_tiled_f32_layout_is_a_permutation_with_coalesced_rows():
+    """gemm.h tiled_f32_offset (mirrored here): the float4 of columns 4j..4j+3 of the 128 rows of a tile are contiguous."""
+    def off(row, col):
+        return (((row >> 7) * 64 + (col >> 2)) * 128 + (row & 127)) * 4 + (col & 3)
+    M = 384
+    idx = np.array([[off(r, c) for c in range(256)] for r in range(M)])
+    assert sorted(idx.reshape(-1).tolist()) == list(range(M * 256))      # bijection onto [0, M * 256)
+    assert (idx[1:128, 8] - idx[:127, 8] == 4).all()                      # consecutive rows: consecutive float4s
+    assert idx[128, 0] == 128 * 256                                       # tiles are contiguous 128 KB blocks
+
+
 def test_chunk_plan_matches_reference_schedule():
     # SURVEY 3.2 probe of the reference: 60 tokens, P = 38, block 5 -> windows of 10, 15, ..., 40, 40, ... tokens,
     # every call emits 9 600 samples, 12 calls in total
