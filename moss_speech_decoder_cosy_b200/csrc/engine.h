@@ -107,7 +107,9 @@ class Engine {
     // flow internals
     struct FlowPlan;
     int build_flow_layout(int nseq_half, const int32_t* lens, bool cfg_double);
-    int estimator_forward(int M, int nseq, int max_len, const float* tbias, int tbias_ld, int chunk, cudaStream_t st);
+    // row0 > 0: run on the rows [row0, row0 + M) of every workspace matrix (the second CFG half on its own stream)
+    int estimator_forward(int M, int nseq, int max_len, const float* tbias, int tbias_ld, int chunk, cudaStream_t st,
+                          int row0 = 0);
     int time_bias(const float* t_dev, int nt, cudaStream_t st);
     int finalize_hift();
     int hift_group(int b0, int b1, const int32_t* lens, int64_t mel_off0, int64_t wav_off0, const float* mel,
@@ -118,6 +120,9 @@ class Engine {
     int num_sms_ = 148;
     bool finalized_ = false;
     bool attn_v1_ = false;
+    bool dual_stream_ = true;          // the two CFG halves of a solve run on two streams (MOSSDEC_DUAL=0 disables)
+    cudaStream_t st2_ = nullptr;
+    cudaEvent_t ev_fork_ = nullptr, ev_join_ = nullptr;
     std::unordered_map<std::string, DevTensor> tensors_;
     std::string err_;
     std::string missing_;

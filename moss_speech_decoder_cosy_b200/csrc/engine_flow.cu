@@ -38,9 +38,20 @@ Engine::Engine(const EngineConfig& cfg) : cfg_(cfg) {
     cudaDeviceGetAttribute(&num_sms_, cudaDevAttrMultiProcessorCount, dev);
     const char* av = getenv("MOSSDEC_ATTN");  // "v1" selects the mma.sync kernel (developer A/B switch)
     attn_v1_ = av != nullptr && av[0] == 'v' && av[1] == '1';
+    const char* dv = getenv("MOSSDEC_DUAL");
+    dual_stream_ = !(dv != nullptr && dv[0] == '0');
+    if (dual_stream_) {
+        if (cudaStreamCreateWithFlags(&st2_, cudaStreamNonBlocking) != cudaSuccess ||
+            cudaEventCreateWithFlags(&ev_fork_, cudaEventDisableTiming) != cudaSuccess ||
+            cudaEventCreateWithFlags(&ev_join_, cudaEventDisableTiming) != cudaSuccess)
+            dual_stream_ = false;
+    }
 }
 
 Engine::~Engine() {
+    if (st2_) cudaStreamDestroy(st2_);
+    if (ev_fork_) cudaEventDestroy(ev_fork_);
+    if (ev_join_) cudaEventDestroy(ev_join_);
     for (auto& kv : tensors_)
         if (kv.second.ptr) cudaFree(kv.second.ptr);
 }
@@ -289,10 +300,22 @@ int Engine::time_bias(const float* t_dev, int nt, cudaStream_t st) {
 // ------------------------------------------------------------------------------------------------ estimator
 // Input: xin_ [M, 320] bf16 (guard rows zero).  Output: dout_ [M, 80] fp32 (guard rows zero).
 int Engine::estimator_forward(int M, int nseq, int max_len, const float* tbias, int tbias_ld, int chunk,
-                              cudaStream_t st) {
+                              cudaStream_t st, int row0) {
     const int C = cfg_.channels, H = cfg_.heads * cfg_.head_dim;
     const int ngroups = cfg_.n_mid + 2;
-    const int32_t* row_seq = layout_.row_seq;
+    const int32_t* row_seq = layout_.row_seq + row0;
+    // workspace views of the rows [row0, row0 + M) (these locals shadow the members on purpose; row0 is a multiple of
+    // 128, so the tiled fp32 matrices are offset by whole tiles).  Sequence starts stay relative to the view: the
+    // second CFG half has the same layout as the first, so it uses the first half's seq_start / seq_len arrays.
+    __nv_bfloat16* const xin_ = this->xin_ + (size_t)row0 * cfg_.in_channels;
+    __nv_bfloat16* const xn_ = this->xn_ + (size_t)row0 * C;
+    __nv_bfloat16* const h1_ = this->h1_ + (size_t)row0 * C;
+    __nv_bfloat16* const qkv_ = this->qkv_ + (size_t)row0 * 3 * H;
+    __nv_bfloat16* const att_ = this->att_ + (size_t)row0 * H;
+    __nv_bfloat16* const cat_ = this->cat_ + (size_t)row0 * 2 * C;
+    float* const hres_ = this->hres_ + (size_t)row0 * C;
+    float* const rres_ = this->rres_ + (size_t)row0 * C;
+    float* const dout_ = this->dout_ + (size_t)row0 * cfg_.n_feats;
 
     auto causal3 = [&](GemmProblem& p, const __nv_bfloat16* a, int cin) {
         p.a[0].ptr = a;

@@ -88,8 +88,21 @@ int Engine::flow_solve(int B, const int32_t* lens, const float* mu, const float*
 
     for (int s = 0; s < n_steps; ++s) {
         // tbias_ld = 0: every sequence reads the row of this step
-        if (estimator_forward(M, flow_nseq_, flow_max_len_, tbias_ + (size_t)s * ngroups * cfg_.channels, 0, chunk, st))
+        const float* tb = tbias_ + (size_t)s * ngroups * cfg_.channels;
+        if (dual_stream_ && !profile_) {
+            // The two CFG halves are independent until the Euler update: each runs its kernel chain on its own
+            // stream, so the partial last wave of one half's persistent kernels (654 tiles on 148 SMs = 4.4 waves)
+            // and its launch gaps are filled by the other half's kernels.  (Profiling runs serially so that the
+            // per-kernel event times are not stretched by co-running kernels.)
+            MD_CUDA(cudaEventRecord(ev_fork_, st));
+            MD_CUDA(cudaStreamWaitEvent(st2_, ev_fork_, 0));
+            if (estimator_forward(flow_rows_half_, flow_nseq_ / 2, flow_max_len_, tb, 0, chunk, st, 0)) return -1;
+            if (estimator_forward(flow_rows_half_, flow_nseq_ / 2, flow_max_len_, tb, 0, chunk, st2_, flow_rows_half_)) return -1;
+            MD_CUDA(cudaEventRecord(ev_join_, st2_));
+            MD_CUDA(cudaStreamWaitEvent(st, ev_join_, 0));
+        } else if (estimator_forward(M, flow_nseq_, flow_max_len_, tb, 0, chunk, st)) {
             return -1;
+        }
         launch_euler_cfg(layout_, dout_, dtv[s], cfg_rate, xstate_, xin_, st);
         ++launches_;
     }
