@@ -11,6 +11,8 @@
 //                  than 2^8 (lazy rescaling), normalised and stored as bf16 at the end.
 // Everything inside a CTA is sequential; 4 CTAs per SM overlap each other's TMA / MMA / softmax phases.  With head_dim
 // 64 the kernel is bound by the exp2 throughput of the SFUs (16 / clk / SM), not by the tensor pipe.
+#include <stdio.h>
+
 #include "kernels.h"
 #include "ptx.cuh"
 
@@ -23,7 +25,6 @@ namespace {
 constexpr int kBQ = 128, kBK = 64, kD = 64;
 constexpr int kQBytes = kBQ * kD * 2;   // 16 KB
 constexpr int kKVBytes = kBK * kD * 2;  // 8 KB
-constexpr int kPBytes = kBQ * kBK * 2;  // 16 KB
 constexpr int kSmem = kQBytes + 4 * kKVBytes + 1024 + 128;
 
 // B operand stored MN-major (rows = K index, 64 N-elements = 128 bytes contiguous per row), 128B swizzle:
@@ -37,16 +38,107 @@ __device__ __forceinline__ uint64_t umma_desc_mn_sw128(uint32_t smem_addr) {
     d |= (uint64_t)2 << 61;
     return d;
 }
-__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+// experiment switches (scripts/build_variant.sh); none is defined in the shipped build
+#ifdef ATT_X_NOEXP
+#define ATT_EX2(x) (x)
+#else
+#define ATT_EX2(x) ex2_approx(x)
+#endif
+#ifdef ATT_X_NOPACK
+#define ATT_PACK(a, b) (__float_as_uint(a) ^ __float_as_uint(b))
+#else
+#define ATT_PACK(a, b) pack_bf16x2(a, b)
+#endif
+#ifdef ATT_TRACE   // clock64 timeline of one CTA's warp 0 over three key tiles, printed by the launcher (experiments only)
+__device__ long long g_att_trace[64];
+#define ATT_STAMP(k) do { if (trace_on && j >= 4 && j < 7) g_att_trace[(j - 4) * 12 + (k)] = clock64(); } while (0)
+#else
+#define ATT_STAMP(k) do { } while (0)
+#endif
+constexpr float kLog2e = 1.4426950408889634f;
+constexpr float kRescaleThreshold = 8.f;   // log2 units: P values stay below 2^8, sums in fp32
+
+// Softmax of one [128 x NK] score tile, thread == query row.  Reads S from TMEM columns [0, NK), writes P (bf16, two keys
+// per 32-bit column) over its first NK / 2 columns -- the A operand of the PV MMA, no shared-memory round trip -- and
+// rescales O (TMEM columns 64..127) when some row of the warp moved its maximum.
+template <int NK>
+__device__ __forceinline__ void softmax_tile(uint32_t t_s, int kbase, int lim, int j, float& m2, float& l, bool trace_on) {
+    float sc[NK];
+#pragma unroll
+#ifdef ATT_X_NOLD
+    for (int i = 0; i < NK; ++i) sc[i] = l + (float)(i & 7);
+#else
+    for (int c = 0; c < NK / 16; ++c) tmem_ld16(t_s + c * 16, sc + c * 16);
+    tmem_ld_wait();
+#endif
+    ATT_STAMP(1);
+    if (kbase + NK > lim) {
+#pragma unroll
+        for (int i = 0; i < NK; ++i)
+            if (kbase + i >= lim) sc[i] = -INFINITY;
+    }
+    // four independent chains (the serial 64-deep max / sum chains were a visible part of the per-tile latency)
+    float mxa = fmaxf(sc[0], sc[1]), mxb = fmaxf(sc[2], sc[3]), mxc = fmaxf(sc[4], sc[5]), mxd = fmaxf(sc[6], sc[7]);
+#pragma unroll
+    for (int i = 8; i < NK; i += 8) {
+        mxa = fmaxf(mxa, fmaxf(sc[i], sc[i + 1]));
+        mxb = fmaxf(mxb, fmaxf(sc[i + 2], sc[i + 3]));
+        mxc = fmaxf(mxc, fmaxf(sc[i + 4], sc[i + 5]));
+        mxd = fmaxf(mxd, fmaxf(sc[i + 6], sc[i + 7]));
+    }
+    const float mx = fmaxf(fmaxf(mxa, mxb), fmaxf(mxc, mxd));
+    const float mx2 = mx * kLog2e;
+    const bool need = mx2 > m2 + kRescaleThreshold;   // also true for the first visible key (m2 == -inf)
+    const float m2n = need ? mx2 : m2;
+    const float factor = (m2 == -INFINITY) ? 0.f : exp2f(m2 - m2n);   // 1 when the maximum is kept
+    const bool any_rescale = __any_sync(0xffffffffu, need && j > 0);
+    const float nms = (m2n == -INFINITY) ? 0.f : -m2n;
+    m2 = m2n;
+    float rsa = 0.f, rsb = 0.f, rsc = 0.f, rsd = 0.f;
+    uint32_t pk[NK / 2];
+#pragma unroll
+    for (int i = 0; i < NK; i += 8) {
+        const float p0 = ATT_EX2(fmaf(sc[i], kLog2e, nms)), p1 = ATT_EX2(fmaf(sc[i + 1], kLog2e, nms));
+        const float p2 = ATT_EX2(fmaf(sc[i + 2], kLog2e, nms)), p3 = ATT_EX2(fmaf(sc[i + 3], kLog2e, nms));
+        const float p4 = ATT_EX2(fmaf(sc[i + 4], kLog2e, nms)), p5 = ATT_EX2(fmaf(sc[i + 5], kLog2e, nms));
+        const float p6 = ATT_EX2(fmaf(sc[i + 6], kLog2e, nms)), p7 = ATT_EX2(fmaf(sc[i + 7], kLog2e, nms));
+        rsa += p0 + p1; rsb += p2 + p3; rsc += p4 + p5; rsd += p6 + p7;
+        pk[i >> 1] = ATT_PACK(p0, p1);
+        pk[(i >> 1) + 1] = ATT_PACK(p2, p3);
+        pk[(i >> 1) + 2] = ATT_PACK(p4, p5);
+        pk[(i >> 1) + 3] = ATT_PACK(p6, p7);
+    }
+    l = fmaf(l, factor, (rsa + rsb) + (rsc + rsd));
+    ATT_STAMP(2);
+    if (any_rescale) {   // warp-uniform: tcgen05.ld / .st are warp-collective; lanes that keep their maximum scale by 1
+        const uint32_t t_o = t_s + 64;
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            float t[16];
+            tmem_ld16(t_o + c * 16, t);
+            tmem_ld_wait();
+#pragma unroll
+            for (int i = 0; i < 16; ++i) t[i] *= factor;
+            tmem_st16(t_o + c * 16, t);
+        }
+    }
+#pragma unroll
+    for (int c = 0; c < NK / 32; ++c) tmem_st16(t_s + c * 16, reinterpret_cast<const float*>(pk + c * 16));
+    if (NK % 32) tmem_st8(t_s + (NK / 32) * 16, reinterpret_cast<const float*>(pk + (NK / 32) * 16));
+    tmem_st_wait();
+    ATT_STAMP(3);
+}
 
 __global__ void __launch_bounds__(128, 4)
 attention_tc_kernel(const __grid_constant__ CUtensorMap tm, __nv_bfloat16* __restrict__ out,
                     const int32_t* __restrict__ seq_start, const int32_t* __restrict__ seq_len, int heads, int chunk) {
     const int s = blockIdx.z, h = blockIdx.y;
-    const int len = seq_len[s];
+    // (shuffle broadcasts tell the compiler these are warp-uniform: loop counters and MMA descriptors stay in uniform registers)
+    const int len = __shfl_sync(0xffffffffu, seq_len[s], 0);
     const int q0 = blockIdx.x * kBQ;
     if (q0 >= len) return;
-    const int start = seq_start[s];
+    const int start = __shfl_sync(0xffffffffu, seq_start[s], 0);
 
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);  // stays in the shared address space (STS / LDS)
@@ -61,7 +153,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tm, __nv_bfloat16* __res
     uint64_t* bar_o = bars + 6;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 7);
 
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int tid = threadIdx.x, warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
     if (tid == 0) {
         tma_prefetch_desc(&tm);
         mbar_init(bar_q, 1);
@@ -80,17 +172,24 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tm, __nv_bfloat16* __res
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
-    const uint32_t tmem = *tmem_slot;
+    const uint32_t tmem = __shfl_sync(0xffffffffu, *tmem_slot, 0);
 
     // keys visible to this query tile
     int kv_end = len;
     if (chunk > 0) kv_end = min(len, ((min(q0 + kBQ, len) - 1) / chunk + 1) * chunk);
     const int nkt = (kv_end + kBK - 1) / kBK;
     const int qcol = h * kD, kcol = (heads + h) * kD, vcol = (2 * heads + h) * kD;
+    // the last key tile only computes the 16-key groups that hold visible keys (T = 648: 8 of 64)
+#ifdef ATT_NO_SHORT_TAIL
+    const int nk_last = kBK;
+#else
+    const int nk_last = ((kv_end - (nkt - 1) * kBK) + 15) & ~15;
+#endif
     const uint32_t idesc_s = umma_idesc_bf16(kBQ, kBK);
+    const uint32_t idesc_s_last = umma_idesc_bf16(kBQ, (uint32_t)nk_last);
     const uint32_t idesc_o = umma_idesc_bf16(kBQ, kD) | (1u << 16);  // B operand MN-major
 
-    if (tid == 0) {
+    if (warp == 0 && elect_one()) {
         mbar_expect_tx(bar_q, kQBytes);
         tma_load_2d(sQ, &tm, qcol, start + q0, bar_q);
         tma_load_2d(sQ + kQBytes / 2, &tm, qcol, start + q0 + 64, bar_q);
@@ -108,7 +207,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tm, __nv_bfloat16* __res
         const uint64_t dq = umma_desc_sw128(smem_u32(sQ));
         const uint64_t dk = umma_desc_sw128(smem_u32(sK));
 #pragma unroll
-        for (int k = 0; k < kD / 16; ++k) umma_bf16(tmem, dq + (uint64_t)(2 * k), dk + (uint64_t)(2 * k), idesc_s, (uint32_t)(k != 0));
+        for (int k = 0; k < kD / 16; ++k) umma_bf16(tmem, dq + (uint64_t)(2 * k), dk + (uint64_t)(2 * k), nkt == 1 ? idesc_s_last : idesc_s, (uint32_t)(k != 0));
         umma_commit(bar_s);
     }
 
@@ -117,118 +216,84 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tm, __nv_bfloat16* __res
     if (chunk > 0) lim = min(len, (min(qi, len - 1) / chunk + 1) * chunk);
     const uint32_t t_s = tmem + ((uint32_t)(warp * 32) << 16);
     const uint32_t t_o = t_s + 64;
-    constexpr float kLog2e = 1.4426950408889634f;
-    constexpr float kRescaleThreshold = 8.f;   // log2 units: P values stay below 2^8, sums in fp32
 
     // Running maximum in log2 units.  O accumulates in TMEM across all key tiles (tcgen05.mma accumulate); it is only
     // rescaled when some row's maximum grows by more than the threshold (lazy rescaling: exact, because numerator and
     // denominator use the same stale maximum).
     float m2 = -INFINITY, l = 0.f;
-
+    // A warp whose 32 query rows all lie past the end of the sequence (the last query tile of T = 648 has 8 rows) only
+    // takes part in the block barriers: its SFU / issue slots go to the other CTAs resident on the SM.
+#ifdef ATT_TRACE
+    const bool trace_on = tid == 0 && blockIdx.x == 2 && blockIdx.y == 3 && blockIdx.z == gridDim.z / 2;
+#else
+    const bool trace_on = false;
+#endif
+#ifdef ATT_NO_IDLE_SKIP
+    const bool active = true;
+#else
+    const bool active = q0 + warp * 32 < len;
+#endif
 
     for (int j = 0; j < nkt; ++j) {
         const int b = j & 1;
         const int kbase = j * kBK;
-        mbar_wait(bar_s, (uint32_t)(j & 1));
-        tc_fence_after();
-        float sc[kBK];
-        tmem_ld16(t_s, sc);
-        tmem_ld16(t_s + 16, sc + 16);
-        tmem_ld16(t_s + 32, sc + 32);
-        tmem_ld16(t_s + 48, sc + 48);
-        tmem_ld_wait();
-        tc_fence_before();   // S may be overwritten by QK(j + 1) after the block barrier below
-        if (kbase + kBK > lim) {
-#pragma unroll
-            for (int i = 0; i < kBK; ++i)
-                if (kbase + i >= lim) sc[i] = -INFINITY;
-        }
-        // four independent chains (the serial 64-deep max / sum chains were a visible part of the per-tile latency)
-        float mxa = fmaxf(sc[0], sc[1]), mxb = fmaxf(sc[2], sc[3]), mxc = fmaxf(sc[4], sc[5]), mxd = fmaxf(sc[6], sc[7]);
-#pragma unroll
-        for (int i = 8; i < kBK; i += 8) {
-            mxa = fmaxf(mxa, fmaxf(sc[i], sc[i + 1]));
-            mxb = fmaxf(mxb, fmaxf(sc[i + 2], sc[i + 3]));
-            mxc = fmaxf(mxc, fmaxf(sc[i + 4], sc[i + 5]));
-            mxd = fmaxf(mxd, fmaxf(sc[i + 6], sc[i + 7]));
-        }
-        const float mx = fmaxf(fmaxf(mxa, mxb), fmaxf(mxc, mxd));
-        const float mx2 = mx * kLog2e;
-        const bool need = mx2 > m2 + kRescaleThreshold;   // also true for the first visible key (m2 == -inf)
-        const float m2n = need ? mx2 : m2;
-        const float factor = (m2 == -INFINITY) ? 0.f : exp2f(m2 - m2n);   // 1 when the maximum is kept
-        const bool any_rescale = __any_sync(0xffffffffu, need && j > 0);
-        const float nms = (m2n == -INFINITY) ? 0.f : -m2n;
-        m2 = m2n;
-        float rsa = 0.f, rsb = 0.f, rsc = 0.f, rsd = 0.f;
-        uint32_t pk[kBK / 2];
-#pragma unroll
-        for (int i = 0; i < kBK; i += 8) {
-            const float p0 = ex2_approx(fmaf(sc[i], kLog2e, nms)), p1 = ex2_approx(fmaf(sc[i + 1], kLog2e, nms));
-            const float p2 = ex2_approx(fmaf(sc[i + 2], kLog2e, nms)), p3 = ex2_approx(fmaf(sc[i + 3], kLog2e, nms));
-            const float p4 = ex2_approx(fmaf(sc[i + 4], kLog2e, nms)), p5 = ex2_approx(fmaf(sc[i + 5], kLog2e, nms));
-            const float p6 = ex2_approx(fmaf(sc[i + 6], kLog2e, nms)), p7 = ex2_approx(fmaf(sc[i + 7], kLog2e, nms));
-            rsa += p0 + p1; rsb += p2 + p3; rsc += p4 + p5; rsd += p6 + p7;
-            pk[i >> 1] = pack_bf16x2(p0, p1);
-            pk[(i >> 1) + 1] = pack_bf16x2(p2, p3);
-            pk[(i >> 1) + 2] = pack_bf16x2(p4, p5);
-            pk[(i >> 1) + 3] = pack_bf16x2(p6, p7);
-        }
-        l = fmaf(l, factor, (rsa + rsb) + (rsc + rsd));
-
-        // bar_s(j) implies that every earlier MMA, PV(j - 1) included, is complete (the tensor pipe runs in order and a
-        // commit covers all prior MMAs): V buffer b^1 (tile j - 1) and K buffer b (tile j) are free, O is stable.
-        if (tid == 0) {
-            if (j + 1 < nkt) {
-                mbar_expect_tx(&bar_v[b ^ 1], kKVBytes);
-                tma_load_2d(sV + (b ^ 1) * kKVBytes, &tm, vcol, start + (j + 1) * kBK, &bar_v[b ^ 1]);
+        const int nk = (j + 1 == nkt) ? nk_last : kBK;   // keys of this tile that take part (multiple of 16)
+        if (active) {
+            mbar_wait(bar_s, (uint32_t)(j & 1));
+            tc_fence_after();
+            ATT_STAMP(0);
+            // bar_s(j) implies that every earlier MMA, PV(j - 1) included, is complete (the tensor pipe runs in order and
+            // a commit covers all prior MMAs): V buffer b^1 (tile j - 1) and K buffer b (tile j) are free, O is stable.
+            if (warp == 0 && elect_one()) {
+                if (j + 1 < nkt) {
+                    mbar_expect_tx(&bar_v[b ^ 1], kKVBytes);
+                    tma_load_2d(sV + (b ^ 1) * kKVBytes, &tm, vcol, start + (j + 1) * kBK, &bar_v[b ^ 1]);
+                }
+                if (j + 2 < nkt) {
+                    mbar_expect_tx(&bar_k[b], kKVBytes);
+                    tma_load_2d(sK + b * kKVBytes, &tm, kcol, start + (j + 2) * kBK, &bar_k[b]);
+                }
             }
-            if (j + 2 < nkt) {
-                mbar_expect_tx(&bar_k[b], kKVBytes);
-                tma_load_2d(sK + b * kKVBytes, &tm, kcol, start + (j + 2) * kBK, &bar_k[b]);
-            }
+            if (nk == 64) softmax_tile<64>(t_s, kbase, lim, j, m2, l, trace_on);
+            else if (nk == 16) softmax_tile<16>(t_s, kbase, lim, j, m2, l, trace_on);
+            else if (nk == 32) softmax_tile<32>(t_s, kbase, lim, j, m2, l, trace_on);
+            else softmax_tile<48>(t_s, kbase, lim, j, m2, l, trace_on);
         }
-        if (any_rescale) {   // warp-uniform: tcgen05.ld / .st are warp-collective; lanes that keep their maximum scale by 1
-#pragma unroll
-            for (int c = 0; c < 4; ++c) {
-                float t[16];
-                tmem_ld16(t_o + c * 16, t);
-                tmem_ld_wait();
-#pragma unroll
-                for (int i = 0; i < 16; ++i) t[i] *= factor;
-                tmem_st16(t_o + c * 16, t);
-            }
-            tmem_st_wait();
-        }
-        // P_j (bf16, two keys per 32-bit column) overwrites the first 32 columns of S_j in tensor memory and is the A
-        // operand of the PV MMA: no shared-memory round trip.  QK(j + 1) is issued behind PV(j), so it cannot clobber it.
-        tmem_st16(t_s, reinterpret_cast<const float*>(pk));
-        tmem_st16(t_s + 16, reinterpret_cast<const float*>(pk + 16));
-        tmem_st_wait();
         tc_fence_before();
         __syncthreads();
-        if (tid == 0) {
+        ATT_STAMP(4);
+        if (warp == 0) {   // warp-uniform branch, one elected lane issues
             tc_fence_after();
             mbar_wait(&bar_v[b], (uint32_t)((j >> 1) & 1));
-            const uint64_t dv = umma_desc_mn_sw128(smem_u32(sV + b * kKVBytes));
-#pragma unroll
-            for (int k = 0; k < kBK / 16; ++k)
-                umma_bf16_ts(tmem + 64, tmem + (uint32_t)(k * 8), dv + (uint64_t)(k * (2048 >> 4)), idesc_o, (uint32_t)((j | k) != 0));
-            if (j + 1 == nkt) umma_commit(bar_o);
+            ATT_STAMP(7);
+            if (elect_one()) {
+                const uint64_t dv = umma_desc_mn_sw128(smem_u32(sV + b * kKVBytes));
+#ifndef ATT_X_NOPV
+                for (int k = 0; k < nk / 16; ++k)
+                    umma_bf16_ts(tmem + 64, tmem + (uint32_t)(k * 8), dv + (uint64_t)(k * (2048 >> 4)), idesc_o, (uint32_t)((j | k) != 0));
+#endif
+                if (j + 1 == nkt) umma_commit(bar_o);
+            }
+            ATT_STAMP(5);
             if (j + 1 < nkt) {   // next scores right behind it on the tensor pipe (every thread has read S_j)
                 mbar_wait(&bar_k[b ^ 1], (uint32_t)(((j + 1) >> 1) & 1));
-                const uint64_t dq = umma_desc_sw128(smem_u32(sQ));
-                const uint64_t dk = umma_desc_sw128(smem_u32(sK + (b ^ 1) * kKVBytes));
+                ATT_STAMP(8);
+                if (elect_one()) {
+                    const uint64_t dq = umma_desc_sw128(smem_u32(sQ));
+                    const uint64_t dk = umma_desc_sw128(smem_u32(sK + (b ^ 1) * kKVBytes));
+                    const uint32_t id = (j + 2 == nkt) ? idesc_s_last : idesc_s;
 #pragma unroll
-                for (int k = 0; k < kD / 16; ++k) umma_bf16(tmem, dq + (uint64_t)(2 * k), dk + (uint64_t)(2 * k), idesc_s, (uint32_t)(k != 0));
-                umma_commit(bar_s);
+                    for (int k = 0; k < kD / 16; ++k) umma_bf16(tmem, dq + (uint64_t)(2 * k), dk + (uint64_t)(2 * k), id, (uint32_t)(k != 0));
+                    umma_commit(bar_s);
+                }
+                ATT_STAMP(6);
             }
         }
     }
 
-    mbar_wait(bar_o, 0);
-    tc_fence_after();
-    {
+    if (active) {
+        mbar_wait(bar_o, 0);
+        tc_fence_after();
         const float inv = l > 0.f ? 1.f / l : 0.f;
         __nv_bfloat16* dst = out + (size_t)(start + qi) * (heads * kD) + h * kD;
 #pragma unroll
@@ -268,6 +333,20 @@ cudaError_t launch_attention_tc(const __nv_bfloat16* qkv, int64_t rows, __nv_bfl
     if (!encode_2d(&tm, qkv, (uint64_t)3 * heads * kD, (uint64_t)rows, (uint64_t)3 * heads * kD, 64)) return cudaErrorInvalidValue;
     dim3 grid((max_len + kBQ - 1) / kBQ, heads, nseq);
     attention_tc_kernel<<<grid, 128, kSmem, st>>>(tm, out, seq_start, seq_len, heads, chunk);
+#ifdef ATT_TRACE
+    static int n_launch = 0;
+    if (++n_launch == 300) {
+        long long tr[64];
+        cudaStreamSynchronize(st);
+        cudaMemcpyFromSymbol(tr, g_att_trace, sizeof(tr));
+        for (int t = 0; t < 3; ++t) {
+            const long long* r = tr + t * 12;
+            fprintf(stderr, "[att trace] tile %d: S ready +0 | ld done %lld | exp done %lld | P stored %lld | barrier %lld | V ready %lld | PV issued %lld | K ready %lld | QK issued %lld | next S ready %lld\n",
+                    t + 4, r[1] - r[0], r[2] - r[0], r[3] - r[0], r[4] - r[0], r[7] - r[0], r[5] - r[0], r[8] - r[0], r[6] - r[0],
+                    t < 2 ? r[12] - r[0] : 0LL);
+        }
+    }
+#endif
     return cudaGetLastError();
 }
 

@@ -86,7 +86,9 @@ ffn_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ C
     uint64_t* acc2_full = p_free + 2;    // MMA -> epilogue
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc2_full + 1);
 
-    const int warp = threadIdx.x >> 5;
+    // (shuffle broadcasts mark values as warp-uniform for the compiler: descriptors and loop state of the TMA / MMA
+    //  warps then live in uniform registers and every tcgen05.mma / TMA is a single instruction, not a per-lane loop)
+    const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);
     const int lane = threadIdx.x & 31;
 
     if (warp == 0 && lane == 0) {
@@ -116,12 +118,12 @@ ffn_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ C
     __syncthreads();
     tc_fence_after();
     cluster_sync_all();   // peers' barriers are initialised before any multicast / remote arrive can reach them
-    const uint32_t tmem_base = *tmem_slot;
-    const int rank = (int)cluster_ctarank();
+    const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);
+    const int rank = __shfl_sync(0xffffffffu, (int)cluster_ctarank(), 0);
 
     if (warp == 0) {
-        // ------------------------------------------------------------ TMA producer
-        if (lane == 0) {
+        // ------------------------------------------------------------ TMA producer (whole warp, one elected lane issues)
+        {
             int stage = 0;
             uint32_t phase = 0;
             auto next_stage = [&]() {
@@ -133,32 +135,38 @@ ffn_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ C
             auto load_g1 = [&](int h) {   // W1 rows [128 h, +128), all K = 256: two stages of two 64-wide k-blocks
                 for (int j = 0; j < 2; ++j) {
                     mbar_wait(&empty[stage], phase ^ 1);
-                    mbar_expect_tx(&full[stage], kFStageBytes);
-                    // this CTA fetches k-block 2j + rank and multicasts it; the peer supplies the other one
-                    uint8_t* dst = sRing + stage * kFStageBytes + rank * (kFStageBytes / 2);
-                    tma_load_2d_mc(dst, &tmW1, (2 * j + rank) * kGemmBK, h * kChunk, &full[stage], kClusterMask);
+                    if (elect_one()) {
+                        mbar_expect_tx(&full[stage], kFStageBytes);
+                        // this CTA fetches k-block 2j + rank and multicasts it; the peer supplies the other one
+                        uint8_t* dst = sRing + stage * kFStageBytes + rank * (kFStageBytes / 2);
+                        tma_load_2d_mc(dst, &tmW1, (2 * j + rank) * kGemmBK, h * kChunk, &full[stage], kClusterMask);
+                    }
                     next_stage();
                 }
             };
             auto load_g2 = [&](int h) {   // W2 all 256 rows, K columns [128 h, +128): two stages of one k-block
                 for (int j = 0; j < 2; ++j) {
                     mbar_wait(&empty[stage], phase ^ 1);
-                    mbar_expect_tx(&full[stage], kFStageBytes);
-                    // rows [128 rank, +128) of the 256-row k-block (8-row swizzle atoms are contiguous: offset 16 KB)
-                    tma_load_2d_mc(sRing + stage * kFStageBytes + rank * (kFStageBytes / 2), &tmW2,
-                                   h * kChunk + j * kGemmBK, rank * (kC / 2), &full[stage], kClusterMask);
+                    if (elect_one()) {
+                        mbar_expect_tx(&full[stage], kFStageBytes);
+                        // rows [128 rank, +128) of the 256-row k-block (8-row swizzle atoms are contiguous: offset 16 KB)
+                        tma_load_2d_mc(sRing + stage * kFStageBytes + rank * (kFStageBytes / 2), &tmW2,
+                                       h * kChunk + j * kGemmBK, rank * (kC / 2), &full[stage], kClusterMask);
+                    }
                     next_stage();
                 }
             };
             int it = 0;
-            if ((int)blockIdx.x < p.num_tiles) l2_prefetch_bulk(p.hres + (size_t)blockIdx.x * kGemmBM * kC, kGemmBM * kC * 4);
+            if ((int)blockIdx.x < p.num_tiles && lane == 0) l2_prefetch_bulk(p.hres + (size_t)blockIdx.x * kGemmBM * kC, kGemmBM * kC * 4);
             for (int tile = blockIdx.x; (tile & ~(kCluster - 1)) < p.num_tiles; tile += gridDim.x, ++it) {  // cluster-uniform trip count
                 if (it > 0) mbar_wait(x_free, (uint32_t)((it - 1) & 1));
-                mbar_expect_tx(x_full, kXBytes);
-                for (int kb = 0; kb < kC / kGemmBK; ++kb)
-                    tma_load_2d(sX + kb * kABytes, &tmX, kb * kGemmBK, tile * kGemmBM, x_full);
+                if (elect_one()) {
+                    mbar_expect_tx(x_full, kXBytes);
+                    for (int kb = 0; kb < kC / kGemmBK; ++kb)
+                        tma_load_2d(sX + kb * kABytes, &tmX, kb * kGemmBK, tile * kGemmBM, x_full);
+                }
                 // the residual rows of the next tile: pulled into L2 a whole tile ahead of their use
-                if (tile + (int)gridDim.x < p.num_tiles)
+                if (tile + (int)gridDim.x < p.num_tiles && lane == 0)
                     l2_prefetch_bulk(p.hres + (size_t)(tile + gridDim.x) * kGemmBM * kC, kGemmBM * kC * 4);
                 load_g1(0);
                 load_g1(1);
@@ -169,8 +177,8 @@ ffn_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ C
             }
         }
     } else if (warp == 1) {
-        // ------------------------------------------------------------ MMA issuer
-        if (lane == 0) {
+        // ------------------------------------------------------------ MMA issuer (whole warp, one elected lane issues)
+        {
             const uint32_t idesc1 = umma_idesc_bf16(kGemmBM, kChunk);
             const uint32_t idesc2 = umma_idesc_bf16(kGemmBM, kC);
             int stage = 0;
@@ -181,7 +189,7 @@ ffn_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ C
                     phase ^= 1;
                 }
             };
-            const bool mtr = p.trace != nullptr && blockIdx.x == 0;
+            const bool mtr = p.trace != nullptr && blockIdx.x == 0 && lane == 0;
             long long w_full = 0, w_ready = 0;
             auto g1 = [&](int b) {
                 const uint32_t d = tmem_base + kAcc1Col + (uint32_t)b * kChunk;
@@ -190,19 +198,21 @@ ffn_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ C
                     mbar_wait(&full[stage], phase);
                     if (mtr) w_full += clock64() - t0;
                     tc_fence_after();
+                    if (elect_one()) {
 #pragma unroll
-                    for (int q = 0; q < 2; ++q) {
-                        const int kb = 2 * j + q;
-                        const uint64_t da = umma_desc_sw128(smem_u32(sX + kb * kABytes));
-                        const uint64_t db = umma_desc_sw128(smem_u32(sRing + stage * kFStageBytes + q * (kFStageBytes / 2)));
+                        for (int q = 0; q < 2; ++q) {
+                            const int kb = 2 * j + q;
+                            const uint64_t da = umma_desc_sw128(smem_u32(sX + kb * kABytes));
+                            const uint64_t db = umma_desc_sw128(smem_u32(sRing + stage * kFStageBytes + q * (kFStageBytes / 2)));
 #pragma unroll
-                        for (int k = 0; k < kGemmBK / 16; ++k)
-                            umma_bf16(d, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc1, (uint32_t)((kb | k) != 0));
+                            for (int k = 0; k < kGemmBK / 16; ++k)
+                                umma_bf16(d, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc1, (uint32_t)((kb | k) != 0));
+                        }
+                        umma_commit_mc(&empty[stage], kClusterMask);   // the stage is refilled by both CTAs: both must see it free
+                        if (j == 1) umma_commit(&a1_full[b]);
                     }
-                    umma_commit_mc(&empty[stage], kClusterMask);   // the stage is refilled by both CTAs: both must see it free
                     next_stage();
                 }
-                umma_commit(&a1_full[b]);
             };
             auto g2 = [&](int h) {
                 const int b = h & 1;
@@ -212,22 +222,24 @@ ffn_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ C
                     mbar_wait(&full[stage], phase);
                     if (mtr) w_full += clock64() - t0;
                     tc_fence_after();
-                    const uint64_t da = umma_desc_sw128(smem_u32(sP + b * kPBytes + j * kABytes));
-                    const uint64_t db = umma_desc_sw128(smem_u32(sRing + stage * kFStageBytes));
+                    if (elect_one()) {
+                        const uint64_t da = umma_desc_sw128(smem_u32(sP + b * kPBytes + j * kABytes));
+                        const uint64_t db = umma_desc_sw128(smem_u32(sRing + stage * kFStageBytes));
 #pragma unroll
-                    for (int k = 0; k < kGemmBK / 16; ++k)
-                        umma_bf16(d, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc2, 1u);  // acc2 was preloaded with hres + b2
-                    umma_commit_mc(&empty[stage], kClusterMask);   // the stage is refilled by both CTAs: both must see it free
+                        for (int k = 0; k < kGemmBK / 16; ++k)
+                            umma_bf16(d, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc2, 1u);  // acc2 was preloaded with hres + b2
+                        umma_commit_mc(&empty[stage], kClusterMask);   // the stage is refilled by both CTAs: both must see it free
+                        if (j == 1) umma_commit(&p_free[b]);
+                    }
                     next_stage();
                 }
-                umma_commit(&p_free[b]);
             };
             int it = 0;
             uint32_t pr_phase[2] = {0, 0};
             for (int tile = blockIdx.x; (tile & ~(kCluster - 1)) < p.num_tiles; tile += gridDim.x, ++it) {  // cluster-uniform trip count
                 mbar_wait(x_full, (uint32_t)(it & 1));
                 tc_fence_after();
-                if (p.trace != nullptr && blockIdx.x == 0) p.trace[it * 48 + 32] = clock64();
+                if (mtr) p.trace[it * 48 + 32] = clock64();
                 g1(0);
                 g1(1);
                 for (int h = 0; h < kNChunk; ++h) {
@@ -237,12 +249,12 @@ ffn_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ C
                     pr_phase[b] ^= 1;
                     tc_fence_after();
                     if (mtr) w_ready += clock64() - t0;
-                    if (p.trace != nullptr && blockIdx.x == 0) p.trace[it * 48 + 33 + h] = clock64();
+                    if (mtr) p.trace[it * 48 + 33 + h] = clock64();
                     if (h + 2 < kNChunk) g1(b);            // G1 first: its result is what the epilogue waits for next
-                    if (h + 2 == kNChunk - 1) umma_commit(x_free);  // last G1 of the tile issued: X may be reloaded
+                    if (h + 2 == kNChunk - 1 && elect_one()) umma_commit(x_free);  // last G1 of the tile issued: X may be reloaded
                     g2(h);
                 }
-                umma_commit(acc2_full);
+                if (elect_one()) umma_commit(acc2_full);
                 if (mtr) {
                     p.trace[it * 48 + 41] = clock64();
                     p.trace[it * 48 + 42] = w_full;

@@ -286,7 +286,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
     uint64_t* tempty = tfull + 2;              // [2]
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
 
-    const int warp = threadIdx.x >> 5;
+    // (shuffle broadcasts mark values as warp-uniform for the compiler: descriptors and loop state of the TMA / MMA
+    //  warps then live in uniform registers and every tcgen05.mma / TMA is a single instruction, not a per-lane loop)
+    const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);
     const int lane = threadIdx.x & 31;
 
     if (warp == 0 && lane == 0) {
@@ -311,13 +313,13 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
-    const uint32_t tmem_base = *tmem_slot;
+    const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);
 
     const uint32_t b_bytes = (uint32_t)p.BN * kGemmBK * 2;
 
     if (warp == 0) {
-        // ------------------------------------------------------------ TMA producer
-        if (lane == 0) {
+        // ------------------------------------------------------------ TMA producer (whole warp, one elected lane issues)
+        {
             int stage = 0;
             uint32_t phase = 0;
             for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
@@ -329,9 +331,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
                     const CUtensorMap* tmA = sg.map ? &tmA1 : &tmA0;
                     for (int j = 0; j < sg.nkb; ++j, ++kb) {
                         mbar_wait(&empty[stage], phase ^ 1);
-                        mbar_expect_tx(&full[stage], kABytes + b_bytes);
-                        tma_load_2d(sA + stage * kABytes, tmA, sg.col0 + j * kGemmBK, m0 + sg.row_shift, &full[stage]);
-                        tma_load_2d(sB + stage * kBBytesMax, &tmB, kb * kGemmBK, n0, &full[stage]);
+                        if (elect_one()) {
+                            mbar_expect_tx(&full[stage], kABytes + b_bytes);
+                            tma_load_2d(sA + stage * kABytes, tmA, sg.col0 + j * kGemmBK, m0 + sg.row_shift, &full[stage]);
+                            tma_load_2d(sB + stage * kBBytesMax, &tmB, kb * kGemmBK, n0, &full[stage]);
+                        }
                         if (++stage == kGemmStages) {
                             stage = 0;
                             phase ^= 1;
@@ -341,8 +345,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
             }
         }
     } else if (warp == 1) {
-        // ------------------------------------------------------------ MMA issuer
-        if (lane == 0) {
+        // ------------------------------------------------------------ MMA issuer (whole warp, one elected lane issues)
+        {
             const uint32_t idesc = umma_idesc_bf16(kGemmBM, (uint32_t)p.BN);
             int stage = 0;
             uint32_t phase = 0;
@@ -355,18 +359,20 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
                 for (int kb = 0; kb < p.total_kb; ++kb) {
                     mbar_wait(&full[stage], phase);
                     tc_fence_after();
-                    const uint64_t da = umma_desc_sw128(smem_u32(sA + stage * kABytes));
-                    const uint64_t db = umma_desc_sw128(smem_u32(sB + stage * kBBytesMax));
+                    if (elect_one()) {
+                        const uint64_t da = umma_desc_sw128(smem_u32(sA + stage * kABytes));
+                        const uint64_t db = umma_desc_sw128(smem_u32(sB + stage * kBBytesMax));
 #pragma unroll
-                    for (int k = 0; k < kGemmBK / 16; ++k)
-                        umma_bf16(d_tmem, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (uint32_t)((kb | k) != 0));
-                    umma_commit(&empty[stage]);
+                        for (int k = 0; k < kGemmBK / 16; ++k)
+                            umma_bf16(d_tmem, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (uint32_t)((kb | k) != 0));
+                        umma_commit(&empty[stage]);
+                        if (kb + 1 == p.total_kb) umma_commit(&tfull[acc]);
+                    }
                     if (++stage == kGemmStages) {
                         stage = 0;
                         phase ^= 1;
                     }
                 }
-                umma_commit(&tfull[acc]);
                 acc ^= 1;
                 if (acc == 0) accphase ^= 1;
             }

@@ -5,7 +5,7 @@ import os
 import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libmossdec.so")
+LIB_PATH = os.environ.get("MOSSDEC_LIB") or os.path.join(_HERE, "lib", "libmossdec.so")   # MOSSDEC_LIB: A/B builds of the same library
 
 F32, BF16, I32 = 0, 1, 2
 

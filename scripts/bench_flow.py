@@ -36,5 +36,11 @@ e1.record()
 torch.cuda.synchronize()
 ms = e0.elapsed_time(e1) / a.reps
 flops = a.steps * 2 * a.B * a.T * (132.162e6 + 0.114688e6 * a.T)
+eng.profile(True)
+for _ in range(a.reps):
+    eng.flow_solve(lens, mu, spks, cond, n_steps=a.steps, chunk=a.chunk)
+pr = eng.profile_read()
+eng.profile(False)
+print(f"  serial per solve: attention {pr['attn_ms'] / a.reps:.2f} ms  ffn {pr['ffn_ms'] / a.reps:.2f} ms  other gemm {pr['gemm_ms'] / a.reps:.2f} ms")
 print(f"flow_solve B={a.B} T={a.T} steps={a.steps}: {ms:.2f} ms  {flops / ms / 1e9:.1f} TFLOP/s  "
       f"launches/solve={eng.launch_count() / a.reps:.0f}  finite={bool(torch.isfinite(mel).all())}")
