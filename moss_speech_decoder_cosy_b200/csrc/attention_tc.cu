@@ -234,6 +234,10 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tm, __nv_bfloat16* __res
     const bool active = q0 + warp * 32 < len;
 #endif
 
+    const uint64_t dq = umma_desc_sw128(smem_u32(sQ));
+    const uint64_t dk0 = umma_desc_sw128(smem_u32(sK)), dk1 = umma_desc_sw128(smem_u32(sK + kKVBytes));
+    const uint64_t dv0 = umma_desc_mn_sw128(smem_u32(sV)), dv1 = umma_desc_mn_sw128(smem_u32(sV + kKVBytes));
+
     for (int j = 0; j < nkt; ++j) {
         const int b = j & 1;
         const int kbase = j * kBK;
@@ -262,32 +266,35 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tm, __nv_bfloat16* __res
         tc_fence_before();
         __syncthreads();
         ATT_STAMP(4);
-        if (warp == 0) {   // warp-uniform branch, one elected lane issues
+        if (warp == 0) {   // warp-uniform branch, one elected lane issues; descriptors were built before the loop
+            const bool more = j + 1 < nkt;
             tc_fence_after();
             mbar_wait(&bar_v[b], (uint32_t)((j >> 1) & 1));
+            if (more) mbar_wait(&bar_k[b ^ 1], (uint32_t)(((j + 1) >> 1) & 1));
             ATT_STAMP(7);
             if (elect_one()) {
-                const uint64_t dv = umma_desc_mn_sw128(smem_u32(sV + b * kKVBytes));
+                const uint64_t dv = b ? dv1 : dv0;
 #ifndef ATT_X_NOPV
-                for (int k = 0; k < nk / 16; ++k)
-                    umma_bf16_ts(tmem + 64, tmem + (uint32_t)(k * 8), dv + (uint64_t)(k * (2048 >> 4)), idesc_o, (uint32_t)((j | k) != 0));
+                if (nk == kBK) {
+#pragma unroll
+                    for (int k = 0; k < kBK / 16; ++k)
+                        umma_bf16_ts(tmem + 64, tmem + (uint32_t)(k * 8), dv + (uint64_t)(k * (2048 >> 4)), idesc_o, (uint32_t)((j | k) != 0));
+                } else {
+                    for (int k = 0; k < nk / 16; ++k)
+                        umma_bf16_ts(tmem + 64, tmem + (uint32_t)(k * 8), dv + (uint64_t)(k * (2048 >> 4)), idesc_o, (uint32_t)((j | k) != 0));
+                }
 #endif
-                if (j + 1 == nkt) umma_commit(bar_o);
-            }
-            ATT_STAMP(5);
-            if (j + 1 < nkt) {   // next scores right behind it on the tensor pipe (every thread has read S_j)
-                mbar_wait(&bar_k[b ^ 1], (uint32_t)(((j + 1) >> 1) & 1));
-                ATT_STAMP(8);
-                if (elect_one()) {
-                    const uint64_t dq = umma_desc_sw128(smem_u32(sQ));
-                    const uint64_t dk = umma_desc_sw128(smem_u32(sK + (b ^ 1) * kKVBytes));
+                if (more) {   // next scores right behind it on the tensor pipe (every thread has read S_j)
+                    const uint64_t dk = b ? dk0 : dk1;
                     const uint32_t id = (j + 2 == nkt) ? idesc_s_last : idesc_s;
 #pragma unroll
                     for (int k = 0; k < kD / 16; ++k) umma_bf16(tmem, dq + (uint64_t)(2 * k), dk + (uint64_t)(2 * k), id, (uint32_t)(k != 0));
                     umma_commit(bar_s);
+                } else {
+                    umma_commit(bar_o);
                 }
-                ATT_STAMP(6);
             }
+            ATT_STAMP(6);
         }
     }
 
@@ -341,8 +348,8 @@ cudaError_t launch_attention_tc(const __nv_bfloat16* qkv, int64_t rows, __nv_bfl
         cudaMemcpyFromSymbol(tr, g_att_trace, sizeof(tr));
         for (int t = 0; t < 3; ++t) {
             const long long* r = tr + t * 12;
-            fprintf(stderr, "[att trace] tile %d: S ready +0 | ld done %lld | exp done %lld | P stored %lld | barrier %lld | V ready %lld | PV issued %lld | K ready %lld | QK issued %lld | next S ready %lld\n",
-                    t + 4, r[1] - r[0], r[2] - r[0], r[3] - r[0], r[4] - r[0], r[7] - r[0], r[5] - r[0], r[8] - r[0], r[6] - r[0],
+            fprintf(stderr, "[att trace] tile %d: S ready +0 | ld done %lld | exp done %lld | P stored %lld | barrier %lld | K,V ready %lld | MMAs issued %lld | next S ready %lld\n",
+                    t + 4, r[1] - r[0], r[2] - r[0], r[3] - r[0], r[4] - r[0], r[7] - r[0], r[6] - r[0],
                     t < 2 ? r[12] - r[0] : 0LL);
         }
     }

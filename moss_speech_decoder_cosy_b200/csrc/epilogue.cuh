@@ -49,6 +49,11 @@ __device__ __forceinline__ float fast_gelu_erf(float x) {
     p = fmaf(p, a, -9.999995828e-01f);
     return fmaf(-a, ex2_approx(p), fmaxf(x, 0.f));
 }
+#ifdef FFN_X_NOEX2   // timing experiment only: the GELU without its SFU instruction
+#define GELU_EX2(x) (x)
+#else
+#define GELU_EX2(x) ex2_approx(x)
+#endif
 // Two GELUs at once, packed to bf16x2: the degree-6 Horner and the final FMA run as FFMA2 (half the FMA-pipe instructions).
 __device__ __forceinline__ uint32_t gelu2_bf16(float x0, float x1) {
     const float a0 = fminf(fabsf(x0), 6.f), a1 = fminf(fabsf(x1), 6.f);
@@ -61,7 +66,7 @@ __device__ __forceinline__ uint32_t gelu2_bf16(float x0, float x1) {
     p = f2_fma(p, a, f2_pack(-9.999995828e-01f, -9.999995828e-01f));
     float p0, p1;
     f2_unpack(p, p0, p1);
-    const uint64_t r = f2_fma(f2_pack(-a0, -a1), f2_pack(ex2_approx(p0), ex2_approx(p1)), f2_pack(fmaxf(x0, 0.f), fmaxf(x1, 0.f)));
+    const uint64_t r = f2_fma(f2_pack(-a0, -a1), f2_pack(GELU_EX2(p0), GELU_EX2(p1)), f2_pack(fmaxf(x0, 0.f), fmaxf(x1, 0.f)));
     float r0, r1;
     f2_unpack(r, r0, r1);
     return pack_bf16x2(r0, r1);

@@ -7,14 +7,15 @@
 // The 1024-wide hidden activation never leaves the SM.  Per 128-row tile:
 //   X tile (128 x 256 bf16, 64 KB) is loaded once by TMA and stays in shared memory;
 //   for each of 8 hidden chunks of 128:  G1: acc1[b] = X . W1[chunk]^T        (tcgen05.mma M128 N128, K = 256)
-//                                        E1: acc1[b] -> +b1 -> GELU -> bf16 -> P[b] in shared memory, already in the
-//                                            128B-swizzled K-major layout the tensor core reads its A operand from
-//                                        G2: acc2 += P[b] . W2[:, chunk]^T    (tcgen05.mma M128 N256, K = 128)
+//                                        E1: acc1[b] -> +b1 -> GELU -> bf16 -> P[b], written back with tcgen05.st over
+//                                            the accumulator columns it was drained from
+//                                        G2: acc2 += P[b] . W2[:, chunk]^T    (tcgen05.mma M128 N256, K = 128, A from TMEM)
 //   acc2 is preloaded with hres + b2 through tcgen05.st at the start of the tile, so the MMAs accumulate the residual
 //   stream themselves;  final: acc2 -> registers -> hres (coalesced stores in the tiled fp32 layout), LayerNorm ->
 //   bf16 -> swizzled smem -> TMA store.
-// acc1 is double buffered in TMEM (2 x 128 columns) next to acc2 (256 columns), P is double buffered in shared memory,
-// so the GELU epilogue of chunk h overlaps G2(h-1) / G1(h+1) on the tensor pipe.  W1 / W2 stream through a 3-stage ring
+// acc1 (and with it P) is double buffered in TMEM (2 x 128 columns) next to acc2 (256 columns), so the GELU epilogue of
+// chunk h overlaps G2(h-1) / G1(h+1) on the tensor pipe.  The kernel is bound by shared-memory bandwidth (operand reads +
+// TMA fills, 128 B/clk/SM): keeping P out of shared memory takes 64 KB per chunk off that path.  W1 / W2 stream through a 4-stage ring
 // of 32 KB TMA stages (1 MB of weights per tile, L2 resident).
 //
 // Warp roles: warp 0 = TMA producer, warp 1 = MMA issuer (+ TMEM alloc), warps 2..17 = epilogue (thread == row; the 4
@@ -29,6 +30,8 @@
 namespace mossdec {
 
 bool encode_2d(CUtensorMap* m, const void* ptr, uint64_t cols, uint64_t rows, uint64_t ld, uint32_t box_rows);
+bool encode_2d_ex(CUtensorMap* m, const void* ptr, uint64_t cols, uint64_t rows, uint64_t ld, uint32_t box_cols,
+                  uint32_t box_rows, int swizzle64);
 
 namespace {
 
@@ -42,14 +45,12 @@ constexpr int kChunk = 128;      // hidden columns per chunk
 constexpr int kNChunk = kHid / kChunk;
 constexpr int kCluster = 2;      // CTAs per cluster: every weight stage is fetched from L2 once and multicast to both
 constexpr uint16_t kClusterMask = (1u << kCluster) - 1;
-constexpr int kFStages = 3;
+constexpr int kFStages = 4;   // L2 -> smem turnaround of a stage (both CTAs free it, refill, multicast) is ~1 700 clk against 512 clk of MMA
 constexpr int kFStageBytes = 32768;
 constexpr int kXBytes = kGemmBM * kC * 2;      // 64 KB
-constexpr int kPBytes = kGemmBM * kChunk * 2;  // 32 KB per buffer
-constexpr int kFfnSmem = kXBytes + 2 * kPBytes + kFStages * kFStageBytes + 1024 /*align*/ + 256 /*barriers*/;
+constexpr int kOutStageBytes = 2048;           // per epilogue warp: 32 rows x 32 bf16 (64B-swizzled), the box of the output TMA store
+constexpr int kFfnSmem = kXBytes + kEpiWarps * kOutStageBytes + kFStages * kFStageBytes + 1024 /*align*/ + 1024 /*b2*/ + 256 /*barriers*/;
 constexpr uint32_t kAcc2Col = 0, kAcc1Col = 256;
-constexpr int kOutStageBytes = 4096;           // per epilogue warp: 32 rows x 64 bf16, the box of the output TMA store
-static_assert(kEpiWarps * kOutStageBytes <= 2 * kPBytes, "final-epilogue staging tiles alias P[0] | P[1]");
 
 struct FfnParams {
     int32_t M, num_tiles;
@@ -64,7 +65,6 @@ struct FfnParams {
 };
 
 __device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
-__device__ __forceinline__ void epi_sync_all() { asm volatile("bar.sync 5, %0;" ::"n"(32 * kEpiWarps) : "memory"); }
 
 __global__ void __cluster_dims__(kCluster, 1, 1) __launch_bounds__(kThreads, 1)
 ffn_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmW1,
@@ -73,16 +73,17 @@ ffn_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ C
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);  // stays in the shared address space (STS / LDS)
     uint8_t* sX = smem;
-    uint8_t* sP = sX + kXBytes;
-    uint8_t* sRing = sP + 2 * kPBytes;
-    uint64_t* bars = reinterpret_cast<uint64_t*>(sRing + kFStages * kFStageBytes);
+    uint8_t* sStg = sX + kXBytes;                      // [16 warps][2 KB] bf16 output staging
+    uint8_t* sRing = sStg + kEpiWarps * kOutStageBytes;
+    float* sB2 = reinterpret_cast<float*>(sRing + kFStages * kFStageBytes);   // [256] second bias
+    uint64_t* bars = reinterpret_cast<uint64_t*>(sB2 + kC);
     uint64_t* full = bars;               // [kFStages]  TMA -> MMA
     uint64_t* empty = full + kFStages;   // [kFStages]  MMA -> TMA
     uint64_t* x_full = empty + kFStages; // TMA -> MMA
     uint64_t* x_free = x_full + 1;       // MMA -> TMA (all G1 of the tile done)
     uint64_t* a1_full = x_free + 1;      // [2] MMA -> epilogue
-    uint64_t* p_ready = a1_full + 2;     // [2] epilogue -> MMA: P[b] written, acc1[b] drained
-    uint64_t* p_free = p_ready + 2;      // [2] MMA -> epilogue: G2 finished reading P[b]
+    uint64_t* p_ready = a1_full + 2;     // [2] epilogue -> MMA: P[b] written over the drained acc1[b]
+    uint64_t* p_free = p_ready + 2;      // [2] (unused since P lives in TMEM: a1_full of G1(h + 2) implies G2(h) is done)
     uint64_t* acc2_full = p_free + 2;    // MMA -> epilogue
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc2_full + 1);
 
@@ -110,6 +111,7 @@ ffn_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ C
         mbar_init(acc2_full, 1);
         mbar_fence_init();
     }
+    if (threadIdx.x >= 64 && threadIdx.x < 64 + kC) sB2[threadIdx.x - 64] = __ldg(p.b2 + threadIdx.x - 64);
     if (warp == 1) {
         tmem_alloc(tmem_slot, kTmemCols);
         tmem_relinquish();
@@ -170,9 +172,9 @@ ffn_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ C
                     l2_prefetch_bulk(p.hres + (size_t)(tile + gridDim.x) * kGemmBM * kC, kGemmBM * kC * 4);
                 load_g1(0);
                 load_g1(1);
-                for (int h = 0; h < kNChunk; ++h) {
-                    if (h + 2 < kNChunk) load_g1(h + 2);
+                for (int h = 0; h < kNChunk; ++h) {   // same order as the MMA warp consumes the ring
                     load_g2(h);
+                    if (h + 2 < kNChunk) load_g1(h + 2);
                 }
             }
         }
@@ -223,13 +225,16 @@ ffn_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ C
                     if (mtr) w_full += clock64() - t0;
                     tc_fence_after();
                     if (elect_one()) {
-                        const uint64_t da = umma_desc_sw128(smem_u32(sP + b * kPBytes + j * kABytes));
+                        // A = P[b] straight from tensor memory (bf16 pairs, written by E1 over the drained acc1[b]):
+                        // K-step kk covers hidden [16 kk, +16) = words [8 (kk & 1), +8) of epilogue part kk >> 1
+                        const uint32_t pa = tmem_base + kAcc1Col + (uint32_t)(b * kChunk);
                         const uint64_t db = umma_desc_sw128(smem_u32(sRing + stage * kFStageBytes));
 #pragma unroll
-                        for (int k = 0; k < kGemmBK / 16; ++k)
-                            umma_bf16(d, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc2, 1u);  // acc2 was preloaded with hres + b2
+                        for (int k = 0; k < kGemmBK / 16; ++k) {
+                            const int kk = j * (kGemmBK / 16) + k;
+                            umma_bf16_ts(d, pa + (uint32_t)((kk >> 1) * 32 + (kk & 1) * 8), db + (uint64_t)(2 * k), idesc2, 1u);  // acc2 was preloaded with hres + b2
+                        }
                         umma_commit_mc(&empty[stage], kClusterMask);   // the stage is refilled by both CTAs: both must see it free
-                        if (j == 1) umma_commit(&p_free[b]);
                     }
                     next_stage();
                 }
@@ -250,9 +255,9 @@ ffn_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ C
                     tc_fence_after();
                     if (mtr) w_ready += clock64() - t0;
                     if (mtr) p.trace[it * 48 + 33 + h] = clock64();
-                    if (h + 2 < kNChunk) g1(b);            // G1 first: its result is what the epilogue waits for next
+                    g2(h);                                 // reads P[b] where acc1[b] was ...
+                    if (h + 2 < kNChunk) g1(b);            // ... so the G1 that overwrites acc1[b] follows it on the (in-order) tensor pipe
                     if (h + 2 == kNChunk - 1 && elect_one()) umma_commit(x_free);  // last G1 of the tile issued: X may be reloaded
-                    g2(h);
                 }
                 if (elect_one()) umma_commit(acc2_full);
                 if (mtr) {
@@ -269,9 +274,8 @@ ffn_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ C
         const int part = ew >> 2;
         const int quarter = warp & 3;
         const int trow = quarter * 32 + lane;  // row of the tile owned by this thread
-        // per-warp 4 KB staging tile (32 rows x 128 B, 128B-swizzled) for the bf16 TMA store; the 16 tiles alias
-        // P[0] | P[1], which no MMA reads between acc2_full and the next tile's first E1
-        uint8_t* stg = sP + ew * kOutStageBytes;
+        // per-warp 4 KB staging tile (32 rows x 128 B, 128B-swizzled) for the bf16 TMA store
+        uint8_t* stg = sStg + ew * kOutStageBytes;
         const uint32_t tlane = tmem_base + ((uint32_t)(quarter * 32) << 16);
         uint32_t a1_phase[2] = {0, 0};
         int it = 0;
@@ -289,25 +293,24 @@ ffn_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ C
             // publishes the stores to the MMA thread.
             {
                 const float* hrow = p.hres + tiled_f32_offset(row, part * 64);  // float4 j of the row: + j * 512 floats
+                float4 t[16];   // all 16 loads of the thread in flight at once: one L2 round trip per tile, not four
+#pragma unroll
+                for (int j = 0; j < 16; ++j) {
+                    t[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+                    if (live) t[j] = *reinterpret_cast<const float4*>(hrow + (size_t)j * 512);
+                }
 #pragma unroll
                 for (int q = 0; q < 4; ++q) {
                     float r[16];
 #pragma unroll
                     for (int i = 0; i < 16; i += 4) {
-                        float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
-                        if (live) t = *reinterpret_cast<const float4*>(hrow + (size_t)(q * 4 + (i >> 2)) * 512);
-                        const float4 bb = ldg4(p.b2 + part * 64 + q * 16 + i);
-                        r[i] = t.x + bb.x; r[i + 1] = t.y + bb.y; r[i + 2] = t.z + bb.z; r[i + 3] = t.w + bb.w;
+                        const float4 bb = *reinterpret_cast<const float4*>(sB2 + part * 64 + q * 16 + i);   // broadcast LDS
+                        const float4 tt = t[q * 4 + (i >> 2)];
+                        r[i] = tt.x + bb.x; r[i + 1] = tt.y + bb.y; r[i + 2] = tt.z + bb.z; r[i + 3] = tt.w + bb.w;
                     }
                     tmem_st16(tlane + kAcc2Col + (uint32_t)(part * 64 + q * 16), r);
                 }
                 tmem_st_wait();
-            }
-            // the previous tile's bf16 TMA store must have finished reading the staging tiles (= P) before any warp's
-            // E1 overwrites them; its latency hid behind the preload above
-            if (it > 0) {
-                if (lane == 0) tma_store_wait_read();
-                epi_sync_all();
             }
             FFN_STAMP(1);
 
@@ -320,8 +323,15 @@ ffn_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ C
             a1_phase[0] ^= 1;
             tc_fence_after();
             tmem_ld16(tlane + kAcc1Col + (uint32_t)(part * 32), va);
+            bool have_va = true;
             for (int h = 0; h < kNChunk; ++h) {
                 const int b = h & 1;
+                if (!have_va) {   // the accumulator was not ready when the previous chunk looked: wait for it now
+                    mbar_wait(&a1_full[b], a1_phase[b]);
+                    a1_phase[b] ^= 1;
+                    tc_fence_after();
+                    tmem_ld16(tlane + kAcc1Col + (uint32_t)(b * kChunk + part * 32), va);
+                }
                 const float* bp = p.b1 + h * kChunk + part * 32;
                 float4 bias[4];
 #pragma unroll
@@ -338,27 +348,24 @@ ffn_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ C
 #pragma unroll
                 for (int i = 0; i < 4; ++i) bias[i] = ldg4(bp + 16 + 4 * i);
                 tmem_ld_wait();   // vb of this chunk: acc1[b] is now fully drained by this thread
-                if (h + 1 < kNChunk) {   // first half of the next chunk (other accumulator buffer) flies during the math below
-                    mbar_wait(&a1_full[b ^ 1], a1_phase[b ^ 1]);
+                // first half of the next chunk (other accumulator buffer) flies during the math below -- if G1 has already
+                // delivered it.  Only probed: blocking here would put G2(h - 1) + G1(h + 1) into every chunk's critical path.
+                have_va = false;
+                if (h + 1 < kNChunk && __shfl_sync(0xffffffffu, (int)mbar_test(&a1_full[b ^ 1], a1_phase[b ^ 1]), 0)) {
                     a1_phase[b ^ 1] ^= 1;
                     tc_fence_after();
                     tmem_ld16(tlane + kAcc1Col + (uint32_t)((b ^ 1) * kChunk + part * 32), va);
+                    have_va = true;
                 }
 #pragma unroll
                 for (int i = 0; i < 4; ++i) {
                     pk[8 + 2 * i] = gelu2_bf16(vb[4 * i] + bias[i].x, vb[4 * i + 1] + bias[i].y);
                     pk[8 + 2 * i + 1] = gelu2_bf16(vb[4 * i + 2] + bias[i].z, vb[4 * i + 3] + bias[i].w);
                 }
-                // P[b] is only needed now: G2(h - 2) must have finished reading it (its latency hid behind the GELU math)
-                if (h >= 2) mbar_wait(&p_free[b], (uint32_t)(((h - 2) >> 1) & 1));
-                // K-major SW128 operand layout: k-block (64 hidden) = 128 rows x 128 B, 16-byte units XOR row % 8
-                uint8_t* prow = sP + b * kPBytes + (part >> 1) * kABytes + trow * 128;
-                const int ub = (part & 1) * 4;
-#pragma unroll
-                for (int u = 0; u < 4; ++u)
-                    *reinterpret_cast<uint4*>(prow + (((ub + u) ^ (trow & 7)) << 4)) =
-                        make_uint4(pk[4 * u], pk[4 * u + 1], pk[4 * u + 2], pk[4 * u + 3]);
-                fence_proxy_async_smem();
+                // P[b] goes back into tensor memory, over the first 16 of the 32 accumulator columns this thread has just
+                // drained (no other thread reads them): G2 takes its A operand from there, no shared-memory round trip
+                tmem_st16(tlane + kAcc1Col + (uint32_t)(b * kChunk + part * 32), reinterpret_cast<const float*>(pk));
+                tmem_st_wait();
                 tc_fence_before();
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&p_ready[b]);
@@ -396,6 +403,8 @@ ffn_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ C
                     }
                 }
             }
+            if (lane == 0) tma_store_wait_read();   // the previous tile's last store has long finished reading this staging tile
+            __syncwarp();
             if (p.ln) {   // (x - mean) * rstd; gamma / beta live in the consumer's weights
                 // row statistics over the 4 warps that share this TMEM lane quarter (slot = head of the staging tile)
                 reinterpret_cast<float2*>(stg)[lane] = make_float2(s, ss);
@@ -404,7 +413,7 @@ ffn_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ C
                 ss = 0.f;
 #pragma unroll
                 for (int q = 0; q < kEpiParts; ++q) {
-                    const float2 o = reinterpret_cast<const float2*>(sP + ((q << 2) | (ew & 3)) * kOutStageBytes)[lane];
+                    const float2 o = reinterpret_cast<const float2*>(sStg + ((q << 2) | (ew & 3)) * kOutStageBytes)[lane];
                     s += o.x;
                     ss += o.y;
                 }
@@ -415,21 +424,29 @@ ffn_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ C
 #pragma unroll
                 for (int i = 0; i < 64; ++i) v[i] = fmaf(v[i], a, bsh);
             }
-            // bf16 tile of this warp (32 rows x 64 columns) -> swizzled staging -> one TMA store
+            // bf16 tile of this warp (32 rows x 64 columns) -> 64B-swizzled 2 KB staging -> two TMA stores of 32 columns
 #pragma unroll
-            for (int u = 0; u < 8; ++u) {
-                uint4 t;
-                t.x = pack_bf16x2(v[u * 8], v[u * 8 + 1]);
-                t.y = pack_bf16x2(v[u * 8 + 2], v[u * 8 + 3]);
-                t.z = pack_bf16x2(v[u * 8 + 4], v[u * 8 + 5]);
-                t.w = pack_bf16x2(v[u * 8 + 6], v[u * 8 + 7]);
-                *reinterpret_cast<uint4*>(stg + lane * 128 + ((u ^ (lane & 7)) << 4)) = t;
-            }
-            fence_proxy_async_smem();
-            __syncwarp();
-            if (lane == 0 && live) {
-                tma_store_2d(&tmOut, stg, part * 64, tile * kGemmBM + quarter * 32);
-                tma_store_commit();
+            for (int hh = 0; hh < 2; ++hh) {
+                if (hh == 1) {
+                    if (lane == 0) tma_store_wait_read();
+                    __syncwarp();
+                }
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    const float* w = v + hh * 32 + u * 8;
+                    uint4 t;
+                    t.x = pack_bf16x2(w[0], w[1]);
+                    t.y = pack_bf16x2(w[2], w[3]);
+                    t.z = pack_bf16x2(w[4], w[5]);
+                    t.w = pack_bf16x2(w[6], w[7]);
+                    *reinterpret_cast<uint4*>(stg + lane * 64 + ((u ^ ((lane >> 1) & 3)) << 4)) = t;
+                }
+                fence_proxy_async_smem();
+                __syncwarp();
+                if (lane == 0 && live) {
+                    tma_store_2d(&tmOut, stg, part * 64 + hh * 32, tile * kGemmBM + quarter * 32);
+                    tma_store_commit();
+                }
             }
             FFN_STAMP(19);
         }
@@ -471,7 +488,7 @@ cudaError_t ffn_tc_launch(const FfnProblem& f, int num_sms, cudaStream_t stream)
     if (!encode_2d(&tX, f.x, kC, (uint64_t)f.M, kC, kGemmBM)) return cudaErrorInvalidValue;
     if (!encode_2d(&tW1, f.w1, kC, kHid, kC, kChunk)) return cudaErrorInvalidValue;
     if (!encode_2d(&tW2, f.w2, kHid, kC, kHid, kC / kCluster)) return cudaErrorInvalidValue;
-    if (!encode_2d(&tOut, f.out_bf16, kC, (uint64_t)f.M, (uint64_t)f.ldo, 32)) return cudaErrorInvalidValue;
+    if (!encode_2d_ex(&tOut, f.out_bf16, kC, (uint64_t)f.M, (uint64_t)f.ldo, 32, 32, 1)) return cudaErrorInvalidValue;
 
     int grid = (p.num_tiles + kCluster - 1) / kCluster * kCluster;
     if (grid > num_sms) grid = num_sms / kCluster * kCluster;
