@@ -9,6 +9,7 @@
 #include "epilogue.cuh"
 
 #include <mutex>
+#include <stdlib.h>
 #include <stdio.h>
 
 namespace mossdec {
@@ -268,7 +269,133 @@ __device__ __forceinline__ void epi_resln(const EpiCtx& c, const CUtensorMap* tm
     }
 }
 
-// kMode: 0 = general epilogue, 1 = epi_fast (bias + act -> bf16), 2 = epi_resln (residual + LayerNorm)
+// ---- the two conv blocks of a resnet (cosyvoice decoder.py:65-78, matcha decoder.py:49-61), N == BN == 256:
+//   kRes == false:  mask(mish(LayerNorm(acc + bias))) + time bias                       -> bf16            (block1)
+//   kRes == true :  mask(mish(LayerNorm(acc + bias))) + fp32 residual -> fp32 stream, plain LayerNorm -> bf16 (block2)
+// The accumulator is read ONCE (pipelined 16-column drains) into 64 registers per thread and handed back to the MMA warp
+// before any of the math, so LayerNorm + Mish + the second LayerNorm run behind the next tile's MMAs.  bias comes from
+// shared memory (sBias, filled once per CTA), gamma / beta and the addend are prefetched one 16-column group ahead.
+template <bool kRes>
+__device__ __forceinline__ void epi_lnact(const EpiCtx& c, const CUtensorMap* tmOut, int part, uint32_t tmem_acc,
+                                          uint64_t* tfull_bar, uint32_t tfull_phase, uint64_t* tempty_bar,
+                                          const float* sBias) {
+    const KParams& p = *c.p;
+    const GemmEpilogue& e = p.epi;
+    const int row = c.row0 + c.lane;
+    const int n = part * 64;
+    float v[64];
+    mbar_wait(tfull_bar, tfull_phase);
+    tc_fence_after();
+    const uint32_t ta = tmem_acc + (uint32_t)n;
+    float s = 0.f, ss = 0.f;
+    {
+        float t0[16], t1[16];
+        tmem_ld16(ta, t0);
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            float* t = (q & 1) ? t1 : t0;
+            tmem_ld_wait();
+            if (q < 3) tmem_ld16(ta + (q + 1) * 16, (q & 1) ? t0 : t1);
+            if (q == 3) {   // accumulator fully read: hand it back to the MMA warp
+                tc_fence_before();
+                __syncwarp();
+                if (c.lane == 0) mbar_arrive(tempty_bar);
+            }
+            float* w = v + q * 16;
+#pragma unroll
+            for (int i = 0; i < 16; i += 4) {
+                const float4 b = *reinterpret_cast<const float4*>(sBias + n + q * 16 + i);   // broadcast LDS
+                w[i] = t[i] + b.x; w[i + 1] = t[i + 1] + b.y; w[i + 2] = t[i + 2] + b.z; w[i + 3] = t[i + 3] + b.w;
+            }
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+                s += w[i];
+                ss = fmaf(w[i], w[i], ss);
+            }
+        }
+    }
+    if (c.lane == 0) tma_store_wait_read();   // the exchange slot is the head of the staging tile the last store read
+    __syncwarp();
+#ifdef LNACT_X_NOEXCH
+    const float2 tot = make_float2(s * 4.f, ss * 4.f);
+#else
+    const float2 tot = group_exchange(c, make_float2(s, ss));
+#endif
+    const float mean = tot.x * (1.f / 256.f);
+    const float rstd = rsqrtf(fmaxf(tot.y * (1.f / 256.f) - mean * mean, 0.f) + e.ln_eps);
+
+    // addend of 16 columns: fp32 residual (lane-major tiled layout) or the time bias row of this row's sequence
+    const float* addp = kRes ? e.resid + tiled_f32_offset(row, n)
+                             : (e.tbias ? e.tbias + (size_t)(c.seq < 0 ? 0 : c.seq) * e.tbias_ld + n : nullptr);
+    // groups of 4 columns, the three parameter vectors of the next group in flight while this one goes through the math
+    auto load4 = [&](int u, float4& a, float4& g, float4& bt) {
+        if (kRes) a = *reinterpret_cast<const float4*>(addp + (size_t)u * 512);
+        else a = addp ? ldg4(addp + 4 * u) : make_float4(0.f, 0.f, 0.f, 0.f);
+        g = ldg4(e.ln1_g + n + 4 * u);
+        bt = ldg4(e.ln1_b + n + 4 * u);
+    };
+    float4 an, gn, bn;
+    load4(0, an, gn, bn);
+    float s2 = 0.f, ss2 = 0.f;
+    const float nmr = -mean * rstd;
+    const float vmask = c.valid ? 1.f : 0.f;
+#pragma unroll
+    for (int u = 0; u < 16; ++u) {
+        const float4 a = an, g = gn, bt = bn;
+        if (u < 15) load4(u + 1, an, gn, bn);
+        float* w = v + 4 * u;
+        const float gx[4] = {g.x, g.y, g.z, g.w}, bx[4] = {bt.x, bt.y, bt.z, bt.w}, ax[4] = {a.x, a.y, a.z, a.w};
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const float y = fmaf(fmaf(w[k], rstd, nmr), gx[k], bx[k]);
+            // (masking by multiplication: a per-element "valid ? f(y) : 0" becomes a branch around every Mish, which
+            //  serialises the unrolled loop; all inputs are finite, padding rows included)
+            w[k] = (fast_mish(y) + ax[k]) * vmask;
+        }
+        if (kRes) {
+            *reinterpret_cast<float4*>(e.out_f32 + tiled_f32_offset(row, n) + (size_t)u * 512) = make_float4(w[0], w[1], w[2], w[3]);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                s2 += w[k];
+                ss2 = fmaf(w[k], w[k], ss2);
+            }
+        }
+    }
+    float a = 1.f, bsh = 0.f;
+    if (kRes) {
+        const float2 t2 = group_exchange(c, make_float2(s2, ss2));
+        const float mean2 = t2.x * (1.f / 256.f);
+        const float rstd2 = rsqrtf(fmaxf(t2.y * (1.f / 256.f) - mean2 * mean2, 0.f) + e.ln_eps);
+        a = c.valid ? rstd2 : 0.f;
+        bsh = c.valid ? -mean2 * rstd2 : 0.f;
+    }
+#pragma unroll
+    for (int hlf = 0; hlf < 2; ++hlf) {
+        float* w = v + hlf * 32;
+        if (hlf == 1) {
+            if (c.lane == 0) tma_store_wait_read();
+            __syncwarp();
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            uint4 t;
+            t.x = pack_bf16x2(fmaf(w[u * 8], a, bsh), fmaf(w[u * 8 + 1], a, bsh));
+            t.y = pack_bf16x2(fmaf(w[u * 8 + 2], a, bsh), fmaf(w[u * 8 + 3], a, bsh));
+            t.z = pack_bf16x2(fmaf(w[u * 8 + 4], a, bsh), fmaf(w[u * 8 + 5], a, bsh));
+            t.w = pack_bf16x2(fmaf(w[u * 8 + 6], a, bsh), fmaf(w[u * 8 + 7], a, bsh));
+            *reinterpret_cast<uint4*>(c.stg + c.lane * 64 + ((u ^ ((c.lane >> 1) & 3)) << 4)) = t;
+        }
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        __syncwarp();
+        if (c.lane == 0) {
+            tma_store_2d(tmOut, c.stg, n + hlf * 32, c.row0);
+            tma_store_commit();
+        }
+    }
+}
+
+// kMode: 0 = general epilogue, 1 = epi_fast (bias + act -> bf16), 2 = epi_resln (residual + LayerNorm),
+//        3 / 4 = epi_lnact (LayerNorm + Mish resnet blocks without / with residual + second LayerNorm)
 template <int kMode>
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__ CUtensorMap tmA1,
@@ -285,6 +412,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
     uint64_t* tfull = bars + 2 * kGemmStages;  // [2]
     uint64_t* tempty = tfull + 2;              // [2]
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
+    float* sBias = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(bars) + 256);   // [256], modes 3 / 4 only
 
     // (shuffle broadcasts mark values as warp-uniform for the compiler: descriptors and loop state of the TMA / MMA
     //  warps then live in uniform registers and every tcgen05.mma / TMA is a single instruction, not a per-lane loop)
@@ -306,6 +434,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
         }
         mbar_fence_init();
     }
+    if (kMode >= 3 && threadIdx.x >= 64 && threadIdx.x < 64 + 256) sBias[threadIdx.x - 64] = __ldg(p.epi.bias + threadIdx.x - 64);
     if (warp == 1) {
         tmem_alloc(tmem_slot, kTmemCols);
         tmem_relinquish();
@@ -408,6 +537,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
             c.taddr = tmem_base + ((uint32_t)(c.quarter * 32) << 16) + (uint32_t)acc * 256u;
             if constexpr (kMode == 2) {
                 epi_resln(c, &tmOut, part, c.taddr, &tfull[acc], accphase, &tempty[acc]);
+                acc ^= 1;
+                if (acc == 0) accphase ^= 1;
+                continue;
+            }
+            if constexpr (kMode >= 3) {
+                epi_lnact<kMode == 4>(c, &tmOut, part, c.taddr, &tfull[acc], accphase, &tempty[acc], sBias);
                 acc ^= 1;
                 if (acc == 0) accphase ^= 1;
                 continue;
@@ -565,6 +700,10 @@ cudaError_t gemm_tc_launch(const GemmProblem& g, int num_sms, cudaStream_t strea
             attr_err = cudaFuncSetAttribute(gemm_tc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
         if (attr_err == cudaSuccess)
             attr_err = cudaFuncSetAttribute(gemm_tc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
+        if (attr_err == cudaSuccess)
+            attr_err = cudaFuncSetAttribute(gemm_tc_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes + 1024);
+        if (attr_err == cudaSuccess)
+            attr_err = cudaFuncSetAttribute(gemm_tc_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes + 1024);
     });
     if (attr_err != cudaSuccess) return attr_err;
 
@@ -606,12 +745,22 @@ cudaError_t gemm_tc_launch(const GemmProblem& g, int num_sms, cudaStream_t strea
                        !e.ln1_g && !e.ln2_g && !e.tbias && !e.out_bf16_lo && !e.accum_f32 && e.act1 == ACT_NONE &&
                        e.act2 == ACT_NONE && e.out_scale == 1.f && g.BN == 256 && g.N == 256 && (g.M % kGemmBM) == 0 &&
                        (e.ldo % 8) == 0 && (reinterpret_cast<uintptr_t>(e.out_bf16) & 15) == 0;
+    // LayerNorm + Mish conv blocks of the resnets (epi_lnact): block1 (+ time bias) and block2 (+ residual + next LayerNorm)
+    const bool ln_common = e.out_bf16 != nullptr && e.ln1_g && e.ln1_b && e.bias && e.act1 == ACT_MISH && !e.ln2_g &&
+                           !e.out_bf16_lo && !e.accum_f32 && e.act2 == ACT_NONE && e.out_scale == 1.f && g.BN == 256 &&
+                           g.N == 256 && (g.M % kGemmBM) == 0 && (e.ldo % 8) == 0 &&
+                           (reinterpret_cast<uintptr_t>(e.out_bf16) & 15) == 0;
+    static const bool force_general = getenv("MOSSDEC_GEMM_GENERAL") != nullptr;   // A/B aid: every epilogue through mode 0
+    const bool lnact_a = !force_general && ln_common && !e.out_f32 && !e.resid && !e.ln2_plain && (!e.tbias || (e.tbias_ld % 4) == 0);
+    const bool lnact_b = !force_general && ln_common && e.out_f32 != nullptr && e.resid != nullptr && e.f32_tiled && e.ln2_plain && !e.tbias;
     CUtensorMap tOut = tB;
-    if ((kp.fast_bf16 || resln) && !encode_2d_ex(&tOut, e.out_bf16, (uint64_t)g.N, (uint64_t)g.M, (uint64_t)e.ldo, 32, 32, 1))
+    if ((kp.fast_bf16 || resln || lnact_a || lnact_b) && !encode_2d_ex(&tOut, e.out_bf16, (uint64_t)g.N, (uint64_t)g.M, (uint64_t)e.ldo, 32, 32, 1))
         return cudaErrorInvalidValue;
 
     const int grid = kp.num_tiles < num_sms ? kp.num_tiles : num_sms;
-    if (resln) gemm_tc_kernel<2><<<grid, kThreads, kSmemBytes, stream>>>(tA0, tA1, tB, tOut, kp);
+    if (lnact_a) gemm_tc_kernel<3><<<grid, kThreads, kSmemBytes + 1024, stream>>>(tA0, tA1, tB, tOut, kp);
+    else if (lnact_b) gemm_tc_kernel<4><<<grid, kThreads, kSmemBytes + 1024, stream>>>(tA0, tA1, tB, tOut, kp);
+    else if (resln) gemm_tc_kernel<2><<<grid, kThreads, kSmemBytes, stream>>>(tA0, tA1, tB, tOut, kp);
     else if (kp.fast_bf16) gemm_tc_kernel<1><<<grid, kThreads, kSmemBytes, stream>>>(tA0, tA1, tB, tOut, kp);
     else gemm_tc_kernel<0><<<grid, kThreads, kSmemBytes, stream>>>(tA0, tA1, tB, tOut, kp);
     return cudaGetLastError();

@@ -217,6 +217,12 @@ __host__ __device__ __forceinline__ uint32_t umma_idesc_bf16(uint32_t M, uint32_
 }
 
 // ---------------------------------------------------------------- math helpers
+// reciprocal on the SFU, no range fix-up branches (the __fdividef intrinsic compiles to a guarded slow path per element)
+__device__ __forceinline__ float rcp_approx(float x) {
+    float y;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
 __device__ __forceinline__ float mish_f(float x) {
     // x * tanh(softplus(x)); softplus threshold 20 like torch
     float sp = x > 20.f ? x : log1pf(__expf(x));

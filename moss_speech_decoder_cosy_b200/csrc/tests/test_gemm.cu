@@ -47,6 +47,7 @@ struct Case {
     int num_segs;
     GemmSeg segs[kGemmMaxSegs];
     bool bias, ln1, rowseq, tbias, resid, accum, outf32, outbf16, ln2;
+    bool tiled = false;   // fp32 residual / output in the lane-major tiled layout, second LayerNorm without affine (N == 256)
     int act1, act2;
     float scale;
 };
@@ -108,7 +109,15 @@ static int run_case(const Case& c, int num_sms) {
         CK(cudaMemcpy(*d, h.data(), h.size() * 4, cudaMemcpyHostToDevice));
     };
     up(&dbias, bias); up(&dg1, g1); up(&db1, b1); up(&dg2, g2); up(&db2, b2); up(&dalpha, alpha); up(&dtb, tb);
-    up(&dresid, resid); up(&dOf, outf_init);
+    if (c.tiled) {   // device copy of the residual in the tiled layout
+        std::vector<float> rt(resid.size());
+        for (int r = 0; r < Mpad; ++r)
+            for (int n = 0; n < c.N; ++n) rt[tiled_f32_offset(r, n)] = resid[(size_t)r * c.N + n];
+        up(&dresid, rt);
+    } else {
+        up(&dresid, resid);
+    }
+    up(&dOf, outf_init);
     CK(cudaMalloc(&drs, Mpad * 4));
     CK(cudaMemcpy(drs, rowseq.data(), Mpad * 4, cudaMemcpyHostToDevice));
     CK(cudaMalloc(&dOb, (size_t)Mpad * c.N * 2));
@@ -133,10 +142,23 @@ static int run_case(const Case& c, int num_sms) {
     e.accum_f32 = c.accum; e.out_scale = c.scale;
     if (c.outf32 || c.accum) { e.out_f32 = dOf; e.ldf = c.N; }
     if (c.outbf16) { e.out_bf16 = dOb; e.ldo = c.N; }
-    if (c.ln2) { e.ln2_g = dg2; e.ln2_b = db2; }
+    if (c.ln2 && !c.tiled) { e.ln2_g = dg2; e.ln2_b = db2; }
+    if (c.tiled) { e.f32_tiled = 1; e.ln2_plain = c.ln2 ? 1 : 0; }
     e.act2 = c.act2; e.act2_p = 0.1f; e.act2_alpha = dalpha;
 
     cudaError_t err = gemm_tc_launch(g, num_sms, 0);
+    if (getenv("GEMM_BENCH") && c.M > 20000) {
+        cudaEvent_t e0, e1;
+        cudaEventCreate(&e0); cudaEventCreate(&e1);
+        for (int i = 0; i < 3; ++i) gemm_tc_launch(g, num_sms, 0);
+        cudaEventRecord(e0);
+        for (int i = 0; i < 10; ++i) gemm_tc_launch(g, num_sms, 0);
+        cudaEventRecord(e1);
+        cudaDeviceSynchronize();
+        float ms = 0;
+        cudaEventElapsedTime(&ms, e0, e1);
+        printf("[%s] %.1f us per launch\n", c.name, ms * 100.f);
+    }
     if (err != cudaSuccess) { printf("[%s] launch error %s\n", c.name, cudaGetErrorString(err)); return 1; }
     err = cudaDeviceSynchronize();
     if (err != cudaSuccess) { printf("[%s] exec error %s\n", c.name, cudaGetErrorString(err)); exit(3); }
@@ -190,7 +212,7 @@ static int run_case(const Case& c, int num_sms) {
             v[n] = x;
         }
         if (c.outf32 || c.accum)
-            for (int n = 0; n < c.N; ++n) max_ef = fmax(max_ef, fabs(v[n] - of[(size_t)r * c.N + n]));
+            for (int n = 0; n < c.N; ++n) max_ef = fmax(max_ef, fabs(v[n] - of[c.tiled ? tiled_f32_offset(r, n) : (size_t)r * c.N + n]));
         if (c.outbf16) {
             if (c.ln2) {
                 double m = 0, q = 0;
@@ -198,7 +220,7 @@ static int run_case(const Case& c, int num_sms) {
                 m /= c.N;
                 for (int n = 0; n < c.N; ++n) q += (v[n] - m) * (v[n] - m);
                 double rs = 1.0 / sqrt(q / c.N + 1e-5);
-                for (int n = 0; n < c.N; ++n) v[n] = valid ? (v[n] - m) * rs * g2[n] + b2[n] : 0;
+                for (int n = 0; n < c.N; ++n) v[n] = valid ? (c.tiled ? (v[n] - m) * rs : (v[n] - m) * rs * g2[n] + b2[n]) : 0;
             } else if (c.act2 != ACT_NONE) {
                 for (int n = 0; n < c.N; ++n) v[n] = valid ? act_ref(v[n], c.act2, 0.1, alpha[n]) : 0;
             }
@@ -269,6 +291,55 @@ int main() {
         c.segs[0] = {0, -2, 0, 4}; c.segs[1] = {0, -1, 0, 4}; c.segs[2] = {0, 0, 0, 4};
         c.ln1 = true; c.act1 = ACT_MISH; c.rowseq = true; c.resid = true; c.outf32 = true; c.ln2 = true;
         fails += run_case(c, sms);
+    }
+    {   // 6b. same on whole tiles: LayerNorm + Mish + time bias through the register-resident epilogue (mode 3)
+        Case c = base("conv3_ln_mish_lnact", 3072, 256, 256, 320);
+        c.num_segs = 3;
+        c.segs[0] = {0, -2, 0, 5}; c.segs[1] = {0, -1, 0, 5}; c.segs[2] = {0, 0, 0, 5};
+        c.ln1 = true; c.act1 = ACT_MISH; c.rowseq = true; c.tbias = true;
+        fails += run_case(c, sms);
+    }
+    {   // 7b. resnet block2 on whole tiles, tiled fp32 stream, plain second LayerNorm (mode 4)
+        Case c = base("conv3_ln_mish_res_ln2_lnact", 83712 / 4, 256, 256, 256);
+        c.num_segs = 3;
+        c.segs[0] = {0, -2, 0, 4}; c.segs[1] = {0, -1, 0, 4}; c.segs[2] = {0, 0, 0, 4};
+        c.ln1 = true; c.act1 = ACT_MISH; c.rowseq = true; c.resid = true; c.outf32 = true; c.ln2 = true; c.tiled = true;
+        fails += run_case(c, sms);
+    }
+    if (getenv("GEMM_BENCH")) {   // config-2 sized resnet blocks (timing)
+        {
+            Case c = base("bench_block1_lnact", 83712, 256, 256, 256);
+            c.num_segs = 3;
+            c.segs[0] = {0, -2, 0, 4}; c.segs[1] = {0, -1, 0, 4}; c.segs[2] = {0, 0, 0, 4};
+            c.ln1 = true; c.act1 = ACT_MISH; c.rowseq = true; c.tbias = true;
+            fails += run_case(c, sms);
+        }
+        {
+            Case c = base("bench_block2_lnact", 83712, 256, 256, 256);
+            c.num_segs = 3;
+            c.segs[0] = {0, -2, 0, 4}; c.segs[1] = {0, -1, 0, 4}; c.segs[2] = {0, 0, 0, 4};
+            c.ln1 = true; c.act1 = ACT_MISH; c.rowseq = true; c.resid = true; c.outf32 = true; c.ln2 = true; c.tiled = true;
+            fails += run_case(c, sms);
+        }
+        {
+            Case c = base("bench_conv3_plain_bf16", 83712, 256, 256, 256);
+            c.num_segs = 3;
+            c.segs[0] = {0, -2, 0, 4}; c.segs[1] = {0, -1, 0, 4}; c.segs[2] = {0, 0, 0, 4};
+            fails += run_case(c, sms);
+        }
+        {
+            Case c = base("bench_dense_k768_lnact", 83712, 256, 256, 768);
+            c.ln1 = true; c.act1 = ACT_MISH; c.rowseq = true; c.tbias = true;
+            fails += run_case(c, sms);
+        }
+        {
+            Case c = base("bench_dense_k768_bf16", 83712, 256, 256, 768);
+            fails += run_case(c, sms);
+        }
+        {
+            Case c = base("bench_qkv", 83712, 1536, 256, 256);
+            fails += run_case(c, sms);
+        }
     }
     {   // 8. N=80 projection
         Case c = base("proj_n80", 1500, 80, 80, 256); c.outf32 = true; c.outbf16 = false; c.rowseq = true;
