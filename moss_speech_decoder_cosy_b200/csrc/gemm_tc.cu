@@ -269,14 +269,15 @@ __device__ __forceinline__ void epi_resln(const EpiCtx& c, const CUtensorMap* tm
     }
 }
 
-// ---- the two conv blocks of a resnet (cosyvoice decoder.py:65-78, matcha decoder.py:49-61), N == BN == 256:
+// ---- single-drain variant of the resnet conv epilogue below (used for block1, where it measured 40 us against 51 us for
+// the two-pass form; block2 is the other way round, 77 us against 74 us):
 //   kRes == false:  mask(mish(LayerNorm(acc + bias))) + time bias                       -> bf16            (block1)
 //   kRes == true :  mask(mish(LayerNorm(acc + bias))) + fp32 residual -> fp32 stream, plain LayerNorm -> bf16 (block2)
 // The accumulator is read ONCE (pipelined 16-column drains) into 64 registers per thread and handed back to the MMA warp
 // before any of the math, so LayerNorm + Mish + the second LayerNorm run behind the next tile's MMAs.  bias comes from
 // shared memory (sBias, filled once per CTA), gamma / beta and the addend are prefetched one 16-column group ahead.
 template <bool kRes>
-__device__ __forceinline__ void epi_lnact(const EpiCtx& c, const CUtensorMap* tmOut, int part, uint32_t tmem_acc,
+__device__ __forceinline__ void epi_lnact_single(const EpiCtx& c, const CUtensorMap* tmOut, int part, uint32_t tmem_acc,
                                           uint64_t* tfull_bar, uint32_t tfull_phase, uint64_t* tempty_bar,
                                           const float* sBias) {
     const KParams& p = *c.p;
@@ -358,6 +359,136 @@ __device__ __forceinline__ void epi_lnact(const EpiCtx& c, const CUtensorMap* tm
             for (int k = 0; k < 4; ++k) {
                 s2 += w[k];
                 ss2 = fmaf(w[k], w[k], ss2);
+            }
+        }
+    }
+    float a = 1.f, bsh = 0.f;
+    if (kRes) {
+        const float2 t2 = group_exchange(c, make_float2(s2, ss2));
+        const float mean2 = t2.x * (1.f / 256.f);
+        const float rstd2 = rsqrtf(fmaxf(t2.y * (1.f / 256.f) - mean2 * mean2, 0.f) + e.ln_eps);
+        a = c.valid ? rstd2 : 0.f;
+        bsh = c.valid ? -mean2 * rstd2 : 0.f;
+    }
+#pragma unroll
+    for (int hlf = 0; hlf < 2; ++hlf) {
+        float* w = v + hlf * 32;
+        if (hlf == 1) {
+            if (c.lane == 0) tma_store_wait_read();
+            __syncwarp();
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            uint4 t;
+            t.x = pack_bf16x2(fmaf(w[u * 8], a, bsh), fmaf(w[u * 8 + 1], a, bsh));
+            t.y = pack_bf16x2(fmaf(w[u * 8 + 2], a, bsh), fmaf(w[u * 8 + 3], a, bsh));
+            t.z = pack_bf16x2(fmaf(w[u * 8 + 4], a, bsh), fmaf(w[u * 8 + 5], a, bsh));
+            t.w = pack_bf16x2(fmaf(w[u * 8 + 6], a, bsh), fmaf(w[u * 8 + 7], a, bsh));
+            *reinterpret_cast<uint4*>(c.stg + c.lane * 64 + ((u ^ ((c.lane >> 1) & 3)) << 4)) = t;
+        }
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        __syncwarp();
+        if (c.lane == 0) {
+            tma_store_2d(tmOut, c.stg, n + hlf * 32, c.row0);
+            tma_store_commit();
+        }
+    }
+}
+
+// ---- the two conv blocks of a resnet (cosyvoice decoder.py:65-78, matcha decoder.py:49-61), N == BN == 256:
+//   kRes == false:  mask(mish(LayerNorm(acc + bias)) + time bias)                       -> bf16            (block1)
+//   kRes == true :  mask(mish(LayerNorm(acc + bias)) + fp32 residual) -> fp32 stream, plain LayerNorm -> bf16 (block2)
+// Each warp owns 32 rows x 64 columns.  The addend (residual rows in the tiled layout, or the time-bias row of the
+// sequence) is loaded into the thread's 64 result registers BEFORE the wait for the accumulator, so its L2 latency hides
+// behind the tile's MMAs; the accumulator is then drained twice with pipelined 16-column tcgen05.ld (statistics, then
+// normalise + Mish + add) -- TMEM reads are cheap next to K = 768 of MMAs, registers are not.  bias comes from shared
+// memory (sBias, filled once per CTA); all masking is by multiplication (a per-element select turns into a branch around
+// every Mish and serialises the unrolled loop).
+template <bool kRes>
+__device__ __forceinline__ void epi_lnact(const EpiCtx& c, const CUtensorMap* tmOut, int part, uint32_t tmem_acc,
+                                          uint64_t* tfull_bar, uint32_t tfull_phase, uint64_t* tempty_bar,
+                                          const float* sBias) {
+    const KParams& p = *c.p;
+    const GemmEpilogue& e = p.epi;
+    const int row = c.row0 + c.lane;
+    const int n = part * 64;
+    float v[64];
+    if (kRes) {
+        const float* q = e.resid + tiled_f32_offset(row, n);
+#pragma unroll
+        for (int u = 0; u < 16; ++u) {
+            const float4 t = *reinterpret_cast<const float4*>(q + (size_t)u * 512);
+            v[4 * u] = t.x; v[4 * u + 1] = t.y; v[4 * u + 2] = t.z; v[4 * u + 3] = t.w;
+        }
+    } else if (e.tbias) {
+        const float* q = e.tbias + (size_t)(c.seq < 0 ? 0 : c.seq) * e.tbias_ld + n;
+#pragma unroll
+        for (int u = 0; u < 16; ++u) {
+            const float4 t = ldg4(q + 4 * u);
+            v[4 * u] = t.x; v[4 * u + 1] = t.y; v[4 * u + 2] = t.z; v[4 * u + 3] = t.w;
+        }
+    } else {
+#pragma unroll
+        for (int i = 0; i < 64; ++i) v[i] = 0.f;
+    }
+    mbar_wait(tfull_bar, tfull_phase);
+    tc_fence_after();
+    const uint32_t ta = tmem_acc + (uint32_t)n;
+    float t0[16], t1[16];
+    float s = 0.f, ss = 0.f;
+    tmem_ld16(ta, t0);
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {   // pass 1: row statistics of acc + bias
+        float* t = (q & 1) ? t1 : t0;
+        tmem_ld_wait();
+        if (q < 3) tmem_ld16(ta + (q + 1) * 16, (q & 1) ? t0 : t1);
+#pragma unroll
+        for (int i = 0; i < 16; i += 4) {
+            const float4 b = *reinterpret_cast<const float4*>(sBias + n + q * 16 + i);   // broadcast LDS
+            const float x0 = t[i] + b.x, x1 = t[i + 1] + b.y, x2 = t[i + 2] + b.z, x3 = t[i + 3] + b.w;
+            s += (x0 + x1) + (x2 + x3);
+            ss = fmaf(x0, x0, fmaf(x1, x1, fmaf(x2, x2, fmaf(x3, x3, ss))));
+        }
+    }
+    tmem_ld16(ta, t0);   // first group of pass 2 flies during the exchange
+    if (c.lane == 0) tma_store_wait_read();   // the exchange slot is the head of the staging tile the last store read
+    __syncwarp();
+    const float2 tot = group_exchange(c, make_float2(s, ss));
+    const float mean = tot.x * (1.f / 256.f);
+    const float rstd = rsqrtf(fmaxf(tot.y * (1.f / 256.f) - mean * mean, 0.f) + e.ln_eps);
+    const float vmask = c.valid ? 1.f : 0.f;
+    float s2 = 0.f, ss2 = 0.f;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {   // pass 2: LayerNorm + Mish + addend
+        float* t = (q & 1) ? t1 : t0;
+        tmem_ld_wait();
+        if (q < 3) tmem_ld16(ta + (q + 1) * 16, (q & 1) ? t0 : t1);
+        if (q == 3) {   // accumulator fully read: hand it back to the MMA warp
+            tc_fence_before();
+            __syncwarp();
+            if (c.lane == 0) mbar_arrive(tempty_bar);
+        }
+        float* w = v + q * 16;
+#pragma unroll
+        for (int i = 0; i < 16; i += 4) {
+            const float4 b = *reinterpret_cast<const float4*>(sBias + n + q * 16 + i);
+            const float4 g = ldg4(e.ln1_g + n + q * 16 + i), bt = ldg4(e.ln1_b + n + q * 16 + i);
+            const float bx[4] = {b.x, b.y, b.z, b.w}, gx[4] = {g.x, g.y, g.z, g.w}, tx[4] = {bt.x, bt.y, bt.z, bt.w};
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const float y = fmaf((t[i + k] + bx[k] - mean) * rstd, gx[k], tx[k]);
+                w[i + k] = (fast_mish(y) + w[i + k]) * vmask;
+            }
+        }
+        if (kRes) {
+            float* dst = e.out_f32 + tiled_f32_offset(row, n + q * 16);
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+                *reinterpret_cast<float4*>(dst + (size_t)u * 512) = make_float4(w[4 * u], w[4 * u + 1], w[4 * u + 2], w[4 * u + 3]);
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+                s2 += w[i];
+                ss2 = fmaf(w[i], w[i], ss2);
             }
         }
     }
@@ -542,7 +673,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
                 continue;
             }
             if constexpr (kMode >= 3) {
-                epi_lnact<kMode == 4>(c, &tmOut, part, c.taddr, &tfull[acc], accphase, &tempty[acc], sBias);
+                if constexpr (kMode == 3) epi_lnact_single<false>(c, &tmOut, part, c.taddr, &tfull[acc], accphase, &tempty[acc], sBias);
+                else epi_lnact<true>(c, &tmOut, part, c.taddr, &tfull[acc], accphase, &tempty[acc], sBias);
                 acc ^= 1;
                 if (acc == 0) accphase ^= 1;
                 continue;

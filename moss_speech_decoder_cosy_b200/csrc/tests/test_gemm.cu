@@ -249,8 +249,7 @@ int main() {
     int fails = 0;
 
     auto base = [](const char* name, int M, int N, int BN, int K) {
-        Case c;
-        memset(&c, 0, sizeof(c));
+        Case c{};
         c.name = name; c.M = M; c.N = N; c.BN = BN;
         c.a_rows[0] = M; c.a_cols[0] = K; c.a_ld[0] = K;
         c.num_segs = 1;
