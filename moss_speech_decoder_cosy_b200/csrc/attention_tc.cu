@@ -14,6 +14,7 @@
 #include <stdio.h>
 
 #include "kernels.h"
+#include "gemm.h"
 #include "ptx.cuh"
 
 namespace mossdec {
@@ -173,6 +174,8 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tm, __nv_bfloat16* __res
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = __shfl_sync(0xffffffffu, *tmem_slot, 0);
+    pdl_wait();     // q | k | v of the preceding GEMM are visible from here on
+    pdl_launch();
 
     // keys visible to this query tile
     int kv_end = len;
@@ -339,7 +342,8 @@ cudaError_t launch_attention_tc(const __nv_bfloat16* qkv, int64_t rows, __nv_bfl
     CUtensorMap tm;
     if (!encode_2d(&tm, qkv, (uint64_t)3 * heads * kD, (uint64_t)rows, (uint64_t)3 * heads * kD, 64)) return cudaErrorInvalidValue;
     dim3 grid((max_len + kBQ - 1) / kBQ, heads, nseq);
-    attention_tc_kernel<<<grid, 128, kSmem, st>>>(tm, out, seq_start, seq_len, heads, chunk);
+    const cudaError_t le = launch_pdl(attention_tc_kernel, grid, dim3(128), kSmem, st, tm, out, seq_start, seq_len, heads, chunk);
+    if (le != cudaSuccess) return le;
 #ifdef ATT_TRACE
     static int n_launch = 0;
     if (++n_launch == 300) {

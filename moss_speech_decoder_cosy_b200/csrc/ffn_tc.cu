@@ -122,6 +122,8 @@ ffn_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ C
     cluster_sync_all();   // peers' barriers are initialised before any multicast / remote arrive can reach them
     const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);
     const int rank = __shfl_sync(0xffffffffu, (int)cluster_ctarank(), 0);
+    pdl_wait();     // everything above overlapped the previous kernel's tail; its results are visible from here on
+    pdl_launch();
 
     if (warp == 0) {
         // ------------------------------------------------------------ TMA producer (whole warp, one elected lane issues)
@@ -492,7 +494,8 @@ cudaError_t ffn_tc_launch(const FfnProblem& f, int num_sms, cudaStream_t stream)
 
     int grid = (p.num_tiles + kCluster - 1) / kCluster * kCluster;
     if (grid > num_sms) grid = num_sms / kCluster * kCluster;
-    ffn_tc_kernel<<<grid, kThreads, kFfnSmem, stream>>>(tX, tW1, tW2, tOut, p);
+    const cudaError_t le = launch_pdl(ffn_tc_kernel, dim3(grid), dim3(kThreads), kFfnSmem, stream, tX, tW1, tW2, tOut, p);
+    if (le != cudaSuccess) return le;
     return cudaGetLastError();
 }
 

@@ -12,6 +12,7 @@
 #include <cuda_runtime.h>
 #include <cuda_bf16.h>
 #include <stdint.h>
+#include <utility>
 
 namespace mossdec {
 
@@ -115,5 +116,23 @@ cudaError_t ffn_tc_launch(const FfnProblem& p, int num_sms, cudaStream_t stream)
 // Enqueue on `stream`.  Returns cudaSuccess or the failing CUDA error; -1 style argument errors
 // are reported as cudaErrorInvalidValue.
 cudaError_t gemm_tc_launch(const GemmProblem& p, int num_sms, cudaStream_t stream);
+
+// Launch with the programmatic-stream-serialization attribute (see ptx.cuh pdl_wait); off unless MOSSDEC_PDL=1 (measured: no gain on this path).
+bool pdl_enabled();
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl_enabled() ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kernel, std::forward<Args>(args)...);
+}
+
 
 }  // namespace mossdec

@@ -574,6 +574,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);
+    pdl_wait();     // everything above overlapped the previous kernel's tail; its results are visible from here on
+    pdl_launch();
 
     const uint32_t b_bytes = (uint32_t)p.BN * kGemmBK * 2;
 
@@ -890,12 +892,22 @@ cudaError_t gemm_tc_launch(const GemmProblem& g, int num_sms, cudaStream_t strea
         return cudaErrorInvalidValue;
 
     const int grid = kp.num_tiles < num_sms ? kp.num_tiles : num_sms;
-    if (lnact_a) gemm_tc_kernel<3><<<grid, kThreads, kSmemBytes + 1024, stream>>>(tA0, tA1, tB, tOut, kp);
-    else if (lnact_b) gemm_tc_kernel<4><<<grid, kThreads, kSmemBytes + 1024, stream>>>(tA0, tA1, tB, tOut, kp);
-    else if (resln) gemm_tc_kernel<2><<<grid, kThreads, kSmemBytes, stream>>>(tA0, tA1, tB, tOut, kp);
-    else if (kp.fast_bf16) gemm_tc_kernel<1><<<grid, kThreads, kSmemBytes, stream>>>(tA0, tA1, tB, tOut, kp);
-    else gemm_tc_kernel<0><<<grid, kThreads, kSmemBytes, stream>>>(tA0, tA1, tB, tOut, kp);
-    return cudaGetLastError();
+    cudaError_t le;
+    if (lnact_a) le = launch_pdl(gemm_tc_kernel<3>, dim3(grid), dim3(kThreads), kSmemBytes + 1024, stream, tA0, tA1, tB, tOut, kp);
+    else if (lnact_b) le = launch_pdl(gemm_tc_kernel<4>, dim3(grid), dim3(kThreads), kSmemBytes + 1024, stream, tA0, tA1, tB, tOut, kp);
+    else if (resln) le = launch_pdl(gemm_tc_kernel<2>, dim3(grid), dim3(kThreads), kSmemBytes, stream, tA0, tA1, tB, tOut, kp);
+    else if (kp.fast_bf16) le = launch_pdl(gemm_tc_kernel<1>, dim3(grid), dim3(kThreads), kSmemBytes, stream, tA0, tA1, tB, tOut, kp);
+    else le = launch_pdl(gemm_tc_kernel<0>, dim3(grid), dim3(kThreads), kSmemBytes, stream, tA0, tA1, tB, tOut, kp);
+    return le != cudaSuccess ? le : cudaGetLastError();
+}
+
+bool pdl_enabled() {
+    static const bool on = [] {
+        const char* v = getenv("MOSSDEC_PDL");
+        return v && v[0] == '1';   // opt-in: measured neutral on one stream and 3 % slower with the two-stream CFG halves
+                                   // (early-scheduled CTAs wait on SMs the other stream's kernel could be using)
+    }();
+    return on;
 }
 
 }  // namespace mossdec

@@ -75,4 +75,5 @@ void launch_hift_istft(const HiftLayout& L, int max_len, const float* post, int 
                        cudaStream_t st);
 void launch_fade(float* speech, const float* prev, const float* w, int n, cudaStream_t st);
 
+
 }  // namespace mossdec
