@@ -584,7 +584,14 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
         {
             int stage = 0;
             uint32_t phase = 0;
-            for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+            // Work unit = `group` consecutive N tiles of one M tile.  When the whole K extent fits the ring (total_kb ==
+            // stages, one segment) the A tile of a unit is fetched once and stays in its stages; only B is refilled for
+            // the following N tiles (these GEMMs are bound by the bytes delivered into the SM, ~42 B/clk/SM chip-wide).
+            for (int unit = blockIdx.x; unit < p.num_units; unit += gridDim.x)
+            for (int ju = 0; ju < p.group; ++ju) {
+                const int tile = unit * p.group + ju;
+                if (tile >= p.num_tiles) break;
+                const bool keep_a = p.a_stationary && ju > 0;
                 const int m0 = (tile / p.tiles_n) * kGemmBM;
                 const int n0 = (tile % p.tiles_n) * p.BN;
                 int kb = 0;
@@ -594,8 +601,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
                     for (int j = 0; j < sg.nkb; ++j, ++kb) {
                         mbar_wait(&empty[stage], phase ^ 1);
                         if (elect_one()) {
-                            mbar_expect_tx(&full[stage], kABytes + b_bytes);
-                            tma_load_2d(sA + stage * kABytes, tmA, sg.col0 + j * kGemmBK, m0 + sg.row_shift, &full[stage]);
+                            mbar_expect_tx(&full[stage], (keep_a ? 0u : (uint32_t)kABytes) + b_bytes);
+                            if (!keep_a) tma_load_2d(sA + stage * kABytes, tmA, sg.col0 + j * kGemmBK, m0 + sg.row_shift, &full[stage]);
                             tma_load_2d(sB + stage * kBBytesMax, &tmB, kb * kGemmBK, n0, &full[stage]);
                         }
                         if (++stage == kGemmStages) {
@@ -614,7 +621,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
             uint32_t phase = 0;
             int acc = 0;
             uint32_t accphase = 0;
-            for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+            for (int unit = blockIdx.x; unit < p.num_units; unit += gridDim.x)
+            for (int ju = 0; ju < p.group; ++ju) {
+                if (unit * p.group + ju >= p.num_tiles) break;
                 mbar_wait(&tempty[acc], accphase ^ 1);
                 tc_fence_after();
                 const uint32_t d_tmem = tmem_base + (uint32_t)acc * 256u;
@@ -657,7 +666,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
         const int cend = cbeg + cbase + (part < crem ? 1 : 0);
         int acc = 0;
         uint32_t accphase = 0;
-        for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+        for (int unit = blockIdx.x; unit < p.num_units; unit += gridDim.x)
+        for (int ju = 0; ju < p.group; ++ju) {
+            const int tile = unit * p.group + ju;
+            if (tile >= p.num_tiles) break;
             const int m0 = (tile / p.tiles_n) * kGemmBM;
             c.n0 = (tile % p.tiles_n) * p.BN;
             c.row0 = m0 + c.quarter * 32;
@@ -848,6 +860,8 @@ cudaError_t gemm_tc_launch(const GemmProblem& g, int num_sms, cudaStream_t strea
     kp.tiles_n = (g.N + g.BN - 1) / g.BN;
     const int tiles_m = (g.M + kGemmBM - 1) / kGemmBM;
     kp.num_tiles = tiles_m * kp.tiles_n;
+    kp.group = 1;
+    kp.a_stationary = 0;
     kp.num_segs = g.num_segs;
     kp.total_kb = 0;
     for (int s = 0; s < g.num_segs; ++s) {
@@ -891,7 +905,16 @@ cudaError_t gemm_tc_launch(const GemmProblem& g, int num_sms, cudaStream_t strea
     if ((kp.fast_bf16 || resln || lnact_a || lnact_b) && !encode_2d_ex(&tOut, e.out_bf16, (uint64_t)g.N, (uint64_t)g.M, (uint64_t)e.ldo, 32, 32, 1))
         return cudaErrorInvalidValue;
 
-    const int grid = kp.num_tiles < num_sms ? kp.num_tiles : num_sms;
+    // A-stationary units (see the producer): K fits the ring exactly, several N tiles per M tile, enough units to fill the GPU
+    if (kp.total_kb == kGemmStages && g.num_segs == 1 && kp.tiles_n > 1) {
+        const int grp = (kp.tiles_n % 3) == 0 ? 3 : ((kp.tiles_n % 2) == 0 ? 2 : 1);
+        if (grp > 1 && kp.num_tiles / grp >= 2 * num_sms) {
+            kp.group = grp;
+            kp.a_stationary = 1;
+        }
+    }
+    kp.num_units = (kp.num_tiles + kp.group - 1) / kp.group;
+    const int grid = kp.num_units < num_sms ? kp.num_units : num_sms;
     cudaError_t le;
     if (lnact_a) le = launch_pdl(gemm_tc_kernel<3>, dim3(grid), dim3(kThreads), kSmemBytes + 1024, stream, tA0, tA1, tB, tOut, kp);
     else if (lnact_b) le = launch_pdl(gemm_tc_kernel<4>, dim3(grid), dim3(kThreads), kSmemBytes + 1024, stream, tA0, tA1, tB, tOut, kp);
