@@ -188,3 +188,46 @@ def test_sharded_decode_world2_gloo(tmp_path):
            "--master-port", "29533", str(script)]
     res = subprocess.run(cmd, capture_output=True, text=True, timeout=240)
     assert res.returncode == 0 and "OK" in res.stdout, res.stdout + res.stderr
+
+
+def test_mish_rational_form_matches_definition():
+    """epilogue.cuh fast_mish: x * n / (n + 2) with n = u (u + 2), u = e^min(x, 20) is x * tanh(softplus(x)) (matcha
+    decoder.py:56 nn.Mish); the kernel evaluates it with ex2.approx / rcp.approx, no branches."""
+    x = np.linspace(-30.0, 30.0, 24001)
+    u = np.exp(np.minimum(x, 20.0))
+    n = u * (u + 2.0)
+    fast = np.where(x > 20.0, x, x * (n / (n + 2.0)))
+    want = x * np.tanh(np.log1p(np.exp(-np.abs(x))) + np.maximum(x, 0.0))
+    assert np.max(np.abs(fast - want)) < 1e-9
+
+
+def test_ffn_p_operand_columns_in_tensor_memory():
+    """ffn_tc.cu: the epilogue part that drained accumulator columns [32 p, 32 p + 32) writes its 16 packed bf16x2 words
+    over columns [32 p, 32 p + 16); K-step kk of FF2 (hidden [16 kk, 16 kk + 16)) must read exactly those words."""
+    written = {}
+    for part in range(4):
+        for w in range(16):                       # word w holds hidden 32 part + 2 w, + 1
+            written[32 * part + w] = (32 * part + 2 * w, 32 * part + 2 * w + 1)
+    for kk in range(8):
+        col = (kk >> 1) * 32 + (kk & 1) * 8
+        hidden = [h for c in range(col, col + 8) for h in written[c]]
+        assert hidden == list(range(16 * kk, 16 * kk + 16))
+
+
+def test_gemm_work_units_cover_every_tile_once_and_share_the_a_tile():
+    """gemm_tc.cu producer / MMA / epilogue loops: unit = `group` consecutive N tiles of one M tile (A fetched once)."""
+    for tiles_m, tiles_n, group, grid in [(654, 6, 3, 148), (654, 6, 1, 148), (7, 4, 2, 5), (3, 6, 3, 148)]:
+        num_tiles = tiles_m * tiles_n
+        num_units = (num_tiles + group - 1) // group
+        seen = []
+        for cta in range(min(grid, num_units)):
+            for unit in range(cta, num_units, grid):
+                ms = set()
+                for j in range(group):
+                    tile = unit * group + j
+                    if tile >= num_tiles:
+                        break
+                    seen.append(tile)
+                    ms.add(tile // tiles_n)
+                assert len(ms) == 1               # tiles_n % group == 0: one A tile per unit
+        assert sorted(seen) == list(range(num_tiles))
