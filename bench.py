@@ -237,18 +237,18 @@ def main():
     # Algorithmic FLOPs per step of the three tensor-core kernels (SURVEY 8d figures):
     frames_steps = B * 10 * 2 * T                                    # frame . CFG branch . Euler step
     flops = {
-        "attention_tc_kernel": frames_steps * ATTN_MFLOP_PER_FRAME_T * T,
+        "attention_ws_kernel": frames_steps * ATTN_MFLOP_PER_FRAME_T * T,
         "ffn_tc_kernel": frames_steps * FFN_FLOP_PER_FRAME,
         "gemm_tc_kernel": frames_steps * (EST_MFLOP_PER_FRAME - FFN_FLOP_PER_FRAME) + B * 4 * N_TOK * HIFT_FLOP_PER_FRAME,
     }
-    times = {"attention_tc_kernel": (prof["attn_ms"], prof["attn_launches"]),
+    times = {"attention_ws_kernel": (prof["attn_ms"], prof["attn_launches"]),
              "ffn_tc_kernel": (prof["ffn_ms"], prof["ffn_launches"]),
              "gemm_tc_kernel": (prof["gemm_ms"], prof["gemm_launches"])}
     traffic = {}
     tpath = os.path.join(ROOT, "profiles", "ncu_dram_traffic.json")   # bytes per launch from the committed ncu --set full capture
     if os.path.exists(tpath):
         traffic = json.load(open(tpath))
-    desc = {"attention_tc_kernel": "tcgen05 flash attention (QK^T and PV on the tensor cores, P in TMEM)",
+    desc = {"attention_ws_kernel": "warp-specialised tcgen05 flash attention (QK^T and PV on the tensor cores, double-buffered S and P in TMEM)",
             "ffn_tc_kernel": "fused feed-forward (FF1 + GELU + FF2 + residual + LayerNorm, tcgen05, hidden on chip)",
             "gemm_tc_kernel": "tcgen05 implicit GEMM (convs, projections, vocoder) with fused epilogues"}
     kernels = {}

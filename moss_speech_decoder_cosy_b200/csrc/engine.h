@@ -120,6 +120,7 @@ class Engine {
     int num_sms_ = 148;
     bool finalized_ = false;
     bool attn_v1_ = false;
+    bool attn_ws_ = false;
     bool dual_stream_ = true;          // the two CFG halves of a solve run on two streams (MOSSDEC_DUAL=0 disables)
     cudaStream_t st2_ = nullptr;
     cudaEvent_t ev_fork_ = nullptr, ev_join_ = nullptr;

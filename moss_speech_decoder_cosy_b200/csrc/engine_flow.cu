@@ -36,8 +36,9 @@ Engine::Engine(const EngineConfig& cfg) : cfg_(cfg) {
     int dev = 0;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&num_sms_, cudaDevAttrMultiProcessorCount, dev);
-    const char* av = getenv("MOSSDEC_ATTN");  // "v1" selects the mma.sync kernel (developer A/B switch)
+    const char* av = getenv("MOSSDEC_ATTN");  // developer A/B switch: "v1" = mma.sync kernel, "tc" = single-buffer tcgen05 kernel
     attn_v1_ = av != nullptr && av[0] == 'v' && av[1] == '1';
+    attn_ws_ = !(av != nullptr && av[0] == 't' && av[1] == 'c');  // default: warp-specialised tcgen05 kernel (attention_ws.cu); "tc" = attention_tc.cu
     const char* dv = getenv("MOSSDEC_DUAL");
     dual_stream_ = !(dv != nullptr && dv[0] == '0');
     if (dual_stream_) {
@@ -395,6 +396,10 @@ int Engine::estimator_forward(int M, int nseq, int max_len, const float* tbias, 
             if (profile_) prof_begin(1, 0.0, st);
             if (attn_v1_) {
                 launch_attention(qkv_, att_, layout_.seq_start, layout_.seq_len, nseq, max_len, cfg_.heads, chunk, st);
+            } else if (attn_ws_) {
+                cudaError_t ae = launch_attention_ws(qkv_, M, att_, layout_.seq_start, layout_.seq_len, nseq, max_len,
+                                                     cfg_.heads, chunk, st);
+                if (ae != cudaSuccess) return fail(std::string("launch_attention_ws: ") + cudaGetErrorString(ae));
             } else {
                 cudaError_t ae = launch_attention_tc(qkv_, M, att_, layout_.seq_start, layout_.seq_len, nseq, max_len,
                                                      cfg_.heads, chunk, st);

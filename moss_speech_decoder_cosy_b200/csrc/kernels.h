@@ -42,6 +42,10 @@ void launch_attention(const __nv_bfloat16* qkv, __nv_bfloat16* out, const int32_
 cudaError_t launch_attention_tc(const __nv_bfloat16* qkv, int64_t rows, __nv_bfloat16* out, const int32_t* seq_start,
                                 const int32_t* seq_len, int nseq, int max_len, int heads, int chunk, cudaStream_t st);
 
+// warp-specialised variant (attention_ws.cu): dedicated TMA / MMA issue warp, 32-key tiles, double-buffered scores in TMEM
+cudaError_t launch_attention_ws(const __nv_bfloat16* qkv, int64_t rows, __nv_bfloat16* out, const int32_t* seq_start,
+                                const int32_t* seq_len, int nseq, int max_len, int heads, int chunk, cudaStream_t st);
+
 // ------------------------------------------------------------------------------------------------ HiFT
 // Packed layout of one group of mel segments: sequence b owns frame rows [seq_start[b], seq_start[b] + seq_len[b]);
 // at least 4 zero guard frames separate sequences.  Stage rows are frame rows x 8 / 40 / 120 (the last stage has one

@@ -20,7 +20,7 @@ if [ $BE -eq 0 ]; then
     --log-file gpurun_out/${TAG}_launches.csv python bench.py --steps 1 --warmup 3 --no-cpu-baseline \
     > gpurun_out/${TAG}_ncu_launches.log 2>&1
   echo "ncu_launches_exit=$?"
-  timeout 900 ncu --set full --clock-control none --import-source on -k regex:'gemm_tc_kernel|attention_tc|ffn_tc' \
+  timeout 900 ncu --set full --clock-control none --import-source on -k regex:'gemm_tc_kernel|attention_ws|attention_tc|ffn_tc' \
     -s 500 -c 8 -o gpurun_out/${TAG}_full python bench.py --steps 1 --warmup 3 --no-cpu-baseline \
     > gpurun_out/${TAG}_ncu_full.log 2>&1
   echo "ncu_full_exit=$?"

@@ -37,7 +37,7 @@ def ncu_csv(rep, page, extra=()):
 
 
 def short(name):
-    for k in ("attention_tc_kernel", "ffn_tc_kernel", "gemm_tc_kernel"):
+    for k in ("attention_ws_kernel", "attention_tc_kernel", "ffn_tc_kernel", "gemm_tc_kernel"):
         if k in name:
             return k + (name[name.index(k) + len(k):name.index("(")] if "<" in name[name.index(k):name.index("(")] else "")
     return name.split("(")[0][-48:]
