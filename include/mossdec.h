@@ -87,6 +87,25 @@ int mossdec_hift(mossdec_handle* h, int32_t B, const int32_t* lens, const float*
 int mossdec_fade_in_out(mossdec_handle* h, float* speech, const float* prev_tail, const float* window2n, int32_t n,
                         void* stream);
 
+/* ---- Secondary configuration: building blocks of the NON-causal cosyvoice1 / Matcha
+ * estimator (GLM_modules/cosyvoice1 uses third_party/Matcha-TTS/matcha/models/components/decoder.py).  Dense
+ * [B, C, T] fp32 tensors exactly as the reference modules take them; block width 256, GroupNorm(8).  Weights are the
+ * tensors "<prefix>.*" uploaded with mossdec_set_tensor (layouts: weights.py pack_cv1_resnet / _downsample / _upsample).
+ *
+ *   mossdec_cv1_resnet_block <- ResnetBlock1D.forward(x, mask, time_emb)   matcha decoder.py:46-61 (Block1D :32-43)
+ *       x [B, Cin, T], mask [B, 1, T], time_emb [B, time_dim] (NULL = no time bias) -> out [B, 256, T]
+ *   mossdec_cv1_downsample   <- Downsample1D.forward   Conv1d(C, C, 3, 2, 1)            matcha decoder.py:64-70
+ *       x [B, C, T] -> out [B, C, (T - 1) / 2 + 1]
+ *   mossdec_cv1_upsample     <- Upsample1D.forward     ConvTranspose1d(C, C, 4, 2, 1)   matcha decoder.py:120-158
+ *       x [B, C, T] -> out [B, C, 2 T]
+ */
+int mossdec_cv1_resnet_block(mossdec_handle* h, const char* prefix, int32_t B, int32_t T, int32_t Cin, const float* x,
+                             const float* mask, const float* time_emb, int32_t time_dim, float* out, void* stream);
+int mossdec_cv1_downsample(mossdec_handle* h, const char* prefix, int32_t B, int32_t T, int32_t C, const float* x, float* out,
+                           void* stream);
+int mossdec_cv1_upsample(mossdec_handle* h, const char* prefix, int32_t B, int32_t T, int32_t C, const float* x, float* out,
+                         void* stream);
+
 /* Test hook: copy up to max_floats of a named fp32 intermediate of the last call ("hift.f0", "hift.p480",
  * "hift.post", "hift.x") to HOST memory; synchronises the device.  Returns floats copied, negative on error. */
 int mossdec_debug_read(mossdec_handle* h, const char* name, float* host_dst, int64_t max_floats);

@@ -75,6 +75,19 @@ int mossdec_fade_in_out(mossdec_handle* h, float* speech, const float* prev_tail
     return h->eng->fade_in_out(speech, prev_tail, window2n, n, (cudaStream_t)stream);
 }
 
+int mossdec_cv1_resnet_block(mossdec_handle* h, const char* prefix, int32_t B, int32_t T, int32_t Cin, const float* x,
+                             const float* mask, const float* time_emb, int32_t time_dim, float* out, void* stream) {
+    return h->eng->cv1_resnet_block(prefix, B, T, Cin, x, mask, time_emb, time_dim, out, (cudaStream_t)stream);
+}
+int mossdec_cv1_downsample(mossdec_handle* h, const char* prefix, int32_t B, int32_t T, int32_t C, const float* x, float* out,
+                           void* stream) {
+    return h->eng->cv1_downsample(prefix, B, T, C, x, out, (cudaStream_t)stream);
+}
+int mossdec_cv1_upsample(mossdec_handle* h, const char* prefix, int32_t B, int32_t T, int32_t C, const float* x, float* out,
+                         void* stream) {
+    return h->eng->cv1_upsample(prefix, B, T, C, x, out, (cudaStream_t)stream);
+}
+
 int mossdec_debug_read(mossdec_handle* h, const char* name, float* host_dst, int64_t max_floats) {
     return h->eng->debug_read(name, host_dst, (size_t)max_floats * 4);
 }

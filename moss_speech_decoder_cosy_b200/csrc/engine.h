@@ -81,6 +81,12 @@ class Engine {
     // test hook: copy a named intermediate of the last call to the host; returns floats copied or -1
     int debug_read(const char* name, void* host_dst, size_t bytes);
     int fade_in_out(float* speech, const float* prev_tail, const float* window2n, int n, cudaStream_t st);
+    // Building blocks of the non-causal cosyvoice1 / Matcha estimator (cv1_ops.cu): dense
+    // [B, C, T] fp32 in / out like the reference modules, weights looked up as "<prefix>.*" (weights.py pack_cv1_*).
+    int cv1_resnet_block(const char* prefix, int B, int T, int Cin, const float* x, const float* mask, const float* temb,
+                         int time_dim, float* out, cudaStream_t st);
+    int cv1_downsample(const char* prefix, int B, int T, int C, const float* x, float* out, cudaStream_t st);
+    int cv1_upsample(const char* prefix, int B, int T, int C, const float* x, float* out, cudaStream_t st);
 
     const char* last_error() const { return err_.c_str(); }
     long launches() const { return launches_; }
@@ -139,6 +145,9 @@ class Engine {
                   *cat_ = nullptr;
     float *xstate_ = nullptr, *hres_ = nullptr, *rres_ = nullptr, *dout_ = nullptr;
     float *temb_ = nullptr, *tbias_ = nullptr, *tvals_ = nullptr;
+
+    // ---- cosyvoice1 building-block workspace (cv1_ops.cu)
+    DeviceBuffer ws_cv1_;
 
     // ---- hift workspace
     DeviceBuffer ws_hift_, ws_hift_layout_;

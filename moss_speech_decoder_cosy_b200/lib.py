@@ -53,6 +53,12 @@ def load_library():
     lib.mossdec_hift.restype = i32
     lib.mossdec_fade_in_out.argtypes = [vp, vp, vp, vp, i32, vp]
     lib.mossdec_fade_in_out.restype = i32
+    lib.mossdec_cv1_resnet_block.argtypes = [vp, ctypes.c_char_p, i32, i32, i32, vp, vp, vp, i32, vp, vp]
+    lib.mossdec_cv1_resnet_block.restype = i32
+    lib.mossdec_cv1_downsample.argtypes = [vp, ctypes.c_char_p, i32, i32, i32, vp, vp, vp]
+    lib.mossdec_cv1_downsample.restype = i32
+    lib.mossdec_cv1_upsample.argtypes = [vp, ctypes.c_char_p, i32, i32, i32, vp, vp, vp]
+    lib.mossdec_cv1_upsample.restype = i32
     lib.mossdec_debug_read.argtypes = [vp, ctypes.c_char_p, vp, i64]
     lib.mossdec_debug_read.restype = i32
     lib.mossdec_profile.argtypes = [vp, i32]
@@ -73,7 +79,8 @@ EXPORTED_SYMBOLS = [
     "mossdec_default_config", "mossdec_create", "mossdec_destroy", "mossdec_last_error", "mossdec_set_tensor",
     "mossdec_finalize", "mossdec_estimator", "mossdec_flow_solve", "mossdec_hift", "mossdec_fade_in_out",
     "mossdec_launch_count", "mossdec_reset_launch_count", "mossdec_debug_read", "mossdec_profile",
-    "mossdec_profile_read", "mossdec_set_hift_group_frames",
+    "mossdec_profile_read", "mossdec_set_hift_group_frames", "mossdec_cv1_resnet_block", "mossdec_cv1_downsample",
+    "mossdec_cv1_upsample",
 ]
 
 
@@ -186,6 +193,36 @@ class Engine:
         n = prev_tail.numel()
         self._check(self.lib.mossdec_fade_in_out(self.h, _ptr(speech), _ptr(prev_tail), _ptr(window2n), n,
                                                  self._stream()), "fade_in_out")
+
+    # ---- cosyvoice1 / Matcha non-causal building blocks; same call shapes as the reference modules
+    def cv1_resnet_block(self, prefix, x, mask, time_emb=None):
+        """ResnetBlock1D.forward(x, mask, time_emb) (matcha decoder.py:56-61): x [B, Cin, T], mask [B, 1, T] -> [B, 256, T]."""
+        B, Cin, T = x.shape
+        x, mask = x.float().contiguous(), mask.float().contiguous()
+        te = None if time_emb is None else time_emb.float().contiguous()
+        out = torch.empty(B, 256, T, device=x.device, dtype=torch.float32)
+        self._check(self.lib.mossdec_cv1_resnet_block(self.h, prefix.encode(), B, T, Cin, _ptr(x), _ptr(mask), _ptr(te),
+                                                      0 if te is None else te.shape[1], _ptr(out), self._stream()),
+                    "cv1_resnet_block")
+        return out
+
+    def cv1_downsample(self, prefix, x):
+        """Downsample1D.forward (matcha decoder.py:69-70): [B, C, T] -> [B, C, (T - 1) // 2 + 1]."""
+        B, C, T = x.shape
+        x = x.float().contiguous()
+        out = torch.empty(B, C, (T - 1) // 2 + 1, device=x.device, dtype=torch.float32)
+        self._check(self.lib.mossdec_cv1_downsample(self.h, prefix.encode(), B, T, C, _ptr(x), _ptr(out), self._stream()),
+                    "cv1_downsample")
+        return out
+
+    def cv1_upsample(self, prefix, x):
+        """Upsample1D.forward with ConvTranspose1d(C, C, 4, 2, 1) (matcha decoder.py:147-150): [B, C, T] -> [B, C, 2 T]."""
+        B, C, T = x.shape
+        x = x.float().contiguous()
+        out = torch.empty(B, C, 2 * T, device=x.device, dtype=torch.float32)
+        self._check(self.lib.mossdec_cv1_upsample(self.h, prefix.encode(), B, T, C, _ptr(x), _ptr(out), self._stream()),
+                    "cv1_upsample")
+        return out
 
     def debug_read(self, name, max_floats):
         buf = torch.empty(int(max_floats), dtype=torch.float32)

@@ -104,3 +104,32 @@ def synth_noise_bank(n_feats: int = 80, length: int = 15000):
     g = torch.Generator(device="cpu")
     g.manual_seed(0)
     return torch.randn([1, n_feats, length], generator=g)
+
+
+def synth_cv1_blocks_state_dict(seed: int = 0, cin: int = 320, time_dim: int = 1024):
+    """Random-init weights of the cosyvoice1 / Matcha building blocks: one ResnetBlock1D(cin, 256,
+    time_dim), one ResnetBlock1D(256, 256, time_dim), Downsample1D(256), Upsample1D(256) (matcha decoder.py:32-158)."""
+    shapes = {}
+    for name, ci in (("res_in", cin), ("res_mid", 256)):
+        shapes.update({
+            f"{name}.block1.block.0.weight": (256, ci, 3), f"{name}.block1.block.0.bias": (256,),
+            f"{name}.block1.block.1.weight": (256,), f"{name}.block1.block.1.bias": (256,),
+            f"{name}.block2.block.0.weight": (256, 256, 3), f"{name}.block2.block.0.bias": (256,),
+            f"{name}.block2.block.1.weight": (256,), f"{name}.block2.block.1.bias": (256,),
+            f"{name}.mlp.1.weight": (256, time_dim), f"{name}.mlp.1.bias": (256,),
+            f"{name}.res_conv.weight": (256, ci, 1), f"{name}.res_conv.bias": (256,),
+        })
+    shapes.update({"down.conv.weight": (256, 256, 3), "down.conv.bias": (256,),
+                   "up.conv.weight": (256, 256, 4), "up.conv.bias": (256,)})
+    sd = {}
+    for key, shape in shapes.items():
+        k = "cv1." + key
+        if len(shape) >= 2:
+            fan_in = int(np.prod(shape[1:]))
+            gain = 2.0 if "block.0.weight" in key else 1.0
+            sd[key] = _normal(seed, k, shape, math.sqrt(gain / fan_in))
+        elif key.endswith("block.1.weight"):   # GroupNorm gamma
+            sd[key] = _normal(seed, k, shape, 0.1, 1.0)
+        else:
+            sd[key] = _normal(seed, k, shape, 0.05)
+    return sd

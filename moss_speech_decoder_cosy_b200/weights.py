@@ -196,3 +196,36 @@ def pack_hift(sd):
     out["hift.post.w"] = _bf16(conv_weight_taps(fold_weight_norm(sd, "conv_post")))  # [18, 7 * 64]
     out["hift.post.b"] = _f32(sd["conv_post.bias"])
     return out
+
+
+# ---- cosyvoice1 / Matcha non-causal building blocks (csrc/cv1_ops.cu) --------------------------------
+def pack_cv1_resnet(sd, src, dst):
+    """matcha ResnetBlock1D (decoder.py:46-61) state_dict keys under `src` -> engine tensors under `dst`.
+
+      block{1,2}.block.0.{weight,bias}  Conv1d k3 pad 1     -> .c{1,2}.w bf16 [256, 3 * ceil64(Cin)] (tap-major K), .c{1,2}.b
+      block{1,2}.block.1.{weight,bias}  GroupNorm(8, 256)   -> .gn{1,2}.g / .gn{1,2}.b
+      mlp.1.{weight,bias}               Linear(time, 256)   -> .mlp.w fp32 [256, time], .mlp.b
+      res_conv.{weight,bias}            Conv1d 1x1          -> .res.w bf16 [256, ceil64(Cin)], .res.b
+    """
+    out = {}
+    for i in (1, 2):
+        out[f"{dst}.c{i}.w"] = _bf16(conv_weight_taps(sd[f"{src}.block{i}.block.0.weight"].float()))
+        out[f"{dst}.c{i}.b"] = _f32(sd[f"{src}.block{i}.block.0.bias"])
+        out[f"{dst}.gn{i}.g"] = _f32(sd[f"{src}.block{i}.block.1.weight"])
+        out[f"{dst}.gn{i}.b"] = _f32(sd[f"{src}.block{i}.block.1.bias"])
+    out[f"{dst}.mlp.w"] = _f32(sd[f"{src}.mlp.1.weight"])
+    out[f"{dst}.mlp.b"] = _f32(sd[f"{src}.mlp.1.bias"])
+    out[f"{dst}.res.w"] = _bf16(conv_weight_taps(sd[f"{src}.res_conv.weight"].float()))
+    out[f"{dst}.res.b"] = _f32(sd[f"{src}.res_conv.bias"])
+    return out
+
+
+def pack_cv1_downsample(sd, src, dst):
+    """matcha Downsample1D (decoder.py:64-70) Conv1d(C, C, 3, 2, 1): tap-major [C, 3C]; the stride lives in the operand view."""
+    return {f"{dst}.w": _bf16(conv_weight_taps(sd[f"{src}.conv.weight"].float())), f"{dst}.b": _f32(sd[f"{src}.conv.bias"])}
+
+
+def pack_cv1_upsample(sd, src, dst):
+    """matcha Upsample1D (decoder.py:120-158) ConvTranspose1d(C, C, 4, 2, 1): polyphase [2C, 3C], bias repeated per phase."""
+    w = sd[f"{src}.conv.weight"].float()
+    return {f"{dst}.w": _bf16(convtranspose_polyphase(w, 2, 1)), f"{dst}.b": _f32(sd[f"{src}.conv.bias"].float().repeat(2))}

@@ -254,3 +254,29 @@ class PortDecoder:
             noise = torch.randn(480 * mel.shape[1], 9)
         wav, _ = hift_inference(self.hsd, mel, noise)
         return wav.unsqueeze(0), mel.unsqueeze(0)
+
+
+# ------------------------------------------------------------------ cosyvoice1 / Matcha non-causal blocks
+def cv1_block1d(x, mask, sd, p, groups=8):
+    """Block1D, third_party/Matcha-TTS/matcha/models/components/decoder.py:32-43: Conv1d(k3, pad 1) -> GroupNorm(8) -> Mish."""
+    y = F.conv1d(x * mask, sd[p + "block.0.weight"], sd[p + "block.0.bias"], padding=1)
+    y = F.group_norm(y, groups, sd[p + "block.1.weight"], sd[p + "block.1.bias"], eps=1e-5)
+    return F.mish(y) * mask
+
+
+def cv1_resnet_block(sd, p, x, mask, temb):
+    """ResnetBlock1D, matcha decoder.py:46-61."""
+    h = cv1_block1d(x, mask, sd, p + "block1.")
+    h = h + F.linear(F.mish(temb), sd[p + "mlp.1.weight"], sd[p + "mlp.1.bias"]).unsqueeze(-1)
+    h = cv1_block1d(h, mask, sd, p + "block2.")
+    return h + F.conv1d(x * mask, sd[p + "res_conv.weight"], sd[p + "res_conv.bias"])
+
+
+def cv1_downsample(sd, p, x):
+    """Downsample1D, matcha decoder.py:64-70: Conv1d(C, C, 3, stride 2, padding 1)."""
+    return F.conv1d(x, sd[p + "conv.weight"], sd[p + "conv.bias"], stride=2, padding=1)
+
+
+def cv1_upsample(sd, p, x):
+    """Upsample1D (use_conv_transpose), matcha decoder.py:120-158: ConvTranspose1d(C, C, 4, stride 2, padding 1)."""
+    return F.conv_transpose1d(x, sd[p + "conv.weight"], sd[p + "conv.bias"], stride=2, padding=1)

@@ -1,0 +1,92 @@
+"""GPU parity, SURVEY section 8 row A9: the cosyvoice1 / Matcha non-causal building blocks (GroupNorm(8) + Mish Block1D /
+ResnetBlock1D, stride-2 Downsample1D, ConvTranspose k4 s2 Upsample1D) through the C-ABI against golden outputs of the
+unmodified reference modules (tests/golden/cv1_blocks.npz, CPU fp32) and, at a larger size, against the CPU oracle.
+
+Tolerance: bf16 operands / fp32 accumulation.  One conv with bf16-rounded inputs and weights differs from fp32 by
+rel-L2 ~3e-3 (2^-9 per operand, averaged over K); a resnet block chains two convs through a normalisation -> 1e-2.
+"""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from conftest import GOLDEN
+
+pytestmark = pytest.mark.gpu
+
+CONV_REL_L2 = 5e-3
+RESNET_REL_L2 = 1e-2
+
+
+def rel_l2(a, b):
+    return float(torch.linalg.norm(a.double() - b.double()) / torch.linalg.norm(b.double()))
+
+
+@pytest.fixture(scope="module")
+def cv1(engine):
+    from moss_speech_decoder_cosy_b200 import synth, weights
+    sd = synth.synth_cv1_blocks_state_dict(0)
+    t = {}
+    t.update(weights.pack_cv1_resnet(sd, "res_in", "cv1.res_in"))
+    t.update(weights.pack_cv1_resnet(sd, "res_mid", "cv1.res_mid"))
+    t.update(weights.pack_cv1_downsample(sd, "down", "cv1.down"))
+    t.update(weights.pack_cv1_upsample(sd, "up", "cv1.up"))
+    engine.load_tensors(t)
+    return engine, sd
+
+
+@pytest.mark.parametrize("tag", ["a", "b"])
+def test_cv1_blocks_match_reference(cv1, tag):
+    engine, _ = cv1
+    z = np.load(os.path.join(GOLDEN, "cv1_blocks.npz"))
+    t = {k[2:]: torch.from_numpy(z[k]).cuda() for k in z.files if k.startswith(tag + "_")}
+    n0 = engine.launch_count()
+    h = engine.cv1_resnet_block("cv1.res_in", t["x"], t["mask"], t["temb"])
+    h2 = engine.cv1_resnet_block("cv1.res_mid", t["res_in"], t["mask"], t["temb"])
+    d = engine.cv1_downsample("cv1.down", t["res_mid"] * t["mask"])
+    u = engine.cv1_upsample("cv1.up", t["down"])
+    torch.cuda.synchronize()
+    assert engine.launch_count() > n0
+    for got, key, tol in ((h, "res_in", RESNET_REL_L2), (h2, "res_mid", RESNET_REL_L2), (d, "down", CONV_REL_L2),
+                          (u, "up", CONV_REL_L2)):
+        assert got.shape == t[key].shape, key
+        assert torch.isfinite(got).all(), key
+        err = rel_l2(got, t[key])
+        print(f"cv1 {tag} {key}: rel_l2={err:.3e} max_abs={float((got - t[key]).abs().max()):.3e}")
+        assert err < tol, key
+
+
+def test_cv1_chain_matches_oracle_large(cv1):
+    """down -> resnet -> up chain at config-2-like size (B2 = 16, T = 648, odd half length 324 -> 162) vs the CPU oracle."""
+    from oracle import port
+    engine, sd = cv1
+    g = torch.Generator().manual_seed(7)
+    B, T = 16, 648
+    x = torch.randn(B, 320, T, generator=g)
+    temb = torch.randn(B, 1024, generator=g)
+    mask = torch.ones(B, 1, T)
+    mask[3, :, 500:] = 0
+    mask[9, :, 301:] = 0
+    with torch.inference_mode():
+        r1 = port.cv1_resnet_block(sd, "res_in.", x, mask, temb)
+        rd = port.cv1_downsample(sd, "down.", r1 * mask)
+        mask2 = mask[:, :, ::2]
+        r2 = port.cv1_resnet_block(sd, "res_mid.", rd, mask2, temb)
+        ru = port.cv1_upsample(sd, "up.", r2 * mask2)
+    h1 = engine.cv1_resnet_block("cv1.res_in", x.cuda(), mask.cuda(), temb.cuda())
+    hd = engine.cv1_downsample("cv1.down", h1 * mask.cuda())
+    h2 = engine.cv1_resnet_block("cv1.res_mid", hd, mask2.contiguous().cuda(), temb.cuda())
+    hu = engine.cv1_upsample("cv1.up", h2 * mask2.cuda())
+    torch.cuda.synchronize()
+    for got, ref, name, tol in ((h1, r1, "resnet", 1e-2), (hd, rd, "down", 1.5e-2), (h2, r2, "resnet2", 2.5e-2),
+                                (hu, ru, "up", 3e-2)):
+        err = rel_l2(got.cpu(), ref)
+        print(f"cv1 chain {name}: rel_l2={err:.3e}")
+        assert got.shape == ref.shape and err < tol, name
+
+
+def test_cv1_missing_weights_fail_loudly(engine):
+    x = torch.zeros(1, 256, 8, device="cuda")
+    with pytest.raises(RuntimeError, match="missing"):
+        engine.cv1_downsample("cv1.nope", x)

@@ -231,3 +231,77 @@ def test_gemm_work_units_cover_every_tile_once_and_share_the_a_tile():
                     ms.add(tile // tiles_n)
                 assert len(ms) == 1               # tiles_n % group == 0: one A tile per unit
         assert sorted(seen) == list(range(num_tiles))
+
+
+# ---- row A9 layouts (csrc/cv1_ops.cu): the operand views the GEMM core is given, emulated in fp32 on the host -----------
+def _rows_layout(x, S, g, rows_total):
+    """[B, C, T] -> channels-last rows, row of (b, t) = b * S + g + t, zero elsewhere (cv1_pack_kernel)."""
+    B, C, T = x.shape
+    rows = torch.zeros(rows_total, C)
+    for b in range(B):
+        rows[b * S + g: b * S + g + T] = x[b].t()
+    return rows
+
+
+def _shifted(rows, shift):
+    out = torch.zeros_like(rows)
+    n = rows.shape[0]
+    if shift >= 0:
+        out[: n - shift] = rows[shift:]
+    else:
+        out[-shift:] = rows[: n + shift]
+    return out
+
+
+def test_cv1_stride2_window_view_equals_conv():
+    """Downsample1D as ONE K = 3C segment over the overlapping-window view (row stride 2C, 3C columns)."""
+    from moss_speech_decoder_cosy_b200 import weights
+    g = torch.Generator().manual_seed(3)
+    for T in (9, 12):
+        B, C = 2, 64
+        x, w, bias = torch.randn(B, C, T, generator=g), torch.randn(C, C, 3, generator=g), torch.randn(C, generator=g)
+        ref = torch.nn.functional.conv1d(x, w, bias, stride=2, padding=1)
+        T_out = (T - 1) // 2 + 1
+        assert ref.shape[-1] == T_out
+        S_out = T_out + 1
+        S_in = 2 * S_out
+        Mp = B * S_out
+        flat = _rows_layout(x, S_in, 1, 2 * Mp + 2).reshape(-1)
+        view = torch.as_strided(flat, (Mp, 3 * C), (2 * C, 1))
+        y = view @ weights.conv_weight_taps(w).t() + bias
+        for b in range(B):
+            torch.testing.assert_close(y[b * S_out: b * S_out + T_out].t(), ref[b], rtol=1e-4, atol=1e-4)
+
+
+def test_cv1_polyphase_convtranspose_and_symmetric_taps():
+    from moss_speech_decoder_cosy_b200 import weights
+    g = torch.Generator().manual_seed(4)
+    B, C, T = 2, 64, 11
+    x = torch.randn(B, C, T, generator=g)
+    S, Mp = T + 2, B * (T + 2)
+    rows = _rows_layout(x, S, 1, Mp)
+    taps = torch.cat([_shifted(rows, -1), rows, _shifted(rows, 1)], dim=1)   # segments with row_shift -1 / 0 / +1
+    # ConvTranspose1d(C, C, 4, 2, 1): N = 2C, output row q holds frames 2q | 2q + 1
+    wt, bt = torch.randn(C, C, 4, generator=g), torch.randn(C, generator=g)
+    ref = torch.nn.functional.conv_transpose1d(x, wt, bt, stride=2, padding=1)
+    y = taps @ weights.convtranspose_polyphase(wt, 2, 1).t() + bt.repeat(2)
+    for b in range(B):
+        got = y[b * S + 1: b * S + 1 + T].reshape(T, 2, C).reshape(2 * T, C).t()
+        torch.testing.assert_close(got, ref[b], rtol=1e-4, atol=1e-4)
+    # symmetric k3 conv (Block1D)
+    w3, b3 = torch.randn(C, C, 3, generator=g), torch.randn(C, generator=g)
+    ref3 = torch.nn.functional.conv1d(x, w3, b3, padding=1)
+    y3 = taps @ weights.conv_weight_taps(w3).t() + b3
+    for b in range(B):
+        torch.testing.assert_close(y3[b * S + 1: b * S + 1 + T].t(), ref3[b], rtol=1e-4, atol=1e-4)
+
+
+def test_cv1_packers_shapes():
+    from moss_speech_decoder_cosy_b200 import synth, weights
+    sd = synth.synth_cv1_blocks_state_dict(0)
+    t = weights.pack_cv1_resnet(sd, "res_in", "cv1.res_in")
+    assert t["cv1.res_in.c1.w"].shape == (256, 3 * 320) and t["cv1.res_in.c1.w"].dtype == torch.bfloat16
+    assert t["cv1.res_in.res.w"].shape == (256, 320) and t["cv1.res_in.mlp.w"].shape == (256, 1024)
+    assert weights.pack_cv1_downsample(sd, "down", "d")["d.w"].shape == (256, 768)
+    u = weights.pack_cv1_upsample(sd, "up", "u")
+    assert u["u.w"].shape == (512, 768) and u["u.b"].shape == (512,)

@@ -67,3 +67,19 @@ def test_token2wav_restatement(sds):
     assert _rel(mel[0], torch.from_numpy(z["mel"])) < 1e-4
     ref = torch.from_numpy(z["wav"])
     assert float(10 * torch.log10(ref.pow(2).sum() / (wav[0] - ref).pow(2).sum())) > 40.0
+
+
+@pytest.mark.parametrize("tag", ["a", "b"])
+def test_cv1_blocks_restatement(tag):
+    """Row A9: the restated Matcha Block1D / ResnetBlock1D / Downsample1D / Upsample1D against the reference's modules."""
+    z = np.load(os.path.join(GOLDEN, "cv1_blocks.npz"))
+    sd = synth.synth_cv1_blocks_state_dict(0)
+    t = {k[2:]: torch.from_numpy(z[k]) for k in z.files if k.startswith(tag + "_")}
+    with torch.inference_mode():
+        h = port.cv1_resnet_block(sd, "res_in.", t["x"], t["mask"], t["temb"])
+        h2 = port.cv1_resnet_block(sd, "res_mid.", h, t["mask"], t["temb"])
+        d = port.cv1_downsample(sd, "down.", h2 * t["mask"])
+        u = port.cv1_upsample(sd, "up.", d)
+    for got, key in ((h, "res_in"), (h2, "res_mid"), (d, "down"), (u, "up")):
+        assert got.shape == t[key].shape
+        assert _rel(got, t[key]) < 1e-5, key
