@@ -152,6 +152,36 @@ __global__ void __launch_bounds__(kC) gn_apply_kernel(const float* __restrict__ 
     }
 }
 
+// Last stage of a ResnetBlock1D: out[b, c, t] = mish(GroupNorm(h)) * mask + resid, written straight in the reference's
+// channel-first layout through a 32-frame smem tile (no fp32 channels-last round trip).  grid (ceil(T / 32), B), 256 threads.
+__global__ void __launch_bounds__(kC) gn_apply_bct_kernel(const float* __restrict__ h, const double* __restrict__ stats,
+                                                           const float* __restrict__ gamma, const float* __restrict__ beta,
+                                                           const float* __restrict__ mask, const float* __restrict__ resid,
+                                                           float* __restrict__ out, int T, int S, int g, float eps) {
+    __shared__ float tile[32][kC + 1];
+    const int b = blockIdx.y, c = threadIdx.x;
+    const double* d = stats + ((size_t)b * kGroups + (c >> 5)) * 2;
+    const double n = 32.0 * (double)T;
+    const double mean = d[0] / n;
+    double var = d[1] / n - mean * mean;
+    if (var < 0.0) var = 0.0;
+    const float rstd = (float)(1.0 / sqrt(var + (double)eps));
+    const float a = rstd * gamma[c], sh = beta[c] - (float)mean * a;
+    const int t0 = blockIdx.x * 32, nt = min(32, T - t0);
+    for (int j = 0; j < nt; ++j) {
+        const size_t idx = ((size_t)b * S + g + t0 + j) * kC + c;
+        const float m = mask ? mask[(size_t)b * T + t0 + j] : 1.f;
+        float v = mish_exact(fmaf(h[idx], a, sh)) * m;
+        if (resid) v += resid[idx];
+        tile[j][c] = v;
+    }
+    __syncthreads();
+    const int lane = c & 31, w = c >> 5;
+    if (lane < nt) {
+        for (int cc = w * 32; cc < w * 32 + 32; ++cc) out[((size_t)b * kC + cc) * T + t0 + lane] = tile[lane][cc];
+    }
+}
+
 inline size_t align256(size_t v) { return (v + 255) & ~(size_t)255; }
 
 }  // namespace
@@ -175,18 +205,18 @@ int Engine::cv1_resnet_block(const char* prefix, int B, int T, int Cin, const fl
     const int S = T + 2, g = 1;
     const int64_t rows = (int64_t)B * S;
     const int Mp = (int)((rows + kGemmBM - 1) / kGemmBM * kGemmBM);
-    // workspace: xa bf16 [Mp, cin_pad] | a1 bf16 [Mp, 256] | h f32 [Mp, 256] | res f32 [Mp, 256] | o f32 [Mp, 256] | row_seq | tbias | stats
+    // workspace: xa bf16 [Mp, cin_pad] | a1 bf16 [Mp, 256] | h f32 [Mp, 256] | res f32 [Mp, 256] | row_seq | tbias | stats
     size_t off = 0;
     auto take = [&](size_t bytes) { size_t o = off; off = align256(off + bytes); return o; };
     const size_t o_xa = take((size_t)(Mp + 2) * cin_pad * 2), o_a1 = take((size_t)(Mp + 2) * kC * 2), o_h = take((size_t)Mp * kC * 4),
-                 o_res = take((size_t)Mp * kC * 4), o_o = take((size_t)Mp * kC * 4), o_rs = take((size_t)Mp * 4),
+                 o_res = take((size_t)Mp * kC * 4), o_rs = take((size_t)Mp * 4),
                  o_tb = take((size_t)B * kC * 4), o_st = take((size_t)B * kGroups * 2 * 8 * 2);
     ws_cv1_.reserve(off);
     char* base = ws_cv1_.as<char>();
     if (!base) return fail("cv1_resnet_block: workspace allocation failed");
     auto* xa = reinterpret_cast<__nv_bfloat16*>(base + o_xa);
     auto* a1 = reinterpret_cast<__nv_bfloat16*>(base + o_a1);
-    float *h = reinterpret_cast<float*>(base + o_h), *res = reinterpret_cast<float*>(base + o_res), *o = reinterpret_cast<float*>(base + o_o);
+    float *h = reinterpret_cast<float*>(base + o_h), *res = reinterpret_cast<float*>(base + o_res);
     auto* row_seq = reinterpret_cast<int32_t*>(base + o_rs);
     float* tbias = reinterpret_cast<float*>(base + o_tb);
     double* stats = reinterpret_cast<double*>(base + o_st);
@@ -232,9 +262,8 @@ int Engine::cv1_resnet_block(const char* prefix, int B, int T, int Cin, const fl
     if (conv3(a1, kC, w2, b2, h)) return -1;
     double* stats2 = stats + (size_t)B * kGroups * 2;
     gn_stats_kernel<<<gs, kC, 0, st>>>(h, stats2, T, S, g);
-    gn_apply_kernel<<<ga, kC, 0, st>>>(h, stats2, g2, be2, mask, nullptr, res, nullptr, o, T, S, g, 1e-5f);
-    cv1_unpack_kernel<<<dim3((T + 31) / 32, kC / 32, B), dim3(32, 8), 0, st>>>(o, out, kC, kC, T, 1, S, g, T);
-    launches_ += 5;
+    gn_apply_bct_kernel<<<dim3((T + 31) / 32, B), kC, 0, st>>>(h, stats2, g2, be2, mask, res, out, T, S, g, 1e-5f);
+    launches_ += 4;
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return fail(std::string("cv1_resnet_block: ") + cudaGetErrorString(e));
     return 0;
