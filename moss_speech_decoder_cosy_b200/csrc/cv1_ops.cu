@@ -39,24 +39,35 @@ __device__ __forceinline__ float mish_exact(float x) {
     return x * tanhf(sp);
 }
 
+// Same form as the GEMM epilogue's Mish (epilogue.cuh fast_mish): u = e^x, tanh(log(1 + u)) = (u^2 + 2u) / (u^2 + 2u + 2); one
+// ex2.approx + one rcp.approx per element, no range fix-up branches (the libm form made the apply kernels SFU / issue bound:
+// 83 us for 21 M elements, profiles/r01_cv1_launches_summary.txt).
+__device__ __forceinline__ float mish_fast(float x) {
+    float u, r;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(u) : "f"(fminf(x, 20.f) * 1.4426950408889634f));
+    const float n = u * (u + 2.f);
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(n + 2.f));
+    return x > 20.f ? x : x * (n * r);
+}
+
 // [B, C, T] fp32 (x mask) -> channels-last bf16 rows; row of (b, t) = b * S + g + t.  32 x 32 smem transpose.
 __global__ void cv1_pack_kernel(const float* __restrict__ x, const float* __restrict__ mask, __nv_bfloat16* __restrict__ out,
                                 int C, int Cpad, int T, int S, int g) {
-    __shared__ float tile[32][33];
-    const int b = blockIdx.z, t0 = blockIdx.x * 32, c0 = blockIdx.y * 32;
-    for (int j = threadIdx.y; j < 32; j += blockDim.y) {
-        const int c = c0 + j, t = t0 + threadIdx.x;
-        float v = 0.f;
-        if (c < C && t < T) {
-            v = x[((size_t)b * C + c) * T + t];
-            if (mask) v *= mask[(size_t)b * T + t];
-        }
-        tile[j][threadIdx.x] = v;
+    // tile of 64 channels x 32 frames; block (32, 8); Cpad % 64 == 0.  Stores are bf16x2: 128 B per warp and row.
+    __shared__ float tile[64][33];
+    const int b = blockIdx.z, t0 = blockIdx.x * 32, c0 = blockIdx.y * 64;
+    const int tr = t0 + threadIdx.x;
+    const float m = (mask && tr < T) ? mask[(size_t)b * T + tr] : 1.f;
+    for (int j = threadIdx.y; j < 64; j += 8) {
+        const int c = c0 + j;
+        tile[j][threadIdx.x] = (c < C && tr < T) ? x[((size_t)b * C + c) * T + tr] * m : 0.f;
     }
     __syncthreads();
-    for (int j = threadIdx.y; j < 32; j += blockDim.y) {
-        const int t = t0 + j, c = c0 + threadIdx.x;
-        if (t < T && c < Cpad) out[((size_t)b * S + g + t) * Cpad + c] = __float2bfloat16(tile[threadIdx.x][j]);
+    for (int j = threadIdx.y; j < 32; j += 8) {
+        const int t = t0 + j, c = c0 + 2 * threadIdx.x;
+        if (t < T)
+            *reinterpret_cast<__nv_bfloat162*>(out + ((size_t)b * S + g + t) * Cpad + c) =
+                __floats2bfloat162_rn(tile[2 * threadIdx.x][j], tile[2 * threadIdx.x + 1][j]);
     }
 }
 
@@ -86,17 +97,25 @@ __global__ void cv1_rowseq_kernel(int32_t* __restrict__ row_seq, int Mp, int B, 
     row_seq[r] = (b < B && t >= 0 && t < T) ? b : -1;
 }
 
-// tbias[b, n] = bias[n] + sum_k w[n, k] * mish(temb[b, k])     (ResnetBlock1D.mlp, decoder.py:49,58); one warp per output
-__global__ void cv1_time_mlp_kernel(const float* __restrict__ temb, const float* __restrict__ w, const float* __restrict__ bias,
-                                    float* __restrict__ tbias, int B, int dim, int n_out) {
-    const int gw = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
-    if (gw >= B * n_out) return;
-    const int b = gw / n_out, n = gw - b * n_out;
-    float acc = 0.f;
-    for (int k = lane; k < dim; k += 32) acc += w[(size_t)n * dim + k] * mish_exact(temb[(size_t)b * dim + k]);
+// tbias[b, n] = bias[n] + sum_k w[n, k] * mish(temb[b, k])     (ResnetBlock1D.mlp, decoder.py:49,58)
+// grid (n_out / 32, B), 256 threads: mish(temb[b]) once per block into smem, then 4 outputs per warp with coalesced weight rows.
+__global__ void __launch_bounds__(256) cv1_time_mlp_kernel(const float* __restrict__ temb, const float* __restrict__ w,
+                                                            const float* __restrict__ bias, float* __restrict__ tbias, int dim,
+                                                            int n_out) {
+    extern __shared__ float tm[];
+    const int b = blockIdx.y, lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    for (int k = threadIdx.x; k < dim; k += 256) tm[k] = mish_exact(temb[(size_t)b * dim + k]);
+    __syncthreads();
+    for (int i = 0; i < 4; ++i) {
+        const int n = blockIdx.x * 32 + wid * 4 + i;
+        if (n >= n_out) break;
+        const float* wr = w + (size_t)n * dim;
+        float acc = 0.f;
+        for (int k = lane; k < dim; k += 32) acc = fmaf(wr[k], tm[k], acc);
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
-    if (lane == 0) tbias[gw] = acc + bias[n];
+        for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+        if (lane == 0) tbias[(size_t)b * n_out + n] = acc + bias[n];
+    }
 }
 
 // GroupNorm statistics of h [rows, 256] fp32: stats[b, g] = {sum, sum of squares} over the T valid rows of utterance b.
@@ -124,61 +143,96 @@ __global__ void __launch_bounds__(kC) gn_stats_kernel(const float* __restrict__ 
     }
 }
 
+struct GnCoef {
+    float a[4], sh[4];
+};
+// per-thread affine of 4 consecutive channels c..c+3 (one group): y = h * a + sh
+__device__ __forceinline__ GnCoef gn_coef(const double* __restrict__ stats, const float* __restrict__ gamma,
+                                          const float* __restrict__ beta, int b, int c, int T, float eps) {
+    const double* d = stats + ((size_t)b * kGroups + (c >> 5)) * 2;
+    const double n = 32.0 * (double)T;
+    const double mean = d[0] / n;
+    double var = d[1] / n - mean * mean;
+    if (var < 0.0) var = 0.0;
+    const float rstd = (float)(1.0 / sqrt(var + (double)eps)), fm = (float)mean;
+    const float4 gm = *reinterpret_cast<const float4*>(gamma + c), bt = *reinterpret_cast<const float4*>(beta + c);
+    GnCoef k;
+    k.a[0] = rstd * gm.x; k.a[1] = rstd * gm.y; k.a[2] = rstd * gm.z; k.a[3] = rstd * gm.w;
+    k.sh[0] = bt.x - fm * k.a[0]; k.sh[1] = bt.y - fm * k.a[1]; k.sh[2] = bt.z - fm * k.a[2]; k.sh[3] = bt.w - fm * k.a[3];
+    return k;
+}
+
 // v = mish(GroupNorm(h)) * mask  [+ tbias[b, c], result * mask: the input of block2]  [+ resid]
-// -> bf16 channels-last (next conv operand) and / or fp32 channels-last.  grid (ceil(T / 8), B), 256 threads, 8 rows each.
+// -> bf16 channels-last (next conv operand) and / or fp32 channels-last.  grid (ceil(T / 32), B), 256 threads: a thread owns 4
+// consecutive channels (16 B loads, 8 B bf16 stores), 64 threads per row, 4 rows per pass.
 __global__ void __launch_bounds__(kC) gn_apply_kernel(const float* __restrict__ h, const double* __restrict__ stats,
                                                        const float* __restrict__ gamma, const float* __restrict__ beta,
                                                        const float* __restrict__ mask, const float* __restrict__ tbias,
                                                        const float* __restrict__ resid, __nv_bfloat16* __restrict__ out_bf16,
                                                        float* __restrict__ out_f32, int T, int S, int g, float eps) {
-    const int b = blockIdx.y, c = threadIdx.x;
-    const double* d = stats + ((size_t)b * kGroups + (c >> 5)) * 2;
-    const double n = 32.0 * (double)T;
-    const double mean = d[0] / n;
-    double var = d[1] / n - mean * mean;
-    if (var < 0.0) var = 0.0;
-    const float rstd = (float)(1.0 / sqrt(var + (double)eps));
-    const float a = rstd * gamma[c], sh = beta[c] - (float)mean * a;
-    const float tb = tbias ? tbias[(size_t)b * kC + c] : 0.f;
-    const int t0 = blockIdx.x * 8, t1 = min(T, t0 + 8);
-    for (int t = t0; t < t1; ++t) {
+    const int b = blockIdx.y, c = (threadIdx.x & 63) * 4, r = threadIdx.x >> 6;
+    const GnCoef k = gn_coef(stats, gamma, beta, b, c, T, eps);
+    float tb[4] = {0.f, 0.f, 0.f, 0.f};
+    if (tbias) {
+        const float4 t4 = *reinterpret_cast<const float4*>(tbias + (size_t)b * kC + c);
+        tb[0] = t4.x; tb[1] = t4.y; tb[2] = t4.z; tb[3] = t4.w;
+    }
+    const int t0 = blockIdx.x * 32, t1 = min(T, t0 + 32);
+    for (int t = t0 + r; t < t1; t += 4) {
         const size_t idx = ((size_t)b * S + g + t) * kC + c;
         const float m = mask ? mask[(size_t)b * T + t] : 1.f;
-        float v = mish_exact(fmaf(h[idx], a, sh)) * m;
-        if (tbias) v = (v + tb) * m;
-        if (resid) v += resid[idx];
-        if (out_bf16) out_bf16[idx] = __float2bfloat16(v);
-        if (out_f32) out_f32[idx] = v;
+        const float4 h4 = *reinterpret_cast<const float4*>(h + idx);
+        float v[4] = {h4.x, h4.y, h4.z, h4.w};
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            v[i] = mish_fast(fmaf(v[i], k.a[i], k.sh[i])) * m;
+            if (tbias) v[i] = (v[i] + tb[i]) * m;
+        }
+        if (resid) {
+            const float4 r4 = *reinterpret_cast<const float4*>(resid + idx);
+            v[0] += r4.x; v[1] += r4.y; v[2] += r4.z; v[3] += r4.w;
+        }
+        if (out_bf16) {
+            __nv_bfloat162 lo = __floats2bfloat162_rn(v[0], v[1]), hi = __floats2bfloat162_rn(v[2], v[3]);
+            uint2 pk;
+            pk.x = *reinterpret_cast<uint32_t*>(&lo);
+            pk.y = *reinterpret_cast<uint32_t*>(&hi);
+            *reinterpret_cast<uint2*>(out_bf16 + idx) = pk;
+        }
+        if (out_f32) *reinterpret_cast<float4*>(out_f32 + idx) = make_float4(v[0], v[1], v[2], v[3]);
     }
 }
 
 // Last stage of a ResnetBlock1D: out[b, c, t] = mish(GroupNorm(h)) * mask + resid, written straight in the reference's
 // channel-first layout through a 32-frame smem tile (no fp32 channels-last round trip).  grid (ceil(T / 32), B), 256 threads.
+// Tile column of channel c = (c & 3) * 64 + (c >> 2): conflict-free for the channel-quad writes and for the frame-major reads.
 __global__ void __launch_bounds__(kC) gn_apply_bct_kernel(const float* __restrict__ h, const double* __restrict__ stats,
                                                            const float* __restrict__ gamma, const float* __restrict__ beta,
                                                            const float* __restrict__ mask, const float* __restrict__ resid,
                                                            float* __restrict__ out, int T, int S, int g, float eps) {
     __shared__ float tile[32][kC + 1];
-    const int b = blockIdx.y, c = threadIdx.x;
-    const double* d = stats + ((size_t)b * kGroups + (c >> 5)) * 2;
-    const double n = 32.0 * (double)T;
-    const double mean = d[0] / n;
-    double var = d[1] / n - mean * mean;
-    if (var < 0.0) var = 0.0;
-    const float rstd = (float)(1.0 / sqrt(var + (double)eps));
-    const float a = rstd * gamma[c], sh = beta[c] - (float)mean * a;
+    const int b = blockIdx.y, q = threadIdx.x & 63, c = q * 4, r = threadIdx.x >> 6;
+    const GnCoef k = gn_coef(stats, gamma, beta, b, c, T, eps);
     const int t0 = blockIdx.x * 32, nt = min(32, T - t0);
-    for (int j = 0; j < nt; ++j) {
+    for (int j = r; j < nt; j += 4) {
         const size_t idx = ((size_t)b * S + g + t0 + j) * kC + c;
         const float m = mask ? mask[(size_t)b * T + t0 + j] : 1.f;
-        float v = mish_exact(fmaf(h[idx], a, sh)) * m;
-        if (resid) v += resid[idx];
-        tile[j][c] = v;
+        const float4 h4 = *reinterpret_cast<const float4*>(h + idx);
+        float v[4] = {h4.x, h4.y, h4.z, h4.w};
+#pragma unroll
+        for (int i = 0; i < 4; ++i) v[i] = mish_fast(fmaf(v[i], k.a[i], k.sh[i])) * m;
+        if (resid) {
+            const float4 r4 = *reinterpret_cast<const float4*>(resid + idx);
+            v[0] += r4.x; v[1] += r4.y; v[2] += r4.z; v[3] += r4.w;
+        }
+#pragma unroll
+        for (int i = 0; i < 4; ++i) tile[j][i * 64 + q] = v[i];
     }
     __syncthreads();
-    const int lane = c & 31, w = c >> 5;
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     if (lane < nt) {
-        for (int cc = w * 32; cc < w * 32 + 32; ++cc) out[((size_t)b * kC + cc) * T + t0 + lane] = tile[lane][cc];
+        for (int cc = w * 32; cc < w * 32 + 32; ++cc)
+            out[((size_t)b * kC + cc) * T + t0 + lane] = tile[lane][(cc & 3) * 64 + (cc >> 2)];
     }
 }
 
@@ -225,10 +279,10 @@ int Engine::cv1_resnet_block(const char* prefix, int B, int T, int Cin, const fl
     cudaMemsetAsync(a1, 0, (size_t)(Mp + 2) * kC * 2, st);
     cudaMemsetAsync(stats, 0, (size_t)B * kGroups * 2 * 8 * 2, st);
     cv1_rowseq_kernel<<<(Mp + 255) / 256, 256, 0, st>>>(row_seq, Mp, B, S, g, T);
-    cv1_pack_kernel<<<dim3((T + 31) / 32, (cin_pad + 31) / 32, B), dim3(32, 8), 0, st>>>(x, mask, xa, Cin, cin_pad, T, S, g);
+    cv1_pack_kernel<<<dim3((T + 31) / 32, cin_pad / 64, B), dim3(32, 8), 0, st>>>(x, mask, xa, Cin, cin_pad, T, S, g);
     launches_ += 2;
     if (temb) {
-        cv1_time_mlp_kernel<<<(B * kC * 32 + 255) / 256, 256, 0, st>>>(temb, wm, bm, tbias, B, time_dim, kC);
+        cv1_time_mlp_kernel<<<dim3(kC / 32, B), 256, (size_t)time_dim * 4, st>>>(temb, wm, bm, tbias, time_dim, kC);
         ++launches_;
     }
 
@@ -242,7 +296,7 @@ int Engine::cv1_resnet_block(const char* prefix, int B, int T, int Cin, const fl
         p.epi.out_f32 = dst; p.epi.ldf = kC;
         return gemm(p, st);
     };
-    const dim3 gs((T + 63) / 64, B), ga((T + 7) / 8, B);
+    const dim3 gs((T + 63) / 64, B), ga((T + 31) / 32, B);
     // block1: conv -> GroupNorm -> Mish -> mask, + time bias; a1 = block2's masked input
     if (conv3(xa, cin_pad, w1, b1, h)) return -1;
     gn_stats_kernel<<<gs, kC, 0, st>>>(h, stats, T, S, g);
@@ -293,7 +347,7 @@ int Engine::cv1_downsample(const char* prefix, int B, int T, int C, const float*
     auto* row_seq = reinterpret_cast<int32_t*>(base + o_rs);
     cudaMemsetAsync(xa, 0, in_bytes, st);
     cv1_rowseq_kernel<<<(Mp + 255) / 256, 256, 0, st>>>(row_seq, Mp, B, S_out, 0, T_out);
-    cv1_pack_kernel<<<dim3((T + 31) / 32, (C + 31) / 32, B), dim3(32, 8), 0, st>>>(x, nullptr, xa, C, C, T, S_in, 1);
+    cv1_pack_kernel<<<dim3((T + 31) / 32, C / 64, B), dim3(32, 8), 0, st>>>(x, nullptr, xa, C, C, T, S_in, 1);
     launches_ += 2;
     GemmProblem p;
     p.a[0].ptr = xa; p.a[0].rows = Mp; p.a[0].cols = 3 * C; p.a[0].ld = 2 * C;   // overlapping windows [x[2m-1] | x[2m] | x[2m+1]]
@@ -333,7 +387,7 @@ int Engine::cv1_upsample(const char* prefix, int B, int T, int C, const float* x
     auto* row_seq = reinterpret_cast<int32_t*>(base + o_rs);
     cudaMemsetAsync(xa, 0, in_bytes, st);
     cv1_rowseq_kernel<<<(Mp + 255) / 256, 256, 0, st>>>(row_seq, Mp, B, S, g, T);
-    cv1_pack_kernel<<<dim3((T + 31) / 32, (C + 31) / 32, B), dim3(32, 8), 0, st>>>(x, nullptr, xa, C, C, T, S, g);
+    cv1_pack_kernel<<<dim3((T + 31) / 32, C / 64, B), dim3(32, 8), 0, st>>>(x, nullptr, xa, C, C, T, S, g);
     launches_ += 2;
     GemmProblem p;
     p.a[0].ptr = xa; p.a[0].rows = Mp; p.a[0].cols = C; p.a[0].ld = C;
