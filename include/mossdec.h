@@ -94,6 +94,8 @@ int mossdec_fade_in_out(mossdec_handle* h, float* speech, const float* prev_tail
  *
  *   mossdec_cv1_resnet_block <- ResnetBlock1D.forward(x, mask, time_emb)   matcha decoder.py:46-61 (Block1D :32-43)
  *       x [B, Cin, T], mask [B, 1, T], time_emb [B, time_dim] (NULL = no time bias) -> out [B, 256, T]
+ *   mossdec_cv1_block1d      <- Block1D.forward(x, mask) (also the decoder's final_block)   matcha decoder.py:32-43
+ *       x [B, Cin, T], mask [B, 1, T] -> out [B, 256, T];  tensors "<prefix>.c.w / .c.b / .gn.g / .gn.b"
  *   mossdec_cv1_downsample   <- Downsample1D.forward   Conv1d(C, C, 3, 2, 1)            matcha decoder.py:64-70
  *       x [B, C, T] -> out [B, C, (T - 1) / 2 + 1]
  *   mossdec_cv1_upsample     <- Upsample1D.forward     ConvTranspose1d(C, C, 4, 2, 1)   matcha decoder.py:120-158
@@ -101,6 +103,8 @@ int mossdec_fade_in_out(mossdec_handle* h, float* speech, const float* prev_tail
  */
 int mossdec_cv1_resnet_block(mossdec_handle* h, const char* prefix, int32_t B, int32_t T, int32_t Cin, const float* x,
                              const float* mask, const float* time_emb, int32_t time_dim, float* out, void* stream);
+int mossdec_cv1_block1d(mossdec_handle* h, const char* prefix, int32_t B, int32_t T, int32_t Cin, const float* x, const float* mask,
+                        float* out, void* stream);
 int mossdec_cv1_downsample(mossdec_handle* h, const char* prefix, int32_t B, int32_t T, int32_t C, const float* x, float* out,
                            void* stream);
 int mossdec_cv1_upsample(mossdec_handle* h, const char* prefix, int32_t B, int32_t T, int32_t C, const float* x, float* out,

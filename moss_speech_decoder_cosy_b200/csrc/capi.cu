@@ -79,6 +79,10 @@ int mossdec_cv1_resnet_block(mossdec_handle* h, const char* prefix, int32_t B, i
                              const float* mask, const float* time_emb, int32_t time_dim, float* out, void* stream) {
     return h->eng->cv1_resnet_block(prefix, B, T, Cin, x, mask, time_emb, time_dim, out, (cudaStream_t)stream);
 }
+int mossdec_cv1_block1d(mossdec_handle* h, const char* prefix, int32_t B, int32_t T, int32_t Cin, const float* x, const float* mask,
+                        float* out, void* stream) {
+    return h->eng->cv1_block1d(prefix, B, T, Cin, x, mask, out, (cudaStream_t)stream);
+}
 int mossdec_cv1_downsample(mossdec_handle* h, const char* prefix, int32_t B, int32_t T, int32_t C, const float* x, float* out,
                            void* stream) {
     return h->eng->cv1_downsample(prefix, B, T, C, x, out, (cudaStream_t)stream);

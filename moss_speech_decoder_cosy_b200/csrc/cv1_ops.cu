@@ -3,6 +3,7 @@
 //
 //   cv1_resnet_block  <- matcha ResnetBlock1D / Block1D   third_party/Matcha-TTS/matcha/models/components/decoder.py:32-61
 //                        (Conv1d k3 pad 1 -> GroupNorm(8) -> Mish, time-MLP bias, 1x1 residual conv)
+//   cv1_block1d       <- matcha Block1D alone (the decoder's final_block)                                 decoder.py:32-43
 //   cv1_downsample    <- Downsample1D  Conv1d(C, C, 3, stride 2, pad 1)            decoder.py:64-70
 //   cv1_upsample      <- Upsample1D    ConvTranspose1d(C, C, 4, stride 2, pad 1)   decoder.py:120-158
 //
@@ -320,6 +321,52 @@ int Engine::cv1_resnet_block(const char* prefix, int B, int T, int Cin, const fl
     launches_ += 4;
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return fail(std::string("cv1_resnet_block: ") + cudaGetErrorString(e));
+    return 0;
+}
+
+// Block1D of the non-causal decoder (decoder.py:32-43; also its `final_block`): out = mish(GroupNorm(conv3(x * mask))) * mask
+int Engine::cv1_block1d(const char* prefix, int B, int T, int Cin, const float* x, const float* mask, float* out, cudaStream_t st) {
+    if (B <= 0 || T <= 0 || Cin <= 0) return fail("cv1_block1d: bad shape");
+    const std::string P(prefix);
+    missing_.clear();
+    const __nv_bfloat16* w = W<__nv_bfloat16>(P + ".c.w");
+    const float *bias = W<float>(P + ".c.b"), *gg = W<float>(P + ".gn.g"), *gb = W<float>(P + ".gn.b");
+    if (!missing_.empty()) return fail("cv1_block1d: missing tensors: " + missing_);
+    const int cin_pad = (Cin + kGemmBK - 1) / kGemmBK * kGemmBK;
+    const DevTensor* tw = find(P + ".c.w");
+    if (tw->shape.size() != 2 || tw->shape[0] != kC || tw->shape[1] != 3 * cin_pad)
+        return fail("cv1_block1d: " + P + ".c.w must be [256, 3 * ceil64(Cin)]");
+    const int S = T + 2, g = 1;
+    const int64_t rows = (int64_t)B * S;
+    const int Mp = (int)((rows + kGemmBM - 1) / kGemmBM * kGemmBM);
+    size_t off = 0;
+    auto take = [&](size_t bytes) { size_t o = off; off = align256(off + bytes); return o; };
+    const size_t o_xa = take((size_t)(Mp + 2) * cin_pad * 2), o_h = take((size_t)Mp * kC * 4), o_rs = take((size_t)Mp * 4),
+                 o_st = take((size_t)B * kGroups * 2 * 8);
+    ws_cv1_.reserve(off);
+    char* base = ws_cv1_.as<char>();
+    if (!base) return fail("cv1_block1d: workspace allocation failed");
+    auto* xa = reinterpret_cast<__nv_bfloat16*>(base + o_xa);
+    float* h = reinterpret_cast<float*>(base + o_h);
+    auto* row_seq = reinterpret_cast<int32_t*>(base + o_rs);
+    double* stats = reinterpret_cast<double*>(base + o_st);
+    cudaMemsetAsync(xa, 0, (size_t)(Mp + 2) * cin_pad * 2, st);
+    cudaMemsetAsync(stats, 0, (size_t)B * kGroups * 2 * 8, st);
+    cv1_rowseq_kernel<<<(Mp + 255) / 256, 256, 0, st>>>(row_seq, Mp, B, S, g, T);
+    cv1_pack_kernel<<<dim3((T + 31) / 32, cin_pad / 64, B), dim3(32, 8), 0, st>>>(x, mask, xa, Cin, cin_pad, T, S, g);
+    GemmProblem p;
+    p.a[0].ptr = xa; p.a[0].rows = Mp; p.a[0].cols = cin_pad; p.a[0].ld = cin_pad;
+    p.num_segs = 3;
+    for (int j = 0; j < 3; ++j) p.segs[j] = {0, j - 1, 0, cin_pad / kGemmBK};
+    p.M = Mp; p.N = kC; p.BN = kC; p.w = w;
+    p.epi.bias = bias; p.epi.row_seq = row_seq;
+    p.epi.out_f32 = h; p.epi.ldf = kC;
+    if (gemm(p, st)) return -1;
+    gn_stats_kernel<<<dim3((T + 63) / 64, B), kC, 0, st>>>(h, stats, T, S, g);
+    gn_apply_bct_kernel<<<dim3((T + 31) / 32, B), kC, 0, st>>>(h, stats, gg, gb, mask, nullptr, out, T, S, g, 1e-5f);
+    launches_ += 4;
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return fail(std::string("cv1_block1d: ") + cudaGetErrorString(e));
     return 0;
 }
 

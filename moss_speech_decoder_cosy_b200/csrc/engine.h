@@ -85,6 +85,7 @@ class Engine {
     // [B, C, T] fp32 in / out like the reference modules, weights looked up as "<prefix>.*" (weights.py pack_cv1_*).
     int cv1_resnet_block(const char* prefix, int B, int T, int Cin, const float* x, const float* mask, const float* temb,
                          int time_dim, float* out, cudaStream_t st);
+    int cv1_block1d(const char* prefix, int B, int T, int Cin, const float* x, const float* mask, float* out, cudaStream_t st);
     int cv1_downsample(const char* prefix, int B, int T, int C, const float* x, float* out, cudaStream_t st);
     int cv1_upsample(const char* prefix, int B, int T, int C, const float* x, float* out, cudaStream_t st);
 

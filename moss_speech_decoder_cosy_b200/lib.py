@@ -55,6 +55,8 @@ def load_library():
     lib.mossdec_fade_in_out.restype = i32
     lib.mossdec_cv1_resnet_block.argtypes = [vp, ctypes.c_char_p, i32, i32, i32, vp, vp, vp, i32, vp, vp]
     lib.mossdec_cv1_resnet_block.restype = i32
+    lib.mossdec_cv1_block1d.argtypes = [vp, ctypes.c_char_p, i32, i32, i32, vp, vp, vp, vp]
+    lib.mossdec_cv1_block1d.restype = i32
     lib.mossdec_cv1_downsample.argtypes = [vp, ctypes.c_char_p, i32, i32, i32, vp, vp, vp]
     lib.mossdec_cv1_downsample.restype = i32
     lib.mossdec_cv1_upsample.argtypes = [vp, ctypes.c_char_p, i32, i32, i32, vp, vp, vp]
@@ -80,7 +82,7 @@ EXPORTED_SYMBOLS = [
     "mossdec_finalize", "mossdec_estimator", "mossdec_flow_solve", "mossdec_hift", "mossdec_fade_in_out",
     "mossdec_launch_count", "mossdec_reset_launch_count", "mossdec_debug_read", "mossdec_profile",
     "mossdec_profile_read", "mossdec_set_hift_group_frames", "mossdec_cv1_resnet_block", "mossdec_cv1_downsample",
-    "mossdec_cv1_upsample",
+    "mossdec_cv1_upsample", "mossdec_cv1_block1d",
 ]
 
 
@@ -204,6 +206,15 @@ class Engine:
         self._check(self.lib.mossdec_cv1_resnet_block(self.h, prefix.encode(), B, T, Cin, _ptr(x), _ptr(mask), _ptr(te),
                                                       0 if te is None else te.shape[1], _ptr(out), self._stream()),
                     "cv1_resnet_block")
+        return out
+
+    def cv1_block1d(self, prefix, x, mask):
+        """Block1D.forward(x, mask) (matcha decoder.py:41-43): x [B, Cin, T], mask [B, 1, T] -> [B, 256, T]."""
+        B, Cin, T = x.shape
+        x, mask = x.float().contiguous(), mask.float().contiguous()
+        out = torch.empty(B, 256, T, device=x.device, dtype=torch.float32)
+        self._check(self.lib.mossdec_cv1_block1d(self.h, prefix.encode(), B, T, Cin, _ptr(x), _ptr(mask), _ptr(out),
+                                                 self._stream()), "cv1_block1d")
         return out
 
     def cv1_downsample(self, prefix, x):

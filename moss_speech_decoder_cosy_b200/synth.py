@@ -108,7 +108,7 @@ def synth_noise_bank(n_feats: int = 80, length: int = 15000):
 
 def synth_cv1_blocks_state_dict(seed: int = 0, cin: int = 320, time_dim: int = 1024):
     """Random-init weights of the cosyvoice1 / Matcha building blocks: one ResnetBlock1D(cin, 256,
-    time_dim), one ResnetBlock1D(256, 256, time_dim), Downsample1D(256), Upsample1D(256) (matcha decoder.py:32-158)."""
+    time_dim), one ResnetBlock1D(256, 256, time_dim), a Block1D(256, 256) (the decoder's final_block), Downsample1D(256), Upsample1D(256) (matcha decoder.py:32-158)."""
     shapes = {}
     for name, ci in (("res_in", cin), ("res_mid", 256)):
         shapes.update({
@@ -119,6 +119,8 @@ def synth_cv1_blocks_state_dict(seed: int = 0, cin: int = 320, time_dim: int = 1
             f"{name}.mlp.1.weight": (256, time_dim), f"{name}.mlp.1.bias": (256,),
             f"{name}.res_conv.weight": (256, ci, 1), f"{name}.res_conv.bias": (256,),
         })
+    shapes.update({"final.block.0.weight": (256, 256, 3), "final.block.0.bias": (256,),
+                   "final.block.1.weight": (256,), "final.block.1.bias": (256,)})
     shapes.update({"down.conv.weight": (256, 256, 3), "down.conv.bias": (256,),
                    "up.conv.weight": (256, 256, 4), "up.conv.bias": (256,)})
     sd = {}

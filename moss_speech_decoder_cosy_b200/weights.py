@@ -220,6 +220,12 @@ def pack_cv1_resnet(sd, src, dst):
     return out
 
 
+def pack_cv1_block1d(sd, src, dst):
+    """matcha Block1D (decoder.py:32-43) keys under `src` (block.0 = Conv1d k3 pad 1, block.1 = GroupNorm(8, 256))."""
+    return {f"{dst}.c.w": _bf16(conv_weight_taps(sd[f"{src}.block.0.weight"].float())), f"{dst}.c.b": _f32(sd[f"{src}.block.0.bias"]),
+            f"{dst}.gn.g": _f32(sd[f"{src}.block.1.weight"]), f"{dst}.gn.b": _f32(sd[f"{src}.block.1.bias"])}
+
+
 def pack_cv1_downsample(sd, src, dst):
     """matcha Downsample1D (decoder.py:64-70) Conv1d(C, C, 3, 2, 1): tap-major [C, 3C]; the stride lives in the operand view."""
     return {f"{dst}.w": _bf16(conv_weight_taps(sd[f"{src}.conv.weight"].float())), f"{dst}.b": _f32(sd[f"{src}.conv.bias"])}

@@ -19,13 +19,15 @@ def _sub(sd, prefix):
 
 def main():
     ref_shims.install()
-    from matcha.models.components.decoder import Downsample1D, ResnetBlock1D, Upsample1D
+    from matcha.models.components.decoder import Block1D, Downsample1D, ResnetBlock1D, Upsample1D
     from moss_speech_decoder_cosy_b200 import synth
 
     sd = synth.synth_cv1_blocks_state_dict(0)
     res_in = ResnetBlock1D(320, 256, 1024).eval()
     res_mid = ResnetBlock1D(256, 256, 1024).eval()
     down, up = Downsample1D(256).eval(), Upsample1D(256, use_conv_transpose=True).eval()
+    final = Block1D(256, 256).eval()
+    final.load_state_dict(_sub(sd, "final"), strict=True)
     res_in.load_state_dict(_sub(sd, "res_in"), strict=True)
     res_mid.load_state_dict(_sub(sd, "res_mid"), strict=True)
     down.load_state_dict(_sub(sd, "down"), strict=True)
@@ -45,8 +47,9 @@ def main():
             h2 = res_mid(h, mask, temb)
             d = down(h2 * mask)
             u = up(d)
+            fb = final(h2, mask)
             out.update({f"{tag}_x": x, f"{tag}_mask": mask, f"{tag}_temb": temb, f"{tag}_res_in": h, f"{tag}_res_mid": h2,
-                        f"{tag}_down": d, f"{tag}_up": u})
+                        f"{tag}_down": d, f"{tag}_up": u, f"{tag}_final": fb})
     _save("cv1_blocks.npz", **out)
 
 

@@ -28,6 +28,7 @@ def main():
     t.update(weights.pack_cv1_resnet(sd, "res_mid", "cv1.res_mid"))
     t.update(weights.pack_cv1_downsample(sd, "down", "cv1.down"))
     t.update(weights.pack_cv1_upsample(sd, "up", "cv1.up"))
+    t.update(weights.pack_cv1_block1d(sd, "final", "cv1.final"))
     eng.load_tensors(t)
     B, T = a.B, a.T
     g = torch.Generator(device="cuda").manual_seed(0)
@@ -42,6 +43,7 @@ def main():
                              2.0 * rows * 256 * (3 * 320 + 3 * 256 + 320), rows * (320 + 256) * 4),
         "resnet_block_256": (lambda: eng.cv1_resnet_block("cv1.res_mid", h, mask, temb),
                              2.0 * rows * 256 * (3 * 256 + 3 * 256 + 256), rows * (256 + 256) * 4),
+        "block1d": (lambda: eng.cv1_block1d("cv1.final", h, mask), 2.0 * rows * 256 * 768, rows * 512 * 4),
         "downsample": (lambda: eng.cv1_downsample("cv1.down", h), 2.0 * (rows / 2) * 256 * 768, rows * 256 * 4 * 1.5),
         "upsample": (lambda: eng.cv1_upsample("cv1.up", h), 2.0 * rows * 256 * 4 * 256, rows * 256 * 4 * 3),
     }

@@ -32,6 +32,7 @@ def cv1(engine):
     t.update(weights.pack_cv1_resnet(sd, "res_mid", "cv1.res_mid"))
     t.update(weights.pack_cv1_downsample(sd, "down", "cv1.down"))
     t.update(weights.pack_cv1_upsample(sd, "up", "cv1.up"))
+    t.update(weights.pack_cv1_block1d(sd, "final", "cv1.final"))
     engine.load_tensors(t)
     return engine, sd
 
@@ -46,10 +47,11 @@ def test_cv1_blocks_match_reference(cv1, tag):
     h2 = engine.cv1_resnet_block("cv1.res_mid", t["res_in"], t["mask"], t["temb"])
     d = engine.cv1_downsample("cv1.down", t["res_mid"] * t["mask"])
     u = engine.cv1_upsample("cv1.up", t["down"])
+    fb = engine.cv1_block1d("cv1.final", t["res_mid"], t["mask"])
     torch.cuda.synchronize()
     assert engine.launch_count() > n0
     for got, key, tol in ((h, "res_in", RESNET_REL_L2), (h2, "res_mid", RESNET_REL_L2), (d, "down", CONV_REL_L2),
-                          (u, "up", CONV_REL_L2)):
+                          (u, "up", CONV_REL_L2), (fb, "final", CONV_REL_L2)):
         assert got.shape == t[key].shape, key
         assert torch.isfinite(got).all(), key
         err = rel_l2(got, t[key])

@@ -80,6 +80,7 @@ def test_cv1_blocks_restatement(tag):
         h2 = port.cv1_resnet_block(sd, "res_mid.", h, t["mask"], t["temb"])
         d = port.cv1_downsample(sd, "down.", h2 * t["mask"])
         u = port.cv1_upsample(sd, "up.", d)
-    for got, key in ((h, "res_in"), (h2, "res_mid"), (d, "down"), (u, "up")):
+        fb = port.cv1_block1d(h2, t["mask"], sd, "final.")
+    for got, key in ((h, "res_in"), (h2, "res_mid"), (d, "down"), (u, "up"), (fb, "final")):
         assert got.shape == t[key].shape
         assert _rel(got, t[key]) < 1e-5, key
