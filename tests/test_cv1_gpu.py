@@ -92,3 +92,32 @@ def test_cv1_missing_weights_fail_loudly(engine):
     x = torch.zeros(1, 256, 8, device="cuda")
     with pytest.raises(RuntimeError, match="missing"):
         engine.cv1_downsample("cv1.nope", x)
+
+
+@pytest.mark.parametrize("B,T", [(1, 1), (3, 2), (2, 5), (1, 33), (5, 127)])
+def test_cv1_edge_lengths_match_oracle(cv1, B, T):
+    """Shortest and tile-straddling lengths (T = 1: a single frame per utterance; 127 / 33: partial 32-frame tiles; B * (T + 2)
+    far below one 128-row GEMM tile) against the CPU oracle, with one fully masked tail."""
+    from oracle import port
+    engine, sd = cv1
+    g = torch.Generator().manual_seed(1000 * B + T)
+    x = torch.randn(B, 320, T, generator=g)
+    temb = torch.randn(B, 1024, generator=g)
+    mask = torch.ones(B, 1, T)
+    if T > 2:
+        mask[-1, :, T // 2:] = 0
+    with torch.inference_mode():
+        r = port.cv1_resnet_block(sd, "res_in.", x, mask, temb)
+        f = port.cv1_block1d(r, mask, sd, "final.")
+        d = port.cv1_downsample(sd, "down.", r)
+        u = port.cv1_upsample(sd, "up.", r)
+    xr = r.cuda()
+    got = (engine.cv1_resnet_block("cv1.res_in", x.cuda(), mask.cuda(), temb.cuda()), engine.cv1_block1d("cv1.final", xr, mask.cuda()),
+           engine.cv1_downsample("cv1.down", xr), engine.cv1_upsample("cv1.up", xr))
+    torch.cuda.synchronize()
+    for o, ref, name, tol in zip(got, (r, f, d, u), ("resnet", "block1d", "down", "up"), (1.5e-2, 1e-2, 5e-3, 5e-3)):
+        assert o.shape == ref.shape, name
+        assert torch.isfinite(o).all(), name
+        err = rel_l2(o.cpu(), ref)
+        print(f"cv1 edge B={B} T={T} {name}: rel_l2={err:.3e}")
+        assert err < tol, name
