@@ -11,8 +11,10 @@
  *   mossdec_set_tensor  <- nn.Module.load_state_dict                  flow_inference.py:59-61
  *
  * All data pointers are DEVICE pointers owned by the caller unless stated otherwise; `stream` is a cudaStream_t
- * passed as void*.  Calls only enqueue work (no host synchronisation except inside mossdec_set_tensor and the
- * small layout uploads at the start of a call).  Return value: 0 = OK, negative = error (message via
+ * passed as void*.  Calls only enqueue work: the per-call layout arrays are staged in pinned host memory and uploaded
+ * with async copies on `stream`, so back-to-back calls on one (also non-blocking) stream are ordered by the stream.
+ * Host synchronisation happens only in mossdec_set_tensor, in mossdec_estimator when a mask is given, in the debug /
+ * profile readers, and when a workspace has to grow (see mossdec_reserve).  Return value: 0 = OK, negative = error (message via
  * mossdec_last_error).  A handle must not be used from two threads at once.
  */
 #ifndef MOSSDEC_H_
@@ -55,9 +57,14 @@ int mossdec_set_tensor(mossdec_handle* h, const char* name, const void* host_dat
 /* Check that every tensor the engine needs is present. */
 int mossdec_finalize(mossdec_handle* h);
 
-/* One estimator evaluation, dense batch.  x, mu, cond, out: [B2, 80, T] fp32; mask: [B2, 1, T] (ignored: all valid);
- * t: [B2]; spks: [B2, 80] (spks / cond may be NULL = zeros).  chunk = 0 -> full attention, > 0 -> block-causal mask
- * with `chunk` mel frames (decoder.py:439-440, streaming=True). */
+/* One estimator evaluation, dense batch.  x, mu, cond, out: [B2, 80, T] fp32; t: [B2]; spks: [B2, 80] (spks / cond may be
+ * NULL = zeros).  mask: [B2, 1, T] fp32 key-padding mask as the reference passes it (decoder.py:405-494), NULL = all
+ * valid.  It must be a prefix mask (1...1 0...0 per sequence, what make_pad_mask produces); masked frames are excluded
+ * from attention and the convolutions' receptive field sees zeros there, the output is zero on them (output * mask).  A
+ * mask of another form is rejected with an error.  With a mask the call synchronises `stream` once (the lengths are read
+ * back), like the TensorRT path it mirrors (flow_matching.py:153-154).  `out` may alias `x`: the TensorRT contract binds
+ * the output onto x (flow_matching.py:143-151).  chunk = 0 -> full attention, > 0 -> block-causal mask with `chunk` mel
+ * frames (decoder.py:439-440, streaming=True). */
 int mossdec_estimator(mossdec_handle* h, int32_t B2, int32_t T, const float* x, const float* mask, const float* mu,
                       const float* t, const float* spks, const float* cond, float* out, int32_t chunk, void* stream);
 
@@ -119,6 +126,22 @@ int mossdec_debug_read(mossdec_handle* h, const char* name, float* host_dst, int
  * FLOPs (2 M N K incl. tile padding), attention ms, attention launches, 0, fused-FFN ms, fused-FFN launches, FFN FLOPs}. */
 void mossdec_profile(mossdec_handle* h, int32_t on);
 int mossdec_profile_read(mossdec_handle* h, double* out9);
+
+/* Pre-size the device workspaces so that the first decode does not allocate: solves of up to `flow_rows` mel frames in
+ * total over up to `flow_seqs` utterances, vocoder groups of up to `hift_frames` frames.  (Workspaces otherwise grow on
+ * demand; growing synchronises the device.) */
+int mossdec_reserve(mossdec_handle* h, int64_t flow_rows, int32_t flow_seqs, int64_t hift_frames);
+
+/* The Euler loop of mossdec_flow_solve is captured into a CUDA graph per packed-row geometry and replayed (the
+ * reference's analogue: the enqueue-once TensorRT execution context, flow_matching.py:133-156).  mode 0 = plain
+ * launches, 1 = capture a geometry the second time it is seen (default), 2 = capture on first sight.  Also settable
+ * with the environment variable MOSSDEC_GRAPH at handle creation. */
+void mossdec_set_graph_mode(mossdec_handle* h, int32_t mode);
+int64_t mossdec_graph_replays(const mossdec_handle* h);
+
+/* CUDA device ordinal the handle was created on.  Every call runs on that device regardless of the caller's current
+ * device (and restores the caller's device before returning). */
+int32_t mossdec_device(const mossdec_handle* h);
 
 /* Frames per vocoder group (bounds the stage-2 working set; default 8192). */
 void mossdec_set_hift_group_frames(mossdec_handle* h, int64_t frames);

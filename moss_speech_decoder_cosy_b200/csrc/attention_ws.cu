@@ -1,8 +1,9 @@
-// Warp-specialised variant of the tcgen05 self-attention (attention_tc.cu has the reference list and the masking rules):
-// the per-tile dependency chain of attention_tc_kernel (S ready -> softmax -> P -> block barrier -> MMA issue -> MMA ->
-// S ready, ~2 500 clk per 64 keys, four chains per SM) is cut by
-//   * a dedicated warp (warp 4) that issues every TMA load and every tcgen05.mma, with mbarriers instead of block barriers;
-//   * key tiles of 32 with a DOUBLE-BUFFERED score tile in tensor memory: S0 | S1 | O = 32 + 32 + 64 = 128 columns, still
+// Self-attention of BasicTransformerBlock (diffusers Attention behind matcha transformer.py:266-271: softmax(q k^T / 8 +
+// additive mask) v, 8 heads of 64) over packed rows, warp-specialised on tcgen05 / TMEM.  The additive mask of the
+// reference ([B, T, T] fp32, cosyvoice/utils/mask.py:161-236 + common.py:160-168) is a predicate here: key j of a sequence
+// is visible to query i iff j < len and (chunk == 0 or j < (i / chunk + 1) * chunk).
+//   * a dedicated warp (warp 4) issues every TMA load and every tcgen05.mma, with mbarriers instead of block barriers;
+//   * key tiles of 32 with a DOUBLE-BUFFERED score tile in tensor memory: S0 | S1 | O = 32 + 32 + 64 = 128 columns,
 //     four CTAs per SM.  QK(j + 2) is issued right behind PV(j), so S_{j+1} is complete before the softmax warps finish
 //     tile j: they never wait for an MMA issue or for MMA latency in steady state.
 //   warps 0..3: thread == query row: tcgen05.ld S_j, predicate mask, online max (lazy rescaling of O), exp2, bf16 P_j
@@ -264,14 +265,18 @@ attention_ws_kernel(const __grid_constant__ CUtensorMap tm, __nv_bfloat16* __res
 
 }  // namespace
 
+cudaError_t attention_ws_init_device() {
+    static std::atomic<uint64_t> done{0};
+    static std::mutex mu;
+    return once_per_device(done, mu, [] {
+        return cudaFuncSetAttribute(attention_ws_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem);
+    });
+}
+
 cudaError_t launch_attention_ws(const __nv_bfloat16* qkv, int64_t rows, __nv_bfloat16* out, const int32_t* seq_start,
                                 const int32_t* seq_len, int nseq, int max_len, int heads, int chunk, cudaStream_t st) {
-    static bool attr_done = false;
-    if (!attr_done) {
-        cudaError_t e = cudaFuncSetAttribute(attention_ws_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem);
-        if (e != cudaSuccess) return e;
-        attr_done = true;
-    }
+    const cudaError_t ie = attention_ws_init_device();
+    if (ie != cudaSuccess) return ie;
     CUtensorMap tm;
     if (!encode_2d(&tm, qkv, (uint64_t)3 * heads * kD, (uint64_t)rows, (uint64_t)3 * heads * kD, kBK)) return cudaErrorInvalidValue;
     dim3 grid((max_len + kBQ - 1) / kBQ, heads, nseq);

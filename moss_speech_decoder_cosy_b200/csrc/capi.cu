@@ -100,6 +100,13 @@ void mossdec_profile(mossdec_handle* h, int32_t on) { h->eng->set_profile(on != 
 int mossdec_profile_read(mossdec_handle* h, double* out9) { return h->eng->profile_read(out9); }
 void mossdec_set_hift_group_frames(mossdec_handle* h, int64_t frames) { h->eng->set_hift_group_frames(frames); }
 
+int mossdec_reserve(mossdec_handle* h, int64_t flow_rows, int32_t flow_seqs, int64_t hift_frames) {
+    return h->eng->reserve(flow_rows, flow_seqs, hift_frames);
+}
+void mossdec_set_graph_mode(mossdec_handle* h, int32_t mode) { h->eng->set_graph_mode(mode); }
+int64_t mossdec_graph_replays(const mossdec_handle* h) { return h->eng->graph_replays(); }
+int32_t mossdec_device(const mossdec_handle* h) { return h->eng->device(); }
+
 int64_t mossdec_launch_count(const mossdec_handle* h) { return h->eng->launches(); }
 void mossdec_reset_launch_count(mossdec_handle* h) { h->eng->reset_launches(); }
 

@@ -244,6 +244,7 @@ inline size_t align256(size_t v) { return (v + 255) & ~(size_t)255; }
 // ResnetBlock1D of the non-causal decoder (decoder.py:46-61): out = block2(block1(x, mask) + mlp(temb), mask) + res_conv(x * mask)
 int Engine::cv1_resnet_block(const char* prefix, int B, int T, int Cin, const float* x, const float* mask, const float* temb,
                              int time_dim, float* out, cudaStream_t st) {
+    DeviceGuard guard_(device_);
     if (B <= 0 || T <= 0 || Cin <= 0) return fail("cv1_resnet_block: bad shape");
     const std::string P(prefix);
     missing_.clear();
@@ -326,6 +327,7 @@ int Engine::cv1_resnet_block(const char* prefix, int B, int T, int Cin, const fl
 
 // Block1D of the non-causal decoder (decoder.py:32-43; also its `final_block`): out = mish(GroupNorm(conv3(x * mask))) * mask
 int Engine::cv1_block1d(const char* prefix, int B, int T, int Cin, const float* x, const float* mask, float* out, cudaStream_t st) {
+    DeviceGuard guard_(device_);
     if (B <= 0 || T <= 0 || Cin <= 0) return fail("cv1_block1d: bad shape");
     const std::string P(prefix);
     missing_.clear();
@@ -372,6 +374,7 @@ int Engine::cv1_block1d(const char* prefix, int B, int T, int Cin, const float* 
 
 // Downsample1D (decoder.py:64-70): Conv1d(C, C, 3, stride 2, padding 1); out [B, C, (T - 1) / 2 + 1]
 int Engine::cv1_downsample(const char* prefix, int B, int T, int C, const float* x, float* out, cudaStream_t st) {
+    DeviceGuard guard_(device_);
     if (B <= 0 || T <= 0 || C <= 0 || (C % kGemmBK) != 0 || C > 256) return fail("cv1_downsample: C must be a multiple of 64, <= 256");
     const std::string P(prefix);
     missing_.clear();
@@ -413,6 +416,7 @@ int Engine::cv1_downsample(const char* prefix, int B, int T, int C, const float*
 
 // Upsample1D (decoder.py:120-158, use_conv_transpose): ConvTranspose1d(C, C, 4, stride 2, padding 1); out [B, C, 2 T]
 int Engine::cv1_upsample(const char* prefix, int B, int T, int C, const float* x, float* out, cudaStream_t st) {
+    DeviceGuard guard_(device_);
     if (B <= 0 || T <= 0 || C <= 0 || (C % kGemmBK) != 0 || C > 256) return fail("cv1_upsample: C must be a multiple of 64, <= 256");
     const std::string P(prefix);
     missing_.clear();

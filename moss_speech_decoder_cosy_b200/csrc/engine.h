@@ -16,6 +16,18 @@
 
 namespace mossdec {
 
+// Every entry point of an Engine runs with the engine's device current and restores the caller's device afterwards.
+struct DeviceGuard {
+    int prev = -1;
+    bool switched = false;
+    explicit DeviceGuard(int dev) {
+        if (cudaGetDevice(&prev) == cudaSuccess && prev != dev) switched = cudaSetDevice(dev) == cudaSuccess;
+    }
+    ~DeviceGuard() {
+        if (switched) cudaSetDevice(prev);
+    }
+};
+
 struct DevTensor {
     void* ptr = nullptr;
     size_t bytes = 0;
@@ -40,10 +52,31 @@ struct EngineConfig {
     float sine_amp = 0.1f, noise_std = 0.003f, voiced_thr = 10.f, lrelu = 0.1f, audio_limit = 0.99f;
 };
 
+// Pinned host staging for the small per-call layout arrays (sequence starts / lengths / row -> sequence maps): the
+// arrays are built in a pinned slot and uploaded with cudaMemcpyAsync on the caller's stream, so an entry point never
+// blocks the host and the copy is ordered behind the kernels of an earlier call on the same stream that still read the
+// previous layout.  A slot is reused only after the copy that read it has completed (event per slot).
+class PinnedStager {
+   public:
+    ~PinnedStager();
+    void* acquire(size_t bytes);   // host pointer to a pinned slot of >= bytes (nullptr on allocation failure)
+    void commit(cudaStream_t st);  // call after the cudaMemcpyAsync(s) reading the slot returned by the last acquire()
+   private:
+    static constexpr int kSlots = 4;
+    struct Slot {
+        void* p = nullptr;
+        size_t cap = 0;
+        cudaEvent_t ev = nullptr;
+        bool pending = false;
+    } slots_[kSlots];
+    int cur_ = -1;
+};
+
 class DeviceBuffer {
    public:
     ~DeviceBuffer() { release(); }
-    // grows (never shrinks); returns true when the allocation moved
+    // grows (never shrinks); returns true when the allocation moved.  Growing synchronises the device (cudaFree of the old
+    // block + a completed memset of the new one), so it is safe with work in flight; steady state never allocates.
     bool reserve(size_t bytes);
     void release();
     template <typename T>
@@ -94,6 +127,14 @@ class Engine {
     void reset_launches() { launches_ = 0; }
     void set_hift_group_frames(int64_t f) { hift_group_frames_ = f > 0 ? f : 8192; }
     int num_sms() const { return num_sms_; }
+    int device() const { return device_; }
+    // Pre-size the workspaces for solves of up to `flow_rows` packed rows per CFG half over `flow_seqs` sequences and
+    // vocoder groups of up to `hift_frames` frames, so that the first real call does not allocate.
+    int reserve(int64_t flow_rows, int flow_seqs, int64_t hift_frames);
+    // CUDA-graph replay of the Euler loop of flow_solve (MOSSDEC_GRAPH=0 disables): 0 = off, 1 = capture a shape the
+    // second time it is seen (default), 2 = capture on first sight
+    void set_graph_mode(int m) { graph_mode_ = m; }
+    long graph_replays() const { return graph_replays_; }
 
    private:
     friend struct FlowRunner;
@@ -113,31 +154,58 @@ class Engine {
 
     // flow internals
     struct FlowPlan;
-    int build_flow_layout(int nseq_half, const int32_t* lens, bool cfg_double);
+    int build_flow_layout(int nseq_half, const int32_t* lens, bool cfg_double, cudaStream_t st, int dense_T = 0);
+    int reserve_flow(size_t M, int nseq);
+    int reserve_hift(int64_t rows_f, int nseq);
+    int run_euler_steps(int n_steps, int chunk, float cfg_rate, const float* dtv, cudaStream_t st);
     // row0 > 0: run on the rows [row0, row0 + M) of every workspace matrix (the second CFG half on its own stream)
     int estimator_forward(int M, int nseq, int max_len, const float* tbias, int tbias_ld, int chunk, cudaStream_t st,
                           int row0 = 0);
-    int time_bias(const float* t_dev, int nt, cudaStream_t st);
+    int time_bias(const float* t_dev, int nt, float* temb, float* tbias, cudaStream_t st);
     int finalize_hift();
     int hift_group(int b0, int b1, const int32_t* lens, int64_t mel_off0, int64_t wav_off0, const float* mel,
                    const float* cache_source, int cache_stride, const int32_t* cache_len, const float* nsf_noise,
                    float* wav_out, float* source_out, uint64_t seed, int flags, cudaStream_t st);
 
     EngineConfig cfg_;
+    int device_ = 0;                   // the device this engine lives on; every entry point runs under it (DeviceGuard)
     int num_sms_ = 148;
     bool finalized_ = false;
-    bool attn_v1_ = false;
-    bool attn_ws_ = false;
     bool dual_stream_ = true;          // the two CFG halves of a solve run on two streams (MOSSDEC_DUAL=0 disables)
     cudaStream_t st2_ = nullptr;
+    cudaStream_t cap_st_ = nullptr;    // capture origin stream (the caller's stream may be the legacy stream, which cannot capture)
     cudaEvent_t ev_fork_ = nullptr, ev_join_ = nullptr;
+    PinnedStager stager_;
+    int32_t* h_mask_lens_ = nullptr;   // pinned [max B2 + 1]: sequence lengths + "not a prefix mask" flag read back by estimator()
+    int32_t* d_mask_lens_ = nullptr;
+    int mask_lens_cap_ = 0;
+
+    // ---- CUDA graphs of the Euler loop (engine_solve.cu)
+    struct GraphKey {
+        int rows_half, nseq_half, max_len, chunk, n_steps, dual;
+        uint32_t cfg_bits;
+        const void *ws, *lay, *tb;
+        bool operator<(const GraphKey& o) const;
+    };
+    struct GraphEntry {
+        cudaGraphExec_t exec = nullptr;
+        long launches = 0;
+        long seen = 0;
+        uint64_t last_use = 0;
+    };
+    std::map<GraphKey, GraphEntry> graphs_;
+    int graph_mode_ = 1;
+    uint64_t graph_clock_ = 0;
+    long graph_replays_ = 0;
+    void drop_graphs();
+    int solve_tbias_steps_ = 0;        // ws_time_solve_ holds the time-embedding biases of an n-step cosine schedule
     std::unordered_map<std::string, DevTensor> tensors_;
     std::string err_;
     std::string missing_;
     long launches_ = 0;
 
     // ---- flow workspace
-    DeviceBuffer ws_flow_, ws_layout_, ws_time_;
+    DeviceBuffer ws_flow_, ws_layout_, ws_time_, ws_time_solve_;
     std::vector<int32_t> h_row_seq_, h_seq_start_, h_seq_len_;
     std::vector<int64_t> h_in_offset_;
     FlowLayout layout_{};

@@ -16,13 +16,15 @@ namespace mossdec {
 
 bool DeviceBuffer::reserve(size_t bytes) {
     if (bytes <= bytes_) return false;
-    release();
+    release();   // cudaFree waits for all work in flight on the device
     if (cudaMalloc(&ptr_, bytes) != cudaSuccess) {
         ptr_ = nullptr;
         bytes_ = 0;
         return true;
     }
+    // (the legacy-stream memset is not ordered against non-blocking caller streams: finish it before anyone launches)
     cudaMemset(ptr_, 0, bytes);
+    cudaDeviceSynchronize();
     bytes_ = bytes;
     return true;
 }
@@ -32,13 +34,48 @@ void DeviceBuffer::release() {
     bytes_ = 0;
 }
 
+PinnedStager::~PinnedStager() {
+    for (auto& sl : slots_) {
+        if (sl.ev) cudaEventDestroy(sl.ev);
+        if (sl.p) cudaFreeHost(sl.p);
+    }
+}
+void* PinnedStager::acquire(size_t bytes) {
+    cur_ = (cur_ + 1) % kSlots;
+    Slot& sl = slots_[cur_];
+    if (sl.pending) {   // the copy that last read this slot (kSlots calls ago) must be done
+        cudaEventSynchronize(sl.ev);
+        sl.pending = false;
+    }
+    if (sl.cap < bytes) {
+        if (sl.p) cudaFreeHost(sl.p);
+        sl.p = nullptr;
+        sl.cap = 0;
+        const size_t cap = (bytes + 65535) & ~size_t(65535);
+        if (cudaMallocHost(&sl.p, cap) != cudaSuccess) {
+            sl.p = nullptr;
+            return nullptr;
+        }
+        sl.cap = cap;
+    }
+    if (!sl.ev && cudaEventCreateWithFlags(&sl.ev, cudaEventDisableTiming) != cudaSuccess) return nullptr;
+    return sl.p;
+}
+void PinnedStager::commit(cudaStream_t st) {
+    if (cur_ < 0) return;
+    Slot& sl = slots_[cur_];
+    if (cudaEventRecord(sl.ev, st) == cudaSuccess) sl.pending = true;
+    else cudaStreamSynchronize(st);
+}
+
 Engine::Engine(const EngineConfig& cfg) : cfg_(cfg) {
-    int dev = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&num_sms_, cudaDevAttrMultiProcessorCount, dev);
-    const char* av = getenv("MOSSDEC_ATTN");  // developer A/B switch: "v1" = mma.sync kernel, "tc" = single-buffer tcgen05 kernel
-    attn_v1_ = av != nullptr && av[0] == 'v' && av[1] == '1';
-    attn_ws_ = !(av != nullptr && av[0] == 't' && av[1] == 'c');  // default: warp-specialised tcgen05 kernel (attention_ws.cu); "tc" = attention_tc.cu
+    cudaGetDevice(&device_);
+    cudaDeviceGetAttribute(&num_sms_, cudaDevAttrMultiProcessorCount, device_);
+    // per-device kernel setup (opt-in shared memory sizes, constant tables) for THIS engine's device
+    gemm_tc_init_device();
+    ffn_tc_init_device();
+    attention_ws_init_device();
+    hift_init_device();
     const char* dv = getenv("MOSSDEC_DUAL");
     dual_stream_ = !(dv != nullptr && dv[0] == '0');
     if (dual_stream_) {
@@ -47,17 +84,30 @@ Engine::Engine(const EngineConfig& cfg) : cfg_(cfg) {
             cudaEventCreateWithFlags(&ev_join_, cudaEventDisableTiming) != cudaSuccess)
             dual_stream_ = false;
     }
+    const char* gv = getenv("MOSSDEC_GRAPH");
+    if (gv != nullptr && gv[0] >= '0' && gv[0] <= '2') graph_mode_ = gv[0] - '0';
+    if (graph_mode_ && cudaStreamCreateWithFlags(&cap_st_, cudaStreamNonBlocking) != cudaSuccess) graph_mode_ = 0;
 }
 
 Engine::~Engine() {
+    DeviceGuard g(device_);
+    cudaDeviceSynchronize();
+    drop_graphs();
     if (st2_) cudaStreamDestroy(st2_);
+    if (cap_st_) cudaStreamDestroy(cap_st_);
     if (ev_fork_) cudaEventDestroy(ev_fork_);
     if (ev_join_) cudaEventDestroy(ev_join_);
+    if (h_mask_lens_) cudaFreeHost(h_mask_lens_);
+    if (d_mask_lens_) cudaFree(d_mask_lens_);
+    for (auto& ev : prof_pool_) cudaEventDestroy(ev);
     for (auto& kv : tensors_)
         if (kv.second.ptr) cudaFree(kv.second.ptr);
 }
 
 int Engine::set_tensor(const char* name, const void* host, int dtype, int ndim, const int64_t* shape) {
+    DeviceGuard g(device_);
+    drop_graphs();            // captured launches hold weight pointers
+    solve_tbias_steps_ = 0;
     DevTensor t;
     t.dtype = dtype;
     size_t n = 1;
@@ -106,6 +156,7 @@ void Engine::prof_begin(int cls, double flops, cudaStream_t st, uint64_t key) {
 void Engine::prof_end(cudaStream_t st) { cudaEventRecord(prof_.back().b, st); }
 
 int Engine::profile_read(double* out) {
+    DeviceGuard g(device_);
     for (int i = 0; i < 9; ++i) out[i] = 0.0;
     if (cudaDeviceSynchronize() != cudaSuccess) return fail("profile_read: sync failed");
     for (auto& r : prof_) {
@@ -169,6 +220,7 @@ static std::string S(const char* fmt, int a = 0, int b = 0) {
 }
 
 int Engine::finalize() {
+    DeviceGuard g(device_);
     missing_.clear();
     const int ngroups = cfg_.n_mid + 2;
     const char* once[] = {"est.time.w1", "est.time.b1", "est.time.w2", "est.time.b2", "est.tbias.w", "est.tbias.b",
@@ -193,35 +245,66 @@ int Engine::finalize() {
 // the same layout rows_half further down (sequence ids nseq_half .. 2*nseq_half-1).
 static constexpr int kGuard = 4;
 
-int Engine::build_flow_layout(int nseq_half, const int32_t* lens, bool cfg_double) {
+int Engine::reserve_flow(size_t M, int nseq) {
+    // layout arrays: [in_offset int64 x nseq | row_seq int32 x M | seq_start x nseq | seq_len x nseq]
+    const size_t lay_bytes = (size_t)M * 4 + (size_t)nseq * (4 + 4 + 8) + 64;
+    ws_layout_.reserve(lay_bytes + 256);
+    if (!ws_layout_.as<void>()) return fail("cudaMalloc(layout) failed");
+    // activation workspace (all buffers have M rows; one slack tile at the end for TMA boxes)
+    const int C = cfg_.channels, H = cfg_.heads * cfg_.head_dim;
+    const size_t Mr = M + kGemmBM;
+    size_t need = 0;
+    auto take = [&](size_t bytes) {
+        need += (bytes + 1023) & ~size_t(1023);
+    };
+    take(Mr * cfg_.in_channels * 2); take(Mr * C * 2); take(Mr * C * 2); take(Mr * 3 * H * 2); take(Mr * H * 2);
+    take(Mr * 4 * C * 2); take(Mr * 2 * C * 2); take(Mr * cfg_.n_feats * 4); take(Mr * C * 4); take(Mr * C * 4);
+    take(Mr * cfg_.n_feats * 4);
+    ws_flow_.reserve(need);
+    if (!ws_flow_.as<void>()) return fail("cudaMalloc(flow workspace) failed");
+    return 0;
+}
+
+int Engine::build_flow_layout(int nseq_half, const int32_t* lens, bool cfg_double, cudaStream_t st, int dense_T) {
     int rows = 0, max_len = 0;
     const int nseq = cfg_double ? 2 * nseq_half : nseq_half;
-    h_seq_start_.assign(nseq, 0);
-    h_seq_len_.assign(nseq, 0);
-    h_in_offset_.assign(nseq, 0);
-    int64_t off = 0;
     for (int s = 0; s < nseq_half; ++s) {
         if (lens[s] <= 0) return fail("sequence length must be positive");
-        rows += kGuard;
-        h_seq_start_[s] = rows;
-        h_seq_len_[s] = lens[s];
-        h_in_offset_[s] = off;
-        off += (int64_t)lens[s] * cfg_.n_feats;
-        rows += lens[s];
+        rows += kGuard + lens[s];
         max_len = lens[s] > max_len ? lens[s] : max_len;
     }
     rows += kGuard;
     const int rows_half = (rows + kGemmBM - 1) / kGemmBM * kGemmBM;
     const int M = cfg_double ? 2 * rows_half : rows_half;
-    h_row_seq_.assign(M, -1);
-    for (int s = 0; s < nseq_half; ++s)
-        for (int t = 0; t < lens[s]; ++t) h_row_seq_[h_seq_start_[s] + t] = s;
+    if (reserve_flow((size_t)M, nseq)) return -1;
+
+    // build the layout arrays in a pinned slot (same order as on the device) and upload them with one async copy
+    const size_t off_rowseq = ((size_t)nseq * 8 + 15) & ~size_t(15);
+    const size_t lay_bytes = off_rowseq + (size_t)M * 4 + (size_t)nseq * 8;
+    uint8_t* hp = static_cast<uint8_t*>(stager_.acquire(lay_bytes));
+    if (!hp) return fail("cudaMallocHost(layout staging) failed");
+    int64_t* h_off = reinterpret_cast<int64_t*>(hp);
+    int32_t* h_rowseq = reinterpret_cast<int32_t*>(hp + off_rowseq);
+    int32_t* h_start = h_rowseq + M;
+    int32_t* h_len = h_start + nseq;
+    for (int i = 0; i < M; ++i) h_rowseq[i] = -1;
+    int64_t off = 0;
+    int r = 0;
+    for (int s = 0; s < nseq_half; ++s) {
+        r += kGuard;
+        h_start[s] = r;
+        h_len[s] = lens[s];
+        h_off[s] = dense_T > 0 ? (int64_t)s * cfg_.n_feats * dense_T : off;
+        off += (int64_t)lens[s] * cfg_.n_feats;
+        for (int t = 0; t < lens[s]; ++t) h_rowseq[r + t] = s;
+        r += lens[s];
+    }
     if (cfg_double) {
         for (int s = 0; s < nseq_half; ++s) {
-            h_seq_start_[nseq_half + s] = h_seq_start_[s] + rows_half;
-            h_seq_len_[nseq_half + s] = lens[s];
-            h_in_offset_[nseq_half + s] = h_in_offset_[s];
-            for (int t = 0; t < lens[s]; ++t) h_row_seq_[rows_half + h_seq_start_[s] + t] = nseq_half + s;
+            h_start[nseq_half + s] = h_start[s] + rows_half;
+            h_len[nseq_half + s] = lens[s];
+            h_off[nseq_half + s] = h_off[s];
+            for (int t = 0; t < lens[s]; ++t) h_rowseq[rows_half + h_start[s] + t] = nseq_half + s;
         }
     }
     flow_M_ = M;
@@ -229,28 +312,21 @@ int Engine::build_flow_layout(int nseq_half, const int32_t* lens, bool cfg_doubl
     flow_nseq_ = nseq;
     flow_max_len_ = max_len;
 
-    // layout arrays
-    const size_t lay_bytes = (size_t)M * 4 + (size_t)nseq * (4 + 4 + 8) + 64;
-    ws_layout_.reserve(lay_bytes + 256);
-    if (!ws_layout_.as<void>()) return fail("cudaMalloc(layout) failed");
     uint8_t* lp = ws_layout_.as<uint8_t>();
-    int64_t* d_off = reinterpret_cast<int64_t*>(lp);
-    int32_t* d_rowseq = reinterpret_cast<int32_t*>(lp + (((size_t)nseq * 8 + 15) & ~size_t(15)));
-    int32_t* d_start = d_rowseq + M;
-    int32_t* d_len = d_start + nseq;
-    MD_CUDA(cudaMemcpy(d_off, h_in_offset_.data(), (size_t)nseq * 8, cudaMemcpyHostToDevice));
-    MD_CUDA(cudaMemcpy(d_rowseq, h_row_seq_.data(), (size_t)M * 4, cudaMemcpyHostToDevice));
-    MD_CUDA(cudaMemcpy(d_start, h_seq_start_.data(), (size_t)nseq * 4, cudaMemcpyHostToDevice));
-    MD_CUDA(cudaMemcpy(d_len, h_seq_len_.data(), (size_t)nseq * 4, cudaMemcpyHostToDevice));
+    MD_CUDA(cudaMemcpyAsync(lp, hp, lay_bytes, cudaMemcpyHostToDevice, st));
+    stager_.commit(st);
+    int32_t* d_rowseq = reinterpret_cast<int32_t*>(lp + off_rowseq);
     layout_.n_feats = cfg_.n_feats;
     layout_.rows_half = rows_half;
     layout_.noise_cstride = cfg_.noise_len;
+    layout_.time_major = 0;
+    layout_.dense_T = dense_T;
     layout_.row_seq = d_rowseq;
-    layout_.seq_start = d_start;
-    layout_.seq_len = d_len;
-    layout_.in_offset = d_off;
+    layout_.seq_start = d_rowseq + M;
+    layout_.seq_len = d_rowseq + M + nseq;
+    layout_.in_offset = reinterpret_cast<int64_t*>(lp);
 
-    // activation workspace (all buffers have M rows; one slack tile at the end for TMA boxes)
+    // activation workspace views (same carving as reserve_flow)
     const int C = cfg_.channels, H = cfg_.heads * cfg_.head_dim;
     const size_t Mr = (size_t)M + kGemmBM;
     size_t need = 0;
@@ -263,8 +339,6 @@ int Engine::build_flow_layout(int nseq_half, const int32_t* lens, bool cfg_doubl
                  o_qkv = take(Mr * 3 * H * 2), o_att = take(Mr * H * 2), o_ff = take(Mr * 4 * C * 2),
                  o_cat = take(Mr * 2 * C * 2), o_xs = take(Mr * cfg_.n_feats * 4), o_hres = take(Mr * C * 4),
                  o_rres = take(Mr * C * 4), o_d = take(Mr * cfg_.n_feats * 4);
-    ws_flow_.reserve(need);
-    if (!ws_flow_.as<void>()) return fail("cudaMalloc(flow workspace) failed");
     uint8_t* b = ws_flow_.as<uint8_t>();
     xin_ = (__nv_bfloat16*)(b + o_xin);
     xn_ = (__nv_bfloat16*)(b + o_xn);
@@ -277,23 +351,15 @@ int Engine::build_flow_layout(int nseq_half, const int32_t* lens, bool cfg_doubl
     hres_ = (float*)(b + o_hres);
     rres_ = (float*)(b + o_rres);
     dout_ = (float*)(b + o_d);
-
-    const int ngroups = cfg_.n_mid + 2;
-    const size_t tbytes = ((size_t)nseq * cfg_.time_dim + (size_t)nseq * ngroups * C + nseq + 64) * 4;
-    ws_time_.reserve(tbytes);
-    if (!ws_time_.as<void>()) return fail("cudaMalloc(time workspace) failed");
-    temb_ = ws_time_.as<float>();
-    tbias_ = temb_ + (size_t)nseq * cfg_.time_dim;
-    tvals_ = tbias_ + (size_t)nseq * ngroups * C;
     return 0;
 }
 
-int Engine::time_bias(const float* t_dev, int nt, cudaStream_t st) {
+int Engine::time_bias(const float* t_dev, int nt, float* temb, float* tbias, cudaStream_t st) {
     const int ngroups = cfg_.n_mid + 2;
     launch_time_embed(t_dev, nt, cfg_.in_channels, cfg_.time_dim, W<float>("est.time.w1"), W<float>("est.time.b1"),
-                      W<float>("est.time.w2"), W<float>("est.time.b2"), temb_, st);
-    launch_time_bias(temb_, nt, cfg_.time_dim, W<float>("est.tbias.w"), W<float>("est.tbias.b"),
-                     ngroups * cfg_.channels, tbias_, st);
+                      W<float>("est.time.w2"), W<float>("est.time.b2"), temb, st);
+    launch_time_bias(temb, nt, cfg_.time_dim, W<float>("est.tbias.w"), W<float>("est.tbias.b"),
+                     ngroups * cfg_.channels, tbias, st);
     launches_ += 2;
     return 0;
 }
@@ -394,16 +460,10 @@ int Engine::estimator_forward(int M, int nseq, int max_len, const float* tbias, 
                 if (gemm(p, st)) return -1;
             }
             if (profile_) prof_begin(1, 0.0, st);
-            if (attn_v1_) {
-                launch_attention(qkv_, att_, layout_.seq_start, layout_.seq_len, nseq, max_len, cfg_.heads, chunk, st);
-            } else if (attn_ws_) {
+            {
                 cudaError_t ae = launch_attention_ws(qkv_, M, att_, layout_.seq_start, layout_.seq_len, nseq, max_len,
                                                      cfg_.heads, chunk, st);
                 if (ae != cudaSuccess) return fail(std::string("launch_attention_ws: ") + cudaGetErrorString(ae));
-            } else {
-                cudaError_t ae = launch_attention_tc(qkv_, M, att_, layout_.seq_start, layout_.seq_len, nseq, max_len,
-                                                     cfg_.heads, chunk, st);
-                if (ae != cudaSuccess) return fail(std::string("launch_attention_tc: ") + cudaGetErrorString(ae));
             }
             if (profile_) prof_end(st);
             ++launches_;

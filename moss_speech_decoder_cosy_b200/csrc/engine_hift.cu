@@ -31,6 +31,30 @@ constexpr int kResK[3] = {3, 7, 11};
 constexpr int kSrcResK[3] = {7, 7, 11};
 constexpr int kDil[3] = {1, 3, 5};
 
+constexpr size_t kHiftSlack = 256;  // rows of slack after every matrix (TMA boxes / shifted windows stay inside)
+constexpr int kHiftBufs = 22;
+
+// Offsets of the vocoder workspace buffers for a group of `rows_f` frame rows; returns the total size.
+size_t hift_carve(int64_t rows_f, int base, size_t* offs) {
+    size_t need = 0;
+    int k = 0;
+    auto take = [&](size_t bytes) {
+        offs[k++] = need;
+        need += (bytes + 1023) & ~size_t(1023);
+    };
+    const size_t slack = kHiftSlack;
+    const size_t Fr = (size_t)rows_f + slack;
+    const size_t M2 = (size_t)rows_f * 120;
+    const size_t S = (M2 + slack) * 64;  // elements of one stage matrix (largest: stage 2; M0*256 and M1*128 are smaller)
+    take(Fr * 128 * 2); take(Fr * 128 * 2);                                      // melb, melb_lo
+    take(Fr * base * 2); take(Fr * base * 2); take(Fr * base * 2); take(Fr * base * 2);   // fa, fb, fa_lo, fb_lo
+    take(Fr * 4 * 4); take(Fr * 16 * 4); take(((size_t)rows_f * 480 + 1024) * 4);     // f0, p480, src
+    take((M2 + 2 * slack) * kStftLd * 2); take((M2 + slack) * 32 * 4);            // stft, post
+    for (int i = 0; i < 5; ++i) take(S * 4);                                      // u, si, x, xr, xs
+    for (int i = 0; i < 6; ++i) take(S * 2);                                      // a0, a1, a2, h, lr, sb
+    return need;
+}
+
 std::string N(const char* fmt, int a = 0, int b = 0, int c = 0) {
     char buf[128];
     snprintf(buf, sizeof buf, fmt, a, b, c);
@@ -146,16 +170,27 @@ int Engine::finalize_hift() {
     return 0;
 }
 
+int Engine::reserve_hift(int64_t rows_f, int nseq) {
+    rows_f = (rows_f + kGemmBM - 1) / kGemmBM * kGemmBM;
+    const size_t n_rs = (size_t)rows_f * (1 + 8 + 40 + 120);
+    ws_hift_layout_.reserve((size_t)nseq * 28 + n_rs * 4 + 1024);
+    if (!ws_hift_layout_.as<void>()) return fail("cudaMalloc(hift layout) failed");
+    size_t offs[kHiftBufs];
+    ws_hift_.reserve(hift_carve(rows_f, cfg_.hift_base, offs));
+    if (!ws_hift_.as<void>()) return fail("cudaMalloc(hift workspace) failed");
+    return 0;
+}
+
 int Engine::hift(int B, const int32_t* lens, const float* mel, const float* cache_source, int cache_stride,
                  const int32_t* cache_len, const float* nsf_noise, float* wav_out, float* source_out, uint64_t seed,
                  int flags, cudaStream_t st) {
+    DeviceGuard g(device_);
     if (!finalized_) return fail("weights not finalized");
     if (!has_hift_) return fail("HiFT tensors missing: " + missing_);
     if (B <= 0) return fail("hift: bad batch");
     for (int b = 0; b < B; ++b)
         if (lens[b] <= 0) return fail("hift: sequence length must be positive");
     if (cfg_.hift_base != 512) return fail("hift: only base_channels = 512 is built");
-    hift_init_constants();
     // split the batch into groups of <= hift_group_frames_ frames so the stage-2 working set stays bounded
     int b0 = 0;
     int64_t mel_off = 0, wav_off = 0;
@@ -181,22 +216,11 @@ int Engine::hift_group(int b0, int b1, const int32_t* lens, int64_t mel_off0, in
                        float* wav_out, float* source_out, uint64_t seed, int flags, cudaStream_t st) {
     const int nseq = b1 - b0;
     HiftRunner R(*this, st);
-    // ---------------------------------------------------------------- host layout
-    std::vector<int32_t> h_start(nseq), h_len(nseq), h_clen(nseq, 0);
-    std::vector<int64_t> h_mel(nseq), h_wav(nseq);
+    // ---------------------------------------------------------------- host layout (built in a pinned slot, one async upload)
     int rows = 0, max_len = 0;
-    int64_t mo = mel_off0, wo = wav_off0;
     for (int s = 0; s < nseq; ++s) {
-        rows += kGuardF;
-        h_start[s] = rows;
-        h_len[s] = lens[b0 + s];
-        h_mel[s] = mo;
-        h_wav[s] = wo;
-        mo += (int64_t)h_len[s] * cfg_.n_feats;
-        wo += (int64_t)h_len[s] * 480;
-        rows += h_len[s];
-        max_len = std::max(max_len, h_len[s]);
-        if (cache_len) h_clen[s] = cache_len[b0 + s];
+        rows += kGuardF + lens[b0 + s];
+        max_len = std::max(max_len, lens[b0 + s]);
     }
     rows += kGuardF;
     const int rows_f = (rows + kGemmBM - 1) / kGemmBM * kGemmBM;
@@ -204,24 +228,41 @@ int Engine::hift_group(int b0, int b1, const int32_t* lens, int64_t mel_off0, in
     R.max_len = max_len;
     for (int i = 0; i < 3; ++i) R.M[i] = (int64_t)rows_f * kScale[i];
     if (R.M[2] > 0x7fffff00LL) return fail("hift: group too large");
+    if (reserve_hift(rows_f, nseq)) return -1;
 
-    // layout arrays: [mel_off | wav_off] int64, [start | len | cache_len] int32, row_seq of 4 levels
-    const size_t n_rs = (size_t)rows_f * (1 + 8 + 40 + 120);
-    ws_hift_layout_.reserve((size_t)nseq * (16 + 12) + n_rs * 4 + 1024);
-    if (!ws_hift_layout_.as<void>()) return fail("cudaMalloc(hift layout) failed");
+    // layout arrays: [mel_off | wav_off] int64, [start | len | cache_len] int32, then row_seq of 4 levels (device-built)
+    const size_t head_bytes = (size_t)nseq * 28;
+    uint8_t* hp = static_cast<uint8_t*>(stager_.acquire(head_bytes));
+    if (!hp) return fail("cudaMallocHost(hift layout staging) failed");
+    {
+        int64_t* h_mel = reinterpret_cast<int64_t*>(hp);
+        int64_t* h_wav = h_mel + nseq;
+        int32_t* h_start = reinterpret_cast<int32_t*>(h_wav + nseq);
+        int32_t* h_len = h_start + nseq;
+        int32_t* h_clen = h_len + nseq;
+        int r = 0;
+        int64_t mo = mel_off0, wo = wav_off0;
+        for (int s = 0; s < nseq; ++s) {
+            r += kGuardF;
+            h_start[s] = r;
+            h_len[s] = lens[b0 + s];
+            h_mel[s] = mo;
+            h_wav[s] = wo;
+            mo += (int64_t)h_len[s] * cfg_.n_feats;
+            wo += (int64_t)h_len[s] * 480;
+            r += h_len[s];
+            h_clen[s] = cache_len ? cache_len[b0 + s] : 0;
+        }
+    }
     uint8_t* lp = ws_hift_layout_.as<uint8_t>();
     int64_t* d_mel = reinterpret_cast<int64_t*>(lp);
     int64_t* d_wav = d_mel + nseq;
     int32_t* d_start = reinterpret_cast<int32_t*>(d_wav + nseq);
     int32_t* d_len = d_start + nseq;
     int32_t* d_clen = d_len + nseq;
-    int32_t* d_rs = reinterpret_cast<int32_t*>(lp + (((size_t)nseq * 28 + 255) & ~size_t(255)));
-    MD_CUDA(cudaMemcpyAsync(d_mel, h_mel.data(), (size_t)nseq * 8, cudaMemcpyHostToDevice, st));
-    MD_CUDA(cudaMemcpyAsync(d_wav, h_wav.data(), (size_t)nseq * 8, cudaMemcpyHostToDevice, st));
-    MD_CUDA(cudaMemcpyAsync(d_start, h_start.data(), (size_t)nseq * 4, cudaMemcpyHostToDevice, st));
-    MD_CUDA(cudaMemcpyAsync(d_len, h_len.data(), (size_t)nseq * 4, cudaMemcpyHostToDevice, st));
-    MD_CUDA(cudaMemcpyAsync(d_clen, h_clen.data(), (size_t)nseq * 4, cudaMemcpyHostToDevice, st));
-    MD_CUDA(cudaStreamSynchronize(st));  // the host vectors above go out of scope
+    int32_t* d_rs = reinterpret_cast<int32_t*>(lp + ((head_bytes + 255) & ~size_t(255)));
+    MD_CUDA(cudaMemcpyAsync(lp, hp, head_bytes, cudaMemcpyHostToDevice, st));
+    stager_.commit(st);
     HiftLayout& L = R.L;
     L.nseq = nseq;
     L.rows_f = rows_f;
@@ -240,25 +281,13 @@ int Engine::hift_group(int b0, int b1, const int32_t* lens, int64_t mel_off0, in
 
     // ---------------------------------------------------------------- workspace
     const int base = cfg_.hift_base;
-    size_t need = 0;
-    auto take = [&](size_t bytes) {
-        size_t o = need;
-        need += (bytes + 1023) & ~size_t(1023);
-        return o;
-    };
-    const size_t slack = 256;  // rows of slack after every matrix (TMA boxes / shifted windows stay inside)
-    const size_t Fr = (size_t)rows_f + slack;
-    const size_t S = ((size_t)R.M[2] + slack) * 64;  // elements of one stage matrix (largest: stage 2; M0*256 and M1*128 are smaller)
-    const size_t o_melb = take(Fr * 128 * 2), o_melb_lo = take(Fr * 128 * 2), o_fa = take(Fr * base * 2),
-                 o_fb = take(Fr * base * 2), o_fa_lo = take(Fr * base * 2), o_fb_lo = take(Fr * base * 2),
-                 o_f0 = take(Fr * 4 * 4), o_p480 = take(Fr * 16 * 4), o_src = take(((size_t)rows_f * 480 + 1024) * 4),
-                 o_stft = take(((size_t)R.M[2] + 2 * slack) * kStftLd * 2), o_post = take(((size_t)R.M[2] + slack) * 32 * 4),
-                 o_u = take(S * 4), o_si = take(S * 4), o_x = take(S * 4), o_xr = take(S * 4), o_xs = take(S * 4),
-                 o_a0 = take(S * 2), o_a1 = take(S * 2), o_a2 = take(S * 2), o_h = take(S * 2), o_lr = take(S * 2),
-                 o_sb = take(S * 2);
-    const bool moved = ws_hift_.reserve(need);
-    (void)moved;
-    if (!ws_hift_.as<void>()) return fail("cudaMalloc(hift workspace) failed");
+    const size_t slack = kHiftSlack;
+    size_t offs[kHiftBufs];
+    hift_carve(rows_f, base, offs);
+    const size_t o_melb = offs[0], o_melb_lo = offs[1], o_fa = offs[2], o_fb = offs[3], o_fa_lo = offs[4], o_fb_lo = offs[5],
+                 o_f0 = offs[6], o_p480 = offs[7], o_src = offs[8], o_stft = offs[9], o_post = offs[10], o_u = offs[11],
+                 o_si = offs[12], o_x = offs[13], o_xr = offs[14], o_xs = offs[15], o_a0 = offs[16], o_a1 = offs[17],
+                 o_a2 = offs[18], o_h = offs[19], o_lr = offs[20], o_sb = offs[21];
     uint8_t* wb = ws_hift_.as<uint8_t>();
     R.melb = (__nv_bfloat16*)(wb + o_melb);
     R.melb_lo = (__nv_bfloat16*)(wb + o_melb_lo);
@@ -426,6 +455,7 @@ int Engine::hift_group(int b0, int b1, const int32_t* lens, int64_t mel_off0, in
 }
 
 int Engine::debug_read(const char* name, void* host_dst, size_t bytes) {
+    DeviceGuard g(device_);
     auto it = taps_.find(name);
     if (it == taps_.end()) return fail(std::string("no such tap: ") + name);
     if (bytes > it->second.second) bytes = it->second.second;
@@ -435,6 +465,7 @@ int Engine::debug_read(const char* name, void* host_dst, size_t bytes) {
 }
 
 int Engine::fade_in_out(float* speech, const float* prev_tail, const float* window2n, int n, cudaStream_t st) {
+    DeviceGuard g(device_);
     if (n <= 0) return 0;
     launch_fade(speech, prev_tail, window2n, n, st);
     ++launches_;

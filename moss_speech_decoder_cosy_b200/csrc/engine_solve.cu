@@ -1,8 +1,17 @@
 // Engine entry points of the flow path: single estimator call (reference TensorRT contract) and the full
 // classifier-free-guidance Euler solve (cosyvoice/flow/flow_matching.py:76-127, 206-230).
+//
+// The Euler loop of a solve (n_steps x {both CFG halves of the estimator on two streams, CFG mix + Euler update}, about
+// 580 launches per step) depends on the call only through the packed-row geometry, so it is captured ONCE per geometry
+// into a CUDA graph and replayed: one cudaGraphLaunch instead of ~5 800 launches, each preceded on the host by 3-4
+// tensor-map encodes.  The reference's analogue is the enqueue-once TensorRT context (flow_matching.py:133-156).
+// What changes from call to call (caller pointers, sequence layout arrays) stays outside the graph: the layout arrays
+// live at fixed device addresses and are refreshed by an async copy, flow_prepare / rows_to_bct are plain launches.
 #include "engine.h"
 
 #include <math.h>
+#include <string.h>
+#include <tuple>
 
 namespace mossdec {
 
@@ -14,17 +23,53 @@ namespace mossdec {
 
 int Engine::estimator(int B2, int T, const float* x, const float* mask, const float* mu, const float* t,
                       const float* spks, const float* cond, float* out, int chunk, cudaStream_t st) {
+    DeviceGuard g(device_);
     if (!finalized_) return fail("weights not finalized");
     if (B2 <= 0 || T <= 0) return fail("estimator: bad shape");
     std::vector<int32_t> lens(B2, T);
-    if (build_flow_layout(B2, lens.data(), /*cfg_double=*/false)) return -1;
-    layout_.time_major = 0;
+    bool ragged = false;
+    if (mask != nullptr) {
+        // The reference multiplies by `mask` after every layer and turns it into the attention bias
+        // (decoder.py:433-494); its masks are prefix masks (make_pad_mask).  Here a masked frame has no row at all:
+        // read the lengths back (this entry point synchronises anyway, like the TensorRT path it mirrors,
+        // flow_matching.py:153-154) and reject anything that is not a prefix mask.
+        if (mask_lens_cap_ < B2 + 1) {
+            if (h_mask_lens_) cudaFreeHost(h_mask_lens_);
+            if (d_mask_lens_) cudaFree(d_mask_lens_);
+            h_mask_lens_ = nullptr;
+            d_mask_lens_ = nullptr;
+            mask_lens_cap_ = 0;
+            MD_CUDA(cudaMallocHost(reinterpret_cast<void**>(&h_mask_lens_), (size_t)(B2 + 1) * 4));
+            MD_CUDA(cudaMalloc(reinterpret_cast<void**>(&d_mask_lens_), (size_t)(B2 + 1) * 4));
+            mask_lens_cap_ = B2 + 1;
+        }
+        MD_CUDA(cudaMemsetAsync(d_mask_lens_ + B2, 0, 4, st));
+        launch_mask_lens(mask, B2, T, d_mask_lens_, d_mask_lens_ + B2, st);
+        ++launches_;
+        MD_CUDA(cudaMemcpyAsync(h_mask_lens_, d_mask_lens_, (size_t)(B2 + 1) * 4, cudaMemcpyDeviceToHost, st));
+        MD_CUDA(cudaStreamSynchronize(st));
+        if (h_mask_lens_[B2] != 0) return fail("estimator: mask must be a prefix (padding) mask: 1...1 0...0 per sequence");
+        for (int b = 0; b < B2; ++b) {
+            lens[b] = h_mask_lens_[b];
+            if (lens[b] <= 0) return fail("estimator: a sequence is fully masked");
+            ragged |= lens[b] != T;
+        }
+    }
+    if (build_flow_layout(B2, lens.data(), /*cfg_double=*/false, st, /*dense_T=*/T)) return -1;
     const int M = flow_M_;
     launch_est_pack(layout_, M, x, mu, spks, cond, mask, xin_, st);
     ++launches_;
-    if (time_bias(t, B2, st)) return -1;
     const int ngroups = cfg_.n_mid + 2;
-    if (estimator_forward(M, B2, T, tbias_, ngroups * cfg_.channels, chunk, st)) return -1;
+    const size_t tbytes = ((size_t)B2 * cfg_.time_dim + (size_t)B2 * ngroups * cfg_.channels + 64) * 4;
+    ws_time_.reserve(tbytes);
+    if (!ws_time_.as<void>()) return fail("cudaMalloc(time workspace) failed");
+    float* temb = ws_time_.as<float>();
+    float* tbias = temb + (size_t)B2 * cfg_.time_dim;
+    if (time_bias(t, B2, temb, tbias, st)) return -1;
+    if (estimator_forward(M, B2, flow_max_len_, tbias, ngroups * cfg_.channels, chunk, st)) return -1;
+    // the input tensors are fully consumed by est_pack, so `out` may alias `x` (the TensorRT contract binds the output
+    // onto x, flow_matching.py:143-151); masked frames of the output are zero like `output * mask` (decoder.py:494)
+    if (ragged) MD_CUDA(cudaMemsetAsync(out, 0, (size_t)B2 * cfg_.n_feats * T * 4, st));
     launch_rows_to_bct(layout_, dout_, 0, out, st);
     ++launches_;
     MD_CUDA(cudaGetLastError());
@@ -42,50 +87,20 @@ static void cosine_t_span(int n, std::vector<float>& ts) {
     }
 }
 
-int Engine::flow_solve(int B, const int32_t* lens, const float* mu, const float* spks, const float* cond,
-                       const float* noise, int noise_len_arg, int n_steps, float cfg_rate, float temperature, int chunk,
-                       float* mel_out, int flags, cudaStream_t st) {
-    if (!finalized_) return fail("weights not finalized");
-    if (B <= 0 || n_steps <= 0) return fail("flow_solve: bad arguments");
-    const int noise_bstride = 0;  // one bank shared by all utterances, like the reference
-    int noise_len = noise_len_arg;
-    if (noise == nullptr) {
-        noise = W<float>("flow.rand_noise");
-        if (!noise) return fail("flow.rand_noise not loaded and no noise given");
-        noise_len = cfg_.noise_len;
-    }
-    for (int b = 0; b < B; ++b)
-        if (lens[b] > noise_len) return fail("sequence longer than the noise bank");
-    if (build_flow_layout(B, lens, /*cfg_double=*/true)) return -1;
-    layout_.noise_cstride = noise_len;
-    layout_.time_major = flags & 1;
-    const int M = flow_M_;
-    launch_flow_prepare(layout_, mu, spks, cond, noise, noise_bstride, temperature, xin_, xstate_, st);
-    ++launches_;
+bool Engine::GraphKey::operator<(const GraphKey& o) const {
+    return std::tie(rows_half, nseq_half, max_len, chunk, n_steps, dual, cfg_bits, ws, lay, tb) <
+           std::tie(o.rows_half, o.nseq_half, o.max_len, o.chunk, o.n_steps, o.dual, o.cfg_bits, o.ws, o.lay, o.tb);
+}
 
-    std::vector<float> ts;
-    cosine_t_span(n_steps, ts);
-    // t accumulates in fp32 exactly like the reference loop (t = t + dt; dt = t_span[step + 1] - t)
-    std::vector<float> tv(n_steps), dtv(n_steps);
-    float t = ts[0], dt = ts[1] - ts[0];
-    for (int s = 1; s <= n_steps; ++s) {
-        tv[s - 1] = t;
-        dtv[s - 1] = dt;
-        t = t + dt;
-        if (s < n_steps) dt = ts[s + 1] - t;
-    }
-    // all time-embedding biases of the solve at once: the timestep is shared by every sequence of the batch
-    // (t_in[:] = t, flow_matching.py:110), so one row per step
+void Engine::drop_graphs() {
+    for (auto& kv : graphs_)
+        if (kv.second.exec) cudaGraphExecDestroy(kv.second.exec);
+    graphs_.clear();
+}
+
+// The Euler loop: every step runs the estimator on both CFG halves and applies the CFG mix + Euler update.
+int Engine::run_euler_steps(int n_steps, int chunk, float cfg_rate, const float* dtv, cudaStream_t st) {
     const int ngroups = cfg_.n_mid + 2;
-    const size_t need = ((size_t)n_steps * cfg_.time_dim + (size_t)n_steps * ngroups * cfg_.channels + n_steps + 64) * 4;
-    ws_time_.reserve(need);
-    if (!ws_time_.as<void>()) return fail("cudaMalloc(time workspace) failed");
-    temb_ = ws_time_.as<float>();
-    tbias_ = temb_ + (size_t)n_steps * cfg_.time_dim;
-    tvals_ = tbias_ + (size_t)n_steps * ngroups * cfg_.channels;
-    MD_CUDA(cudaMemcpyAsync(tvals_, tv.data(), (size_t)n_steps * 4, cudaMemcpyHostToDevice, st));
-    if (time_bias(tvals_, n_steps, st)) return -1;
-
     for (int s = 0; s < n_steps; ++s) {
         // tbias_ld = 0: every sequence reads the row of this step
         const float* tb = tbias_ + (size_t)s * ngroups * cfg_.channels;
@@ -100,15 +115,127 @@ int Engine::flow_solve(int B, const int32_t* lens, const float* mu, const float*
             if (estimator_forward(flow_rows_half_, flow_nseq_ / 2, flow_max_len_, tb, 0, chunk, st2_, flow_rows_half_)) return -1;
             MD_CUDA(cudaEventRecord(ev_join_, st2_));
             MD_CUDA(cudaStreamWaitEvent(st, ev_join_, 0));
-        } else if (estimator_forward(M, flow_nseq_, flow_max_len_, tb, 0, chunk, st)) {
+        } else if (estimator_forward(flow_M_, flow_nseq_, flow_max_len_, tb, 0, chunk, st)) {
             return -1;
         }
         launch_euler_cfg(layout_, dout_, dtv[s], cfg_rate, xstate_, xin_, st);
         ++launches_;
     }
+    return 0;
+}
+
+int Engine::flow_solve(int B, const int32_t* lens, const float* mu, const float* spks, const float* cond,
+                       const float* noise, int noise_len_arg, int n_steps, float cfg_rate, float temperature, int chunk,
+                       float* mel_out, int flags, cudaStream_t st) {
+    DeviceGuard g(device_);
+    if (!finalized_) return fail("weights not finalized");
+    if (B <= 0 || n_steps <= 0) return fail("flow_solve: bad arguments");
+    const int noise_bstride = 0;  // one bank shared by all utterances, like the reference
+    int noise_len = noise_len_arg;
+    if (noise == nullptr) {
+        noise = W<float>("flow.rand_noise");
+        if (!noise) return fail("flow.rand_noise not loaded and no noise given");
+        noise_len = cfg_.noise_len;
+    }
+    for (int b = 0; b < B; ++b)
+        if (lens[b] > noise_len) return fail("sequence longer than the noise bank");
+    if (build_flow_layout(B, lens, /*cfg_double=*/true, st)) return -1;
+    layout_.noise_cstride = noise_len;
+    layout_.time_major = flags & 1;
+    launch_flow_prepare(layout_, mu, spks, cond, noise, noise_bstride, temperature, xin_, xstate_, st);
+    ++launches_;
+
+    std::vector<float> ts;
+    cosine_t_span(n_steps, ts);
+    // t accumulates in fp32 exactly like the reference loop (t = t + dt; dt = t_span[step + 1] - t)
+    std::vector<float> tv(n_steps), dtv(n_steps);
+    float t = ts[0], dt = ts[1] - ts[0];
+    for (int s = 1; s <= n_steps; ++s) {
+        tv[s - 1] = t;
+        dtv[s - 1] = dt;
+        t = t + dt;
+        if (s < n_steps) dt = ts[s + 1] - t;
+    }
+    // All time-embedding biases of the solve at once: the timestep is shared by every sequence of the batch
+    // (t_in[:] = t, flow_matching.py:110), so one row per step.  They depend on n_steps only: computed once and kept.
+    const int ngroups = cfg_.n_mid + 2;
+    const size_t need = ((size_t)n_steps * cfg_.time_dim + (size_t)n_steps * ngroups * cfg_.channels + n_steps + 64) * 4;
+    if (ws_time_solve_.reserve(need)) solve_tbias_steps_ = 0;
+    if (!ws_time_solve_.as<void>()) return fail("cudaMalloc(time workspace) failed");
+    temb_ = ws_time_solve_.as<float>();
+    tbias_ = temb_ + (size_t)n_steps * cfg_.time_dim;
+    tvals_ = tbias_ + (size_t)n_steps * ngroups * cfg_.channels;
+    if (solve_tbias_steps_ != n_steps) {
+        float* hp = static_cast<float*>(stager_.acquire((size_t)n_steps * 4));
+        if (!hp) return fail("cudaMallocHost(staging) failed");
+        memcpy(hp, tv.data(), (size_t)n_steps * 4);
+        MD_CUDA(cudaMemcpyAsync(tvals_, hp, (size_t)n_steps * 4, cudaMemcpyHostToDevice, st));
+        stager_.commit(st);
+        if (time_bias(tvals_, n_steps, temb_, tbias_, st)) return -1;
+        solve_tbias_steps_ = n_steps;
+    }
+
+    bool done = false;
+    if (graph_mode_ > 0 && !profile_) {
+        GraphKey key{flow_rows_half_, B, flow_max_len_, chunk, n_steps, dual_stream_ ? 1 : 0, 0u,
+                     ws_flow_.as<void>(), ws_layout_.as<void>(), ws_time_solve_.as<void>()};
+        memcpy(&key.cfg_bits, &cfg_rate, 4);
+        GraphEntry& ge = graphs_[key];
+        ++ge.seen;
+        ge.last_use = ++graph_clock_;
+        if (ge.exec == nullptr && ge.seen >= (graph_mode_ >= 2 ? 1 : 2)) {
+            // capture on an internal stream (the caller's may be the legacy stream, which cannot capture)
+            const long l0 = launches_;
+            cudaGraph_t graph = nullptr;
+            if (cudaStreamBeginCapture(cap_st_, cudaStreamCaptureModeThreadLocal) == cudaSuccess) {
+                const int rc = run_euler_steps(n_steps, chunk, cfg_rate, dtv.data(), cap_st_);
+                const cudaError_t ee = cudaStreamEndCapture(cap_st_, &graph);
+                if (rc == 0 && ee == cudaSuccess && graph != nullptr &&
+                    cudaGraphInstantiate(&ge.exec, graph, 0) == cudaSuccess) {
+                    ge.launches = launches_ - l0;
+                } else {
+                    ge.exec = nullptr;
+                    graph_mode_ = 0;   // capture is not possible here: fall back to plain launches for good
+                    cudaGetLastError();
+                }
+                if (graph) cudaGraphDestroy(graph);
+            } else {
+                graph_mode_ = 0;
+                cudaGetLastError();
+            }
+            launches_ = l0;
+            if (graphs_.size() > 24) {   // bound the cache: drop the least recently used executable
+                auto victim = graphs_.end();
+                for (auto it = graphs_.begin(); it != graphs_.end(); ++it)
+                    if (it->second.exec && &it->second != &ge && (victim == graphs_.end() || it->second.last_use < victim->second.last_use))
+                        victim = it;
+                if (victim != graphs_.end()) {
+                    cudaGraphExecDestroy(victim->second.exec);
+                    graphs_.erase(victim);
+                }
+            }
+        }
+        if (ge.exec != nullptr) {
+            MD_CUDA(cudaGraphLaunch(ge.exec, st));
+            launches_ += ge.launches;
+            ++graph_replays_;
+            done = true;
+        }
+    }
+    if (!done && run_euler_steps(n_steps, chunk, cfg_rate, dtv.data(), st)) return -1;
     launch_rows_to_bct(layout_, xstate_, 0, mel_out, st);
     ++launches_;
     MD_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int Engine::reserve(int64_t flow_rows, int flow_seqs, int64_t hift_frames) {
+    DeviceGuard g(device_);
+    if (flow_rows > 0) {
+        const size_t rows_half = ((size_t)flow_rows + 4 * (size_t)(flow_seqs + 1) + kGemmBM - 1) / kGemmBM * kGemmBM;
+        if (reserve_flow(2 * rows_half, 2 * (flow_seqs > 0 ? flow_seqs : 1))) return -1;
+    }
+    if (hift_frames > 0 && reserve_hift(hift_frames, flow_seqs > 0 ? flow_seqs : 1)) return -1;
     return 0;
 }
 

@@ -176,6 +176,52 @@ __device__ __forceinline__ float2 group_exchange(const EpiCtx& c, float2 mine) {
     return t;
 }
 
+// LayerNorm statistics of a row whose columns are split over the kEpiParts warps of a group, without the
+// E[x^2] - mean^2 cancellation: every warp contributes the mean and the centred sum of squares (M2) of ITS columns,
+// the parts are merged with the parallel-variance formula  M2 = sum M2_p + n_p * sum (mean_p - mean)^2  (equal counts).
+// Returns (mean, rstd).  A residual stream with a DC offset of many standard deviations keeps full fp32 accuracy.
+__device__ __forceinline__ float2 group_mean_rstd(const EpiCtx& c, float mean_p, float m2_p, float n_p, float eps) {
+    reinterpret_cast<float2*>(c.stg)[c.lane] = make_float2(mean_p, m2_p);
+    group_sync(c.quarter);
+    float2 o[kEpiParts];
+    float mean = 0.f;
+#pragma unroll
+    for (int part = 0; part < kEpiParts; ++part) {
+        o[part] = reinterpret_cast<const float2*>(c.stg_all + ((part << 2) | (c.ew & 3)) * kStageBytes)[c.lane];
+        mean += o[part].x;
+    }
+    group_sync(c.quarter);
+    mean *= (1.f / kEpiParts);
+    float m2 = 0.f;
+#pragma unroll
+    for (int part = 0; part < kEpiParts; ++part) {
+        const float d = o[part].x - mean;
+        m2 += o[part].y + n_p * d * d;
+    }
+    return make_float2(mean, rsqrtf(m2 / (n_p * kEpiParts) + eps));
+}
+// mean and centred sum of squares of NV register values (two passes over registers)
+template <int NV>
+__device__ __forceinline__ float2 local_mean_m2(const float* v) {
+    float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+#pragma unroll
+    for (int i = 0; i < NV; i += 4) {
+        s0 += v[i]; s1 += v[i + 1]; s2 += v[i + 2]; s3 += v[i + 3];
+    }
+    const float mean = ((s0 + s1) + (s2 + s3)) * (1.f / NV);
+    float q0 = 0.f, q1 = 0.f, q2 = 0.f, q3 = 0.f;
+#pragma unroll
+    for (int i = 0; i < NV; i += 4) {
+        const float d0 = v[i] - mean, d1 = v[i + 1] - mean, d2 = v[i + 2] - mean, d3 = v[i + 3] - mean;
+        q0 = fmaf(d0, d0, q0); q1 = fmaf(d1, d1, q1); q2 = fmaf(d2, d2, q2); q3 = fmaf(d3, d3, q3);
+    }
+    return make_float2(mean, (q0 + q1) + (q2 + q3));
+}
+// the same from shifted running sums  s = sum (x - K), ss = sum (x - K)^2  over n values (K = any value of the row)
+__device__ __forceinline__ float2 shifted_mean_m2(float K, float s, float ss, float n) {
+    return make_float2(K + s / n, fmaxf(ss - s * s / n, 0.f));
+}
+
 // coalesced global -> registers (thread == row) through the staging tile; fp32, 32 columns starting at column nb
 // (two rounds of 16 columns = 64-byte rows)
 __device__ __forceinline__ void load_rows_f32(const EpiCtx& c, const float* base, int ld, int nb, int nlim, float* out32) {

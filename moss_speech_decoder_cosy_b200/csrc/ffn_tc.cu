@@ -379,8 +379,7 @@ ffn_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ C
             tc_fence_after();
             FFN_STAMP(18);
             float v[64];
-            float s = 0.f, ss = 0.f;
-            {   // drain 16 columns at a time, the next load in flight while this one is stored / reduced
+            {   // drain 16 columns at a time, the next load in flight while this one is stored
                 const uint32_t ta = tlane + kAcc2Col + (uint32_t)(part * 64);
                 tmem_ld16(ta, v);
 #pragma unroll
@@ -398,30 +397,33 @@ ffn_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ C
                         for (int u = 0; u < 4; ++u)
                             *reinterpret_cast<float4*>(dst + (size_t)u * 512) = make_float4(w[4 * u], w[4 * u + 1], w[4 * u + 2], w[4 * u + 3]);
                     }
-#pragma unroll
-                    for (int i = 0; i < 16; ++i) {
-                        s += w[i];
-                        ss = fmaf(w[i], w[i], ss);
-                    }
                 }
             }
             if (lane == 0) tma_store_wait_read();   // the previous tile's last store has long finished reading this staging tile
             __syncwarp();
             if (p.ln) {   // (x - mean) * rstd; gamma / beta live in the consumer's weights
-                // row statistics over the 4 warps that share this TMEM lane quarter (slot = head of the staging tile)
-                reinterpret_cast<float2*>(stg)[lane] = make_float2(s, ss);
+                // row statistics over the 4 warps that share this TMEM lane quarter (slot = head of the staging tile):
+                // per-warp mean and centred sum of squares, merged with the parallel-variance formula (no E[x^2] - mean^2
+                // cancellation when the residual stream carries a large mean)
+                const float2 lm = local_mean_m2<64>(v);
+                reinterpret_cast<float2*>(stg)[lane] = lm;
                 group_sync(quarter);
-                s = 0.f;
-                ss = 0.f;
+                float2 o[kEpiParts];
+                float mean = 0.f;
 #pragma unroll
                 for (int q = 0; q < kEpiParts; ++q) {
-                    const float2 o = reinterpret_cast<const float2*>(sStg + ((q << 2) | (ew & 3)) * kOutStageBytes)[lane];
-                    s += o.x;
-                    ss += o.y;
+                    o[q] = reinterpret_cast<const float2*>(sStg + ((q << 2) | (ew & 3)) * kOutStageBytes)[lane];
+                    mean += o[q].x;
                 }
                 group_sync(quarter);
-                const float mean = s * (1.f / kC);
-                const float rstd = rsqrtf(fmaxf(ss * (1.f / kC) - mean * mean, 0.f) + p.ln_eps);
+                mean *= (1.f / kEpiParts);
+                float m2 = 0.f;
+#pragma unroll
+                for (int q = 0; q < kEpiParts; ++q) {
+                    const float d = o[q].x - mean;
+                    m2 += o[q].y + 64.f * d * d;
+                }
+                const float rstd = rsqrtf(m2 * (1.f / kC) + p.ln_eps);
                 const float a = valid ? rstd : 0.f, bsh = valid ? -mean * rstd : 0.f;
 #pragma unroll
                 for (int i = 0; i < 64; ++i) v[i] = fmaf(v[i], a, bsh);
@@ -464,14 +466,18 @@ ffn_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ C
 
 }  // namespace
 
+cudaError_t ffn_tc_init_device() {
+    static std::atomic<uint64_t> done{0};
+    static std::mutex mu;
+    return once_per_device(done, mu, [] {
+        return cudaFuncSetAttribute(ffn_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kFfnSmem);
+    });
+}
+
 cudaError_t ffn_tc_launch(const FfnProblem& f, int num_sms, cudaStream_t stream) {
     if (f.M <= 0 || (f.M % kGemmBM) != 0 || !f.x || !f.w1 || !f.w2 || !f.b1 || !f.b2 || !f.hres || !f.out_bf16)
         return cudaErrorInvalidValue;
-    static std::once_flag attr_once;
-    static cudaError_t attr_err = cudaSuccess;
-    std::call_once(attr_once, [] {
-        attr_err = cudaFuncSetAttribute(ffn_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kFfnSmem);
-    });
+    const cudaError_t attr_err = ffn_tc_init_device();
     if (attr_err != cudaSuccess) return attr_err;
 
     FfnParams p;

@@ -135,7 +135,8 @@ __global__ void rows_to_bct_kernel(FlowLayout L, const float* __restrict__ rows,
     const int s = L.row_seq[row];
     if (s < 0) return;
     const int t = row - L.seq_start[s];
-    out[L.in_offset[s] + (L.time_major ? (size_t)t * C + c : (size_t)c * L.seq_len[s] + t)] = rows[(size_t)(row + row_offset) * C + c];
+    const int cs = L.dense_T > 0 ? L.dense_T : L.seq_len[s];   // channel stride of the channel-first form
+    out[L.in_offset[s] + (L.time_major ? (size_t)t * C + c : (size_t)c * cs + t)] = rows[(size_t)(row + row_offset) * C + c];
 }
 
 // generic estimator entry: x/mu/cond [nseq, C, T] + spks [nseq, C] -> bf16 rows [M, 4C] (all sequences explicit)
@@ -154,16 +155,39 @@ __global__ void est_pack_kernel(FlowLayout L, int nseq_rows, const float* __rest
         return;
     }
     const int t = row - L.seq_start[s];
-    const int T = L.seq_len[s];
+    const int T = L.dense_T > 0 ? L.dense_T : L.seq_len[s];
     const size_t off = L.in_offset[s] + (L.time_major ? (size_t)t * C + c : (size_t)c * T + t);
-    (void)mask;
+    (void)mask;   // prefix masks are turned into sequence lengths by the caller (mask_lens_kernel); masked frames have no row
     xr[c] = __float2bfloat16(x[off]);
     xr[C + c] = __float2bfloat16(mu[off]);
     xr[2 * C + c] = __float2bfloat16(spks ? spks[(size_t)s * C + c] : 0.f);
     xr[3 * C + c] = __float2bfloat16(cond ? cond[off] : 0.f);
 }
 
+// mask [B, 1, T] fp32 -> lens[b] = number of non-zero entries; bad[0] != 0 if some mask is not of the prefix form
+// 1 ... 1 0 ... 0 (the only form `make_pad_mask` produces, cosyvoice/utils/mask.py:239-265).  One block per sequence.
+__global__ void mask_lens_kernel(const float* __restrict__ mask, int T, int32_t* __restrict__ lens, int32_t* __restrict__ bad) {
+    __shared__ int s_cnt, s_last;
+    if (threadIdx.x == 0) { s_cnt = 0; s_last = 0; }
+    __syncthreads();
+    const float* m = mask + (size_t)blockIdx.x * T;
+    int cnt = 0, last = 0;
+    for (int t = threadIdx.x; t < T; t += blockDim.x)
+        if (m[t] != 0.f) { ++cnt; last = t + 1; }
+    atomicAdd(&s_cnt, cnt);
+    atomicMax(&s_last, last);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        lens[blockIdx.x] = s_cnt;
+        if (s_cnt != s_last) atomicExch(bad, 1);
+    }
+}
+
 }  // namespace
+
+void launch_mask_lens(const float* mask, int B, int T, int32_t* lens, int32_t* bad, cudaStream_t st) {
+    mask_lens_kernel<<<B, 256, 0, st>>>(mask, T, lens, bad);
+}
 
 void launch_time_embed(const float* t, int nseq, int dim_in, int dim_h, const float* w1, const float* b1,
                        const float* w2, const float* b2, float* temb_mish, cudaStream_t st) {

@@ -12,6 +12,8 @@
 #include <cuda_runtime.h>
 #include <cuda_bf16.h>
 #include <stdint.h>
+#include <atomic>
+#include <mutex>
 #include <utility>
 
 namespace mossdec {
@@ -113,9 +115,32 @@ struct FfnProblem {
 };
 cudaError_t ffn_tc_launch(const FfnProblem& p, int num_sms, cudaStream_t stream);
 
+// Per-device one-time setup (opt-in shared-memory sizes of the kernels, constant tables): function attributes and
+// __constant__ symbols live per device / context, so they are keyed by the CURRENT device ordinal under a mutex.
+// The Engine constructor calls these on its device; the launchers re-check with an atomic bitmask (one relaxed load).
+cudaError_t gemm_tc_init_device();
+cudaError_t ffn_tc_init_device();
+cudaError_t attention_ws_init_device();
+cudaError_t hift_init_device();
+
 // Enqueue on `stream`.  Returns cudaSuccess or the failing CUDA error; -1 style argument errors
 // are reported as cudaErrorInvalidValue.
 cudaError_t gemm_tc_launch(const GemmProblem& p, int num_sms, cudaStream_t stream);
+
+// Runs `init` once per CUDA device (bit d of `done` = device d initialised).
+template <typename F>
+inline cudaError_t once_per_device(std::atomic<uint64_t>& done, std::mutex& mu, F init) {
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    const uint64_t bit = 1ull << (dev & 63);
+    if (done.load(std::memory_order_acquire) & bit) return cudaSuccess;
+    std::lock_guard<std::mutex> lk(mu);
+    if (done.load(std::memory_order_relaxed) & bit) return cudaSuccess;
+    e = init();
+    if (e == cudaSuccess) done.fetch_or(bit, std::memory_order_release);
+    return e;
+}
 
 // Launch with the programmatic-stream-serialization attribute (see ptx.cuh pdl_wait); off unless MOSSDEC_PDL=1 (measured: no gain on this path).
 bool pdl_enabled();

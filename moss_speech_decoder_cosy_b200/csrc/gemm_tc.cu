@@ -20,7 +20,7 @@ namespace {
 // W16 == 4 is the bf16-only fast path (no fp32 input / output); W16 == 2 handles everything.
 template <int W16>
 __device__ __forceinline__ void epi_main(const EpiCtx& c, int cbeg, int cend, float mean1, float rstd1, float& s2,
-                                         float& ss2) {
+                                         float& ss2, float& k2) {
     constexpr int NV = W16 * 16;
     const KParams& p = *c.p;
     const GemmEpilogue& e = p.epi;
@@ -98,11 +98,13 @@ __device__ __forceinline__ void epi_main(const EpiCtx& c, int cbeg, int cend, fl
                 if (e.f32_tiled) store_rows_f32_tiled(e.out_f32, c.row0 + c.lane, nb, v);
                 else store_rows_f32(c, e.out_f32, e.ldf, nb, nlim, v);
             }
-            if (e.ln2_g || e.ln2_plain) {
+            if (e.ln2_g || e.ln2_plain) {   // sums shifted by the first value of the row part
+                if (cc == cbeg) k2 = v[0];
 #pragma unroll
                 for (int i = 0; i < NV; ++i) {
-                    s2 += v[i];
-                    ss2 += v[i] * v[i];
+                    const float d = v[i] - k2;
+                    s2 += d;
+                    ss2 = fmaf(d, d, ss2);
                 }
                 continue;  // bf16 side is produced by the second pass
             }
@@ -214,7 +216,6 @@ __device__ __forceinline__ void epi_resln(const EpiCtx& c, const CUtensorMap* tm
     mbar_wait(tfull_bar, tfull_phase);
     tc_fence_after();
     const uint32_t ta = tmem_acc + (uint32_t)n;
-    float s = 0.f, ss = 0.f;
     float t0[16], t1[16];
     tmem_ld16(ta, t0);
 #pragma unroll
@@ -234,17 +235,13 @@ __device__ __forceinline__ void epi_resln(const EpiCtx& c, const CUtensorMap* tm
 #pragma unroll
         for (int u = 0; u < 4; ++u)
             *reinterpret_cast<float4*>(dst + (size_t)u * 512) = make_float4(w[4 * u], w[4 * u + 1], w[4 * u + 2], w[4 * u + 3]);
-#pragma unroll
-        for (int i = 0; i < 16; ++i) {
-            s += w[i];
-            ss = fmaf(w[i], w[i], ss);
-        }
     }
     if (c.lane == 0) tma_store_wait_read();   // the exchange slot is the head of the staging tile the last store read
     __syncwarp();
-    const float2 tot = group_exchange(c, make_float2(s, ss));
-    const float mean = tot.x * (1.f / 256.f);
-    const float rstd = rsqrtf(fmaxf(tot.y * (1.f / 256.f) - mean * mean, 0.f) + e.ln_eps);
+    // centred statistics (no E[x^2] - mean^2 cancellation when the residual stream carries a large mean)
+    const float2 lm = local_mean_m2<64>(v);
+    const float2 mr = group_mean_rstd(c, lm.x, lm.y, 64.f, e.ln_eps);
+    const float mean = mr.x, rstd = mr.y;
     const float a = c.valid ? rstd : 0.f, bsh = c.valid ? -mean * rstd : 0.f;
 #pragma unroll
     for (int hlf = 0; hlf < 2; ++hlf) {
@@ -288,7 +285,6 @@ __device__ __forceinline__ void epi_lnact_single(const EpiCtx& c, const CUtensor
     mbar_wait(tfull_bar, tfull_phase);
     tc_fence_after();
     const uint32_t ta = tmem_acc + (uint32_t)n;
-    float s = 0.f, ss = 0.f;
     {
         float t0[16], t1[16];
         tmem_ld16(ta, t0);
@@ -308,22 +304,13 @@ __device__ __forceinline__ void epi_lnact_single(const EpiCtx& c, const CUtensor
                 const float4 b = *reinterpret_cast<const float4*>(sBias + n + q * 16 + i);   // broadcast LDS
                 w[i] = t[i] + b.x; w[i + 1] = t[i + 1] + b.y; w[i + 2] = t[i + 2] + b.z; w[i + 3] = t[i + 3] + b.w;
             }
-#pragma unroll
-            for (int i = 0; i < 16; ++i) {
-                s += w[i];
-                ss = fmaf(w[i], w[i], ss);
-            }
         }
     }
     if (c.lane == 0) tma_store_wait_read();   // the exchange slot is the head of the staging tile the last store read
     __syncwarp();
-#ifdef LNACT_X_NOEXCH
-    const float2 tot = make_float2(s * 4.f, ss * 4.f);
-#else
-    const float2 tot = group_exchange(c, make_float2(s, ss));
-#endif
-    const float mean = tot.x * (1.f / 256.f);
-    const float rstd = rsqrtf(fmaxf(tot.y * (1.f / 256.f) - mean * mean, 0.f) + e.ln_eps);
+    const float2 lm = local_mean_m2<64>(v);
+    const float2 mr = group_mean_rstd(c, lm.x, lm.y, 64.f, e.ln_eps);
+    const float mean = mr.x, rstd = mr.y;
 
     // addend of 16 columns: fp32 residual (lane-major tiled layout) or the time bias row of this row's sequence
     const float* addp = kRes ? e.resid + tiled_f32_offset(row, n)
@@ -337,7 +324,6 @@ __device__ __forceinline__ void epi_lnact_single(const EpiCtx& c, const CUtensor
     };
     float4 an, gn, bn;
     load4(0, an, gn, bn);
-    float s2 = 0.f, ss2 = 0.f;
     const float nmr = -mean * rstd;
     const float vmask = c.valid ? 1.f : 0.f;
 #pragma unroll
@@ -353,22 +339,15 @@ __device__ __forceinline__ void epi_lnact_single(const EpiCtx& c, const CUtensor
             //  serialises the unrolled loop; all inputs are finite, padding rows included)
             w[k] = (fast_mish(y) + ax[k]) * vmask;
         }
-        if (kRes) {
+        if (kRes)
             *reinterpret_cast<float4*>(e.out_f32 + tiled_f32_offset(row, n) + (size_t)u * 512) = make_float4(w[0], w[1], w[2], w[3]);
-#pragma unroll
-            for (int k = 0; k < 4; ++k) {
-                s2 += w[k];
-                ss2 = fmaf(w[k], w[k], ss2);
-            }
-        }
     }
     float a = 1.f, bsh = 0.f;
     if (kRes) {
-        const float2 t2 = group_exchange(c, make_float2(s2, ss2));
-        const float mean2 = t2.x * (1.f / 256.f);
-        const float rstd2 = rsqrtf(fmaxf(t2.y * (1.f / 256.f) - mean2 * mean2, 0.f) + e.ln_eps);
-        a = c.valid ? rstd2 : 0.f;
-        bsh = c.valid ? -mean2 * rstd2 : 0.f;
+        const float2 lm2 = local_mean_m2<64>(v);
+        const float2 mr2 = group_mean_rstd(c, lm2.x, lm2.y, 64.f, e.ln_eps);
+        a = c.valid ? mr2.y : 0.f;
+        bsh = c.valid ? -mr2.x * mr2.y : 0.f;
     }
 #pragma unroll
     for (int hlf = 0; hlf < 2; ++hlf) {
@@ -435,17 +414,18 @@ __device__ __forceinline__ void epi_lnact(const EpiCtx& c, const CUtensorMap* tm
     tc_fence_after();
     const uint32_t ta = tmem_acc + (uint32_t)n;
     float t0[16], t1[16];
-    float s = 0.f, ss = 0.f;
+    float s = 0.f, ss = 0.f, K = 0.f;
     tmem_ld16(ta, t0);
 #pragma unroll
-    for (int q = 0; q < 4; ++q) {   // pass 1: row statistics of acc + bias
+    for (int q = 0; q < 4; ++q) {   // pass 1: row statistics of acc + bias, sums shifted by the row's first value
         float* t = (q & 1) ? t1 : t0;
         tmem_ld_wait();
         if (q < 3) tmem_ld16(ta + (q + 1) * 16, (q & 1) ? t0 : t1);
+        if (q == 0) K = t[0] + sBias[n];
 #pragma unroll
         for (int i = 0; i < 16; i += 4) {
             const float4 b = *reinterpret_cast<const float4*>(sBias + n + q * 16 + i);   // broadcast LDS
-            const float x0 = t[i] + b.x, x1 = t[i + 1] + b.y, x2 = t[i + 2] + b.z, x3 = t[i + 3] + b.w;
+            const float x0 = t[i] + b.x - K, x1 = t[i + 1] + b.y - K, x2 = t[i + 2] + b.z - K, x3 = t[i + 3] + b.w - K;
             s += (x0 + x1) + (x2 + x3);
             ss = fmaf(x0, x0, fmaf(x1, x1, fmaf(x2, x2, fmaf(x3, x3, ss))));
         }
@@ -453,11 +433,10 @@ __device__ __forceinline__ void epi_lnact(const EpiCtx& c, const CUtensorMap* tm
     tmem_ld16(ta, t0);   // first group of pass 2 flies during the exchange
     if (c.lane == 0) tma_store_wait_read();   // the exchange slot is the head of the staging tile the last store read
     __syncwarp();
-    const float2 tot = group_exchange(c, make_float2(s, ss));
-    const float mean = tot.x * (1.f / 256.f);
-    const float rstd = rsqrtf(fmaxf(tot.y * (1.f / 256.f) - mean * mean, 0.f) + e.ln_eps);
+    const float2 lm = shifted_mean_m2(K, s, ss, 64.f);
+    const float2 mr = group_mean_rstd(c, lm.x, lm.y, 64.f, e.ln_eps);
+    const float mean = mr.x, rstd = mr.y;
     const float vmask = c.valid ? 1.f : 0.f;
-    float s2 = 0.f, ss2 = 0.f;
 #pragma unroll
     for (int q = 0; q < 4; ++q) {   // pass 2: LayerNorm + Mish + addend
         float* t = (q & 1) ? t1 : t0;
@@ -485,20 +464,14 @@ __device__ __forceinline__ void epi_lnact(const EpiCtx& c, const CUtensorMap* tm
 #pragma unroll
             for (int u = 0; u < 4; ++u)
                 *reinterpret_cast<float4*>(dst + (size_t)u * 512) = make_float4(w[4 * u], w[4 * u + 1], w[4 * u + 2], w[4 * u + 3]);
-#pragma unroll
-            for (int i = 0; i < 16; ++i) {
-                s2 += w[i];
-                ss2 = fmaf(w[i], w[i], ss2);
-            }
         }
     }
     float a = 1.f, bsh = 0.f;
     if (kRes) {
-        const float2 t2 = group_exchange(c, make_float2(s2, ss2));
-        const float mean2 = t2.x * (1.f / 256.f);
-        const float rstd2 = rsqrtf(fmaxf(t2.y * (1.f / 256.f) - mean2 * mean2, 0.f) + e.ln_eps);
-        a = c.valid ? rstd2 : 0.f;
-        bsh = c.valid ? -mean2 * rstd2 : 0.f;
+        const float2 lm2 = local_mean_m2<64>(v);
+        const float2 mr2 = group_mean_rstd(c, lm2.x, lm2.y, 64.f, e.ln_eps);
+        a = c.valid ? mr2.y : 0.f;
+        bsh = c.valid ? -mr2.x * mr2.y : 0.f;
     }
 #pragma unroll
     for (int hlf = 0; hlf < 2; ++hlf) {
@@ -703,27 +676,31 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
                 continue;
             } else {
             float mean1 = 0.f, rstd1 = 1.f;
-            if (e.ln1_g != nullptr) {  // LayerNorm over the whole row (N == BN): statistics of acc + bias
-                float s = 0.f, ss = 0.f;
+            // (LayerNorm in this general mode needs BN % 64 == 0 so that the four warps of a group own equal column counts)
+            if (e.ln1_g != nullptr) {  // LayerNorm over the whole row (N == BN): statistics of acc + bias, shifted sums
+                float s = 0.f, ss = 0.f, K = 0.f;
                 for (int cc = cbeg; cc < cend; ++cc) {
                     float v[16];
                     tmem_ld16(c.taddr + (uint32_t)(cc * 16), v);
                     tmem_ld_wait();
+                    if (cc == cbeg) K = v[0] + (e.bias ? __ldg(e.bias + c.n0 + cc * 16) : 0.f);
 #pragma unroll
                     for (int i = 0; i < 16; i += 4) {
                         float4 b = make_float4(0.f, 0.f, 0.f, 0.f);
                         if (e.bias) b = ldg4(e.bias + c.n0 + cc * 16 + i);
-                        const float x0 = v[i] + b.x, x1 = v[i + 1] + b.y, x2 = v[i + 2] + b.z, x3 = v[i + 3] + b.w;
+                        const float x0 = v[i] + b.x - K, x1 = v[i + 1] + b.y - K, x2 = v[i + 2] + b.z - K, x3 = v[i + 3] + b.w - K;
                         s += (x0 + x1) + (x2 + x3);
                         ss += (x0 * x0 + x1 * x1) + (x2 * x2 + x3 * x3);
                     }
                 }
-                const float2 t = group_exchange(c, make_float2(s, ss));
-                mean1 = t.x / (float)p.BN;
-                rstd1 = rsqrtf(fmaxf(t.y / (float)p.BN - mean1 * mean1, 0.f) + e.ln_eps);
+                const float np = (float)((cend - cbeg) * 16);
+                const float2 lm = shifted_mean_m2(K, s, ss, np);
+                const float2 mr = group_mean_rstd(c, lm.x, lm.y, np, e.ln_eps);
+                mean1 = mr.x;
+                rstd1 = mr.y;
             }
-            float s2 = 0.f, ss2 = 0.f;
-            epi_main<2>(c, cbeg, cend, mean1, rstd1, s2, ss2);
+            float s2 = 0.f, ss2 = 0.f, k2 = 0.f;
+            epi_main<2>(c, cbeg, cend, mean1, rstd1, s2, ss2, k2);
 
             // all TMEM reads of this tile are done: hand the accumulator back before the (TMEM-free) LN2 pass
             tc_fence_before();
@@ -733,9 +710,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
             if (acc == 0) accphase ^= 1;
 
             if (e.ln2_g != nullptr || e.ln2_plain) {  // second LayerNorm on the fp32 value just stored -> bf16 operand of the next GEMM
-                const float2 t = group_exchange(c, make_float2(s2, ss2));
-                const float mean2 = t.x / (float)p.BN;
-                const float rstd2 = rsqrtf(fmaxf(t.y / (float)p.BN - mean2 * mean2, 0.f) + e.ln_eps);
+                const float np2 = (float)((cend - cbeg) * 16);
+                const float2 lm2 = shifted_mean_m2(k2, s2, ss2, np2);
+                const float2 mr2 = group_mean_rstd(c, lm2.x, lm2.y, np2, e.ln_eps);
+                const float mean2 = mr2.x, rstd2 = mr2.y;
                 for (int cc = cbeg; cc < cend; cc += 2) {
                     const int nb = c.n0 + cc * 16;
                     const int nlim = min(p.N, nb + min(2, cend - cc) * 16);
@@ -828,29 +806,32 @@ bool encode_2d_ex(CUtensorMap* m, const void* ptr, uint64_t cols, uint64_t rows,
     return true;
 }
 
+cudaError_t gemm_tc_init_device() {
+    static std::atomic<uint64_t> done{0};
+    static std::mutex mu;
+    return once_per_device(done, mu, [] {
+        if (!get_encode_fn()) return cudaErrorNotSupported;
+        cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(gemm_tc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(gemm_tc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(gemm_tc_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes + 1024);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(gemm_tc_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes + 1024);
+        return e;
+    });
+}
+
 cudaError_t gemm_tc_launch(const GemmProblem& g, int num_sms, cudaStream_t stream) {
     if (g.M <= 0 || g.N <= 0 || g.BN < 16 || g.BN > 256 || (g.BN % 16) != 0 || g.num_segs < 1 ||
         g.num_segs > kGemmMaxSegs)
         return cudaErrorInvalidValue;
     if (g.epi.ln1_g && g.BN != g.N) return cudaErrorInvalidValue;
     if ((g.epi.ln2_g || g.epi.ln2_plain) && (g.BN != g.N || g.epi.accum_f32)) return cudaErrorInvalidValue;
+    if ((g.epi.ln1_g || g.epi.ln2_g || g.epi.ln2_plain) && (g.BN % 64) != 0) return cudaErrorInvalidValue;  // equal column counts per epilogue warp
     if (g.epi.f32_tiled && (g.N != 256 || g.BN != 256 || g.epi.accum_f32 || (g.epi.resid && g.epi.ldr != 256) ||
                             (g.epi.out_f32 && g.epi.ldf != 256)))
         return cudaErrorInvalidValue;
 
-    static std::once_flag attr_once;
-    static cudaError_t attr_err = cudaSuccess;
-    std::call_once(attr_once, [] {
-        attr_err = cudaFuncSetAttribute(gemm_tc_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
-        if (attr_err == cudaSuccess)
-            attr_err = cudaFuncSetAttribute(gemm_tc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
-        if (attr_err == cudaSuccess)
-            attr_err = cudaFuncSetAttribute(gemm_tc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
-        if (attr_err == cudaSuccess)
-            attr_err = cudaFuncSetAttribute(gemm_tc_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes + 1024);
-        if (attr_err == cudaSuccess)
-            attr_err = cudaFuncSetAttribute(gemm_tc_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes + 1024);
-    });
+    const cudaError_t attr_err = gemm_tc_init_device();
     if (attr_err != cudaSuccess) return attr_err;
 
     KParams kp;

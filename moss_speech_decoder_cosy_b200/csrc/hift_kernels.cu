@@ -6,6 +6,7 @@
 // All sequences of a group are packed on one row axis (see HiftLayout in kernels.h); frame-rate rows scale by
 // 8 / 40 / 120 through the three upsampling stages, so a row index maps between stages by a multiplication.
 #include "kernels.h"
+#include "gemm.h"
 #include "ptx.cuh"
 
 namespace mossdec {
@@ -331,20 +332,22 @@ __global__ void fade_kernel(float* __restrict__ speech, const float* __restrict_
 
 }  // namespace
 
-void hift_init_constants() {
-    static bool done = false;
-    if (done) return;
-    float hann[16], cs[16], sn[16];
-    for (int n = 0; n < 16; ++n) {
-        const double a = 2.0 * 3.14159265358979323846 * n / 16.0;
-        hann[n] = (float)(0.5 - 0.5 * cos(a));  // scipy.signal.get_window("hann", 16, fftbins=True) as float32
-        cs[n] = (float)cos(a);
-        sn[n] = (float)sin(a);
-    }
-    cudaMemcpyToSymbol(c_hann16, hann, sizeof hann);
-    cudaMemcpyToSymbol(c_cos16, cs, sizeof cs);
-    cudaMemcpyToSymbol(c_sin16, sn, sizeof sn);
-    done = true;
+cudaError_t hift_init_device() {
+    static std::atomic<uint64_t> done{0};
+    static std::mutex mu;
+    return once_per_device(done, mu, [] {
+        float hann[16], cs[16], sn[16];
+        for (int n = 0; n < 16; ++n) {
+            const double a = 2.0 * 3.14159265358979323846 * n / 16.0;
+            hann[n] = (float)(0.5 - 0.5 * cos(a));  // scipy.signal.get_window("hann", 16, fftbins=True) as float32
+            cs[n] = (float)cos(a);
+            sn[n] = (float)sin(a);
+        }
+        cudaError_t e = cudaMemcpyToSymbol(c_hann16, hann, sizeof hann);
+        if (e == cudaSuccess) e = cudaMemcpyToSymbol(c_cos16, cs, sizeof cs);
+        if (e == cudaSuccess) e = cudaMemcpyToSymbol(c_sin16, sn, sizeof sn);
+        return e;
+    });
 }
 
 void launch_hift_row_seq(const HiftLayout& L, int scale, int extra, int rows, int32_t* out, cudaStream_t st) {

@@ -13,6 +13,7 @@ struct FlowLayout {
     int32_t rows_half;        // rows of one CFG half (multiple of 128)
     int32_t noise_cstride;    // channel stride of the noise bank
     int32_t time_major;       // ragged tensors are [T_b, C] (1) instead of the reference's [C, T_b] (0)
+    int32_t dense_T;          // > 0: tensors are dense [nseq, C, dense_T] (channel stride dense_T); 0: ragged
     const int32_t* row_seq;   // [2 * rows_half] sequence id or -1
     const int32_t* seq_start; // [nseq] first row
     const int32_t* seq_len;   // [nseq] frames
@@ -29,20 +30,15 @@ void launch_flow_prepare(const FlowLayout& L, const float* mu, const float* spks
 void launch_euler_cfg(const FlowLayout& L, const float* d, float dt, float cfg_rate, float* xstate,
                       __nv_bfloat16* xin, cudaStream_t st);
 void launch_rows_to_bct(const FlowLayout& L, const float* rows, int row_offset, float* out, cudaStream_t st);
+void launch_mask_lens(const float* mask, int B, int T, int32_t* lens, int32_t* bad, cudaStream_t st);
 void launch_est_pack(const FlowLayout& L, int nrows, const float* x, const float* mu, const float* spks,
                      const float* cond, const float* mask, __nv_bfloat16* xin, cudaStream_t st);
 
 // Self-attention over packed rows.  qkv: bf16 [M, 3*H*64] = [q | k | v], q pre-scaled by 1/sqrt(64).
 // Key j of sequence s is visible to query i iff j < len_s and (chunk == 0 or j < (i / chunk + 1) * chunk)
 // (cosyvoice/utils/mask.py:127-158 + key padding).  out: bf16 [M, H*64].
-void launch_attention(const __nv_bfloat16* qkv, __nv_bfloat16* out, const int32_t* seq_start, const int32_t* seq_len,
-                      int nseq, int max_len, int heads, int chunk, cudaStream_t st);
-
-// tcgen05 / TMEM version (attention_tc.cu); qkv has `rows` rows of 3*H*64 bf16.
-cudaError_t launch_attention_tc(const __nv_bfloat16* qkv, int64_t rows, __nv_bfloat16* out, const int32_t* seq_start,
-                                const int32_t* seq_len, int nseq, int max_len, int heads, int chunk, cudaStream_t st);
-
-// warp-specialised variant (attention_ws.cu): dedicated TMA / MMA issue warp, 32-key tiles, double-buffered scores in TMEM
+// warp-specialised tcgen05 / TMEM kernel (attention_ws.cu): dedicated TMA / MMA issue warp, 32-key tiles, double-buffered
+// scores in TMEM; qkv has `rows` rows of 3*H*64 bf16.
 cudaError_t launch_attention_ws(const __nv_bfloat16* qkv, int64_t rows, __nv_bfloat16* out, const int32_t* seq_start,
                                 const int32_t* seq_len, int nseq, int max_len, int heads, int chunk, cudaStream_t st);
 
@@ -60,7 +56,6 @@ struct HiftLayout {
     const int64_t* wav_off;    // [nseq] sample offset inside the ragged [480 T_b] output
 };
 
-void hift_init_constants();
 void launch_hift_row_seq(const HiftLayout& L, int scale, int extra, int rows, int32_t* out, cudaStream_t st);
 void launch_hift_pack_mel(const HiftLayout& L, const int32_t* row_seq, const float* mel, __nv_bfloat16* out,
                           __nv_bfloat16* out_lo, cudaStream_t st);

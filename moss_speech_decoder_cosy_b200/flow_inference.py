@@ -24,18 +24,53 @@ TOKEN_MEL_RATIO = 4
 PRE_LOOKAHEAD = 3
 
 
+_DEFAULTS = {"static_chunk_size": 25, "inference_cfg_rate": 0.7, "sample_rate": 24000, "n_timesteps": 10,
+             "estimator_chunk_frames": None}
+
+
 def _read_config(config_path):
     """The reference instantiates its models from a hyperpyyaml object graph (flow_inference.py:53-55).  Only scalar
-    hyper-parameters matter here; they are picked out of the yaml text when present, else the pinned defaults of
-    SURVEY.md 8(a0) apply."""
-    cfg = {"static_chunk_size": 25, "inference_cfg_rate": 0.7, "sample_rate": 24000, "n_timesteps": 10}
-    if config_path and os.path.exists(config_path):
-        text = open(config_path).read()
-        for key, cast in (("static_chunk_size", int), ("inference_cfg_rate", float), ("sample_rate", int)):
-            m = re.search(rf"^\s*{key}\s*:\s*([0-9.eE+-]+)\s*$", text, re.M)
-            if m:
-                cfg[key] = cast(float(m.group(1)))
+    hyper-parameters matter here; they are read from the yaml text -- plain scalars and hyperpyyaml `!ref <name>`
+    aliases of plain scalars.  A key that is present but cannot be resolved raises (no silent default); absent keys take
+    the pinned defaults of SURVEY.md 8(a0).  `estimator_chunk_frames` (mel frames of the estimator's block-causal
+    attention, decoder.py:439-440) defaults to static_chunk_size * token_mel_ratio, as upstream CosyVoice2 configures it."""
+    cfg = dict(_DEFAULTS)
+    if config_path is None:
+        return cfg
+    if not os.path.exists(config_path):
+        raise FileNotFoundError(f"config_path {config_path!r} does not exist")   # the reference's open() raises
+    text = open(config_path).read()
+    scalars = {m.group(1): m.group(2) for m in re.finditer(r"^\s*([A-Za-z_][\w]*)\s*:\s*([-+0-9.eE]+)\s*(?:#.*)?$", text, re.M)}
+
+    def resolve(key, cast):
+        m = re.search(rf"^\s*{key}\s*:\s*(.+?)\s*(?:#.*)?$", text, re.M)
+        if not m:
+            return None
+        val = m.group(1).strip()
+        ref = re.fullmatch(r"!ref\s*<\s*([\w]+)\s*>", val)
+        if ref:
+            if ref.group(1) not in scalars:
+                raise ValueError(f"{config_path}: `{key}: {val}` refers to `{ref.group(1)}`, which is not a plain scalar")
+            val = scalars[ref.group(1)]
+        try:
+            return cast(float(val))
+        except ValueError:
+            raise ValueError(f"{config_path}: cannot parse `{key}: {val}` as a number") from None
+
+    for key, cast in (("static_chunk_size", int), ("inference_cfg_rate", float), ("sample_rate", int),
+                      ("n_timesteps", int), ("estimator_chunk_frames", int)):
+        v = resolve(key, cast)
+        if v is not None:
+            cfg[key] = v
     return cfg
+
+
+def _load_checkpoint(path, what):
+    """torch.load of a reference-format checkpoint; a path that is given but missing raises like the reference's
+    torch.load (flow_inference.py:59-61) instead of silently decoding with random weights."""
+    if not os.path.exists(path):
+        raise FileNotFoundError(f"{what} checkpoint {path!r} does not exist (pass None for the synthetic random-init weights)")
+    return torch.load(path, map_location="cpu")
 
 
 class _FlowFacade:
@@ -89,13 +124,14 @@ class AudioDecoder(torch.nn.Module):
         self.device = torch.device(device if device != "cuda" else f"cuda:{torch.cuda.current_device()}")
         torch.cuda.set_device(self.device)
         self.scratch_configs = _read_config(config_path)
-        # checkpoints in the reference's state_dict format (flow_inference.py:59-61); random-init when absent
+        # checkpoints in the reference's state_dict format (flow_inference.py:59-61).  Random-init weights of the reference
+        # architecture only when NO path is given (tests / benchmarks: checkpoints are not available offline).
         if flow_state_dict is None:
-            flow_state_dict = (torch.load(flow_ckpt_path, map_location="cpu") if flow_ckpt_path and
-                               os.path.exists(flow_ckpt_path) else synth.synth_flow_state_dict(seed))
+            flow_state_dict = (_load_checkpoint(flow_ckpt_path, "flow") if flow_ckpt_path is not None
+                               else synth.synth_flow_state_dict(seed))
         if hift_state_dict is None:
-            hift_state_dict = (torch.load(hift_ckpt_path, map_location="cpu") if hift_ckpt_path and
-                               os.path.exists(hift_ckpt_path) else synth.synth_hift_state_dict(seed))
+            hift_state_dict = (_load_checkpoint(hift_ckpt_path, "hift") if hift_ckpt_path is not None
+                               else synth.synth_hift_state_dict(seed))
         self.engine = lib.Engine()
         tensors = weights.pack_estimator(flow_state_dict)
         tensors["flow.rand_noise"] = synth.synth_noise_bank()[0].contiguous()   # flow_matching.py:202-203
@@ -108,7 +144,9 @@ class AudioDecoder(torch.nn.Module):
         self.sample_rate = self.scratch_configs["sample_rate"]
         self.feat_extractor = None      # prompt mel extractor (matcha mel_spectrogram) -- SURVEY 8(f) N2
         self.campplus_session = None    # x-vector ONNX session stays with the caller (CPU, out of scope)
-        self.static_chunk_size = int(self.scratch_configs["static_chunk_size"])   # tokens
+        self.static_chunk_size = int(self.scratch_configs["static_chunk_size"])   # tokens (encoder chunk masks)
+        ecf = self.scratch_configs["estimator_chunk_frames"]
+        self.estimator_chunk_frames = int(ecf) if ecf is not None else self.static_chunk_size * TOKEN_MEL_RATIO
         self.n_timesteps = int(self.scratch_configs["n_timesteps"])
         self.inference_cfg_rate = float(self.scratch_configs["inference_cfg_rate"])
 
@@ -196,7 +234,7 @@ class AudioDecoder(torch.nn.Module):
         spks = frontend.speaker_projection(self.enc_weights, embeddings)
         mel = self.engine.flow_solve(T, mu.reshape(-1), spks, cond.reshape(-1), n_steps=self.n_timesteps,
                                      cfg_rate=self.inference_cfg_rate,
-                                     chunk=self.static_chunk_size * TOKEN_MEL_RATIO if streaming else 0,
+                                     chunk=self.estimator_chunk_frames if streaming else 0,
                                      time_major=True).view(-1, 80)
         return {"mel": mel, "frames": T, "prompt_frames": F_}
 

@@ -69,6 +69,14 @@ def load_library():
     lib.mossdec_profile_read.restype = i32
     lib.mossdec_set_hift_group_frames.argtypes = [vp, i64]
     lib.mossdec_set_hift_group_frames.restype = None
+    lib.mossdec_reserve.argtypes = [vp, i64, i32, i64]
+    lib.mossdec_reserve.restype = i32
+    lib.mossdec_set_graph_mode.argtypes = [vp, i32]
+    lib.mossdec_set_graph_mode.restype = None
+    lib.mossdec_graph_replays.argtypes = [vp]
+    lib.mossdec_graph_replays.restype = i64
+    lib.mossdec_device.argtypes = [vp]
+    lib.mossdec_device.restype = i32
     lib.mossdec_launch_count.argtypes = [vp]
     lib.mossdec_launch_count.restype = i64
     lib.mossdec_reset_launch_count.argtypes = [vp]
@@ -82,7 +90,8 @@ EXPORTED_SYMBOLS = [
     "mossdec_finalize", "mossdec_estimator", "mossdec_flow_solve", "mossdec_hift", "mossdec_fade_in_out",
     "mossdec_launch_count", "mossdec_reset_launch_count", "mossdec_debug_read", "mossdec_profile",
     "mossdec_profile_read", "mossdec_set_hift_group_frames", "mossdec_cv1_resnet_block", "mossdec_cv1_downsample",
-    "mossdec_cv1_upsample", "mossdec_cv1_block1d",
+    "mossdec_cv1_upsample", "mossdec_cv1_block1d", "mossdec_reserve", "mossdec_set_graph_mode", "mossdec_graph_replays",
+    "mossdec_device",
 ]
 
 
@@ -144,14 +153,15 @@ class Engine:
     def _stream():
         return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
 
-    def estimator(self, x, mask, mu, t, spks, cond, chunk=0):
+    def estimator(self, x, mask, mu, t, spks, cond, chunk=0, out_alias_x=False):
         """Same contract as ConditionalCFM.forward_estimator (flow_matching.py:129): fp32 CUDA tensors [B2,80,T]."""
         B2, _, T = x.shape
         x, mu = x.float().contiguous(), mu.float().contiguous()
         t = t.float().contiguous()
         spks = None if spks is None else spks.float().contiguous()
         cond = None if cond is None else cond.float().contiguous()
-        out = torch.empty_like(x)
+        mask = None if mask is None else mask.float().contiguous()
+        out = x if out_alias_x else torch.empty_like(x)
         self._check(self.lib.mossdec_estimator(self.h, B2, T, _ptr(x), _ptr(mask), _ptr(mu), _ptr(t), _ptr(spks),
                                                _ptr(cond), _ptr(out), int(chunk), self._stream()), "estimator")
         return out
@@ -250,6 +260,20 @@ class Engine:
         self._check(self.lib.mossdec_profile_read(self.h, out), "profile_read")
         return {"gemm_ms": out[0], "gemm_launches": int(out[1]), "gemm_hw_flops": out[2], "attn_ms": out[3],
                 "attn_launches": int(out[4]), "ffn_ms": out[6], "ffn_launches": int(out[7]), "ffn_hw_flops": out[8]}
+
+    def reserve(self, flow_rows=0, flow_seqs=1, hift_frames=0):
+        """Pre-size the workspaces (mossdec_reserve) so the first decode of that size does not allocate."""
+        self._check(self.lib.mossdec_reserve(self.h, int(flow_rows), int(flow_seqs), int(hift_frames)), "reserve")
+
+    def set_graph_mode(self, mode):
+        self.lib.mossdec_set_graph_mode(self.h, int(mode))
+
+    def graph_replays(self):
+        return int(self.lib.mossdec_graph_replays(self.h))
+
+    @property
+    def device_index(self):
+        return int(self.lib.mossdec_device(self.h))
 
     def set_hift_group_frames(self, frames):
         self.lib.mossdec_set_hift_group_frames(self.h, int(frames))

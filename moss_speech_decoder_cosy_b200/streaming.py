@@ -58,9 +58,12 @@ def _hift_chunks(dec, mels, caches, finalize, nsf_noise=None):
         off += n
         if caches[b] is not None:
             prev = caches[b]['speech'].reshape(-1)
-            k = min(int(prev.numel()), S, n)
-            # speech[:k] = speech[:k] * w[:k] + prev[-k:] * w[k:]   (window of 2 * source_cache_len)
-            dec.engine.fade_in_out(speech, prev[-k:].contiguous(), dec._speech_window_dev)
+            if int(prev.numel()) != S or n < S:
+                # the reference's fade_in_out (flow_inference.py:35-43) fails with a shape error here (a previous chunk
+                # shorter than mel_cache_len frames); a shorter fade would need differently aligned window halves
+                raise ValueError(f"cross-fade needs {S} cached and {S} new samples, got {int(prev.numel())} / {n}")
+            # speech[:S] = speech[:S] * w[:S] + prev * w[S:]   (Hamming window of 2 * source_cache_len)
+            dec.engine.fade_in_out(speech, prev.contiguous(), dec._speech_window_dev)
         if not finalize:
             new_caches.append({'mel': full[b][-dec.mel_cache_len:].t().unsqueeze(0).contiguous(),
                                'source': source[-S:].clone().view(1, 1, -1), 'speech': speech[-S:].clone().view(1, -1)})
