@@ -84,3 +84,43 @@ def test_cv1_blocks_restatement(tag):
     for got, key in ((h, "res_in"), (h2, "res_mid"), (d, "down"), (u, "up"), (fb, "final")):
         assert got.shape == t[key].shape
         assert _rel(got, t[key]) < 1e-5, key
+
+
+def _check_fp(z, *tensors):
+    from oracle import cases
+    if not np.allclose(cases.fingerprint(*tensors), z["fp"], rtol=1e-6, atol=1e-6):
+        pytest.skip("torch CPU generator differs from the build that produced the fixture")
+
+
+@pytest.mark.parametrize("T", [150, 296])
+@pytest.mark.parametrize("mode", ["full", "chunk"])
+def test_estimator_restatement_chunk20(sds, T, mode):
+    """static_chunk_size = 5 tokens = 20 mel frames (every shipped MOSS script streams with block 5): the visibility edge
+    of the block-causal mask (decoder.py:439-440, mask.py:127-158) falls inside key and query tiles."""
+    from oracle import cases
+    z = np.load(os.path.join(GOLDEN, f"estimator_c20_T{T}.npz"))
+    c = cases.estimator_inputs(T, int(z["seed"]))
+    _check_fp(z, c["x"], c["cond"], c["spks"])
+    with torch.inference_mode():
+        out = port.estimator(sds[0], c["x"], c["mask"], c["mu"], c["t"], c["spks"], c["cond"],
+                             chunk=int(z["chunk"]) if mode == "chunk" else 0)
+    ref = torch.from_numpy(z["out_full" if mode == "full" else "out_chunk"])
+    torch.testing.assert_close(out, ref, rtol=1e-2, atol=1e-4)
+    assert _rel(out, ref) < 1e-5
+
+
+@pytest.mark.parametrize("mode", ["full", "chunk"])
+def test_estimator_restatement_padding_mask(sds, mode):
+    """Ragged key-padding mask (lens 150 / 97) through the reference's mask path (decoder.py:433-494)."""
+    from oracle import cases
+    z = np.load(os.path.join(GOLDEN, "estimator_c20_mask.npz"))
+    c = cases.estimator_inputs(150, int(z["seed"]), lens=[int(v) for v in z["lens"]])
+    _check_fp(z, c["x"], c["cond"], c["spks"])
+    with torch.inference_mode():
+        out = port.estimator(sds[0], c["x"], c["mask"], c["mu"], c["t"], c["spks"], c["cond"],
+                             chunk=int(z["chunk"]) if mode == "chunk" else 0)
+    ref = torch.from_numpy(z["out_full" if mode == "full" else "out_chunk"])
+    # the reference leaves garbage-free zeros on masked frames (output * mask)
+    assert float(ref[1, :, 97:].abs().max()) == 0.0
+    torch.testing.assert_close(out, ref, rtol=1e-2, atol=1e-4)
+    assert _rel(out, ref) < 1e-5
