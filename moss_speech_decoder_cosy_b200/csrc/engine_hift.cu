@@ -32,7 +32,7 @@ constexpr int kSrcResK[3] = {7, 7, 11};
 constexpr int kDil[3] = {1, 3, 5};
 
 constexpr size_t kHiftSlack = 256;  // rows of slack after every matrix (TMA boxes / shifted windows stay inside)
-constexpr int kHiftBufs = 22;
+constexpr int kHiftBufs = 20;
 
 // Offsets of the vocoder workspace buffers for a group of `rows_f` frame rows; returns the total size.
 size_t hift_carve(int64_t rows_f, int base, size_t* offs) {
@@ -46,8 +46,8 @@ size_t hift_carve(int64_t rows_f, int base, size_t* offs) {
     const size_t Fr = (size_t)rows_f + slack;
     const size_t M2 = (size_t)rows_f * 120;
     const size_t S = (M2 + slack) * 64;  // elements of one stage matrix (largest: stage 2; M0*256 and M1*128 are smaller)
-    take(Fr * 128 * 2); take(Fr * 128 * 2);                                      // melb, melb_lo
-    take(Fr * base * 2); take(Fr * base * 2); take(Fr * base * 2); take(Fr * base * 2);   // fa, fb, fa_lo, fb_lo
+    take(Fr * 128 * 2); take(Fr * 80 * 4);                                       // melb (bf16, 128 wide), mel32 (fp32 rows)
+    take(Fr * base * 4); take(Fr * base * 4);                                    // fa, fb: fp32 activations of the f0 predictor
     take(Fr * 4 * 4); take(Fr * 16 * 4); take(((size_t)rows_f * 480 + 1024) * 4);     // f0, p480, src
     take((M2 + 2 * slack) * kStftLd * 2); take((M2 + slack) * 32 * 4);            // stft, post
     for (int i = 0; i < 5; ++i) take(S * 4);                                      // u, si, x, xr, xs
@@ -70,8 +70,8 @@ struct HiftRunner {
     int64_t M[3] = {0, 0, 0};
     int32_t *rs_f = nullptr, *rs[3] = {nullptr, nullptr, nullptr};
     // frame level
-    __nv_bfloat16 *melb = nullptr, *melb_lo = nullptr, *fa = nullptr, *fb = nullptr, *fa_lo = nullptr, *fb_lo = nullptr,
-                  *stft = nullptr;
+    __nv_bfloat16 *melb = nullptr, *stft = nullptr;
+    float *mel32 = nullptr, *fa = nullptr, *fb = nullptr;   // fp32 rows of the f0 predictor (f0_fp32.cu)
     float *f0 = nullptr, *p480 = nullptr, *src = nullptr, *post = nullptr;
     // stage buffers (sized for the largest stage)
     float *u = nullptr, *si = nullptr, *x = nullptr, *xr = nullptr, *xs = nullptr;
@@ -151,7 +151,7 @@ struct HiftRunner {
 int Engine::finalize_hift() {
     missing_.clear();
     for (int i = 0; i < 5; ++i) {
-        find(N("hift.f0.c%d.w", i));
+        find(N("hift.f0.c%d.wt", i));
         find(N("hift.f0.c%d.b", i));
     }
     const char* once[] = {"hift.f0.cls.w", "hift.f0.cls.b", "hift.src.w", "hift.src.b", "hift.pre.w", "hift.pre.b",
@@ -284,17 +284,15 @@ int Engine::hift_group(int b0, int b1, const int32_t* lens, int64_t mel_off0, in
     const size_t slack = kHiftSlack;
     size_t offs[kHiftBufs];
     hift_carve(rows_f, base, offs);
-    const size_t o_melb = offs[0], o_melb_lo = offs[1], o_fa = offs[2], o_fb = offs[3], o_fa_lo = offs[4], o_fb_lo = offs[5],
-                 o_f0 = offs[6], o_p480 = offs[7], o_src = offs[8], o_stft = offs[9], o_post = offs[10], o_u = offs[11],
-                 o_si = offs[12], o_x = offs[13], o_xr = offs[14], o_xs = offs[15], o_a0 = offs[16], o_a1 = offs[17],
-                 o_a2 = offs[18], o_h = offs[19], o_lr = offs[20], o_sb = offs[21];
+    const size_t o_melb = offs[0], o_mel32 = offs[1], o_fa = offs[2], o_fb = offs[3],
+                 o_f0 = offs[4], o_p480 = offs[5], o_src = offs[6], o_stft = offs[7], o_post = offs[8], o_u = offs[9],
+                 o_si = offs[10], o_x = offs[11], o_xr = offs[12], o_xs = offs[13], o_a0 = offs[14], o_a1 = offs[15],
+                 o_a2 = offs[16], o_h = offs[17], o_lr = offs[18], o_sb = offs[19];
     uint8_t* wb = ws_hift_.as<uint8_t>();
     R.melb = (__nv_bfloat16*)(wb + o_melb);
-    R.melb_lo = (__nv_bfloat16*)(wb + o_melb_lo);
-    R.fa = (__nv_bfloat16*)(wb + o_fa);
-    R.fb = (__nv_bfloat16*)(wb + o_fb);
-    R.fa_lo = (__nv_bfloat16*)(wb + o_fa_lo);
-    R.fb_lo = (__nv_bfloat16*)(wb + o_fb_lo);
+    R.mel32 = (float*)(wb + o_mel32);
+    R.fa = (float*)(wb + o_fa);
+    R.fb = (float*)(wb + o_fb);
     R.f0 = (float*)(wb + o_f0);
     R.p480 = (float*)(wb + o_p480);
     R.src = (float*)(wb + o_src);
@@ -306,46 +304,25 @@ int Engine::hift_group(int b0, int b1, const int32_t* lens, int64_t mel_off0, in
     R.h = (__nv_bfloat16*)(wb + o_h); R.lr = (__nv_bfloat16*)(wb + o_lr); R.sb = (__nv_bfloat16*)(wb + o_sb);
 
     // ---------------------------------------------------------------- f0 predictor (f0_predictor.py:55-60)
-    launch_hift_pack_mel(L, R.rs_f, mel, R.melb, R.melb_lo, st);
+    // fp32 on the CUDA cores with round-to-nearest FMAs (f0_fp32.cu explains why the tensor cores are not used here)
+    launch_hift_pack_mel(L, R.rs_f, mel, R.melb, R.mel32, st);
     ++launches_;
-    {   // split-bf16: segments [a_hi taps | a_hi taps | a_lo taps] against weights [w_hi | w_lo | w_hi]
-        auto split_taps = [&](GemmProblem& p, const __nv_bfloat16* hi, const __nv_bfloat16* lo, int cin_pad, int k) {
-            p.a[0].ptr = hi; p.a[0].rows = rows_f; p.a[0].cols = cin_pad; p.a[0].ld = cin_pad;
-            p.a[1].ptr = lo; p.a[1].rows = rows_f; p.a[1].cols = cin_pad; p.a[1].ld = cin_pad;
-            p.num_segs = 3 * k;
-            for (int part = 0; part < 3; ++part)
-                for (int j = 0; j < k; ++j)
-                    p.segs[part * k + j] = {part == 2 ? 1 : 0, j - (k - 1) / 2, 0, cin_pad / kGemmBK};
-            p.M = rows_f;
-        };
-        const __nv_bfloat16 *in_hi = R.melb, *in_lo = R.melb_lo;
-        int cin = 128;
-        __nv_bfloat16* outs[2] = {R.fa, R.fb};
-        __nv_bfloat16* outs_lo[2] = {R.fa_lo, R.fb_lo};
+    {
+        const float* in = R.mel32;
+        int cin = cfg_.n_feats;
+        float* outs[2] = {R.fa, R.fb};
         for (int i = 0; i < 5; ++i) {
-            GemmProblem p;
-            split_taps(p, in_hi, in_lo, cin, 3);
-            p.w = W<__nv_bfloat16>(N("hift.f0.c%d.w", i));
-            p.N = base; p.BN = 256;
-            p.epi.bias = W<float>(N("hift.f0.c%d.b", i));
-            p.epi.act1 = ACT_ELU;
-            p.epi.row_seq = R.rs_f;
-            p.epi.out_bf16 = outs[i & 1]; p.epi.ldo = base;
-            p.epi.out_bf16_lo = outs_lo[i & 1];
-            if (gemm(p, st)) return -1;
-            in_hi = outs[i & 1];
-            in_lo = outs_lo[i & 1];
+            cudaError_t ce = launch_conv3_elu_f32(in, rows_f, cin, W<float>(N("hift.f0.c%d.wt", i)), base,
+                                                  W<float>(N("hift.f0.c%d.b", i)), R.rs_f, outs[i & 1], st);
+            if (ce != cudaSuccess) return fail(std::string("launch_conv3_elu_f32: ") + cudaGetErrorString(ce));
+            ++launches_;
+            in = outs[i & 1];
             cin = base;
         }
-        GemmProblem p;  // classifier Linear(512 -> 1) + abs
-        split_taps(p, in_hi, in_lo, base, 1);
-        p.w = W<__nv_bfloat16>("hift.f0.cls.w");
-        p.N = 1; p.BN = 16;
-        p.epi.bias = W<float>("hift.f0.cls.b");
-        p.epi.act1 = ACT_ABS;
-        p.epi.row_seq = R.rs_f;
-        p.epi.out_f32 = R.f0; p.epi.ldf = 4;
-        if (gemm(p, st)) return -1;
+        cudaError_t ce = launch_f0_classifier(in, rows_f, base, W<float>("hift.f0.cls.w"), W<float>("hift.f0.cls.b"), R.rs_f,
+                                              R.f0, 4, st);
+        if (ce != cudaSuccess) return fail(std::string("launch_f0_classifier: ") + cudaGetErrorString(ce));
+        ++launches_;
     }
     // ---------------------------------------------------------------- NSF source + STFT (generator.py:574-580, 521-522)
     float* src = source_out ? source_out : R.src - wav_off0;  // ragged [480 T_b] signal addressed by wav_off

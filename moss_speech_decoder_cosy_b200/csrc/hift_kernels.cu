@@ -46,7 +46,7 @@ __global__ void hift_row_seq_kernel(HiftLayout L, int scale, int extra, int rows
 // ragged fp32 mel [80, T_b] blocks -> bf16 rows [rows_f, 128] (columns >= 80 and guard rows are zero); `out_lo`
 // receives the bf16 remainder mel - bf16(mel) for the split-bf16 f0 predictor.
 __global__ void hift_pack_mel_kernel(HiftLayout L, const int32_t* __restrict__ row_seq, const float* __restrict__ mel,
-                                     __nv_bfloat16* __restrict__ out, __nv_bfloat16* __restrict__ out_lo) {
+                                     __nv_bfloat16* __restrict__ out, float* __restrict__ out32) {
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= L.rows_f * 128) return;
     const int row = idx >> 7, c = idx & 127;
@@ -56,9 +56,8 @@ __global__ void hift_pack_mel_kernel(HiftLayout L, const int32_t* __restrict__ r
         const int t = row - L.seq_start[s];
         v = mel[L.mel_off[s] + (L.time_major ? (int64_t)t * 80 + c : (int64_t)c * L.seq_len[s] + t)];
     }
-    const __nv_bfloat16 hi = __float2bfloat16(v);
-    out[idx] = hi;
-    out_lo[idx] = __float2bfloat16(v - __bfloat162float(hi));
+    out[idx] = __float2bfloat16(v);              // conv_pre operand (bf16, 128 wide)
+    if (c < 80) out32[(size_t)row * 80 + c] = v;   // f0 predictor input (fp32 rows)
 }
 
 // Frame-rate phase of every harmonic: rad = (f0 * h / sr) % 1 per frame (the x480 nearest upsampling followed by
@@ -354,9 +353,9 @@ void launch_hift_row_seq(const HiftLayout& L, int scale, int extra, int rows, in
     hift_row_seq_kernel<<<(rows + 255) / 256, 256, 0, st>>>(L, scale, extra, rows, out);
 }
 void launch_hift_pack_mel(const HiftLayout& L, const int32_t* row_seq, const float* mel, __nv_bfloat16* out,
-                          __nv_bfloat16* out_lo, cudaStream_t st) {
+                          float* out32, cudaStream_t st) {
     const int n = L.rows_f * 128;
-    hift_pack_mel_kernel<<<(n + 255) / 256, 256, 0, st>>>(L, row_seq, mel, out, out_lo);
+    hift_pack_mel_kernel<<<(n + 255) / 256, 256, 0, st>>>(L, row_seq, mel, out, out32);
 }
 void launch_hift_phase(const HiftLayout& L, const float* f0, int f0_ld, float sample_rate, float upsample, int n_harm,
                        float* p480, cudaStream_t st) {

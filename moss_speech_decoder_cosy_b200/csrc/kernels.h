@@ -58,7 +58,12 @@ struct HiftLayout {
 
 void launch_hift_row_seq(const HiftLayout& L, int scale, int extra, int rows, int32_t* out, cudaStream_t st);
 void launch_hift_pack_mel(const HiftLayout& L, const int32_t* row_seq, const float* mel, __nv_bfloat16* out,
-                          __nv_bfloat16* out_lo, cudaStream_t st);
+                          float* out32, cudaStream_t st);
+// fp32 f0 predictor (f0_fp32.cu): Conv1d(k3, pad 1) + ELU over packed rows, weights Wt [3 * Cin, N] (k = tap * Cin + c)
+cudaError_t launch_conv3_elu_f32(const float* in, int M, int Cin, const float* wt, int N, const float* bias,
+                                 const int32_t* row_seq, float* out, cudaStream_t st);
+cudaError_t launch_f0_classifier(const float* h, int M, int C, const float* w, const float* b, const int32_t* row_seq,
+                                 float* f0, int f0_ld, cudaStream_t st);
 void launch_hift_phase(const HiftLayout& L, const float* f0, int f0_ld, float sample_rate, float upsample, int n_harm,
                        float* p480, cudaStream_t st);
 void launch_hift_source(const HiftLayout& L, int max_len, const float* f0, int f0_ld, const float* p480,

@@ -152,13 +152,6 @@ def source_down_weight(w: torch.Tensor) -> torch.Tensor:
     return _pad_k(out.reshape(c, k * STFT_LD))
 
 
-def split_bf16_weight(w2d: torch.Tensor) -> torch.Tensor:
-    """fp32 [N, K] -> bf16 [N, 3K] = [w_hi | w_lo | w_hi], matched by A segments [a_hi | a_hi | a_lo]."""
-    hi = w2d.to(torch.bfloat16)
-    lo = (w2d - hi.float()).to(torch.bfloat16)
-    return torch.cat([hi, lo, hi], dim=1).contiguous()
-
-
 def _pack_resblock(out, sd, src, dst, n_layers=3):
     """ResBlock (generator.py:46-101): convs1[l] (dilated), convs2[l], Snake alphas."""
     for l in range(n_layers):
@@ -173,12 +166,14 @@ def _pack_resblock(out, sd, src, dst, n_layers=3):
 def pack_hift(sd):
     """HiFTGenerator + ConvRNNF0Predictor (hifigan/generator.py:392-502, f0_predictor.py:22-53)."""
     out = {}
-    # The f0 predictor runs in split-bf16 ("bf16x3": a*w ~= a_hi*w_hi + a_hi*w_lo + a_lo*w_hi, fp32 accumulate): the NSF
-    # phase integrates f0 over the whole utterance (generator.py:280), so f0 needs ~1e-5 relative accuracy.
+    # The f0 predictor runs in fp32 on the CUDA cores (csrc/f0_fp32.cu): the NSF phase integrates f0 over the whole
+    # utterance (generator.py:280), and the tensor cores' truncating fp32 accumulation biases f0 by ~2e-5 relative.
+    # Weights transposed to [3 * Cin, Cout], K index = tap * Cin + channel, tap j reads input row r + j - 1.
     for i, idx in enumerate((0, 2, 4, 6, 8)):                                     # f0_predictor.condnet
-        out[f"hift.f0.c{i}.w"] = split_bf16_weight(conv_weight_taps(fold_weight_norm(sd, f"f0_predictor.condnet.{idx}")))
+        w = fold_weight_norm(sd, f"f0_predictor.condnet.{idx}").float()           # [Cout, Cin, 3]
+        out[f"hift.f0.c{i}.wt"] = _f32(w.permute(2, 1, 0).reshape(-1, w.shape[0]))
         out[f"hift.f0.c{i}.b"] = _f32(sd[f"f0_predictor.condnet.{idx}.bias"])
-    out["hift.f0.cls.w"] = split_bf16_weight(sd["f0_predictor.classifier.weight"].float())    # [1, 3 * 512]
+    out["hift.f0.cls.w"] = _f32(sd["f0_predictor.classifier.weight"].float().reshape(-1))     # [512]
     out["hift.f0.cls.b"] = _f32(sd["f0_predictor.classifier.bias"])
     out["hift.src.w"] = _f32(sd["m_source.l_linear.weight"].reshape(-1))          # generator.py:380
     out["hift.src.b"] = _f32(sd["m_source.l_linear.bias"])

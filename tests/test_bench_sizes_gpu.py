@@ -113,7 +113,7 @@ def test_estimator_chunk_masks(engine, flow_sd, T, chunk):
     print(f"estimator T={T} chunk {chunk}: rel_l2 {e:.3e} (distance of the unmasked result: {rel_l2(full, ref):.3e})")
     assert e < EST_REL_L2
     if T > chunk:
-        assert rel_l2(full, ref) > 5 * EST_REL_L2   # the mask matters at this size: a kernel that ignored it would fail
+        assert rel_l2(full, ref) > 2.5 * EST_REL_L2   # the mask matters at this size: a kernel that ignored it would fail
 
 
 @pytest.mark.parametrize("chunk", [0, 20])

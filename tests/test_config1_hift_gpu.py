@@ -6,11 +6,14 @@
     waveform SNR (whole utterance and per second), band distance -- the length-dependent bounds are stated below;
   * HiFT at T' = 3000 frames (config 4, 60 s) against the oracle run on this box's host cores.
 
-Why the waveform bound depends on length: the NSF source integrates the predicted f0 into the sine phase
-(generator.py:275-283), so an f0 error of df Hz on a voiced stretch of D seconds shifts the k-th harmonic by 2 pi k df D
-radians.  The f0 predictor runs in split-bf16 (rel. error <= 2e-4), which holds the SOURCE to >= 30 dB SNR over 10 s;
-the waveform then carries the bf16 error of ~60 conv layers on top.  Bounds: source SNR >= 30 dB (10 s) / >= 25 dB (60 s),
-waveform SNR >= 20 dB (10 s) / >= 15 dB (60 s), band distance <= 1 dB.
+Length dependence: the NSF source integrates the predicted f0 into the sine phase (generator.py:275-283), so an f0 BIAS
+of df Hz over a voiced stretch of D seconds shifts the k-th harmonic by 2 pi k df D radians.  The tensor cores accumulate
+with truncation, which biased a split-bf16 f0 predictor by -1.9e-5 relative and let the waveform SNR fall from 30 dB in
+the first second to 10 dB in the tenth (profiles/r02_f0_bias.txt).  The predictor therefore runs in fp32 with
+round-to-nearest FMAs (csrc/f0_fp32.cu): f0 is unbiased at the 1e-6 level and the SNR no longer depends on length --
+measured 53 / 54 dB (source) and 41 / 41 dB (waveform) at 10 s / 60 s, flat per second.  Bounds, for ANY length up to the
+60 s of config 4: f0 rtol 5e-5 (atol 5e-4 Hz), source SNR >= 45 dB, waveform SNR >= 36 dB whole and >= 34 dB in every
+window, band distance <= 0.3 dB.
 """
 import os
 
@@ -26,7 +29,7 @@ pytestmark = pytest.mark.gpu
 MEL_REL_L2 = 1.5e-2
 MEL_RTOL, MEL_ATOL = 5e-2, 0.15
 BAND_DB = 3.0            # end to end through a bf16 mel (HiFT is ill-conditioned in its mel input, see test_e2e_gpu.py)
-F0_RTOL, F0_ATOL = 2e-4, 2e-3
+F0_RTOL, F0_ATOL = 5e-5, 5e-4
 
 
 @pytest.fixture(scope="module")
@@ -83,10 +86,10 @@ def test_hift_500_frames_on_reference_mel(decoder):
           f"wav SNR {s_wav:.1f} dB (per second: {', '.join(f'{v:.0f}' for v in per_s)}), band distance {d:.2f} dB")
     assert torch.allclose(f0, f0_ref, rtol=F0_RTOL, atol=F0_ATOL)
     assert voiced > 0.05, "fixture must exercise the sine branch of SineGen2"
-    assert s_src > 30.0
-    assert s_wav > 20.0
-    assert min(per_s) > 15.0
-    assert d < 1.0
+    assert s_src > 45.0
+    assert s_wav > 36.0
+    assert min(per_s) > 34.0
+    assert d < 0.3
 
 
 def test_hift_3000_frames_vs_oracle(decoder):
@@ -110,6 +113,7 @@ def test_hift_3000_frames_vs_oracle(decoder):
     print(f"HiFT T'=3000 vs oracle: source SNR {s_src:.1f} dB, wav SNR {s_wav:.1f} dB (per 10 s: "
           f"{', '.join(f'{v:.0f}' for v in per10)}), band distance {d:.2f} dB")
     assert torch.isfinite(wav).all() and wav.shape == ref_wav.shape
-    assert s_src > 25.0
-    assert s_wav > 15.0
-    assert d < 1.0
+    assert s_src > 45.0
+    assert s_wav > 36.0
+    assert min(per10) > 34.0
+    assert d < 0.3

@@ -1,7 +1,7 @@
 """GPU parity of the AudioDecoder mirror against the reference's REAL AudioDecoder (CPU fp32 golden, made by
 oracle/make_golden_hift.py): token2wav with prompt, stream_inference with a sliding window, and the batched paths.
 
-Tolerances: mel rel-L2 <= 4.8e-2 (bf16 storage / fp32 accumulation).  The NSF phase integrates f0 over the
+Tolerances: mel rel-L2 <= 1.5e-2 (bf16 storage / fp32 accumulation; PyTorch's own all-bf16 run: 4.8e-2).  The NSF phase integrates f0 over the
 utterance, so a waveform compared through a bf16 mel is only phase-coherent over short spans: end-to-end waveforms are
 held to a log-spectral (mel-cepstral-like) distance bound, the strict waveform SNR bound lives in test_hift_gpu.py where
 both sides get the same mel.
@@ -16,13 +16,13 @@ from conftest import GOLDEN
 
 pytestmark = pytest.mark.gpu
 
-MEL_REL_L2 = 4.8e-2
+MEL_REL_L2 = 1.5e-2
 # End-to-end waveform bound.  HiFT is ill-conditioned in its mel input: the NSF phase integrates the predicted f0, so
 # the REFERENCE ITSELF (CPU fp32), fed its own mel perturbed by 0.8 % relative noise -- the size of our bf16 mel
 # error -- moves by band_db = 2.2 dB and drops to 2.5 dB waveform SNR (0.1 %: 1.3 dB / 9.7 dB; another NSF noise seed
 # alone: 0.9 dB).  Measured with oracle/ on this fixture; our end-to-end output sits at 2.2 dB, i.e. at that floor.
 BAND_DB = 3.0
-REFMEL_SNR_DB = 18.0   # same mel + same NSF noise on both sides, 120 frames (phase drift grows with length)
+REFMEL_SNR_DB = 36.0   # same mel + same NSF noise on both sides (fp32 f0 predictor: no phase drift with length)
 
 
 from parity_metrics import band_db, rel_l2, snr_db  # noqa: E402

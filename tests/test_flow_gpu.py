@@ -1,7 +1,8 @@
 """GPU parity: estimator + Euler solve through the C-ABI vs golden outputs of the unmodified reference (CPU fp32).
 
 Tolerances (bf16 storage / fp32 accumulation): the reference's own all-bf16 PyTorch run differs from
-fp32 by rel-L2 2.2e-2 per estimator call and 4.8e-2 after 10 Euler steps; we require to be no worse than that.
+fp32 by rel-L2 2.2e-2 per estimator call and 4.8e-2 after 10 Euler steps; the bounds here are 1.6e-2 and 1.5e-2
+(measured 1.1-1.4e-2 and 6-10e-3: fp32 residual stream, LayerNorm statistics, Euler state and CFG mix).
 """
 import os
 
@@ -13,8 +14,8 @@ from conftest import GOLDEN
 
 pytestmark = pytest.mark.gpu
 
-EST_REL_L2 = 2.2e-2
-MEL_REL_L2 = 4.8e-2
+EST_REL_L2 = 1.6e-2
+MEL_REL_L2 = 1.5e-2
 
 
 def rel_l2(a, b):

@@ -1,8 +1,8 @@
 """GPU parity: HiFT vocoder through the C-ABI vs golden outputs of the unmodified reference (CPU fp32) with the NSF
 noise draws injected into both sides (generator.py:334).
 
-Tolerances (bf16 GEMM operands, fp32 accumulation / residual stream): waveform SNR >= 28 dB and
-source-signal SNR >= 33 dB against the fp32 reference.
+Tolerances (bf16 GEMM operands, fp32 accumulation / residual stream; fp32 f0 predictor): waveform SNR >= 36 dB
+and source-signal SNR >= 45 dB against the fp32 reference, f0 rtol 5e-5 / atol 5e-4 Hz (measured: 41 dB, 70 dB, 1.5e-5).
 """
 import os
 
@@ -14,8 +14,8 @@ from conftest import GOLDEN
 
 pytestmark = pytest.mark.gpu
 
-WAV_SNR_DB = 28.0
-SRC_SNR_DB = 33.0
+WAV_SNR_DB = 36.0
+SRC_SNR_DB = 45.0
 
 
 def snr_db(x, ref):
@@ -40,7 +40,7 @@ def test_hift_matches_reference(engine, name):
     f0 = engine.debug_read("hift.f0", (T + 8) * 4).reshape(-1, 4)[4:4 + T, 0]
     f0_ref = torch.from_numpy(z["f0"])
     print(f"{name}: f0 max rel err {float(((f0 - f0_ref).abs() / f0_ref.abs().clamp_min(1.0)).max()):.2e}")
-    assert torch.allclose(f0, f0_ref, rtol=2e-4, atol=2e-3)
+    assert torch.allclose(f0, f0_ref, rtol=5e-5, atol=5e-4)
     s_src, s_wav = snr_db(src, ref_src), snr_db(wav, ref_wav)
     print(f"{name}: source SNR {s_src:.1f} dB, wav SNR {s_wav:.1f} dB, max|wav| {float(wav.abs().max()):.3f}")
     assert torch.isfinite(wav).all()

@@ -78,14 +78,21 @@ def test_source_down_window_weight(k, stride, pad):
     torch.testing.assert_close(a @ wp.t(), ref, rtol=1e-4, atol=1e-4)
 
 
-def test_weight_norm_fold_and_split_bf16():
+def test_weight_norm_fold_and_f0_fp32_layout():
     conv = torch.nn.utils.parametrizations.weight_norm(torch.nn.Conv1d(6, 5, 3))
     sd = {"c." + k: v for k, v in conv.state_dict().items()}
     torch.testing.assert_close(weights.fold_weight_norm(sd, "c"), conv.weight.detach())
-    w = torch.randn(7, 64)
-    s = weights.split_bf16_weight(w).float()
-    assert (s[:, :64] + s[:, 64:128] - w).abs().max() < 2e-5 * w.abs().max()
-    assert torch.equal(s[:, :64], s[:, 128:])
+    # f0 predictor weights (fp32, csrc/f0_fp32.cu): Wt [3 * Cin, Cout], k = tap * Cin + c, tap j reads row r + j - 1
+    h = weights.pack_hift(synth.synth_hift_state_dict(0))
+    wt = h["hift.f0.c1.wt"]
+    assert wt.dtype == torch.float32 and wt.shape == (3 * 512, 512) and h["hift.f0.c0.wt"].shape == (240, 512)
+    w = weights.fold_weight_norm(synth.synth_hift_state_dict(0), "f0_predictor.condnet.2").float()
+    g = torch.Generator().manual_seed(0)
+    x = torch.randn(1, 512, 9, generator=g)
+    ref = F.conv1d(x, w, padding=1)[0].t()                                       # [T, Cout]
+    rows = F.pad(x[0].t(), (0, 0, 1, 1))                                          # zero guard rows = conv padding
+    a = torch.cat([rows[j:j + 9] for j in range(3)], 1)                           # taps -1, 0, +1 as K slabs
+    torch.testing.assert_close(a @ wt, ref, rtol=1e-4, atol=1e-4)
 
 
 def test_pack_shapes_and_schema():
@@ -94,7 +101,7 @@ def test_pack_shapes_and_schema():
     assert t["est.tf0.0.qkv.w"].shape == (1536, 256) and t["est.tbias.w"].shape == (14 * 256, 1024)
     h = weights.pack_hift(synth.synth_hift_state_dict(0))
     assert h["hift.up0.w"].shape == (2048, 1536) and h["hift.sd0.w"].shape == (256, 768)
-    assert h["hift.f0.c0.w"].shape == (512, 3 * 384) and h["hift.post.w"].shape == (18, 448)
+    assert h["hift.f0.cls.w"].shape == (512,) and h["hift.post.w"].shape == (18, 448)
 
 
 def test_layernorm_affine_folded_into_consumer_weights():

@@ -22,7 +22,7 @@ from parity_metrics import band_db, rel_l2, snr_db
 pytestmark = pytest.mark.gpu
 
 MEL_REL_L2 = 1.5e-2        # per chunk, bf16 storage / fp32 accumulation
-CHUNK_SNR_DB = 25.0        # same mel + same NSF noise, 20-40 frames per call
+CHUNK_SNR_DB = 36.0        # same mel + same NSF noise (measured 41 dB)
 BAND_DB = 3.0
 
 CASES = ["stream_chunks_N33_P7", "stream_chunks_c5_N33_P7", "stream_chunks_N60_P38"]
@@ -140,7 +140,7 @@ def test_stream_teacher_forced_chunks(decoders, name):
             if not fin:
                 c = dec.hift_cache_dict[uuid]
                 assert rel_l2(c["mel"][0], torch.from_numpy(z[f"mel_{i}"])[:, -dec.mel_cache_len:]) < 1e-6
-                assert snr_db(c["source"], torch.from_numpy(z[f"hsrc_{i}"])[-S:]) > 30.0
+                assert snr_db(c["source"], torch.from_numpy(z[f"hsrc_{i}"])[-S:]) > 45.0
                 assert torch.allclose(c["source"].reshape(-1).cpu(), torch.from_numpy(z[f"cache_{i + 1}"]), atol=5e-2)
             k[0] += 1
     finally:
