@@ -96,33 +96,26 @@ def _conformer_layer(x, L, pe, mask, heads):
     bd = torch.matmul(q_v, p.transpose(-2, -1))                                     # [B, H, T, 2T-1]
     # rel_shift (attention.py:223-244): bd[i, j] <- raw[i, j + T - 1 - i]
     bd = F.pad(bd, (1, 0)).view(B, heads, 2 * T, T)[:, :, 1:].reshape(B, heads, T, 2 * T - 1)[..., :T]
-    if x.is_cuda:
-        # softmax((q_u k^T + bd) / sqrt(dk)) v as ONE fused attention call: the positional term (and the -inf mask)
-        # rides in as the additive bias, so the [B, H, T, T] content scores / probabilities are never materialised
-        # (they were ~10 full passes over 0.4-0.9 GB tensors per mel-rate layer at batch 64).
-        Tp = (T + 7) // 8 * 8                                                       # bias row stride: multiple of 8
-        bias = torch.empty(B, heads, T, Tp, dtype=x.dtype, device=x.device)[..., :T]
-        torch.mul(bd, 1.0 / math.sqrt(dk), out=bias)
-        bias.masked_fill_(~mask, float("-inf"))
-        o = F.scaled_dot_product_attention(q_u, k, v, attn_mask=bias, scale=1.0 / math.sqrt(dk))
-        o = o.transpose(1, 2).reshape(B, T, D)
-    else:
-        ac = torch.matmul(q_u, k.transpose(-2, -1))                                 # [B, H, T, T]
-        scores = (ac + bd).float() / math.sqrt(dk)
-        scores = scores.masked_fill(~mask, float("-inf"))
-        attn = torch.softmax(scores, dim=-1).masked_fill(~mask, 0.0).to(x.dtype)
-        o = torch.matmul(attn, v).transpose(1, 2).reshape(B, T, D)
+    # softmax((q_u k^T + bd) / sqrt(dk)) v as ONE fused attention call: the positional term (and the -inf mask)
+    # rides in as the additive bias, so the [B, H, T, T] content scores / probabilities are never materialised
+    # (they were ~10 full passes over 0.4-0.9 GB tensors per mel-rate layer at batch 64).
+    Tp = (T + 7) // 8 * 8                                                       # bias row stride: multiple of 8
+    bias = torch.empty(B, heads, T, Tp, dtype=x.dtype, device=x.device)[..., :T]
+    torch.mul(bd, 1.0 / math.sqrt(dk), out=bias)
+    bias.masked_fill_(~mask, float("-inf"))
+    o = F.scaled_dot_product_attention(q_u, k, v, attn_mask=bias, scale=1.0 / math.sqrt(dk))
+    o = o.transpose(1, 2).reshape(B, T, D)
     x = x + F.linear(o, L["out_w"], L["out_b"])
     y = F.layer_norm(x.float(), (D,), L["n2"][0], L["n2"][1], 1e-12).to(x.dtype)
     return x + F.linear(F.silu(F.linear(y, L["w1"], L["b1"])), L["w2"], L["b2"])
 
 
 @torch.inference_mode()
-def encode(W: EncoderWeights, tokens, lens, ctx_len, chunk_tokens=0, max_batch_elems=1 << 28, _allow_cpu=False):
+def encode(W: EncoderWeights, tokens, lens, ctx_len, chunk_tokens=0, max_batch_elems=1 << 28):
     """tokens: int64 [B, Lmax + ctx_len] (prompt + new tokens, right padded; the last `ctx_len` VALID tokens of each
     row are look-ahead context when ctx_len > 0, flow.py:262-263); lens: int64 [B] tokens INCLUDING context.
     Returns mu [B, 4 * (Lmax), 80] fp32 (rows beyond 4 * (lens - ctx_len) are padding) and the main lengths."""
-    if not tokens.is_cuda and not _allow_cpu:  # _allow_cpu: CPU-side unit tests of this host logic only
+    if not tokens.is_cuda:
         raise RuntimeError("mossdec front end runs on CUDA tensors only (no CPU path)")
     B, Ltot = tokens.shape
     main = lens - ctx_len
@@ -130,7 +123,7 @@ def encode(W: EncoderWeights, tokens, lens, ctx_len, chunk_tokens=0, max_batch_e
     # sub-batch so the [B, H, T, 2T-1] score tensors of the mel-rate layers stay bounded
     per = max(1, int(max_batch_elems // max(1, W.heads * (4 * T) * (8 * T))))
     if per < B:
-        outs = [encode(W, tokens[i:i + per], lens[i:i + per], ctx_len, chunk_tokens, max_batch_elems, _allow_cpu)[0]
+        outs = [encode(W, tokens[i:i + per], lens[i:i + per], ctx_len, chunk_tokens, max_batch_elems)[0]
                 for i in range(0, B, per)]
         Tm = max(o.shape[1] for o in outs)
         return torch.cat([F.pad(o, (0, 0, 0, Tm - o.shape[1])) for o in outs], 0), main

@@ -1,6 +1,6 @@
 """TEST INFRASTRUCTURE ONLY -- second set of golden vectors from the UNMODIFIED reference (CPU, fp32):
 
-    python -m oracle.make_golden_r2 [est_c20] [stream] [config1]
+    python -m oracle.make_golden_r2 [est_c20] [stream] [config1] [encoder]
 
   est_c20 : estimator with static_chunk_size = 5 tokens = 20 mel frames (the mask edge falls inside a 32-key tile and
             inside a 128-row query tile; cosyvoice/flow/decoder.py:439-440, utils/mask.py:127-158) at T = 150 and 296, and a
@@ -8,6 +8,7 @@
   stream  : `stream_inference` (flow_inference.py:166-243) with a spy on every `hift.inference` call: per chunk the mel
             handed to the vocoder (cached 8 frames + new frames), its waveform / source outputs, and the speech chunk
             `token2wav_streaming` returns after the cross-fade -- the three cache tensors are slices of these.
+  encoder : taps of the reference's UpsampleConformerEncoder (pins oracle/port.py:encoder_forward)
   config1 : BASELINE.json config 1 -- one 10 s utterance (125 tokens, no prompt) through `AudioDecoder.token2wav`.
 
 Inputs are regenerated from seeds by oracle/cases.py; fixtures hold outputs + an input fingerprint.
@@ -109,8 +110,44 @@ def gen_config1():
           fp=cases.fingerprint(token.float(), emb))
 
 
+def gen_encoder_taps():
+    """Taps of the reference's UpsampleConformerEncoder (upsample_encoder.py:244-307) behind input_embedding: after the
+    pre-lookahead layer, after the 6 token-rate layers, after the up-conv, after after_norm, and mu = encoder_proj(h).
+    Case a: 20 tokens, non-streaming, finalize (no context).  Case b: 23 tokens of which 3 are look-ahead context,
+    streaming with static_chunk_size = 5 tokens (chunk masks at token and mel rate)."""
+    arrays = {}
+    for tag, L, ctx, chunk_tokens, streaming, seed in (("a", 20, 0, 25, False, 610), ("b", 23, 3, 5, True, 611)):
+        flow = build_ref.build_flow(static_chunk_tokens=chunk_tokens)
+        enc = flow.encoder
+        taps = {}
+        hooks = [enc.pre_lookahead_layer.register_forward_hook(lambda m, i, o: taps.__setitem__("pre_lookahead", o[0].clone())),
+                 enc.encoders[-1].register_forward_hook(lambda m, i, o: taps.__setitem__("encoders", o[0][0].clone())),
+                 enc.up_layer.register_forward_hook(lambda m, i, o: taps.__setitem__("up_layer", o[0][0].t().clone())),
+                 enc.after_norm.register_forward_hook(lambda m, i, o: taps.__setitem__("final", o[0].clone()))]
+        g = torch.Generator().manual_seed(seed)
+        tokens = torch.randint(0, 16384, (1, L), generator=g)
+        with torch.inference_mode():
+            emb = flow.input_embedding(tokens)
+            if ctx:
+                h, _ = enc(emb[:, :-ctx], torch.tensor([L]), context=emb[:, -ctx:], streaming=streaming)
+            else:
+                h, _ = enc(emb, torch.tensor([L]), streaming=streaming)
+            mu = flow.encoder_proj(h)
+        for hk in hooks:
+            hk.remove()
+        arrays[f"{tag}_tokens"] = tokens[0]
+        arrays[f"{tag}_ctx"] = np.int64(ctx)
+        arrays[f"{tag}_chunk_tokens"] = np.int64(chunk_tokens if streaming else 0)
+        arrays[f"{tag}_mu"] = mu[0]
+        for k, v in taps.items():
+            arrays[f"{tag}_{k}"] = v
+    _save("encoder_taps.npz", **arrays)
+
+
 def main(argv):
-    what = set(argv) or {"est_c20", "stream", "config1"}
+    what = set(argv) or {"est_c20", "stream", "config1", "encoder"}
+    if "encoder" in what:
+        gen_encoder_taps()
     if "est_c20" in what:
         gen_est_c20()
     if "stream" in what:

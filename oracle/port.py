@@ -6,9 +6,10 @@ unmodified reference (tests/golden/*.npz, produced in the build container by ora
 reference's own classes): see tests/test_oracle_cpu.py.  Nothing in the product imports it.
 
 Every function cites the reference code it restates (paths relative to GLM_modules/).  Weights are read from
-reference-format state_dicts (flow.pt / hift.pt key names).  The encoder front end reuses
-moss_speech_decoder_cosy_b200.frontend.encode in fp32 (itself a restatement validated to 3e-6 against
-cosyvoice/transformer/upsample_encoder.py:244-307).
+reference-format state_dicts (flow.pt / hift.pt key names).  Nothing here imports the product package: the encoder front
+end (`encoder_forward`) is its own restatement of cosyvoice/transformer/upsample_encoder.py:244-307, pinned to taps of the
+reference's UpsampleConformerEncoder (tests/golden/encoder_taps.npz).  All functions follow the device of their inputs, so
+the same restatement also serves as the "eager PyTorch on the GPU" line of bench.py.
 """
 import math
 
@@ -22,7 +23,7 @@ def _sinusoidal(t, dim=320, scale=1000.0):
     """SinusoidalPosEmb, matcha/models/components/decoder.py:20-29."""
     half = dim // 2
     emb = math.log(10000) / (half - 1)
-    emb = torch.exp(torch.arange(half, dtype=torch.float32) * -emb)
+    emb = torch.exp(torch.arange(half, dtype=torch.float32, device=t.device) * -emb)
     emb = scale * t.unsqueeze(1) * emb.unsqueeze(0)
     return torch.cat([emb.sin(), emb.cos()], dim=-1)
 
@@ -62,7 +63,7 @@ def _attn_bias(mask, chunk):
     B, _, T = mask.shape
     m = mask.bool().expand(B, T, T).clone()
     if chunk > 0:
-        ar = torch.arange(T)
+        ar = torch.arange(T, device=mask.device)
         m &= (ar.unsqueeze(0) < ((ar // chunk + 1) * chunk).unsqueeze(1)).unsqueeze(0)
     return (1.0 - m.float()) * -1.0e10
 
@@ -98,9 +99,10 @@ def solve_euler(sd, mu, spks, cond, noise, n_steps=10, cfg_rate=0.7, chunk=0):
     """CausalConditionalCFM.forward + ConditionalCFM.solve_euler, cosyvoice/flow/flow_matching.py:206-230, 76-127.
     mu, cond: [1, 80, T]; spks [1, 80]; noise [80, >=T] (the fixed bank)."""
     T = mu.shape[2]
-    x = noise[:, :T].unsqueeze(0).clone()
-    mask = torch.ones(1, 1, T)
-    t_span = torch.linspace(0, 1, n_steps + 1)
+    dev = mu.device
+    x = noise[:, :T].unsqueeze(0).clone().to(dev)
+    mask = torch.ones(1, 1, T, device=dev)
+    t_span = torch.linspace(0, 1, n_steps + 1, device=dev)
     t_span = 1 - torch.cos(t_span * 0.5 * torch.pi)
     t, dt = t_span[0], t_span[1] - t_span[0]
     for step in range(1, n_steps + 1):
@@ -157,7 +159,7 @@ def nsf_source(sd, f0, noise, sr=24000.0, up=480, sine_amp=0.1, noise_std=0.003,
     """f0_upsamp + SourceModuleHnNSF2 / SineGen2, generator.py:437,575, 261-283, 314-339, 383-384.
     f0 [T]; noise [480 T, 9] = the randn_like draw of generator.py:334 (injected).  Returns s [480 T]."""
     T = f0.shape[0]
-    h = torch.arange(1, 10, dtype=torch.float32)
+    h = torch.arange(1, 10, dtype=torch.float32, device=f0.device)
     rad = ((f0.unsqueeze(1) * h) / sr) % 1                      # per frame: the x480 / (1/480) resampling pair is the identity
     phase = torch.cumsum(rad.double(), dim=0).float() * 2 * np.pi       # torch CPU cumsum accumulates in double
     ph = F.interpolate((phase * up).t().unsqueeze(0), scale_factor=float(up), mode="linear")[0].t()   # [480 T, 9]
@@ -171,7 +173,7 @@ def nsf_source(sd, f0, noise, sr=24000.0, up=480, sine_amp=0.1, noise_std=0.003,
 def hift_decode(sd, mel, s, lrelu=0.1, limit=0.99):
     """HiFTGenerator.decode, generator.py:520-552.  mel [1, 80, T], s [1, 480 T] -> wav [1, 480 T]."""
     win = torch.from_numpy(__import__("scipy.signal", fromlist=["get_window"]).get_window("hann", 16, fftbins=True)
-                           .astype(np.float32))
+                           .astype(np.float32)).to(mel.device)
     spec = torch.view_as_real(torch.stft(s, 16, 4, 16, window=win, return_complex=True))
     s_stft = torch.cat([spec[..., 0], spec[..., 1]], dim=1)
     x = F.conv1d(mel, _wn(sd, "conv_pre"), sd["conv_pre.bias"], padding=3)
@@ -217,30 +219,134 @@ def noise_bank():
     return torch.randn([1, 80, 15000], generator=g)[0]
 
 
-class PortDecoder:
-    """AudioDecoder.token2wav (flow_inference.py:94-123) restated on CPU fp32 (batch 1, like the reference)."""
+# ------------------------------------------------------------------------------------------------ encoder front end
+def _rel_pos_table(T, d_model, device):
+    """EspnetRelPositionalEncoding.extend_pe / position_encoding, cosyvoice/transformer/embedding.py:224-302: rows
+    m = 0 .. 2T-2 hold the sinusoid of relative position T-1-m."""
+    rel = torch.arange(T - 1, -T, -1, dtype=torch.float32, device=device).unsqueeze(1)
+    div = torch.exp(torch.arange(0, d_model, 2, dtype=torch.float32, device=device) * -(math.log(10000.0) / d_model))
+    pe = torch.zeros(2 * T - 1, d_model, device=device)
+    pe[:, 0::2] = torch.sin(rel * div)
+    pe[:, 1::2] = torch.cos(rel * div)
+    return pe
 
-    def __init__(self, flow_sd, hift_sd, static_chunk_tokens=25):
-        from moss_speech_decoder_cosy_b200 import frontend
-        self.fsd = {k: v.float() for k, v in flow_sd.items()}
-        self.hsd = {k: v.float() for k, v in hift_sd.items()}
-        self.enc = frontend.EncoderWeights(self.fsd, "cpu", torch.float32)
-        self._frontend = frontend
-        self.bank = noise_bank()
+
+def _enc_mask(T, chunk, device):
+    """add_optional_chunk_mask with a static chunk and full left context (cosyvoice/utils/mask.py:161-236); batch 1, no
+    padding.  [T, T] bool, key j visible to query i iff chunk == 0 or j < (i // chunk + 1) * chunk."""
+    if chunk <= 0:
+        return torch.ones(T, T, dtype=torch.bool, device=device)
+    ar = torch.arange(T, device=device)
+    return ar.unsqueeze(0) < ((ar // chunk + 1) * chunk).unsqueeze(1)
+
+
+def _conformer_layer(x, sd, p, pe, mask, heads=8):
+    """ConformerEncoderLayer without macaron / conv module, pre-norm (encoder_layer.py:196-236) around
+    RelPositionMultiHeadedAttention (attention.py:215-330; LayerNorm eps 1e-12, encoder_layer.py:71-73)."""
+    T, D = x.shape
+    dk = D // heads
+    a = p + "self_attn."
+    y = F.layer_norm(x, (D,), sd[p + "norm_mha.weight"], sd[p + "norm_mha.bias"], 1e-12)
+    q = F.linear(y, sd[a + "linear_q.weight"], sd[a + "linear_q.bias"]).view(T, heads, dk)
+    k = F.linear(y, sd[a + "linear_k.weight"], sd[a + "linear_k.bias"]).view(T, heads, dk).transpose(0, 1)
+    v = F.linear(y, sd[a + "linear_v.weight"], sd[a + "linear_v.bias"]).view(T, heads, dk).transpose(0, 1)
+    pp = F.linear(pe, sd[a + "linear_pos.weight"]).view(2 * T - 1, heads, dk).transpose(0, 1)     # [H, 2T-1, dk]
+    q_u = (q + sd[a + "pos_bias_u"]).transpose(0, 1)                                               # [H, T, dk]
+    q_v = (q + sd[a + "pos_bias_v"]).transpose(0, 1)
+    ac = torch.matmul(q_u, k.transpose(-2, -1))                                                    # [H, T, T]
+    bd = torch.matmul(q_v, pp.transpose(-2, -1))                                                   # [H, T, 2T-1]
+    # rel_shift (attention.py:223-244): bd[i, j] <- raw[i, j + T - 1 - i]
+    bd = F.pad(bd, (1, 0)).view(heads, 2 * T, T)[:, 1:].reshape(heads, T, 2 * T - 1)[..., :T]
+    scores = (ac + bd) / math.sqrt(dk)
+    scores = scores.masked_fill(~mask, float("-inf"))
+    attn = torch.softmax(scores, dim=-1).masked_fill(~mask, 0.0)                                   # attention.py:120-135
+    o = torch.matmul(attn, v).transpose(0, 1).reshape(T, D)
+    x = x + F.linear(o, sd[a + "linear_out.weight"], sd[a + "linear_out.bias"])
+    y = F.layer_norm(x, (D,), sd[p + "norm_ff.weight"], sd[p + "norm_ff.bias"], 1e-12)
+    f = p + "feed_forward."
+    return x + F.linear(F.silu(F.linear(y, sd[f + "w_1.weight"], sd[f + "w_1.bias"])), sd[f + "w_2.weight"], sd[f + "w_2.bias"])
+
+
+def encoder_forward(sd, tokens, ctx_len=0, chunk_tokens=0, taps=None):
+    """`input_embedding` + UpsampleConformerEncoder.forward + `encoder_proj` (flow.py:254-265,
+    upsample_encoder.py:244-307) for ONE utterance.  tokens: int64 [L] = prompt + new tokens; the last `ctx_len` of them
+    are the look-ahead context (flow.py:262-263, 3 when finalize is False).  Returns mu [4 * (L - ctx_len), 80].
+    `taps` (dict) receives intermediate activations for pinning."""
+    dev = tokens.device
+    D = sd["input_embedding.weight"].shape[1]
+    e = "encoder."
+    x = sd["input_embedding.weight"][tokens.clamp(min=0)]                                          # flow.py:256
+    # LinearNoSubsampling + EspnetRelPositionalEncoding (subsampling.py:85-93, embedding.py:262); the context tokens go
+    # through the same `embed` (upsample_encoder.py:283-286; the offset only moves pos_emb, which is not used for them)
+    x = F.layer_norm(F.linear(x, sd[e + "embed.out.0.weight"], sd[e + "embed.out.0.bias"]), (D,),
+                     sd[e + "embed.out.1.weight"], sd[e + "embed.out.1.bias"], 1e-5) * math.sqrt(D)
+    T = tokens.shape[0] - ctx_len
+    inputs = x[:T]
+    # PreLookaheadLayer (upsample_encoder.py:81-98): conv1 k4 over [inputs | context | zero pad], leaky_relu, causal conv2 k3
+    y = F.pad(x.t().unsqueeze(0), (0, 3 - ctx_len))
+    y = F.leaky_relu(F.conv1d(y, sd[e + "pre_lookahead_layer.conv1.weight"], sd[e + "pre_lookahead_layer.conv1.bias"]))
+    y = F.conv1d(F.pad(y, (2, 0)), sd[e + "pre_lookahead_layer.conv2.weight"], sd[e + "pre_lookahead_layer.conv2.bias"])
+    x = y[0].t() + inputs
+    if taps is not None:
+        taps["pre_lookahead"] = x.clone()
+    mask = _enc_mask(T, chunk_tokens, dev)
+    pe = _rel_pos_table(T, D, dev)
+    i = 0
+    while e + f"encoders.{i}.norm_mha.weight" in sd:
+        x = _conformer_layer(x, sd, e + f"encoders.{i}.", pe, mask)
+        i += 1
+    if taps is not None:
+        taps["encoders"] = x.clone()
+    # Upsample1D (upsample_encoder.py:37-64): nearest x stride, left pad 2 * stride, conv k = 2 * stride + 1
+    stride = (sd[e + "up_layer.conv.weight"].shape[2] - 1) // 2
+    y = x.t().unsqueeze(0).repeat_interleave(stride, dim=2)
+    y = F.conv1d(F.pad(y, (2 * stride, 0)), sd[e + "up_layer.conv.weight"], sd[e + "up_layer.conv.bias"])
+    x = y[0].t()
+    if taps is not None:
+        taps["up_layer"] = x.clone()
+    T2 = stride * T
+    x = F.layer_norm(F.linear(x, sd[e + "up_embed.out.0.weight"], sd[e + "up_embed.out.0.bias"]), (D,),
+                     sd[e + "up_embed.out.1.weight"], sd[e + "up_embed.out.1.bias"], 1e-5) * math.sqrt(D)
+    mask = _enc_mask(T2, chunk_tokens * stride, dev)
+    pe = _rel_pos_table(T2, D, dev)
+    i = 0
+    while e + f"up_encoders.{i}.norm_mha.weight" in sd:
+        x = _conformer_layer(x, sd, e + f"up_encoders.{i}.", pe, mask)
+        i += 1
+    x = F.layer_norm(x, (D,), sd[e + "after_norm.weight"], sd[e + "after_norm.bias"], 1e-5)
+    if taps is not None:
+        taps["final"] = x.clone()
+    return F.linear(x, sd["encoder_proj.weight"], sd["encoder_proj.bias"])                       # flow.py:265
+
+
+def speaker_projection(sd, embedding):
+    """flow.py:250-251: L2-normalise, then spk_embed_affine_layer."""
+    return F.linear(F.normalize(embedding.float(), dim=1), sd["spk_embed_affine_layer.weight"],
+                    sd["spk_embed_affine_layer.bias"])
+
+
+class PortDecoder:
+    """AudioDecoder.token2wav (flow_inference.py:94-123) restated in fp32 (batch 1, like the reference), on the device of
+    the weights (CPU for the oracle / CPU baseline, CUDA for bench.py's eager-PyTorch-on-the-GPU line)."""
+
+    def __init__(self, flow_sd, hift_sd, static_chunk_tokens=25, device="cpu"):
+        self.device = torch.device(device)
+        self.fsd = {k: v.float().to(self.device) for k, v in flow_sd.items()}
+        self.hsd = {k: v.float().to(self.device) for k, v in hift_sd.items()}
+        self.bank = noise_bank().to(self.device)
         self.chunk = static_chunk_tokens
 
     @torch.inference_mode()
     def flow(self, token, prompt_token, prompt_feat, embedding, streaming=False, finalize=True):
         """CausalMaskedDiffWithXvec.inference, flow.py:237-283 -> (mel [80, 4N], full [80, T])."""
-        tok = torch.cat([prompt_token.reshape(-1).long(), token.reshape(-1).long()]).unsqueeze(0)
+        dev = self.device
+        tok = torch.cat([prompt_token.reshape(-1).long(), token.reshape(-1).long()]).to(dev)
         ctx = 0 if finalize else 3
-        mu, _ = self._frontend.encode(self.enc, tok, torch.tensor([tok.shape[1]]), ctx,
-                                      self.chunk if streaming else 0, _allow_cpu=True)
-        mu = mu.transpose(1, 2)
+        mu = encoder_forward(self.fsd, tok, ctx, self.chunk if streaming else 0).t().unsqueeze(0)
         T, F1 = mu.shape[2], prompt_feat.shape[1]
-        cond = torch.zeros(1, 80, T)
-        cond[:, :, :F1] = prompt_feat.transpose(1, 2)
-        spks = self._frontend.speaker_projection(self.enc, embedding)
+        cond = torch.zeros(1, 80, T, device=dev)
+        cond[:, :, :F1] = prompt_feat.to(dev).transpose(1, 2)
+        spks = speaker_projection(self.fsd, embedding.to(dev))
         full = solve_euler(self.fsd, mu, spks, cond, self.bank, chunk=self.chunk * 4 if streaming else 0)[0]
         return full[:, F1:], full
 
@@ -252,7 +358,7 @@ class PortDecoder:
         mel, _ = self.flow(token, prompt_token, prompt_feat, embedding)
         if noise is None:
             noise = torch.randn(480 * mel.shape[1], 9)
-        wav, _ = hift_inference(self.hsd, mel, noise)
+        wav, _ = hift_inference(self.hsd, mel, noise.to(self.device))
         return wav.unsqueeze(0), mel.unsqueeze(0)
 
 

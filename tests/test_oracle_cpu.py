@@ -124,3 +124,20 @@ def test_estimator_restatement_padding_mask(sds, mode):
     assert float(ref[1, :, 97:].abs().max()) == 0.0
     torch.testing.assert_close(out, ref, rtol=1e-2, atol=1e-4)
     assert _rel(out, ref) < 1e-5
+
+
+@pytest.mark.parametrize("tag", ["a", "b"])
+def test_encoder_restatement_taps(sds, tag):
+    """oracle/port.py:encoder_forward against taps of the reference's UpsampleConformerEncoder: non-streaming (a) and
+    streaming with a 3-token look-ahead context and 5-token chunk masks (b)."""
+    z = np.load(os.path.join(GOLDEN, "encoder_taps.npz"))
+    fsd = {k: v.float() for k, v in sds[0].items()}
+    taps = {}
+    with torch.inference_mode():
+        mu = port.encoder_forward(fsd, torch.from_numpy(z[f"{tag}_tokens"]), int(z[f"{tag}_ctx"]),
+                                  int(z[f"{tag}_chunk_tokens"]), taps=taps)
+    for k in ("pre_lookahead", "encoders", "up_layer", "final"):
+        ref = torch.from_numpy(z[f"{tag}_{k}"])
+        assert taps[k].shape == ref.shape, (k, taps[k].shape, ref.shape)
+        assert _rel(taps[k], ref) < 3e-6, (k, _rel(taps[k], ref))
+    assert _rel(mu, torch.from_numpy(z[f"{tag}_mu"])) < 3e-6
