@@ -126,6 +126,10 @@ int mossdec_debug_read(mossdec_handle* h, const char* name, float* host_dst, int
  * FLOPs (2 M N K incl. tile padding), attention ms, attention launches, 0, fused-FFN ms, fused-FFN launches, FFN FLOPs}. */
 void mossdec_profile(mossdec_handle* h, int32_t on);
 int mossdec_profile_read(mossdec_handle* h, double* out9);
+/* Bandwidth-class kernels ("euler_cfg_kernel", "flow_prepare_kernel", "hift_source_kernel", "hift_stft_kernel",
+ * "hift_fuse_snake_kernel", "hift_istft_kernel") are timed the same way while profiling is on; after a
+ * mossdec_profile_read, out3 = {device ms, launches, ALGORITHMIC bytes moved (SURVEY.md 8d figures)} of `name`. */
+int mossdec_profile_named(mossdec_handle* h, const char* name, double* out3);
 
 /* Pre-size the device workspaces so that the first decode does not allocate: solves of up to `flow_rows` mel frames in
  * total over up to `flow_seqs` utterances, vocoder groups of up to `hift_frames` frames.  (Workspaces otherwise grow on

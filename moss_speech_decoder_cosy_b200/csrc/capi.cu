@@ -98,6 +98,7 @@ int mossdec_debug_read(mossdec_handle* h, const char* name, float* host_dst, int
 
 void mossdec_profile(mossdec_handle* h, int32_t on) { h->eng->set_profile(on != 0); }
 int mossdec_profile_read(mossdec_handle* h, double* out9) { return h->eng->profile_read(out9); }
+int mossdec_profile_named(mossdec_handle* h, const char* name, double* out3) { return h->eng->profile_named(name, out3); }
 void mossdec_set_hift_group_frames(mossdec_handle* h, int64_t frames) { h->eng->set_hift_group_frames(frames); }
 
 int mossdec_reserve(mossdec_handle* h, int64_t flow_rows, int32_t flow_seqs, int64_t hift_frames) {

@@ -111,6 +111,8 @@ class Engine {
     // per-launch device timing of the GEMM (0), attention (1) and fused-FFN (2) kernels with CUDA events on the launch stream
     void set_profile(bool on) { profile_ = on; }
     int profile_read(double* out9);
+    // {ms, launches, algorithmic bytes} of a named bandwidth kernel accumulated by profile_read() calls; clears the entry
+    int profile_named(const char* name, double* out3);
     // test hook: copy a named intermediate of the last call to the host; returns floats copied or -1
     int debug_read(const char* name, void* host_dst, size_t bytes);
     int fade_in_out(float* speech, const float* prev_tail, const float* window2n, int n, cudaStream_t st);
@@ -230,6 +232,20 @@ class Engine {
     cudaEvent_t prof_event();
     void prof_begin(int cls, double flops, cudaStream_t st, uint64_t key = 0);
     void prof_end(cudaStream_t st);
+    // bandwidth-class kernels: event pair around the launch + its ALGORITHMIC bytes, accumulated per kernel name
+    struct BwRec { cudaEvent_t a, b; const char* name; double bytes; };
+    struct BwAcc { double ms = 0, n = 0, bytes = 0; };
+    std::vector<BwRec> bw_prof_;
+    std::map<std::string, BwAcc> bw_acc_;
+    void bw_begin(const char* name, double bytes, cudaStream_t st) {
+        if (!profile_) return;
+        BwRec r{prof_event(), prof_event(), name, bytes};
+        cudaEventRecord(r.a, st);
+        bw_prof_.push_back(r);
+    }
+    void bw_end(cudaStream_t st) {
+        if (profile_) cudaEventRecord(bw_prof_.back().b, st);
+    }
     int64_t hift_group_frames_ = 8192;  // frames per HiFT group (bounds the stage-2 working set)
 };
 

@@ -172,6 +172,17 @@ int Engine::profile_read(double* out) {
         prof_pool_.push_back(r.b);
     }
     prof_.clear();
+    for (auto& r : bw_prof_) {
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, r.a, r.b);
+        BwAcc& a = bw_acc_[r.name];
+        a.ms += ms;
+        a.n += 1;
+        a.bytes += r.bytes;
+        prof_pool_.push_back(r.a);
+        prof_pool_.push_back(r.b);
+    }
+    bw_prof_.clear();
     if (getenv("MOSSDEC_PROFILE_DUMP")) {  // per GEMM shape/epilogue breakdown (developer aid)
         for (auto& kv : prof_by_key_) {
             const uint64_t k = kv.first;
@@ -183,6 +194,17 @@ int Engine::profile_read(double* out) {
         }
     }
     prof_by_key_.clear();
+    return 0;
+}
+
+int Engine::profile_named(const char* name, double* out3) {
+    auto it = bw_acc_.find(name);
+    out3[0] = out3[1] = out3[2] = 0.0;
+    if (it == bw_acc_.end()) return 0;
+    out3[0] = it->second.ms;
+    out3[1] = it->second.n;
+    out3[2] = it->second.bytes;
+    bw_acc_.erase(it);
     return 0;
 }
 

@@ -326,11 +326,19 @@ int Engine::hift_group(int b0, int b1, const int32_t* lens, int64_t mel_off0, in
     }
     // ---------------------------------------------------------------- NSF source + STFT (generator.py:574-580, 521-522)
     float* src = source_out ? source_out : R.src - wav_off0;  // ragged [480 T_b] signal addressed by wav_off
+    double frames = 0;
+    for (int s = 0; s < nseq; ++s) frames += lens[b0 + s];
     launch_hift_phase(L, R.f0, 4, cfg_.sample_rate, 480.f, cfg_.n_harm, R.p480, st);
+    // per frame: 480 samples written (fp32) + 480 x 9 injected noise draws read (none with the device Philox stream)
+    bw_begin("hift_source_kernel", frames * (480.0 * 4 + (nsf_noise ? 480.0 * 9 * 4 : 0.0)), st);
     launch_hift_source(L, max_len, R.f0, 4, R.p480, nsf_noise, W<float>("hift.src.w"), W<float>("hift.src.b"),
                        cache_source ? cache_source + (size_t)b0 * cache_stride : nullptr, cache_stride, d_clen,
                        cfg_.n_harm, cfg_.sine_amp, cfg_.noise_std, cfg_.voiced_thr, 480, seed, src, st);
+    bw_end(st);
+    // per stage-2 row (120 per frame): 4 new samples read, 24 bf16 written
+    bw_begin("hift_stft_kernel", (double)R.M[2] * (4.0 * 4 + 24.0 * 2), st);
     launch_hift_stft(L, R.rs[2], (int)R.M[2], src, R.stft, st);
+    bw_end(st);
     launches_ += 3;
 
     // ---------------------------------------------------------------- conv_pre (generator.py:524) -> leaky_relu
@@ -392,9 +400,12 @@ int Engine::hift_group(int b0, int b1, const int32_t* lens, int64_t mel_off0, in
             if (R.resblock(N("hift.srb%d", i), C, kSrcResK[i], Mi, R.rs[i], R.si, R.sb, R.si, R.sb, fin)) return -1;
         }
         // x = ups(x) (+ reflection pad) + si; Snake operands of the three ResBlocks
+        // per element: read u, si (fp32), write x (fp32) + three bf16 Snake operands
+        bw_begin("hift_fuse_snake_kernel", (double)Mi * C * (3.0 * 4 + 3.0 * 2), st);
         launch_hift_fuse_snake(L, R.rs[i], kScale[i], reflect, Mi, C, R.u, R.si, W<float>(N("hift.rb%d.0.a1.0", i)),
                                W<float>(N("hift.rb%d.1.a1.0", i)), W<float>(N("hift.rb%d.2.a1.0", i)), R.x, R.a[0],
                                R.a[1], R.a[2], st);
+        bw_end(st);
         ++launches_;
         for (int r = 0; r < 3; ++r) {   // xs = sum_r resblocks[3 i + r](x); x = xs / 3; next operand = leaky_relu(x)
             HiftRunner::Final fin;
@@ -422,7 +433,10 @@ int Engine::hift_group(int b0, int b1, const int32_t* lens, int64_t mel_off0, in
         p.epi.out_f32 = R.post; p.epi.ldf = 32;
         if (gemm(p, st)) return -1;
     }
+    // per frame: 120 rows x 32 fp32 of conv_post output read (18 used, 32-wide rows), 480 samples written
+    bw_begin("hift_istft_kernel", frames * (120.0 * 32 * 4 + 480.0 * 4), st);
     launch_hift_istft(L, max_len, R.post, 32, cfg_.audio_limit, wav_out, st);
+    bw_end(st);
     ++launches_;
     taps_["hift.f0"] = {R.f0, (size_t)rows_f * 4 * 4};          // [rows_f, 4] fp32, column 0; first sequence at row 4
     taps_["hift.p480"] = {R.p480, (size_t)rows_f * 16 * 4};

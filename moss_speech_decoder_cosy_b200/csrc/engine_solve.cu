@@ -118,7 +118,10 @@ int Engine::run_euler_steps(int n_steps, int chunk, float cfg_rate, const float*
         } else if (estimator_forward(flow_M_, flow_nseq_, flow_max_len_, tb, 0, chunk, st)) {
             return -1;
         }
+        // read d_cond, d_uncond, x + write x (4 x 80 fp32 = 1 280 B per frame) + bf16 x slab of both halves
+        bw_begin("euler_cfg_kernel", (double)flow_rows_half_ * (4.0 * 80 * 4 + 2.0 * 80 * 2), st);
         launch_euler_cfg(layout_, dout_, dtv[s], cfg_rate, xstate_, xin_, st);
+        bw_end(st);
         ++launches_;
     }
     return 0;
@@ -142,7 +145,11 @@ int Engine::flow_solve(int B, const int32_t* lens, const float* mu, const float*
     if (build_flow_layout(B, lens, /*cfg_double=*/true, st)) return -1;
     layout_.noise_cstride = noise_len;
     layout_.time_major = flags & 1;
+    // algorithmic bytes per row of the conditional half: read mu, cond, noise (3 x 80 fp32), write xstate (80 fp32) and
+    // the 320-channel bf16 input rows of both CFG halves
+    bw_begin("flow_prepare_kernel", (double)flow_rows_half_ * (4.0 * 80 * 4 + 2.0 * 320 * 2), st);
     launch_flow_prepare(layout_, mu, spks, cond, noise, noise_bstride, temperature, xin_, xstate_, st);
+    bw_end(st);
     ++launches_;
 
     std::vector<float> ts;

@@ -165,6 +165,7 @@ class AudioDecoder(torch.nn.Module):
         self.speech_window = np.hamming(2 * self.source_cache_len)
         self._speech_window_dev = torch.from_numpy(self.speech_window.astype(np.float32)).to(self.device)
         self._seed = 0
+        self.last_h2d_bytes = 0
 
     def _next_seed(self):
         self._seed += 1
@@ -198,6 +199,8 @@ class AudioDecoder(torch.nn.Module):
         F_ = [int(pf.shape[1]) for pf in prompt_feats]
         feats = [pf.reshape(-1, 80) for pf in prompt_feats if pf.shape[1]]
         feat_cat = torch.cat(feats, 0).float() if feats else torch.zeros(0, 80)
+        embeddings = embeddings.float()
+        self.last_h2d_bytes = tok.nbytes + feat_cat.nbytes + embeddings.nbytes   # what this call copies host -> device
         return self.flow_device(tok.to(dev, non_blocking=True), lens_tok, feat_cat.to(dev, non_blocking=True), F_,
                                 embeddings.to(dev, non_blocking=True), streaming, finalize)
 

@@ -67,6 +67,8 @@ def load_library():
     lib.mossdec_profile.restype = None
     lib.mossdec_profile_read.argtypes = [vp, ctypes.POINTER(ctypes.c_double)]
     lib.mossdec_profile_read.restype = i32
+    lib.mossdec_profile_named.argtypes = [vp, ctypes.c_char_p, ctypes.POINTER(ctypes.c_double)]
+    lib.mossdec_profile_named.restype = i32
     lib.mossdec_set_hift_group_frames.argtypes = [vp, i64]
     lib.mossdec_set_hift_group_frames.restype = None
     lib.mossdec_reserve.argtypes = [vp, i64, i32, i64]
@@ -91,7 +93,7 @@ EXPORTED_SYMBOLS = [
     "mossdec_launch_count", "mossdec_reset_launch_count", "mossdec_debug_read", "mossdec_profile",
     "mossdec_profile_read", "mossdec_set_hift_group_frames", "mossdec_cv1_resnet_block", "mossdec_cv1_downsample",
     "mossdec_cv1_upsample", "mossdec_cv1_block1d", "mossdec_reserve", "mossdec_set_graph_mode", "mossdec_graph_replays",
-    "mossdec_device",
+    "mossdec_device", "mossdec_profile_named",
 ]
 
 
@@ -274,6 +276,18 @@ class Engine:
     @property
     def device_index(self):
         return int(self.lib.mossdec_device(self.h))
+
+    BANDWIDTH_KERNELS = ("euler_cfg_kernel", "flow_prepare_kernel", "hift_source_kernel", "hift_stft_kernel",
+                         "hift_fuse_snake_kernel", "hift_istft_kernel")
+
+    def profile_bandwidth(self):
+        """{kernel: {ms, launches, bytes}} of the bandwidth-class kernels since the last profile_read()."""
+        out = {}
+        for name in self.BANDWIDTH_KERNELS:
+            v = (ctypes.c_double * 3)()
+            self._check(self.lib.mossdec_profile_named(self.h, name.encode(), v), "profile_named")
+            out[name] = {"ms": v[0], "launches": int(v[1]), "bytes": v[2]}
+        return out
 
     def set_hift_group_frames(self, frames):
         self.lib.mossdec_set_hift_group_frames(self.h, int(frames))
