@@ -94,6 +94,14 @@ int mossdec_hift(mossdec_handle* h, int32_t B, const int32_t* lens, const float*
 int mossdec_fade_in_out(mossdec_handle* h, float* speech, const float* prev_tail, const float* window2n, int32_t n,
                         void* stream);
 
+/* Prompt mel front end = the reference's `feat_extractor`, matcha mel_spectrogram
+ * (GLM_modules/third_party/Matcha-TTS/matcha/utils/audio.py:45-82) with n_fft = win = 1920, hop 480, 80 mels, 24 kHz,
+ * fmin 0, fmax 8000, center = False, called by GLM4Encoder._extract_speech_feat (whisper_encoder_decoder.py:191-195).
+ * wav: device fp32 [n_samples] in [-1, 1]; mel_out: device fp32 [80, T] with T = n_samples / 480 (floor; the caller
+ * allocates 80 * (n_samples / 480) floats).  Needs the tensors "mel.dft" and "mel.fb" (mel_frontend.py).  Returns T,
+ * negative on error. */
+int32_t mossdec_mel_spectrogram(mossdec_handle* h, const float* wav, int64_t n_samples, float* mel_out, void* stream);
+
 /* ---- Secondary configuration: building blocks of the NON-causal cosyvoice1 / Matcha
  * estimator (GLM_modules/cosyvoice1 uses third_party/Matcha-TTS/matcha/models/components/decoder.py).  Dense
  * [B, C, T] fp32 tensors exactly as the reference modules take them; block width 256, GroupNorm(8).  Weights are the

@@ -116,6 +116,9 @@ class Engine {
     // test hook: copy a named intermediate of the last call to the host; returns floats copied or -1
     int debug_read(const char* name, void* host_dst, size_t bytes);
     int fade_in_out(float* speech, const float* prev_tail, const float* window2n, int n, cudaStream_t st);
+    // matcha mel_spectrogram (n_fft 1920, hop 480, 80 mels, 24 kHz, fmax 8000, center False; mel_kernels.cu):
+    // wav device [L] -> mel_out device [80, T], T = (L - 480) / 480 + 1.  Returns T, negative on error.
+    int mel_spectrogram(const float* wav, int64_t L, float* mel_out, cudaStream_t st);
     // Building blocks of the non-causal cosyvoice1 / Matcha estimator (cv1_ops.cu): dense
     // [B, C, T] fp32 in / out like the reference modules, weights looked up as "<prefix>.*" (weights.py pack_cv1_*).
     int cv1_resnet_block(const char* prefix, int B, int T, int Cin, const float* x, const float* mask, const float* temb,
@@ -219,6 +222,7 @@ class Engine {
 
     // ---- cosyvoice1 building-block workspace (cv1_ops.cu)
     DeviceBuffer ws_cv1_;
+    DeviceBuffer ws_mel_;   // prompt mel front end (mel_kernels.cu)
 
     // ---- hift workspace
     DeviceBuffer ws_hift_, ws_hift_layout_;

@@ -1,19 +1,26 @@
-// ConvRNNF0Predictor (cosyvoice/hifigan/f0_predictor.py:31-60: 5 x {Conv1d(k3, pad 1) + ELU}, Linear(512 -> 1), abs) in
-// FP32 on the CUDA cores -- the one dense contraction of the path that deliberately does NOT run on the tensor cores.
+// FP32 contractions on the CUDA cores -- the dense contractions of the path that deliberately do NOT run on the tensor
+// cores: the f0 predictor of the vocoder and the prompt mel front end (both feed quantities whose errors are integrated
+// or logarithmically expanded downstream; both are ~1 % of the work).
 //
-// Why: the NSF source integrates the predicted f0 into the sine phase over the whole utterance (generator.py:275-283), so
-// a RELATIVE BIAS of the f0 predictor of 1e-5 turns into a phase error of the k-th harmonic of 2 pi k f0 1e-5 t.  tcgen05
-// accumulates its fp32 partial sums with truncation (round toward zero): measured on B200 (profiles/r02_f0_bias.txt), the
-// split-bf16 tensor-core version of this predictor had a mean signed relative f0 error of -1.9e-5 over the voiced frames
-// of a 10 s utterance (the CPU simulation of the same split with round-to-nearest accumulation: +7e-7), and the source
-// signal fell from 30 dB SNR in the first second to 10 dB in the tenth.  With round-to-nearest FMAs the error is
-// unbiased and at the 1e-6 level of the reference's own fp32 convolutions.  The predictor is 1 % of the vocoder's FLOPs.
+// (1) ConvRNNF0Predictor (cosyvoice/hifigan/f0_predictor.py:31-60: 5 x {Conv1d(k3, pad 1) + ELU}, Linear(512 -> 1), abs).
+// Why fp32: the NSF source integrates the predicted f0 into the sine phase over the whole utterance
+// (generator.py:275-283), so a RELATIVE BIAS of the f0 predictor of 1e-5 turns into a phase error of the k-th harmonic
+// of 2 pi k f0 1e-5 t.  tcgen05 accumulates its fp32 partial sums with truncation (round toward zero): measured on B200
+// (profiles/r02_f0_bias.txt), the split-bf16 tensor-core version of this predictor had a mean signed relative f0 error
+// of -1.9e-5 over the voiced frames of a 10 s utterance (the CPU simulation of the same split with round-to-nearest
+// accumulation: +7e-7), and the source signal fell from 30 dB SNR in the first second to 10 dB in the tenth.  With
+// round-to-nearest FMAs the error is unbiased and at the 1e-6 level of the reference's own fp32 convolutions.
 //
-//   conv3_elu_f32_kernel : out[m, n] = rowmask[m] * elu(bias[n] + sum_{tap, c} in[m + tap - 1, c] * Wt[tap * Cin + c, n])
+// (2) matcha mel_spectrogram (third_party/Matcha-TTS/matcha/utils/audio.py:45-82) behind AudioDecoder.feat_extractor:
+// reflect pad, 1920-point windowed DFT (hop 480) as an fp32 GEMM over the overlapping-window view of the padded signal,
+// magnitude, Slaney mel filterbank GEMM, log(clamp(., 1e-5)).  log-mel needs the quiet bins right (-100 dB below the loud
+// ones); a few hundred frames per prompt, run once per speaker.
+//
+//   conv_f32_kernel<kTaps, kAct> : out[m, n] = rowmask[m] * act(bias[n] + sum_{tap, c} in[m + tap - kTaps / 2, c] * Wt[tap * Cin + c, n])
 //       classic register-tiled SGEMM: 128 x 128 block tile, 16-wide K slabs, 256 threads x (8 x 8) outputs, operands
 //       double-buffered in shared memory, the next slab's global loads in flight during the math, packed fma.rn.f32x2.
 //       Rows of different utterances are separated by zero guard rows (engine_hift.cu), so the +-1 row taps see the
-//       conv's zero padding; rows outside [0, M) read as zero.
+//       conv's zero padding; rows outside [0, M) read as zero.  `ld_in` < Cin gives overlapping windows (STFT frames).
 //   f0_classifier_kernel : f0[m] = | w . h[m, :] + b |   (one warp per row)
 #include "kernels.h"
 #include "ptx.cuh"
@@ -24,16 +31,17 @@ namespace {
 
 constexpr int kBM = 128, kBN = 128, kBK = 16, kPadA = 4;
 
+template <int kTaps, int kAct>   // kAct: 0 = none, 1 = ELU
 __global__ void __launch_bounds__(256, 2)
-conv3_elu_f32_kernel(const float* __restrict__ in, int M, int Cin, const float* __restrict__ wt, int N,
-                     const float* __restrict__ bias, const int32_t* __restrict__ row_seq, float* __restrict__ out) {
+conv_f32_kernel(const float* __restrict__ in, int M, int64_t ld_in, int Cin, const float* __restrict__ wt, int N,
+                const float* __restrict__ bias, const int32_t* __restrict__ row_seq, float* __restrict__ out) {
     __shared__ __align__(16) float sA[2][kBK][kBM + kPadA];
     __shared__ __align__(16) float sB[2][kBK][kBN];
     const int tid = threadIdx.x;
     const int tx = tid & 15, ty = tid >> 4;
     const int m0 = blockIdx.x * kBM, n0 = blockIdx.y * kBN;
     const int slabs_per_tap = Cin / kBK;
-    const int nslab = 3 * slabs_per_tap;
+    const int nslab = kTaps * slabs_per_tap;
 
     // global -> register staging of one K slab: A 128 rows x 16 floats (2 float4 per thread), B 16 x 128 (2 float4)
     float4 ra[2], rb[2];
@@ -43,9 +51,9 @@ conv3_elu_f32_kernel(const float* __restrict__ in, int M, int Cin, const float* 
         for (int i = 0; i < 2; ++i) {
             const int f = tid + 256 * i;
             const int r = f >> 2, kq = f & 3;
-            const int row = m0 + r + tap - 1;
+            const int row = m0 + r + tap - kTaps / 2;
             ra[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (row >= 0 && row < M) ra[i] = __ldg(reinterpret_cast<const float4*>(in + (size_t)row * Cin + c0 + kq * 4));
+            if (row >= 0 && row < M) ra[i] = __ldg(reinterpret_cast<const float4*>(in + (size_t)row * ld_in + c0 + kq * 4));
             const int kb = f >> 5, nq = f & 31;
             rb[i] = __ldg(reinterpret_cast<const float4*>(wt + (size_t)(s * kBK + kb) * N + n0 + nq * 4));
         }
@@ -98,12 +106,12 @@ conv3_elu_f32_kernel(const float* __restrict__ in, int M, int Cin, const float* 
         }
     }
 
-    // epilogue: bias + ELU (F.elu: x > 0 ? x : expm1(x)), guard rows forced to zero
+    // epilogue: bias + activation (F.elu: x > 0 ? x : expm1(x)), guard rows forced to zero
     float bv[8];
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
-        bv[j] = __ldg(bias + n0 + tx * 4 + j);
-        bv[4 + j] = __ldg(bias + n0 + 64 + tx * 4 + j);
+        bv[j] = bias ? __ldg(bias + n0 + tx * 4 + j) : 0.f;
+        bv[4 + j] = bias ? __ldg(bias + n0 + 64 + tx * 4 + j) : 0.f;
     }
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
@@ -118,7 +126,7 @@ conv3_elu_f32_kernel(const float* __restrict__ in, int M, int Cin, const float* 
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
             const float x = v[j] + bv[j];
-            v[j] = valid ? (x > 0.f ? x : expm1f(x)) : 0.f;
+            v[j] = valid ? (kAct == 1 ? (x > 0.f ? x : expm1f(x)) : x) : 0.f;
         }
         float* o = out + (size_t)row * N + n0 + tx * 4;
         *reinterpret_cast<float4*>(o) = make_float4(v[0], v[1], v[2], v[3]);
@@ -153,7 +161,16 @@ cudaError_t launch_conv3_elu_f32(const float* in, int M, int Cin, const float* w
                                  const int32_t* row_seq, float* out, cudaStream_t st) {
     if (M <= 0 || (Cin % kBK) != 0 || (N % kBN) != 0) return cudaErrorInvalidValue;
     dim3 grid((M + kBM - 1) / kBM, N / kBN);
-    conv3_elu_f32_kernel<<<grid, 256, 0, st>>>(in, M, Cin, wt, N, bias, row_seq, out);
+    conv_f32_kernel<3, 1><<<grid, 256, 0, st>>>(in, M, (int64_t)Cin, Cin, wt, N, bias, row_seq, out);
+    return cudaGetLastError();
+}
+
+// out [M, N] = in_view [M, K] . Wt [K, N], row m of the view starts at in + m * ld_in (ld_in < K: overlapping windows)
+cudaError_t launch_gemm_f32(const float* in, int M, int64_t ld_in, int K, const float* wt, int N, float* out,
+                            cudaStream_t st) {
+    if (M <= 0 || (K % kBK) != 0 || (N % kBN) != 0 || (ld_in % 4) != 0) return cudaErrorInvalidValue;
+    dim3 grid((M + kBM - 1) / kBM, N / kBN);
+    conv_f32_kernel<1, 0><<<grid, 256, 0, st>>>(in, M, ld_in, K, wt, N, nullptr, nullptr, out);
     return cudaGetLastError();
 }
 

@@ -62,6 +62,8 @@ void launch_hift_pack_mel(const HiftLayout& L, const int32_t* row_seq, const flo
 // fp32 f0 predictor (f0_fp32.cu): Conv1d(k3, pad 1) + ELU over packed rows, weights Wt [3 * Cin, N] (k = tap * Cin + c)
 cudaError_t launch_conv3_elu_f32(const float* in, int M, int Cin, const float* wt, int N, const float* bias,
                                  const int32_t* row_seq, float* out, cudaStream_t st);
+// generic fp32 GEMM on the CUDA cores: out [M, N] = view [M, K] . Wt [K, N]; row m of the view starts at in + m * ld_in
+cudaError_t launch_gemm_f32(const float* in, int M, int64_t ld_in, int K, const float* wt, int N, float* out, cudaStream_t st);
 cudaError_t launch_f0_classifier(const float* h, int M, int C, const float* w, const float* b, const int32_t* row_seq,
                                  float* f0, int f0_ld, cudaStream_t st);
 void launch_hift_phase(const HiftLayout& L, const float* f0, int f0_ld, float sample_rate, float upsample, int n_harm,

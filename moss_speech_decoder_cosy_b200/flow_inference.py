@@ -18,7 +18,7 @@ from collections import defaultdict
 import numpy as np
 import torch
 
-from . import frontend, lib, synth, weights
+from . import frontend, lib, mel_frontend, synth, weights
 
 TOKEN_MEL_RATIO = 4
 PRE_LOOKAHEAD = 3
@@ -71,6 +71,32 @@ def _load_checkpoint(path, what):
     if not os.path.exists(path):
         raise FileNotFoundError(f"{what} checkpoint {path!r} does not exist (pass None for the synthetic random-init weights)")
     return torch.load(path, map_location="cpu")
+
+
+class _MissingCampplus:
+    """Stands in for `campplus_session` when it cannot be built; any use raises with the reason (the reference fails in
+    its constructor instead, flow_inference.py:86-89)."""
+
+    def __init__(self, why):
+        self.why = why
+
+    def __getattr__(self, name):
+        raise RuntimeError(f"campplus_session is unavailable: {self.why}")
+
+
+def _make_campplus_session(campplus_model):
+    if campplus_model is None:
+        return _MissingCampplus("no campplus_model path was given")
+    try:
+        import onnxruntime
+    except ImportError:
+        return _MissingCampplus("onnxruntime is not installed")
+    if not os.path.exists(campplus_model):
+        raise FileNotFoundError(f"campplus_model {campplus_model!r} does not exist")
+    option = onnxruntime.SessionOptions()
+    option.graph_optimization_level = onnxruntime.GraphOptimizationLevel.ORT_ENABLE_ALL
+    option.intra_op_num_threads = 1
+    return onnxruntime.InferenceSession(campplus_model, sess_options=option, providers=["CPUExecutionProvider"])
 
 
 class _FlowFacade:
@@ -136,14 +162,18 @@ class AudioDecoder(torch.nn.Module):
         tensors = weights.pack_estimator(flow_state_dict)
         tensors["flow.rand_noise"] = synth.synth_noise_bank()[0].contiguous()   # flow_matching.py:202-203
         tensors.update(weights.pack_hift(hift_state_dict))
+        tensors.update(mel_frontend.pack_mel_tensors())
         self.engine.load_tensors(tensors)
         self.engine.finalize()
         self.enc_weights = frontend.EncoderWeights(flow_state_dict, self.device)
         self.flow = _FlowFacade(self)
         self.hift = _HiftFacade(self)
         self.sample_rate = self.scratch_configs["sample_rate"]
-        self.feat_extractor = None      # prompt mel extractor (matcha mel_spectrogram) -- SURVEY 8(f) N2
-        self.campplus_session = None    # x-vector ONNX session stays with the caller (CPU, out of scope)
+        # prompt mel extractor = matcha mel_spectrogram (flow_inference.py:64, whisper_encoder_decoder.py:192), on the device
+        self.feat_extractor = mel_frontend.MelExtractor(self.engine, self.device)
+        # campplus x-vector session, built exactly like the reference (flow_inference.py:86-89); the model itself is
+        # out of scope (CPU ONNX, its embedding is an input of the path)
+        self.campplus_session = _make_campplus_session(campplus_model)
         self.static_chunk_size = int(self.scratch_configs["static_chunk_size"])   # tokens (encoder chunk masks)
         ecf = self.scratch_configs["estimator_chunk_frames"]
         self.estimator_chunk_frames = int(ecf) if ecf is not None else self.static_chunk_size * TOKEN_MEL_RATIO

@@ -53,6 +53,8 @@ def load_library():
     lib.mossdec_hift.restype = i32
     lib.mossdec_fade_in_out.argtypes = [vp, vp, vp, vp, i32, vp]
     lib.mossdec_fade_in_out.restype = i32
+    lib.mossdec_mel_spectrogram.argtypes = [vp, vp, i64, vp, vp]
+    lib.mossdec_mel_spectrogram.restype = i32
     lib.mossdec_cv1_resnet_block.argtypes = [vp, ctypes.c_char_p, i32, i32, i32, vp, vp, vp, i32, vp, vp]
     lib.mossdec_cv1_resnet_block.restype = i32
     lib.mossdec_cv1_block1d.argtypes = [vp, ctypes.c_char_p, i32, i32, i32, vp, vp, vp, vp]
@@ -93,7 +95,7 @@ EXPORTED_SYMBOLS = [
     "mossdec_launch_count", "mossdec_reset_launch_count", "mossdec_debug_read", "mossdec_profile",
     "mossdec_profile_read", "mossdec_set_hift_group_frames", "mossdec_cv1_resnet_block", "mossdec_cv1_downsample",
     "mossdec_cv1_upsample", "mossdec_cv1_block1d", "mossdec_reserve", "mossdec_set_graph_mode", "mossdec_graph_replays",
-    "mossdec_device", "mossdec_profile_named",
+    "mossdec_device", "mossdec_profile_named", "mossdec_mel_spectrogram",
 ]
 
 
@@ -118,6 +120,7 @@ class Engine:
         if rc != 0:
             raise RuntimeError(f"mossdec_create failed ({rc})")
         self.h = h
+        self._device_index = None
 
     @staticmethod
     def default_config():
@@ -151,9 +154,9 @@ class Engine:
     def finalize(self):
         self._check(self.lib.mossdec_finalize(self.h), "finalize")
 
-    @staticmethod
-    def _stream():
-        return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+    def _stream(self):
+        # torch's current stream ON THE ENGINE'S DEVICE (the caller's current device may be another GPU)
+        return ctypes.c_void_p(torch.cuda.current_stream(self.device_index).cuda_stream)
 
     def estimator(self, x, mask, mu, t, spks, cond, chunk=0, out_alias_x=False):
         """Same contract as ConditionalCFM.forward_estimator (flow_matching.py:129): fp32 CUDA tensors [B2,80,T]."""
@@ -207,6 +210,17 @@ class Engine:
         n = prev_tail.numel()
         self._check(self.lib.mossdec_fade_in_out(self.h, _ptr(speech), _ptr(prev_tail), _ptr(window2n), n,
                                                  self._stream()), "fade_in_out")
+
+    def mel_spectrogram(self, wav):
+        """matcha mel_spectrogram (audio.py:45-82; n_fft 1920, hop 480, 80 mels, 24 kHz): wav fp32 CUDA [L] -> [80, L // 480]."""
+        wav = wav.float().contiguous()
+        L = wav.numel()
+        out = torch.empty(80, max(L // 480, 0), device=wav.device, dtype=torch.float32)
+        T = self.lib.mossdec_mel_spectrogram(self.h, _ptr(wav), L, _ptr(out), self._stream())
+        if T < 0:
+            raise RuntimeError(f"mel_spectrogram failed: {self.lib.mossdec_last_error(self.h).decode()}")
+        assert T == out.shape[1], (T, out.shape)
+        return out
 
     # ---- cosyvoice1 / Matcha non-causal building blocks (SURVEY 8 row A9); same call shapes as the reference modules
     def cv1_resnet_block(self, prefix, x, mask, time_emb=None):
@@ -275,7 +289,9 @@ class Engine:
 
     @property
     def device_index(self):
-        return int(self.lib.mossdec_device(self.h))
+        if self._device_index is None:
+            self._device_index = int(self.lib.mossdec_device(self.h))
+        return self._device_index
 
     BANDWIDTH_KERNELS = ("euler_cfg_kernel", "flow_prepare_kernel", "hift_source_kernel", "hift_stft_kernel",
                          "hift_fuse_snake_kernel", "hift_istft_kernel")

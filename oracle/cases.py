@@ -59,3 +59,17 @@ def fingerprint(*tensors):
         d = t.double().reshape(-1)
         out += [float(d.sum()), float(d.abs().sum()), float(d[0]), float(d[-1])]
     return np.asarray(out)
+
+
+def prompt_waveform(seed, n_samples, sr=24000):
+    """A speech-like test waveform in [-1, 1]: a few harmonics of a gliding f0 under a slow amplitude envelope with a
+    near-silent stretch, plus low-level noise -- so the log-mel covers its whole dynamic range down to the 1e-5 clamp."""
+    g = torch.Generator().manual_seed(int(seed))
+    t = torch.arange(n_samples, dtype=torch.float64) / sr
+    f0 = 110.0 + 60.0 * torch.sin(2 * np.pi * 0.7 * t)
+    phase = 2 * np.pi * torch.cumsum(f0, 0) / sr
+    y = sum((0.5 / k) * torch.sin(k * phase + k) for k in range(1, 12))
+    env = (0.55 + 0.45 * torch.sin(2 * np.pi * 1.3 * t)).clamp_min(0.0) ** 2
+    env[int(0.45 * n_samples):int(0.6 * n_samples)] *= 1e-4
+    y = 0.6 * env * y + 2e-4 * torch.randn(n_samples, generator=g, dtype=torch.float64)
+    return y.clamp(-1, 1).float().unsqueeze(0)

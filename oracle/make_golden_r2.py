@@ -144,8 +144,28 @@ def gen_encoder_taps():
     _save("encoder_taps.npz", **arrays)
 
 
+def gen_mel_frontend():
+    """The reference's feat_extractor = matcha mel_spectrogram (matcha/utils/audio.py:45-82, the UNMODIFIED function, with
+    librosa.filters.mel supplied by the restated Slaney filterbank) on a seeded 2.0 s waveform and on one whose length
+    is not a multiple of the hop."""
+    from . import ref_shims
+    ref_shims.install()
+    from matcha.utils.audio import mel_spectrogram
+    arrays = {}
+    for tag, n in (("a", 48000), ("b", 30000 + 123)):
+        y = cases.prompt_waveform(700 + n, n)
+        with torch.inference_mode():
+            mel = mel_spectrogram(y, 1920, 80, 24000, 480, 1920, 0, 8000, center=False)
+        arrays[f"{tag}_n"] = np.int64(n)
+        arrays[f"{tag}_mel"] = mel[0]
+        arrays[f"{tag}_fp"] = cases.fingerprint(y)
+    _save("mel_frontend.npz", **arrays)
+
+
 def main(argv):
-    what = set(argv) or {"est_c20", "stream", "config1", "encoder"}
+    what = set(argv) or {"est_c20", "stream", "config1", "encoder", "mel"}
+    if "mel" in what:
+        gen_mel_frontend()
     if "encoder" in what:
         gen_encoder_taps()
     if "est_c20" in what:

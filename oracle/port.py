@@ -362,6 +362,44 @@ class PortDecoder:
         return wav.unsqueeze(0), mel.unsqueeze(0)
 
 
+# ------------------------------------------------------------------------------------------------ prompt mel front end
+def slaney_mel_filterbank(sr, n_fft, n_mels, fmin, fmax):
+    """librosa.filters.mel(sr=, n_fft=, n_mels=, fmin=, fmax=) with its defaults htk=False, norm='slaney' (librosa 0.10 /
+    0.11, pinned by the reference's requirements; call site matcha/utils/audio.py:53).  Published algorithm restated:
+    Slaney mel scale (linear 200/3 Hz per mel below 1 kHz, log with step log(6.4)/27 above), n_mels + 2 equally spaced
+    mel points, triangular weights from the two neighbouring ramps, each filter scaled by 2 / (f[i+2] - f[i]).
+    Returns float32 [n_mels, 1 + n_fft // 2]."""
+    f_sp, min_log_hz = 200.0 / 3, 1000.0
+    min_log_mel, logstep = min_log_hz / f_sp, math.log(6.4) / 27.0
+
+    def hz_to_mel(f):
+        return min_log_mel + math.log(f / min_log_hz) / logstep if f >= min_log_hz else f / f_sp
+
+    def mel_to_hz(m):
+        return min_log_hz * math.exp(logstep * (m - min_log_mel)) if m >= min_log_mel else f_sp * m
+    lo, hi = hz_to_mel(fmin), hz_to_mel(fmax)
+    mel_f = np.array([mel_to_hz(lo + (hi - lo) * i / (n_mels + 1)) for i in range(n_mels + 2)], dtype=np.float64)
+    freqs = np.linspace(0.0, sr / 2.0, 1 + n_fft // 2)
+    w = np.zeros((n_mels, freqs.shape[0]), dtype=np.float64)
+    for i in range(n_mels):
+        lower = (freqs - mel_f[i]) / (mel_f[i + 1] - mel_f[i])
+        upper = (mel_f[i + 2] - freqs) / (mel_f[i + 2] - mel_f[i + 1])
+        w[i] = np.maximum(0.0, np.minimum(lower, upper)) * (2.0 / (mel_f[i + 2] - mel_f[i]))
+    return w.astype(np.float32)
+
+
+def mel_spectrogram(y, n_fft=1920, num_mels=80, sampling_rate=24000, hop_size=480, win_size=1920, fmin=0, fmax=8000):
+    """matcha mel_spectrogram, third_party/Matcha-TTS/matcha/utils/audio.py:45-82 (center=False): y [1, L] -> [1, 80, T]."""
+    fb = torch.from_numpy(slaney_mel_filterbank(sampling_rate, n_fft, num_mels, fmin, fmax)).to(y.device)
+    pad = int((n_fft - hop_size) / 2)
+    y = F.pad(y.unsqueeze(1), (pad, pad), mode="reflect").squeeze(1)
+    spec = torch.view_as_real(torch.stft(y, n_fft, hop_length=hop_size, win_length=win_size,
+                                         window=torch.hann_window(win_size).to(y.device), center=False, pad_mode="reflect",
+                                         normalized=False, onesided=True, return_complex=True))
+    spec = torch.sqrt(spec.pow(2).sum(-1) + 1e-9)
+    return torch.log(torch.clamp(torch.matmul(fb, spec), min=1e-5))
+
+
 # ------------------------------------------------------------------ cosyvoice1 / Matcha non-causal blocks (SURVEY 8 A9)
 def cv1_block1d(x, mask, sd, p, groups=8):
     """Block1D, third_party/Matcha-TTS/matcha/models/components/decoder.py:32-43: Conv1d(k3, pad 1) -> GroupNorm(8) -> Mish."""

@@ -147,6 +147,13 @@ def install(with_audio_decoder: bool = True):
             pm.__path__ = [os.path.join(REF_ROOT, *pkg.split("."))]
         _mod("cosyvoice.llm.llm", TransformerLM=_Unsupported, Qwen2LM=_Unsupported)
         _mod("cosyvoice.cli.model", CosyVoiceModel=_Unsupported, CosyVoice2Model=_Unsupported)
+    # matcha/utils/audio.py:4 imports librosa.filters.mel (librosa pinned 0.10.2 / 0.11.0, absent offline): the stand-in is
+    # the restated Slaney filterbank of oracle/port.py, itself cross-checked against torchaudio's independent
+    # implementation (tests/test_oracle_cpu.py::test_slaney_filterbank_matches_torchaudio)
+    if "librosa" not in sys.modules:
+        from . import port as _port
+        _mod("librosa")
+        _mod("librosa.filters", mel=lambda sr, n_fft, n_mels, fmin, fmax: _port.slaney_mel_filterbank(sr, n_fft, n_mels, fmin, fmax))
     if with_audio_decoder:
         if "hyperpyyaml" not in sys.modules:
             _mod("hyperpyyaml", load_hyperpyyaml=lambda f: _HYPER["cfg"])

@@ -141,3 +141,34 @@ def test_encoder_restatement_taps(sds, tag):
         assert taps[k].shape == ref.shape, (k, taps[k].shape, ref.shape)
         assert _rel(taps[k], ref) < 3e-6, (k, _rel(taps[k], ref))
     assert _rel(mu, torch.from_numpy(z[f"{tag}_mu"])) < 3e-6
+
+
+def test_slaney_filterbank_matches_torchaudio():
+    """librosa is absent offline: the restated filterbank (oracle) and the product's table builder are held against
+    torchaudio's independent Slaney implementation (same published algorithm as librosa.filters.mel)."""
+    import torchaudio
+    from moss_speech_decoder_cosy_b200 import mel_frontend
+    ref = torchaudio.functional.melscale_fbanks(961, 0.0, 8000.0, 80, 24000, norm="slaney", mel_scale="slaney").t().double()
+    ours = torch.from_numpy(port.slaney_mel_filterbank(24000, 1920, 80, 0, 8000)).double()
+    prod = torch.from_numpy(mel_frontend.slaney_mel_filterbank()).double()
+    assert ours.shape == ref.shape == prod.shape == (80, 961)
+    assert float((ours - ref).abs().max()) < 1e-7 and float((prod - ref).abs().max()) < 1e-7
+    assert float(ours.sum(1).min()) > 0        # no empty filter at n_fft = 1920
+
+
+@pytest.mark.parametrize("tag", ["a", "b"])
+def test_mel_spectrogram_restatement(tag):
+    """oracle/port.py:mel_spectrogram against the UNMODIFIED matcha mel_spectrogram (golden), incl. a length that is not a
+    multiple of the hop."""
+    from oracle import cases
+    z = np.load(os.path.join(GOLDEN, "mel_frontend.npz"))
+    n = int(z[f"{tag}_n"])
+    y = cases.prompt_waveform(700 + n, n)
+    if not np.allclose(cases.fingerprint(y), z[f"{tag}_fp"], rtol=1e-6, atol=1e-6):
+        pytest.skip("torch CPU generator differs from the build that produced the fixture")
+    with torch.inference_mode():
+        mel = port.mel_spectrogram(y)[0]
+    ref = torch.from_numpy(z[f"{tag}_mel"])
+    assert mel.shape == ref.shape == (80, n // 480)
+    assert float(ref.min()) < -8.5 and float(ref.max()) > 1.0       # the fixture spans 10 nepers: near-silence to loud frames
+    torch.testing.assert_close(mel, ref, rtol=1e-5, atol=1e-5)
