@@ -320,7 +320,7 @@ def main():
     T = 4 * (N_PROMPT + N_TOK)
     dec.engine.reserve(flow_rows=B * T, flow_seqs=B, hift_frames=8192)
     # device-resident copies for the kernel-side leg; the end-to-end leg goes through decode_batch with the host lists
-    tok_d = torch.stack([torch.cat([ptoks[b].reshape(-1).long(), toks[b].reshape(-1)]) for b in range(B)]).to(dev)
+    tok_d = torch.cat([torch.cat([ptoks[b].reshape(-1).long(), toks[b].reshape(-1)]) for b in range(B)]).to(dev)
     feat_d = torch.cat([pf.reshape(-1, 80) for pf in pfeats], 0).to(dev)
     emb_d = emb.to(dev)
     wav_h = torch.empty(B * N_TOK * 1920, dtype=torch.float32).pin_memory()

@@ -8,6 +8,8 @@
  *   mossdec_estimator   <- ConditionalCFM.forward_estimator          flow_matching.py:129-156 / decoder.py:405-494
  *   mossdec_flow_solve  <- CausalConditionalCFM.forward + solve_euler flow_matching.py:206-230, 76-127
  *   mossdec_hift        <- HiFTGenerator.inference                    hifigan/generator.py:570-582
+ *   mossdec_token2mel   <- CausalMaskedDiffWithXvec.inference         cosyvoice/flow/flow.py:237-283 (encoder + solve)
+ *   mossdec_mel_spectrogram <- feat_extractor (matcha mel_spectrogram) third_party/Matcha-TTS/matcha/utils/audio.py:45-82
  *   mossdec_set_tensor  <- nn.Module.load_state_dict                  flow_inference.py:59-61
  *
  * All data pointers are DEVICE pointers owned by the caller unless stated otherwise; `stream` is a cudaStream_t
@@ -90,6 +92,28 @@ int mossdec_hift(mossdec_handle* h, int32_t B, const int32_t* lens, const float*
                  int32_t cache_stride, const int32_t* cache_len, const float* nsf_noise, float* wav_out,
                  float* source_out, uint64_t seed, int32_t flags, void* stream);
 
+/* mossdec_hift over the GENERATED part of flow results: the mel block of utterance b holds mel_skip[b] + lens[b] frames
+ * (time-major [frames, 80], what mossdec_token2mel writes); the first mel_skip[b] (prompt) frames are passed over
+ * (flow.py:281 feat[:, :, mel_len1:]).  lens / mel_skip: HOST arrays.  No source cache (non-streaming call). */
+int mossdec_hift_skip(mossdec_handle* h, int32_t B, const int32_t* lens, const int32_t* mel_skip, const float* mel,
+                      const float* nsf_noise, float* wav_out, float* source_out, uint64_t seed, void* stream);
+
+/* CausalMaskedDiffWithXvec.inference (flow.py:237-283) for B independent utterances (the reference asserts B == 1):
+ * speaker projection (L2-normalise + Linear 192 -> 80), token embedding, UpsampleConformerEncoder, encoder_proj, prompt
+ * condition, then the CFG Euler solve -- all on this library's kernels (row N1).
+ *   n_tok[b] (HOST): tokens of utterance b = prompt tokens + new tokens (+ ctx_len look-ahead tokens at the end when the
+ *     call is not final, flow.py:262-263: ctx_len = pre_lookahead_len = 3, else 0);
+ *   tokens: device int64, the utterances' token ids back to back (negative ids are clamped to 0 like flow.py:256);
+ *   prompt_frames[b] (HOST) / prompt_feat: device fp32 ragged [prompt_frames[b], 80] prompt mels back to back;
+ *   embedding: device fp32 [B, 192];
+ *   chunk_tokens: 0 = full attention (streaming = False), else the encoder's static_chunk_size in tokens;
+ *   est_chunk_frames: the estimator's block-causal chunk in mel frames (0 = full attention);
+ *   mel_out: device fp32 ragged time-major [4 * (n_tok[b] - ctx_len), 80] blocks = `feat` of flow.py:272-280 (prompt
+ *     frames included; strip them with mossdec_hift_skip or by offset). */
+int mossdec_token2mel(mossdec_handle* h, int32_t B, const int32_t* n_tok, const int64_t* tokens, const int32_t* prompt_frames,
+                      const float* prompt_feat, const float* embedding, int32_t ctx_len, int32_t chunk_tokens,
+                      int32_t est_chunk_frames, int32_t n_steps, float cfg_rate, float* mel_out, void* stream);
+
 /* Streaming glue (flow_inference.py:35-43,151-156): speech[:n] = speech[:n]*w[:n] + prev_tail[:n]*w[n:], fp32, device. */
 int mossdec_fade_in_out(mossdec_handle* h, float* speech, const float* prev_tail, const float* window2n, int32_t n,
                         void* stream);
@@ -126,7 +150,7 @@ int mossdec_cv1_upsample(mossdec_handle* h, const char* prefix, int32_t B, int32
                          void* stream);
 
 /* Test hook: copy up to max_floats of a named fp32 intermediate of the last call ("hift.f0", "hift.p480",
- * "hift.post", "hift.x") to HOST memory; synchronises the device.  Returns floats copied, negative on error. */
+ * "hift.post", "hift.x"; "enc.mu", "enc.cond", "enc.spks" after mossdec_token2mel) to HOST memory; synchronises the device.  Returns floats copied, negative on error. */
 int mossdec_debug_read(mossdec_handle* h, const char* name, float* host_dst, int64_t max_floats);
 
 /* Per-launch device timing (CUDA events on the launch stream) of the three tensor-core kernels.

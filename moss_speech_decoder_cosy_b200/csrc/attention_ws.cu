@@ -44,13 +44,24 @@ constexpr float kRescaleThreshold = 8.f;   // log2 units: P values stay below 2^
 
 // Softmax of one [128 x NK] score tile (NK = 16 or 32), thread == query row.  `o_stable` is the barrier whose phase
 // `o_phase` completes with PV(j - 1): O may only be rescaled once that MMA has finished.
-template <int NK>
+// `bias` (kBias only): bf16 additive score term of this thread's query row, element kbase + i for key kbase + i (the
+// relative-position term matrix_bd of the conformer encoder, already shifted to this row; engine_encoder.cu).
+template <int NK, bool kBias>
 __device__ __forceinline__ void softmax_tile(uint32_t t_s, uint32_t t_o, int kbase, int lim, int j, float& m2, float& l,
-                                             uint64_t* o_stable, uint32_t o_phase) {
+                                             uint64_t* o_stable, uint32_t o_phase, const unsigned short* bias) {
     float sc[NK];
+    unsigned short braw[kBias ? NK : 1];
+    if (kBias) {   // issued before the TMEM load so both latencies overlap
+#pragma unroll
+        for (int i = 0; i < NK; ++i) braw[i] = __ldg(bias + kbase + i);
+    }
 #pragma unroll
     for (int c = 0; c < NK / 16; ++c) tmem_ld16(t_s + c * 16, sc + c * 16);
     tmem_ld_wait();
+    if (kBias) {
+#pragma unroll
+        for (int i = 0; i < NK; ++i) sc[i] += __uint_as_float((uint32_t)braw[i] << 16);
+    }
     if (kbase + NK > lim) {
 #pragma unroll
         for (int i = 0; i < NK; ++i)
@@ -104,9 +115,11 @@ __device__ __forceinline__ void softmax_tile(uint32_t t_s, uint32_t t_o, int kba
     tmem_st_wait();
 }
 
+template <bool kBias>
 __global__ void __launch_bounds__(kThreadsWs, 4)
 attention_ws_kernel(const __grid_constant__ CUtensorMap tm, __nv_bfloat16* __restrict__ out,
-                    const int32_t* __restrict__ seq_start, const int32_t* __restrict__ seq_len, int heads, int chunk) {
+                    const int32_t* __restrict__ seq_start, const int32_t* __restrict__ seq_len, int heads, int chunk,
+                    const __nv_bfloat16* __restrict__ bias, int64_t bias_head_stride, int bias_ld, int bias_tmax) {
     const int s = blockIdx.z, h = blockIdx.y;
     const int len = __shfl_sync(0xffffffffu, seq_len[s], 0);
     const int q0 = blockIdx.x * kBQ;
@@ -224,14 +237,21 @@ attention_ws_kernel(const __grid_constant__ CUtensorMap tm, __nv_bfloat16* __res
         const uint32_t t_lane = tmem + ((uint32_t)(warp * 32) << 16);
         const uint32_t t_o = t_lane + 64;
         float m2 = -INFINITY, l = 0.f;
+        // relative-position bias row of this query: element j holds the term of key j (m = tmax - 1 - qi + j of the table)
+        const unsigned short* brow = nullptr;
+        if (kBias) {
+            const int qc = min(qi, len - 1);   // padding lanes of the last tile read a valid row
+            brow = reinterpret_cast<const unsigned short*>(bias) + (size_t)h * bias_head_stride +
+                   (size_t)(start + qc) * bias_ld + (bias_tmax - 1 - qc);
+        }
         for (int j = 0; j < nkt; ++j) {
             const int b = j & 1;
             mbar_wait(&s_full[b], (uint32_t)((j >> 1) & 1));
             tc_fence_after();
             uint64_t* o_stable = &kv_empty[(j + kNS - 1) % kNS];                      // completes with PV(j - 1)
             const uint32_t o_phase = (uint32_t)((((j > 0 ? j - 1 : 0)) / kNS) & 1);
-            if (j + 1 == nkt && nk_last == 16) softmax_tile<16>(t_lane + (uint32_t)(b * kBK), t_o, j * kBK, lim, j, m2, l, o_stable, o_phase);
-            else softmax_tile<32>(t_lane + (uint32_t)(b * kBK), t_o, j * kBK, lim, j, m2, l, o_stable, o_phase);
+            if (j + 1 == nkt && nk_last == 16) softmax_tile<16, kBias>(t_lane + (uint32_t)(b * kBK), t_o, j * kBK, lim, j, m2, l, o_stable, o_phase, brow);
+            else softmax_tile<32, kBias>(t_lane + (uint32_t)(b * kBK), t_o, j * kBK, lim, j, m2, l, o_stable, o_phase, brow);
             tc_fence_before();
             __syncwarp();
             if ((tid & 31) == 0) mbar_arrive(&p_ready[b]);
@@ -269,18 +289,32 @@ cudaError_t attention_ws_init_device() {
     static std::atomic<uint64_t> done{0};
     static std::mutex mu;
     return once_per_device(done, mu, [] {
-        return cudaFuncSetAttribute(attention_ws_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem);
+        cudaError_t e = cudaFuncSetAttribute(attention_ws_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(attention_ws_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem);
+        return e;
     });
 }
 
 cudaError_t launch_attention_ws(const __nv_bfloat16* qkv, int64_t rows, __nv_bfloat16* out, const int32_t* seq_start,
                                 const int32_t* seq_len, int nseq, int max_len, int heads, int chunk, cudaStream_t st) {
+    return launch_attention_ws_ex(qkv, rows, 3 * heads * kD, out, seq_start, seq_len, nseq, max_len, heads, chunk, nullptr, 0, 0,
+                                  0, st);
+}
+
+cudaError_t launch_attention_ws_ex(const __nv_bfloat16* qkv, int64_t rows, int qkv_ld, __nv_bfloat16* out,
+                                   const int32_t* seq_start, const int32_t* seq_len, int nseq, int max_len, int heads, int chunk,
+                                   const __nv_bfloat16* bias, int64_t bias_head_stride, int bias_ld, int bias_tmax,
+                                   cudaStream_t st) {
     const cudaError_t ie = attention_ws_init_device();
     if (ie != cudaSuccess) return ie;
     CUtensorMap tm;
-    if (!encode_2d(&tm, qkv, (uint64_t)3 * heads * kD, (uint64_t)rows, (uint64_t)3 * heads * kD, kBK)) return cudaErrorInvalidValue;
+    if (!encode_2d(&tm, qkv, (uint64_t)qkv_ld, (uint64_t)rows, (uint64_t)qkv_ld, kBK)) return cudaErrorInvalidValue;
     dim3 grid((max_len + kBQ - 1) / kBQ, heads, nseq);
-    attention_ws_kernel<<<grid, kThreadsWs, kSmem, st>>>(tm, out, seq_start, seq_len, heads, chunk);
+    if (bias != nullptr)
+        attention_ws_kernel<true><<<grid, kThreadsWs, kSmem, st>>>(tm, out, seq_start, seq_len, heads, chunk, bias,
+                                                                   bias_head_stride, bias_ld, bias_tmax);
+    else
+        attention_ws_kernel<false><<<grid, kThreadsWs, kSmem, st>>>(tm, out, seq_start, seq_len, heads, chunk, nullptr, 0, 0, 0);
     return cudaGetLastError();
 }
 

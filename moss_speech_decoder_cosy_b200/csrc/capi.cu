@@ -70,6 +70,19 @@ int mossdec_hift(mossdec_handle* h, int32_t B, const int32_t* lens, const float*
                         (cudaStream_t)stream);
 }
 
+int mossdec_hift_skip(mossdec_handle* h, int32_t B, const int32_t* lens, const int32_t* mel_skip, const float* mel,
+                      const float* nsf_noise, float* wav_out, float* source_out, uint64_t seed, void* stream) {
+    return h->eng->hift(B, lens, mel, nullptr, 0, nullptr, nsf_noise, wav_out, source_out, seed, MOSSDEC_TIME_MAJOR,
+                        (cudaStream_t)stream, mel_skip);
+}
+
+int mossdec_token2mel(mossdec_handle* h, int32_t B, const int32_t* n_tok, const int64_t* tokens, const int32_t* prompt_frames,
+                      const float* prompt_feat, const float* embedding, int32_t ctx_len, int32_t chunk_tokens,
+                      int32_t est_chunk_frames, int32_t n_steps, float cfg_rate, float* mel_out, void* stream) {
+    return h->eng->token2mel(B, n_tok, tokens, prompt_frames, prompt_feat, embedding, ctx_len, chunk_tokens, est_chunk_frames,
+                             n_steps, cfg_rate, mel_out, (cudaStream_t)stream);
+}
+
 int mossdec_fade_in_out(mossdec_handle* h, float* speech, const float* prev_tail, const float* window2n, int32_t n,
                         void* stream) {
     return h->eng->fade_in_out(speech, prev_tail, window2n, n, (cudaStream_t)stream);

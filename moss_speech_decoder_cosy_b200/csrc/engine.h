@@ -107,7 +107,7 @@ class Engine {
     // HiFT vocoder for B ragged mel segments ([80, T_b] back to back) -> wav [480 T_b] back to back.
     int hift(int B, const int32_t* lens, const float* mel, const float* cache_source, int cache_stride,
              const int32_t* cache_len, const float* nsf_noise, float* wav_out, float* source_out, uint64_t seed,
-             int flags, cudaStream_t st);
+             int flags, cudaStream_t st, const int32_t* mel_skip = nullptr);
     // per-launch device timing of the GEMM (0), attention (1) and fused-FFN (2) kernels with CUDA events on the launch stream
     void set_profile(bool on) { profile_ = on; }
     int profile_read(double* out9);
@@ -116,6 +116,12 @@ class Engine {
     // test hook: copy a named intermediate of the last call to the host; returns floats copied or -1
     int debug_read(const char* name, void* host_dst, size_t bytes);
     int fade_in_out(float* speech, const float* prev_tail, const float* window2n, int n, cudaStream_t st);
+    // CausalMaskedDiffWithXvec.inference for B utterances (flow.py:237-283; engine_encoder.cu): tokens = ragged device
+    // int64 (prompt + new tokens + `ctx` look-ahead tokens per utterance, n_tok[b] each, HOST counts), prompt_feat =
+    // ragged device [F_b, 80], embedding device [B, 192] -> mel_out ragged time-major [4 (n_tok[b] - ctx), 80].
+    int token2mel(int B, const int32_t* n_tok, const int64_t* tokens, const int32_t* prompt_frames, const float* prompt_feat,
+                  const float* embedding, int ctx, int chunk_tokens, int est_chunk_frames, int n_steps, float cfg_rate,
+                  float* mel_out, cudaStream_t st);
     // matcha mel_spectrogram (n_fft 1920, hop 480, 80 mels, 24 kHz, fmax 8000, center False; mel_kernels.cu):
     // wav device [L] -> mel_out device [80, T], T = (L - 480) / 480 + 1.  Returns T, negative on error.
     int mel_spectrogram(const float* wav, int64_t L, float* mel_out, cudaStream_t st);
@@ -168,6 +174,13 @@ class Engine {
                           int row0 = 0);
     int time_bias(const float* t_dev, int nt, float* temb, float* tbias, cudaStream_t st);
     int finalize_hift();
+    int finalize_encoder();
+    int encode_group(int b0, int b1, const int32_t* n_tok, const int64_t* tok_off, const int64_t* mel_off,
+                     const int32_t* prompt_frames, const int64_t* feat_off, const int64_t* tokens, const float* prompt_feat,
+                     int ctx, int chunk_tokens, float* mu, float* cond, cudaStream_t st);
+    int encoder_layer(int l, int R, const int32_t* row_seq, const int32_t* seq_start, const int32_t* seq_len, int nseq,
+                      int max_len, int chunk, const __nv_bfloat16* P, int npad, int tmax, bool emit_bf16, cudaStream_t st);
+    int encoder_pos_tables(int l0, int l1, int tmax, int npad, __nv_bfloat16* P, cudaStream_t st);
     int hift_group(int b0, int b1, const int32_t* lens, int64_t mel_off0, int64_t wav_off0, const float* mel,
                    const float* cache_source, int cache_stride, const int32_t* cache_len, const float* nsf_noise,
                    float* wav_out, float* source_out, uint64_t seed, int flags, cudaStream_t st);
@@ -224,6 +237,15 @@ class Engine {
     DeviceBuffer ws_cv1_;
     DeviceBuffer ws_mel_;   // prompt mel front end (mel_kernels.cu)
 
+    // ---- encoder front end (engine_encoder.cu)
+    DeviceBuffer ws_enc_, ws_enc_layout_, ws_mu_;
+    bool has_encoder_ = false;
+    std::string enc_missing_;
+    float *enc_x32_ = nullptr, *enc_pe_ = nullptr, *enc_ptmp_ = nullptr;
+    __nv_bfloat16 *enc_xn_ = nullptr, *enc_qkv_ = nullptr, *enc_att_ = nullptr, *enc_ffh_ = nullptr, *enc_bias_ = nullptr;
+    int enc_tmax_cached_ = -1;
+    const void *enc_ptok_cached_ = nullptr, *enc_pmel_cached_ = nullptr;
+
     // ---- hift workspace
     DeviceBuffer ws_hift_, ws_hift_layout_;
     bool has_hift_ = false;
@@ -250,6 +272,7 @@ class Engine {
     void bw_end(cudaStream_t st) {
         if (profile_) cudaEventRecord(bw_prof_.back().b, st);
     }
+    const int32_t* hift_mel_skip_ = nullptr;   // (valid during a hift() call) leading frames of every mel block to skip
     int64_t hift_group_frames_ = 8192;  // frames per HiFT group (bounds the stage-2 working set)
 };
 

@@ -108,6 +108,7 @@ int Engine::set_tensor(const char* name, const void* host, int dtype, int ndim, 
     DeviceGuard g(device_);
     drop_graphs();            // captured launches hold weight pointers
     solve_tbias_steps_ = 0;
+    enc_tmax_cached_ = -1;
     DevTensor t;
     t.dtype = dtype;
     size_t n = 1;
@@ -258,7 +259,8 @@ int Engine::finalize() {
     }
     if (!missing_.empty()) return fail("missing estimator tensors: " + missing_);
     finalized_ = true;
-    finalize_hift();  // HiFT tensors are optional at load time; mossdec_hift fails loudly if they are absent
+    finalize_hift();     // HiFT tensors are optional at load time; mossdec_hift fails loudly if they are absent
+    finalize_encoder();  // likewise the encoder front end (mossdec_token2mel)
     return 0;
 }
 

@@ -183,7 +183,7 @@ int Engine::reserve_hift(int64_t rows_f, int nseq) {
 
 int Engine::hift(int B, const int32_t* lens, const float* mel, const float* cache_source, int cache_stride,
                  const int32_t* cache_len, const float* nsf_noise, float* wav_out, float* source_out, uint64_t seed,
-                 int flags, cudaStream_t st) {
+                 int flags, cudaStream_t st, const int32_t* mel_skip) {
     DeviceGuard g(device_);
     if (!finalized_) return fail("weights not finalized");
     if (!has_hift_) return fail("HiFT tensors missing: " + missing_);
@@ -191,6 +191,8 @@ int Engine::hift(int B, const int32_t* lens, const float* mel, const float* cach
     for (int b = 0; b < B; ++b)
         if (lens[b] <= 0) return fail("hift: sequence length must be positive");
     if (cfg_.hift_base != 512) return fail("hift: only base_channels = 512 is built");
+    if (mel_skip != nullptr && !(flags & 1)) return fail("hift: mel_skip needs the time-major mel layout");
+    hift_mel_skip_ = mel_skip;
     // split the batch into groups of <= hift_group_frames_ frames so the stage-2 working set stays bounded
     int b0 = 0;
     int64_t mel_off = 0, wav_off = 0;
@@ -202,7 +204,7 @@ int Engine::hift(int B, const int32_t* lens, const float* mel, const float* cach
                        source_out, seed, flags, st))
             return -1;
         for (int b = b0; b < b1; ++b) {
-            mel_off += (int64_t)lens[b] * cfg_.n_feats;
+            mel_off += (int64_t)(lens[b] + (mel_skip ? mel_skip[b] : 0)) * cfg_.n_feats;
             wav_off += (int64_t)lens[b] * 480;
         }
         b0 = b1;
@@ -244,11 +246,12 @@ int Engine::hift_group(int b0, int b1, const int32_t* lens, int64_t mel_off0, in
         int64_t mo = mel_off0, wo = wav_off0;
         for (int s = 0; s < nseq; ++s) {
             r += kGuardF;
+            const int skip = hift_mel_skip_ ? hift_mel_skip_[b0 + s] : 0;   // leading (prompt) frames of the block to pass over
             h_start[s] = r;
             h_len[s] = lens[b0 + s];
-            h_mel[s] = mo;
+            h_mel[s] = mo + (int64_t)skip * cfg_.n_feats;
             h_wav[s] = wo;
-            mo += (int64_t)h_len[s] * cfg_.n_feats;
+            mo += (int64_t)(h_len[s] + skip) * cfg_.n_feats;
             wo += (int64_t)h_len[s] * 480;
             r += h_len[s];
             h_clen[s] = cache_len ? cache_len[b0 + s] : 0;

@@ -81,6 +81,7 @@ struct GemmOperandA {
 struct GemmProblem {
     GemmOperandA a[2];
     const __nv_bfloat16* w = nullptr;  // [N, K] K-major, K = 64 * total k-blocks
+    int64_t w_ld = 0;                  // row stride of w in elements (0 = K); > K selects a column slab of a wider matrix
     int32_t M = 0;                     // output rows; buffers must be padded to a multiple of 128 rows
     int32_t N = 0;
     int32_t BN = 0;                    // n-tile (multiple of 16, <= 256)

@@ -861,7 +861,7 @@ cudaError_t gemm_tc_launch(const GemmProblem& g, int num_sms, cudaStream_t strea
         tA1 = tA0;
     }
     const uint64_t K = (uint64_t)kp.total_kb * kGemmBK;
-    if (!encode_2d(&tB, g.w, K, (uint64_t)g.N, K, (uint32_t)g.BN)) return cudaErrorInvalidValue;
+    if (!encode_2d(&tB, g.w, K, (uint64_t)g.N, g.w_ld > 0 ? (uint64_t)g.w_ld : K, (uint32_t)g.BN)) return cudaErrorInvalidValue;
 
     // "bias + activation + mask -> bf16" epilogues leave through TMA stores (epi_fast)
     const GemmEpilogue& e = g.epi;

@@ -41,6 +41,44 @@ void launch_est_pack(const FlowLayout& L, int nrows, const float* x, const float
 // scores in TMEM; qkv has `rows` rows of 3*H*64 bf16.
 cudaError_t launch_attention_ws(const __nv_bfloat16* qkv, int64_t rows, __nv_bfloat16* out, const int32_t* seq_start,
                                 const int32_t* seq_len, int nseq, int max_len, int heads, int chunk, cudaStream_t st);
+// general form: qkv rows of `qkv_ld` bf16 ([q | k | v | ...], q / k / v of head h at columns h*64, (H+h)*64, (2H+h)*64), output
+// rows of H*64; optional additive score bias (bf16) bias[h][row][bias_tmax - 1 - t + j] for query position t and key j
+// (the shifted relative-position term of the conformer encoder, attention.py:223-244, 317-324), NULL = none.
+cudaError_t launch_attention_ws_ex(const __nv_bfloat16* qkv, int64_t rows, int qkv_ld, __nv_bfloat16* out,
+                                   const int32_t* seq_start, const int32_t* seq_len, int nseq, int max_len, int heads, int chunk,
+                                   const __nv_bfloat16* bias, int64_t bias_head_stride, int bias_ld, int bias_tmax,
+                                   cudaStream_t st);
+
+// ------------------------------------------------------------------------------------------------ encoder front end
+// Packed token-rate layout of a group of utterances (device pointers): sequence b owns token rows
+// [seq_start[b], seq_start[b] + n_tok[b]) (prompt + new tokens + look-ahead context), >= 4 zero guard rows between
+// sequences.  The mel-rate matrices use the same axis scaled by 4 (the x4 up-conv is a polyphase GEMM whose
+// [rows, 4 * 512] output IS the [4 * rows, 512] mel-rate matrix).
+struct EncLayout {
+    int32_t rows;                  // token-rate rows incl. guards, multiple of 128 (mel-rate rows = 4 * rows)
+    int32_t nseq;
+    const int32_t* row_seq_all;    // [rows]      sequence id of rows that hold a token (context included), -1 on guard rows
+    const int32_t* row_seq_main;   // [rows]      the same, but -1 on the look-ahead context rows
+    const int32_t* row_seq_mel;    // [4 * rows]  mel-rate rows of the main tokens
+    const int32_t* seq_start;      // [nseq] first token row
+    const int32_t* seq_len;        // [nseq] main tokens (attention length at token rate)
+    const int32_t* seq_start4;     // [nseq] 4 * seq_start
+    const int32_t* seq_len4;       // [nseq] 4 * seq_len
+    const int32_t* prompt_frames;  // [nseq] prompt mel frames F_b
+    const int64_t* tok_off;        // [nseq] offset into the ragged token array
+    const int64_t* mel_off;        // [nseq] FRAME offset into the ragged mu / cond outputs
+    const int64_t* feat_off;       // [nseq] FRAME offset into the ragged prompt_feat input
+};
+void launch_enc_gather(const EncLayout& L, const int64_t* tokens, const __nv_bfloat16* emb, int vocab, __nv_bfloat16* out,
+                       cudaStream_t st);
+void launch_layernorm512(const float* x, int rows, const float* gamma, const float* beta, float eps, float scale,
+                         const int32_t* row_seq, float* out_f32, __nv_bfloat16* out_bf16, cudaStream_t st);
+void launch_rel_pos_table(int tmax, int rows, float* pe, cudaStream_t st);
+void launch_f32_to_bf16(const float* x, int64_t n, __nv_bfloat16* y, cudaStream_t st);
+void launch_spk_project(const float* emb, int B, int dim_in, const float* w, const float* bias, int dim_out, float* out,
+                        cudaStream_t st);
+void launch_enc_finish(const EncLayout& L, const float* mu_rows, const float* prompt_feat, float* mu, float* cond,
+                       cudaStream_t st);
 
 // ------------------------------------------------------------------------------------------------ HiFT
 // Packed layout of one group of mel segments: sequence b owns frame rows [seq_start[b], seq_start[b] + seq_len[b]);

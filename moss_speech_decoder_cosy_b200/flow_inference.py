@@ -18,7 +18,7 @@ from collections import defaultdict
 import numpy as np
 import torch
 
-from . import frontend, lib, mel_frontend, synth, weights
+from . import lib, mel_frontend, synth, weights
 
 TOKEN_MEL_RATIO = 4
 PRE_LOOKAHEAD = 3
@@ -162,10 +162,10 @@ class AudioDecoder(torch.nn.Module):
         tensors = weights.pack_estimator(flow_state_dict)
         tensors["flow.rand_noise"] = synth.synth_noise_bank()[0].contiguous()   # flow_matching.py:202-203
         tensors.update(weights.pack_hift(hift_state_dict))
+        tensors.update(weights.pack_encoder(flow_state_dict))
         tensors.update(mel_frontend.pack_mel_tensors())
         self.engine.load_tensors(tensors)
         self.engine.finalize()
-        self.enc_weights = frontend.EncoderWeights(flow_state_dict, self.device)
         self.flow = _FlowFacade(self)
         self.hift = _HiftFacade(self)
         self.sample_rate = self.scratch_configs["sample_rate"]
@@ -217,93 +217,79 @@ class AudioDecoder(torch.nn.Module):
 
         tokens[b]: int [1, N_b]; prompt_tokens[b]: int [1, P_b]; prompt_feats[b]: float [1, F_b, 80];
         embeddings: float [B, 192].  Returns ragged time-major mel [sum T_b, 80] (prompt frames included), the
-        per-utterance frame counts T_b and prompt frame counts F_b."""
+        per-utterance frame counts T_b and prompt frame counts F_b.  Host work: one concatenation per input kind into
+        pinned memory; everything else is mossdec_token2mel."""
         dev = self.device
         B = len(tokens)
-        rows = [torch.cat([prompt_tokens[b].reshape(-1).long().cpu(), tokens[b].reshape(-1).long().cpu()])
-                for b in range(B)]
-        lens_tok = [int(r.numel()) for r in rows]
-        tok = torch.zeros(B, max(lens_tok), dtype=torch.long).pin_memory()
-        for b, r in enumerate(rows):
-            tok[b, :lens_tok[b]] = r
+        rows = [t.reshape(-1) for b in range(B) for t in (prompt_tokens[b], tokens[b])]
+        n_tok = [int(rows[2 * b].numel() + rows[2 * b + 1].numel()) for b in range(B)]
+        tok = torch.cat([r.long() for r in rows]).pin_memory()
         F_ = [int(pf.shape[1]) for pf in prompt_feats]
         feats = [pf.reshape(-1, 80) for pf in prompt_feats if pf.shape[1]]
-        feat_cat = torch.cat(feats, 0).float() if feats else torch.zeros(0, 80)
-        embeddings = embeddings.float()
+        feat_cat = (torch.cat(feats, 0).float() if feats else torch.zeros(1, 80)).pin_memory()
+        embeddings = embeddings.float().contiguous()
         self.last_h2d_bytes = tok.nbytes + feat_cat.nbytes + embeddings.nbytes   # what this call copies host -> device
-        return self.flow_device(tok.to(dev, non_blocking=True), lens_tok, feat_cat.to(dev, non_blocking=True), F_,
+        return self.flow_device(tok.to(dev, non_blocking=True), n_tok, feat_cat.to(dev, non_blocking=True), F_,
                                 embeddings.to(dev, non_blocking=True), streaming, finalize)
 
     @torch.inference_mode()
-    def flow_device(self, tok, lens_tok, prompt_feat_cat, prompt_frames, embeddings, streaming, finalize):
-        """Device-resident core of flow_batch: tok int64 [B, Lmax] (prompt + new tokens, right padded), lens_tok host
-        list, prompt_feat_cat [sum F_b, 80] (prompt mels back to back), prompt_frames host list F_b, embeddings
-        [B, 192] -- all tensors already on the device."""
-        dev = self.device
-        B = len(lens_tok)
+    def flow_device(self, tok, n_tok, prompt_feat_cat, prompt_frames, embeddings, streaming, finalize):
+        """Device-resident core of flow_batch: tok int64 [sum n_tok] (prompt + new tokens of every utterance back to back),
+        n_tok host list, prompt_feat_cat fp32 [sum F_b, 80] (prompt mels back to back), prompt_frames host list F_b,
+        embeddings fp32 [B, 192] -- all tensors already on the device."""
         ctx = 0 if finalize else PRE_LOOKAHEAD
-        if min(lens_tok) - ctx <= 0:
+        if min(n_tok) - ctx <= 0:
             raise ValueError("every utterance needs at least one token besides the look-ahead context")
-        lens_t = torch.tensor(lens_tok, dtype=torch.long).to(dev, non_blocking=True)
-        chunk_tokens = self.static_chunk_size if streaming else 0
-        mu_pad, main = frontend.encode(self.enc_weights, tok, lens_t, ctx, chunk_tokens)
-        T = [(n - ctx) * TOKEN_MEL_RATIO for n in lens_tok]
+        T = [(n - ctx) * TOKEN_MEL_RATIO for n in n_tok]
         F_ = list(prompt_frames)
-        Tmax = mu_pad.shape[1]
-        if all(t == Tmax for t in T):
-            mu = mu_pad.reshape(-1, 80)
-        else:
-            valid = torch.arange(Tmax, device=dev).unsqueeze(0) < (main * TOKEN_MEL_RATIO).unsqueeze(1)
-            mu = mu_pad[valid]
         if any(f > t for f, t in zip(F_, T)):
             raise ValueError("prompt_feat longer than the decoded sequence")
-        cond = torch.zeros(sum(T), 80, device=dev)                    # flow.py:268-270
-        if sum(F_):
-            dst, off = [], 0
-            for t, f in zip(T, F_):
-                dst.append(torch.arange(off, off + f))
-                off += t
-            cond.index_copy_(0, torch.cat(dst).to(dev, non_blocking=True), prompt_feat_cat.float())
-        spks = frontend.speaker_projection(self.enc_weights, embeddings)
-        mel = self.engine.flow_solve(T, mu.reshape(-1), spks, cond.reshape(-1), n_steps=self.n_timesteps,
-                                     cfg_rate=self.inference_cfg_rate,
-                                     chunk=self.estimator_chunk_frames if streaming else 0,
-                                     time_major=True).view(-1, 80)
+        mel = self.engine.token2mel(n_tok, tok, F_, prompt_feat_cat, embeddings, ctx,
+                                    self.static_chunk_size if streaming else 0,
+                                    self.estimator_chunk_frames if streaming else 0,
+                                    n_steps=self.n_timesteps, cfg_rate=self.inference_cfg_rate)
         return {"mel": mel, "frames": T, "prompt_frames": F_}
 
     @torch.inference_mode()
     def vocode_generated(self, r, nsf_noise=None, seed=None):
-        """Strip the prompt frames of a flow result (flow.py:281) and run the vocoder on the generated part."""
+        """Run the vocoder on the generated part of a flow result (the prompt frames are passed over, flow.py:281)."""
         T, F_ = r["frames"], r["prompt_frames"]
         gen = [t - f for t, f in zip(T, F_)]
-        if any(F_):
-            idx, off = [], 0
-            for t, f in zip(T, F_):
-                idx.append(torch.arange(off + f, off + t))
-                off += t
-            mel = r["mel"].index_select(0, torch.cat(idx).to(self.device, non_blocking=True))
-        else:
-            mel = r["mel"]
-        wav, _ = self.engine.hift(gen, mel.reshape(-1), nsf_noise=self._noise_for(gen, nsf_noise),
-                                  seed=self._next_seed() if seed is None else seed, want_source=False, time_major=True)
-        return {"wav": wav, "wav_lens": [g * 480 for g in gen], "mel": mel, "mel_lens": gen}
+        wav, _ = self.engine.hift_skip(gen, F_, r["mel"], nsf_noise=self._noise_for(gen, nsf_noise),
+                                       seed=self._next_seed() if seed is None else seed)
+        return {"wav": wav, "wav_lens": [g * 480 for g in gen], "flow": r, "mel_lens": gen}
+
+    def generated_mel(self, r):
+        """Ragged time-major mel [sum 4 N_b, 80] of the generated frames of a flow result."""
+        if not any(r["prompt_frames"]):
+            return r["mel"]
+        parts, off = [], 0
+        for t, f in zip(r["frames"], r["prompt_frames"]):
+            parts.append(r["mel"][off + f:off + t])
+            off += t
+        return torch.cat(parts, 0)
 
     @torch.inference_mode()
-    def decode_batch(self, tokens, prompt_tokens=None, prompt_feats=None, embeddings=None, nsf_noise=None, seed=None):
+    def decode_batch(self, tokens, prompt_tokens=None, prompt_feats=None, embeddings=None, nsf_noise=None, seed=None,
+                     want_mel=False):
         """token2wav (flow_inference.py:94-123) for B independent utterances in one pass.
 
-        Returns {"wav": ragged fp32 [sum 1920 N_b], "wav_lens", "mel": ragged time-major [sum 4 N_b, 80], "mel_lens"}."""
+        Returns {"wav": ragged fp32 [sum 1920 N_b], "wav_lens", "mel_lens", "flow": the flow result}; with want_mel also
+        "mel": ragged time-major [sum 4 N_b, 80] (the generated frames gathered out of the flow result)."""
         B = len(tokens)
         prompt_tokens = prompt_tokens or [torch.zeros(1, 0, dtype=torch.int32)] * B
         prompt_feats = prompt_feats or [torch.zeros(1, 0, 80)] * B
         if embeddings is None:
             embeddings = torch.zeros(B, 192)
         r = self.flow_batch(tokens, prompt_tokens, prompt_feats, embeddings, streaming=False, finalize=True)
-        return self.vocode_generated(r, nsf_noise, seed)
+        out = self.vocode_generated(r, nsf_noise, seed)
+        if want_mel:
+            out["mel"] = self.generated_mel(r)
+        return out
 
     def token2wav_batch(self, tokens, prompt_tokens=None, prompt_feats=None, embeddings=None, **kw):
         """List-of-utterances convenience wrapper: returns [(tts_speech [1, 1920 N_b], tts_mel [1, 80, 4 N_b])]."""
-        r = self.decode_batch(tokens, prompt_tokens, prompt_feats, embeddings, **kw)
+        r = self.decode_batch(tokens, prompt_tokens, prompt_feats, embeddings, want_mel=True, **kw)
         out, wo, mo = [], 0, 0
         for wl, ml in zip(r["wav_lens"], r["mel_lens"]):
             out.append((r["wav"][wo:wo + wl].view(1, -1), r["mel"][mo:mo + ml].t().unsqueeze(0)))

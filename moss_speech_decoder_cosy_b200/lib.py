@@ -51,6 +51,10 @@ def load_library():
     lib.mossdec_hift.argtypes = [vp, i32, ctypes.POINTER(i32), vp, vp, i32, ctypes.POINTER(i32), vp, vp, vp,
                                  ctypes.c_uint64, i32, vp]
     lib.mossdec_hift.restype = i32
+    lib.mossdec_hift_skip.argtypes = [vp, i32, ctypes.POINTER(i32), ctypes.POINTER(i32), vp, vp, vp, vp, ctypes.c_uint64, vp]
+    lib.mossdec_hift_skip.restype = i32
+    lib.mossdec_token2mel.argtypes = [vp, i32, ctypes.POINTER(i32), vp, ctypes.POINTER(i32), vp, vp, i32, i32, i32, i32, f32, vp, vp]
+    lib.mossdec_token2mel.restype = i32
     lib.mossdec_fade_in_out.argtypes = [vp, vp, vp, vp, i32, vp]
     lib.mossdec_fade_in_out.restype = i32
     lib.mossdec_mel_spectrogram.argtypes = [vp, vp, i64, vp, vp]
@@ -95,7 +99,7 @@ EXPORTED_SYMBOLS = [
     "mossdec_launch_count", "mossdec_reset_launch_count", "mossdec_debug_read", "mossdec_profile",
     "mossdec_profile_read", "mossdec_set_hift_group_frames", "mossdec_cv1_resnet_block", "mossdec_cv1_downsample",
     "mossdec_cv1_upsample", "mossdec_cv1_block1d", "mossdec_reserve", "mossdec_set_graph_mode", "mossdec_graph_replays",
-    "mossdec_device", "mossdec_profile_named", "mossdec_mel_spectrogram",
+    "mossdec_device", "mossdec_profile_named", "mossdec_mel_spectrogram", "mossdec_hift_skip", "mossdec_token2mel",
 ]
 
 
@@ -205,6 +209,30 @@ class Engine:
                                           _ptr(nsf_noise), _ptr(wav), _ptr(src), int(seed), int(bool(time_major)),
                                           self._stream()), "hift")
         return wav, src
+
+    def hift_skip(self, lens, skip, mel, nsf_noise=None, seed=0, want_source=False):
+        """Vocoder over the generated part of flow results: block b of `mel` (time-major) holds skip[b] + lens[b] frames."""
+        total = int(sum(lens)) * 480
+        wav = torch.empty(total, dtype=torch.float32, device=mel.device)
+        src = torch.empty(total, dtype=torch.float32, device=mel.device) if want_source else None
+        if nsf_noise is not None:
+            nsf_noise = nsf_noise.float().contiguous()
+        self._check(self.lib.mossdec_hift_skip(self.h, len(lens), _i32_array(lens), _i32_array(skip), _ptr(mel), _ptr(nsf_noise),
+                                               _ptr(wav), _ptr(src), int(seed), self._stream()), "hift_skip")
+        return wav, src
+
+    def token2mel(self, n_tok, tokens, prompt_frames, prompt_feat, embedding, ctx_len, chunk_tokens, est_chunk_frames,
+                  n_steps=10, cfg_rate=0.7):
+        """CausalMaskedDiffWithXvec.inference for a ragged batch (mossdec_token2mel): tokens int64 CUDA (ragged),
+        prompt_feat fp32 CUDA ragged [F_b, 80], embedding fp32 CUDA [B, 192] -> mel fp32 ragged time-major [sum T_b, 80]."""
+        B = len(n_tok)
+        frames = sum(4 * (int(n) - ctx_len) for n in n_tok)
+        out = torch.empty(frames, 80, dtype=torch.float32, device=tokens.device)
+        self._check(self.lib.mossdec_token2mel(self.h, B, _i32_array(n_tok), _ptr(tokens), _i32_array(prompt_frames),
+                                               _ptr(prompt_feat), _ptr(embedding), int(ctx_len), int(chunk_tokens),
+                                               int(est_chunk_frames), int(n_steps), float(cfg_rate), _ptr(out), self._stream()),
+                    "token2mel")
+        return out
 
     def fade_in_out(self, speech, prev_tail, window2n):
         n = prev_tail.numel()

@@ -230,3 +230,59 @@ def pack_cv1_upsample(sd, src, dst):
     """matcha Upsample1D (decoder.py:120-158) ConvTranspose1d(C, C, 4, 2, 1): polyphase [2C, 3C], bias repeated per phase."""
     w = sd[f"{src}.conv.weight"].float()
     return {f"{dst}.w": _bf16(convtranspose_polyphase(w, 2, 1)), f"{dst}.b": _f32(sd[f"{src}.conv.bias"].float().repeat(2))}
+
+
+def pack_encoder(sd, heads=8):
+    """Token -> mu front end (csrc/engine_encoder.cu): input_embedding, spk_embed_affine_layer, encoder_proj (flow.py:180-183)
+    and UpsampleConformerEncoder (upsample_encoder.py:105-242; key names: SURVEY.md appendix A)."""
+    out = {}
+    g = lambda k: sd[k].float()
+    out["enc.emb"] = _bf16(g("input_embedding.weight"))
+    out["spk.w"], out["spk.b"] = _f32(g("spk_embed_affine_layer.weight")), _f32(g("spk_embed_affine_layer.bias"))
+    out["enc.proj.w"], out["enc.proj.b"] = _bf16(g("encoder_proj.weight")), _f32(g("encoder_proj.bias"))
+    e = "encoder."
+    for i, n in enumerate(("embed", "up_embed")):                                   # LinearNoSubsampling, subsampling.py:70-93
+        out[f"enc.embed{i}.w"], out[f"enc.embed{i}.b"] = _bf16(g(e + f"{n}.out.0.weight")), _f32(g(e + f"{n}.out.0.bias"))
+        out[f"enc.embed{i}.ln.g"], out[f"enc.embed{i}.ln.b"] = _f32(g(e + f"{n}.out.1.weight")), _f32(g(e + f"{n}.out.1.bias"))
+    # PreLookaheadLayer (upsample_encoder.py:67-98): conv1 tap j reads token t + j, conv2 tap j reads token t + j - 2
+    out["enc.pl.c1.w"] = _bf16(conv_weight_taps(g(e + "pre_lookahead_layer.conv1.weight")))
+    out["enc.pl.c1.b"] = _f32(g(e + "pre_lookahead_layer.conv1.bias"))
+    out["enc.pl.c2.w"] = _bf16(conv_weight_taps(g(e + "pre_lookahead_layer.conv2.weight")))
+    out["enc.pl.c2.b"] = _f32(g(e + "pre_lookahead_layer.conv2.bias"))
+    names = []
+    for grp in ("encoders", "up_encoders"):
+        i = 0
+        while e + f"{grp}.{i}.norm_mha.weight" in sd:
+            names.append(f"{grp}.{i}")
+            i += 1
+    if len(names) != 10:
+        raise ValueError(f"expected 6 + 4 conformer layers, found {len(names)}")
+    for l, n in enumerate(names):
+        p, a, o = e + n + ".", e + n + ".self_attn.", f"enc.L{l}."
+        dk = g(a + "linear_q.weight").shape[0] // heads
+        sc = 1.0 / math.sqrt(dk)
+        wq, bq = g(a + "linear_q.weight"), g(a + "linear_q.bias")
+        u, v = g(a + "pos_bias_u").reshape(-1), g(a + "pos_bias_v").reshape(-1)    # [heads, dk] head-major == channel order
+        # [(q + pos_bias_u) / sqrt(dk) | k | v | (q + pos_bias_v) / sqrt(dk)]   (attention.py:305-324)
+        out[o + "qkv.w"] = _bf16(torch.cat([wq * sc, g(a + "linear_k.weight"), g(a + "linear_v.weight"), wq * sc], 0))
+        out[o + "qkv.b"] = _f32(torch.cat([(bq + u) * sc, g(a + "linear_k.bias"), g(a + "linear_v.bias"), (bq + v) * sc], 0))
+        out[o + "pos.wt"] = _f32(g(a + "linear_pos.weight").t())                    # [in, out], fp32 (csrc/f0_fp32.cu GEMM)
+        out[o + "o.w"], out[o + "o.b"] = _bf16(g(a + "linear_out.weight")), _f32(g(a + "linear_out.bias"))
+        out[o + "n1.g"], out[o + "n1.b"] = _f32(g(p + "norm_mha.weight")), _f32(g(p + "norm_mha.bias"))
+        out[o + "n2.g"], out[o + "n2.b"] = _f32(g(p + "norm_ff.weight")), _f32(g(p + "norm_ff.bias"))
+        out[o + "ff1.w"], out[o + "ff1.b"] = _bf16(g(p + "feed_forward.w_1.weight")), _f32(g(p + "feed_forward.w_1.bias"))
+        out[o + "ff2.w"], out[o + "ff2.b"] = _bf16(g(p + "feed_forward.w_2.weight")), _f32(g(p + "feed_forward.w_2.bias"))
+    # Upsample1D (upsample_encoder.py:37-64): nearest x s, left pad 2 s, conv k = 2 s + 1  ->  polyphase form over three
+    # token rows: out[s q + r] = sum_d (sum_{j : (r + j) // s == d} W_j) x[q - 2 + d];  weight [(r, cout), (d, cin)]
+    w = g(e + "up_layer.conv.weight")                                              # [Cout, Cin, 2 s + 1]
+    s_ = (w.shape[2] - 1) // 2
+    if s_ != 4:
+        raise ValueError("the encoder front end is built for upsample stride 4 (token_mel_ratio 4)")
+    wp = torch.zeros(s_, w.shape[0], 3, w.shape[1])
+    for r in range(s_):
+        for j in range(w.shape[2]):
+            wp[r, :, (r + j) // s_, :] += w[:, :, j]
+    out["enc.up.w"] = _bf16(wp.reshape(s_ * w.shape[0], 3 * w.shape[1]))
+    out["enc.up.b"] = _f32(g(e + "up_layer.conv.bias").repeat(s_))
+    out["enc.after.g"], out["enc.after.b"] = _f32(g(e + "after_norm.weight")), _f32(g(e + "after_norm.bias"))
+    return out
