@@ -82,20 +82,25 @@ __device__ __forceinline__ void softmax_tile(uint32_t t_s, uint32_t t_o, int kba
     const bool any_rescale = __any_sync(0xffffffffu, need && j > 0);
     const float nms = (m2n == -INFINITY) ? 0.f : -m2n;
     m2 = m2n;
-    float rsa = 0.f, rsb = 0.f, rsc = 0.f, rsd = 0.f;
+    // exponent arguments and row sums as packed f32x2 (fma.rn.f32x2 / add.rn.f32x2): the softmax warps are bound by issue
+    // slots, and this halves the FP32 instructions around every pair of MUFU.EX2
+    uint64_t rs0 = 0ull, rs1 = 0ull;
     uint32_t pk[NK / 2];
+    const uint64_t l2e = f2_pack(kLog2e, kLog2e), nms2 = f2_pack(nms, nms);
 #pragma unroll
-    for (int i = 0; i < NK; i += 8) {
-        const float p0 = ex2_approx(fmaf(sc[i], kLog2e, nms)), p1 = ex2_approx(fmaf(sc[i + 1], kLog2e, nms));
-        const float p2 = ex2_approx(fmaf(sc[i + 2], kLog2e, nms)), p3 = ex2_approx(fmaf(sc[i + 3], kLog2e, nms));
-        const float p4 = ex2_approx(fmaf(sc[i + 4], kLog2e, nms)), p5 = ex2_approx(fmaf(sc[i + 5], kLog2e, nms));
-        const float p6 = ex2_approx(fmaf(sc[i + 6], kLog2e, nms)), p7 = ex2_approx(fmaf(sc[i + 7], kLog2e, nms));
-        rsa += p0 + p1; rsb += p2 + p3; rsc += p4 + p5; rsd += p6 + p7;
+    for (int i = 0; i < NK; i += 4) {
+        float x0, x1, x2, x3;
+        f2_unpack(f2_fma(f2_pack(sc[i], sc[i + 1]), l2e, nms2), x0, x1);
+        f2_unpack(f2_fma(f2_pack(sc[i + 2], sc[i + 3]), l2e, nms2), x2, x3);
+        const float p0 = ex2_approx(x0), p1 = ex2_approx(x1), p2 = ex2_approx(x2), p3 = ex2_approx(x3);
+        rs0 = f2_add(rs0, f2_pack(p0, p1));
+        rs1 = f2_add(rs1, f2_pack(p2, p3));
         pk[i >> 1] = pack_bf16x2(p0, p1);
         pk[(i >> 1) + 1] = pack_bf16x2(p2, p3);
-        pk[(i >> 1) + 2] = pack_bf16x2(p4, p5);
-        pk[(i >> 1) + 3] = pack_bf16x2(p6, p7);
     }
+    float rsa, rsb, rsc, rsd;
+    f2_unpack(rs0, rsa, rsb);
+    f2_unpack(rs1, rsc, rsd);
     l = fmaf(l, factor, (rsa + rsb) + (rsc + rsd));
     if (any_rescale) {   // warp-uniform; lanes that keep their maximum scale by 1
         mbar_wait(o_stable, o_phase);   // PV(j - 1) has finished accumulating into O
