@@ -37,7 +37,9 @@ BATCH, N_TOK, N_PROMPT = 64, 125, 37
 EST_MFLOP_PER_FRAME = 132.162e6      # estimator GEMM-class FLOPs per frame per CFG branch per step
 ATTN_MFLOP_PER_FRAME_T = 0.114688e6  # attention FLOPs per frame per branch per step, times T
 HIFT_FLOP_PER_FRAME = 612.296e6      # vocoder GEMM-class FLOPs per generated frame
-FFN_FLOP_PER_FRAME = 56 * 2 * 2 * 256 * 1024   # 56 transformer blocks x (FF1 + FF2), per frame per branch per step
+# 56 transformer blocks x (attention out-projection 512 -> 256, fused into the kernel as its prologue GEMM, + FF1 + FF2),
+# per frame per branch per step
+FFN_FLOP_PER_FRAME = 56 * (2 * 256 * 512 + 2 * 2 * 256 * 1024)
 WORKLOAD = "config2: batch 64 x 10 s utterances (125 tokens), 37-token/148-frame prompt + speaker embedding, CFG 0.7, 10 Euler steps, flow + HiFT"
 
 
@@ -396,7 +398,7 @@ def main():
     if os.path.exists(tpath):
         traffic = json.load(open(tpath))
     desc = {"attention_ws_kernel": "warp-specialised tcgen05 flash attention (QK^T and PV on the tensor cores, double-buffered S and P in TMEM)",
-            "ffn_tc_kernel": "fused feed-forward (FF1 + GELU + FF2 + residual + LayerNorm, tcgen05, hidden on chip)",
+            "ffn_tc_kernel": "fused transformer tail (attention out-projection + residual + LayerNorm + FF1 + GELU + FF2 + residual + LayerNorm, tcgen05, hidden on chip)",
             "gemm_tc_kernel": "tcgen05 implicit GEMM family (convs, projections, vocoder) with fused epilogues"}
     kernels = {}
     for k, (kms, kn) in times.items():

@@ -189,6 +189,7 @@ class Engine {
     int device_ = 0;                   // the device this engine lives on; every entry point runs under it (DeviceGuard)
     int num_sms_ = 148;
     bool finalized_ = false;
+    bool fuse_oproj_ = true;           // attention out-projection fused into ffn_tc_kernel (MOSSDEC_FUSE_OPROJ=0: separate GEMM)
     bool dual_stream_ = true;          // the two CFG halves of a solve run on two streams (MOSSDEC_DUAL=0 disables)
     cudaStream_t st2_ = nullptr;
     cudaStream_t cap_st_ = nullptr;    // capture origin stream (the caller's stream may be the legacy stream, which cannot capture)

@@ -84,6 +84,8 @@ Engine::Engine(const EngineConfig& cfg) : cfg_(cfg) {
             cudaEventCreateWithFlags(&ev_join_, cudaEventDisableTiming) != cudaSuccess)
             dual_stream_ = false;
     }
+    const char* fv = getenv("MOSSDEC_FUSE_OPROJ");
+    fuse_oproj_ = !(fv != nullptr && fv[0] == '0');
     const char* gv = getenv("MOSSDEC_GRAPH");
     if (gv != nullptr && gv[0] >= '0' && gv[0] <= '2') graph_mode_ = gv[0] - '0';
     if (graph_mode_ && cudaStreamCreateWithFlags(&cap_st_, cudaStreamNonBlocking) != cudaSuccess) graph_mode_ = 0;
@@ -228,7 +230,7 @@ int Engine::gemm(const GemmProblem& p, cudaStream_t st) {
 
 int Engine::ffn(const FfnProblem& f, cudaStream_t st) {
     if (cfg_.channels != 256) return fail("fused FFN is built for channels == 256");
-    if (profile_) prof_begin(2, 2.0 * f.M * 256.0 * 1024.0 * 2.0, st, ((uint64_t)f.M << 40) | 0xfffu);
+    if (profile_) prof_begin(2, 2.0 * f.M * 256.0 * (1024.0 * 2.0 + (f.att ? 512.0 : 0.0)), st, ((uint64_t)f.M << 40) | 0xfffu);
     cudaError_t e = ffn_tc_launch(f, num_sms_, st);
     if (profile_) prof_end(st);
     ++launches_;
@@ -491,7 +493,7 @@ int Engine::estimator_forward(int M, int nseq, int max_len, const float* tbias, 
             }
             if (profile_) prof_end(st);
             ++launches_;
-            {   // out projection + residual, emits norm3
+            if (!fuse_oproj_) {   // out projection + residual, emits norm3 (separate launch: MOSSDEC_FUSE_OPROJ=0)
                 GemmProblem p;
                 dense(p, att_, H);
                 p.w = W<__nv_bfloat16>(t + "o.w");
@@ -508,6 +510,11 @@ int Engine::estimator_forward(int M, int nseq, int max_len, const float* tbias, 
                 // norm1 or the masked bf16 copy for the next conv
                 FfnProblem f;
                 f.x = xn_; f.M = M;
+                if (fuse_oproj_) {   // attention out-projection + residual + norm3 as the prologue GEMM of the same kernel
+                    f.att = att_;
+                    f.wo = W<__nv_bfloat16>(t + "o.w");
+                    f.bo = W<float>(t + "o.b");
+                }
                 f.w1 = W<__nv_bfloat16>(t + "ff1.w"); f.b1 = W<float>(t + "ff1.b");
                 f.w2 = W<__nv_bfloat16>(t + "ff2.w"); f.b2 = W<float>(t + "ff2.b");
                 f.hres = hres_;

@@ -20,6 +20,15 @@
 //
 // Warp roles: warp 0 = TMA producer, warp 1 = MMA issuer (+ TMEM alloc), warps 2..17 = epilogue (thread == row; the 4
 // warps that share a TMEM lane quarter split the columns).
+//
+// kFused: the attention out-projection of the same transformer block (matcha transformer.py:274-297: to_out + residual,
+// then norm3) runs as a PROLOGUE GEMM of the tile instead of as its own launch:
+//   acc2 := hres + bo (tcgen05.st preload)  ->  acc2 += att . Wo^T   (K = 512: eight att k-blocks through the four 16 KB
+//   slots of the X region, Wo k-blocks through the weight ring)  ->  epilogue warps read acc2 (the new residual stream h1,
+//   which stays in tensor memory), normalise it and write X = LayerNorm(h1) as bf16 straight into the shared-memory X tile
+//   in the 128B-swizzled K-major layout the MMA expects  ->  feed-forward as above, b2 added in the final drain.
+// This removes the out-projection launch with its two HBM round trips per block: the bf16 X tile (written + read back)
+// and the fp32 stream (read + rewritten) -- about 250 MB per block at the benchmarked size.
 #include "gemm.h"
 #include "ptx.cuh"
 #include "epilogue.cuh"
@@ -56,6 +65,7 @@ struct FfnParams {
     int32_t M, num_tiles;
     const float* b1;
     const float* b2;
+    const float* bo;    // fused mode: bias of the attention out-projection
     int32_t ln;         // 1: out = (hres - mean) * rstd (affine folded into the consumer's weights), 0: out = bf16(hres)
     const int32_t* row_seq;
     float* hres;        // [M, 256] fp32 in the lane-major tiled layout (gemm.h tiled_f32_offset), read and written
@@ -66,10 +76,16 @@ struct FfnParams {
 
 __device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
+constexpr int kOK = 512;                 // K of the fused out-projection (heads * head_dim)
+constexpr int kOKB = kOK / kGemmBK;      // 8 k-blocks
+constexpr int kASlots = kXBytes / kABytes;   // 4: att k-blocks cycle through the X region
+
+// tmX: legacy = the normalised input X [M, 256]; fused = the attention output [M, 512].  tmWo: fused only.
+template <bool kFused>
 __global__ void __cluster_dims__(kCluster, 1, 1) __launch_bounds__(kThreads, 1)
-ffn_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmW1,
-              const __grid_constant__ CUtensorMap tmW2, const __grid_constant__ CUtensorMap tmOut,
-              const __grid_constant__ FfnParams p) {
+ffn_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmWo,
+              const __grid_constant__ CUtensorMap tmW1, const __grid_constant__ CUtensorMap tmW2,
+              const __grid_constant__ CUtensorMap tmOut, const __grid_constant__ FfnParams p) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);  // stays in the shared address space (STS / LDS)
     uint8_t* sX = smem;
@@ -85,7 +101,12 @@ ffn_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ C
     uint64_t* p_ready = a1_full + 2;     // [2] epilogue -> MMA: P[b] written over the drained acc1[b]
     uint64_t* p_free = p_ready + 2;      // [2] (unused since P lives in TMEM: a1_full of G1(h + 2) implies G2(h) is done)
     uint64_t* acc2_full = p_free + 2;    // MMA -> epilogue
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc2_full + 1);
+    uint64_t* a_full = acc2_full + 1;    // [kASlots] fused: TMA -> MMA, att k-block landed in slot
+    uint64_t* a_empty = a_full + kASlots;   // [kASlots] fused: MMA -> TMA, slot may take k-block kb + 4
+    uint64_t* acc2_init = a_empty + kASlots;   // fused: epilogue -> MMA, acc2 preloaded with hres + bo
+    uint64_t* oproj_full = acc2_init + 1;   // fused: MMA -> epilogue, out-projection accumulated
+    uint64_t* x_ready = oproj_full + 1;     // fused: epilogue -> MMA, X tile written to shared memory
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(x_ready + 1);
 
     // (shuffle broadcasts mark values as warp-uniform for the compiler: descriptors and loop state of the TMA / MMA
     //  warps then live in uniform registers and every tcgen05.mma / TMA is a single instruction, not a per-lane loop)
@@ -94,6 +115,7 @@ ffn_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ C
 
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmX);
+        if (kFused) tma_prefetch_desc(&tmWo);
         tma_prefetch_desc(&tmW1);
         tma_prefetch_desc(&tmW2);
         tma_prefetch_desc(&tmOut);
@@ -109,6 +131,13 @@ ffn_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ C
             mbar_init(&p_free[i], 1);
         }
         mbar_init(acc2_full, 1);
+        for (int i = 0; i < kASlots; ++i) {
+            mbar_init(&a_full[i], 1);
+            mbar_init(&a_empty[i], 1);
+        }
+        mbar_init(acc2_init, kEpiWarps);
+        mbar_init(oproj_full, 1);
+        mbar_init(x_ready, kEpiWarps);
         mbar_fence_init();
     }
     if (threadIdx.x >= 64 && threadIdx.x < 64 + kC) sB2[threadIdx.x - 64] = __ldg(p.b2 + threadIdx.x - 64);
@@ -164,7 +193,25 @@ ffn_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ C
             if ((int)blockIdx.x < p.num_tiles && lane == 0) l2_prefetch_bulk(p.hres + (size_t)blockIdx.x * kGemmBM * kC, kGemmBM * kC * 4);
             for (int tile = blockIdx.x; (tile & ~(kCluster - 1)) < p.num_tiles; tile += gridDim.x, ++it) {  // cluster-uniform trip count
                 if (it > 0) mbar_wait(x_free, (uint32_t)((it - 1) & 1));
-                if (elect_one()) {
+                if constexpr (kFused) {
+                    // out-projection operands in consumption order: att k-block kb -> slot kb % 4 of the X region (the
+                    // second four wait for the MMAs of the first four), Wo k-block kb -> the weight ring (multicast halves)
+                    for (int kb = 0; kb < kOKB; ++kb) {
+                        const int slot = kb & (kASlots - 1);
+                        if (kb >= kASlots) mbar_wait(&a_empty[slot], (uint32_t)(it & 1));
+                        if (elect_one()) {
+                            mbar_expect_tx(&a_full[slot], kABytes);
+                            tma_load_2d(sX + slot * kABytes, &tmX, kb * kGemmBK, tile * kGemmBM, &a_full[slot]);
+                        }
+                        mbar_wait(&empty[stage], phase ^ 1);
+                        if (elect_one()) {
+                            mbar_expect_tx(&full[stage], kFStageBytes);
+                            tma_load_2d_mc(sRing + stage * kFStageBytes + rank * (kFStageBytes / 2), &tmWo, kb * kGemmBK,
+                                           rank * (kC / 2), &full[stage], kClusterMask);
+                        }
+                        next_stage();
+                    }
+                } else if (elect_one()) {
                     mbar_expect_tx(x_full, kXBytes);
                     for (int kb = 0; kb < kC / kGemmBK; ++kb)
                         tma_load_2d(sX + kb * kABytes, &tmX, kb * kGemmBK, tile * kGemmBM, x_full);
@@ -244,7 +291,30 @@ ffn_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ C
             int it = 0;
             uint32_t pr_phase[2] = {0, 0};
             for (int tile = blockIdx.x; (tile & ~(kCluster - 1)) < p.num_tiles; tile += gridDim.x, ++it) {  // cluster-uniform trip count
-                mbar_wait(x_full, (uint32_t)(it & 1));
+                if constexpr (kFused) {
+                    mbar_wait(acc2_init, (uint32_t)(it & 1));   // acc2 = hres + bo in tensor memory
+                    tc_fence_after();
+                    for (int kb = 0; kb < kOKB; ++kb) {
+                        const int slot = kb & (kASlots - 1);
+                        mbar_wait(&a_full[slot], (uint32_t)(kb >= kASlots));   // two completions per tile and slot
+                        mbar_wait(&full[stage], phase);
+                        tc_fence_after();
+                        if (elect_one()) {
+                            const uint64_t da = umma_desc_sw128(smem_u32(sX + slot * kABytes));
+                            const uint64_t db = umma_desc_sw128(smem_u32(sRing + stage * kFStageBytes));
+#pragma unroll
+                            for (int k = 0; k < kGemmBK / 16; ++k)
+                                umma_bf16(tmem_base + kAcc2Col, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc2, 1u);
+                            umma_commit_mc(&empty[stage], kClusterMask);
+                            if (kb < kASlots) umma_commit(&a_empty[slot]);
+                            if (kb + 1 == kOKB) umma_commit(oproj_full);
+                        }
+                        next_stage();
+                    }
+                    mbar_wait(x_ready, (uint32_t)(it & 1));   // X = LayerNorm(h1) written to shared memory by the epilogue warps
+                } else {
+                    mbar_wait(x_full, (uint32_t)(it & 1));
+                }
                 tc_fence_after();
                 if (mtr) p.trace[it * 48 + 32] = clock64();
                 g1(0);
@@ -306,7 +376,9 @@ ffn_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ C
                     float r[16];
 #pragma unroll
                     for (int i = 0; i < 16; i += 4) {
-                        const float4 bb = *reinterpret_cast<const float4*>(sB2 + part * 64 + q * 16 + i);   // broadcast LDS
+                        // legacy: + b2 (broadcast LDS).  fused: + bo here, b2 in the final drain
+                        const float4 bb = kFused ? ldg4(p.bo + part * 64 + q * 16 + i)
+                                                 : *reinterpret_cast<const float4*>(sB2 + part * 64 + q * 16 + i);
                         const float4 tt = t[q * 4 + (i >> 2)];
                         r[i] = tt.x + bb.x; r[i + 1] = tt.y + bb.y; r[i + 2] = tt.z + bb.z; r[i + 3] = tt.w + bb.w;
                     }
@@ -315,6 +387,63 @@ ffn_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ C
                 tmem_st_wait();
             }
             FFN_STAMP(1);
+            if constexpr (kFused) {
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(acc2_init);
+                // ---- out-projection done: h1 = acc2.  X = LayerNorm(h1) (affine folded into W1 / b1) -> bf16 -> shared memory
+                mbar_wait(oproj_full, (uint32_t)(it & 1));
+                tc_fence_after();
+                float v[64];
+                {
+                    const uint32_t ta = tlane + kAcc2Col + (uint32_t)(part * 64);
+                    tmem_ld16(ta, v);
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        tmem_ld_wait();
+                        if (q < 3) tmem_ld16(ta + (q + 1) * 16, v + (q + 1) * 16);
+                    }
+                }
+                if (lane == 0) tma_store_wait_read();   // the exchange slot is the head of the staging tile the last store read
+                __syncwarp();
+                const float2 lm = local_mean_m2<64>(v);
+                reinterpret_cast<float2*>(stg)[lane] = lm;
+                group_sync(quarter);
+                float2 o[kEpiParts];
+                float mean = 0.f;
+#pragma unroll
+                for (int q = 0; q < kEpiParts; ++q) {
+                    o[q] = reinterpret_cast<const float2*>(sStg + ((q << 2) | (ew & 3)) * kOutStageBytes)[lane];
+                    mean += o[q].x;
+                }
+                group_sync(quarter);
+                mean *= (1.f / kEpiParts);
+                float m2 = 0.f;
+#pragma unroll
+                for (int q = 0; q < kEpiParts; ++q) {
+                    const float d = o[q].x - mean;
+                    m2 += o[q].y + 64.f * d * d;
+                }
+                const float rstd = rsqrtf(m2 * (1.f / kC) + p.ln_eps);
+                const float a = valid ? rstd : 0.f, bsh = valid ? -mean * rstd : 0.f;
+                // this thread's 64 columns are exactly k-block `part` of the X tile: row trow, 8 chunks of 16 bytes, chunk
+                // index XOR (row & 7) = the 128-byte swizzle TMA would have applied (conflict-free per quarter warp)
+                uint8_t* xrow = sX + part * kABytes + trow * 128;
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    const float* w = v + 8 * j;
+                    uint4 t;
+                    t.x = pack_bf16x2(fmaf(w[0], a, bsh), fmaf(w[1], a, bsh));
+                    t.y = pack_bf16x2(fmaf(w[2], a, bsh), fmaf(w[3], a, bsh));
+                    t.z = pack_bf16x2(fmaf(w[4], a, bsh), fmaf(w[5], a, bsh));
+                    t.w = pack_bf16x2(fmaf(w[6], a, bsh), fmaf(w[7], a, bsh));
+                    *reinterpret_cast<uint4*>(xrow + ((j ^ (trow & 7)) << 4)) = t;
+                }
+                fence_proxy_async_smem();   // generic-proxy stores -> visible to the tensor core's async-proxy reads
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(x_ready);
+            }
 
             // ---- E1: hidden chunks -> GELU -> P[b].  TMEM -> register reads run at ~64 B/clk/SM (a 128 x 128 fp32 chunk
             // takes ~1000 clk to drain), so they are software-pipelined against the math: each thread's 32 columns
@@ -387,6 +516,13 @@ ffn_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ C
                     tmem_ld_wait();
                     if (q < 3) tmem_ld16(ta + (q + 1) * 16, v + (q + 1) * 16);
                     float* w = v + q * 16;
+                    if constexpr (kFused) {   // b2 was not part of the preload here
+#pragma unroll
+                        for (int i = 0; i < 16; i += 4) {
+                            const float4 bb = *reinterpret_cast<const float4*>(sB2 + part * 64 + q * 16 + i);   // broadcast LDS
+                            w[i] += bb.x; w[i + 1] += bb.y; w[i + 2] += bb.z; w[i + 3] += bb.w;
+                        }
+                    }
                     if (!valid) {
 #pragma unroll
                         for (int i = 0; i < 16; ++i) w[i] = 0.f;
@@ -470,13 +606,17 @@ cudaError_t ffn_tc_init_device() {
     static std::atomic<uint64_t> done{0};
     static std::mutex mu;
     return once_per_device(done, mu, [] {
-        return cudaFuncSetAttribute(ffn_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kFfnSmem);
+        cudaError_t e = cudaFuncSetAttribute(ffn_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFfnSmem);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(ffn_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFfnSmem);
+        return e;
     });
 }
 
 cudaError_t ffn_tc_launch(const FfnProblem& f, int num_sms, cudaStream_t stream) {
-    if (f.M <= 0 || (f.M % kGemmBM) != 0 || !f.x || !f.w1 || !f.w2 || !f.b1 || !f.b2 || !f.hres || !f.out_bf16)
+    const bool fused = f.att != nullptr;
+    if (f.M <= 0 || (f.M % kGemmBM) != 0 || !f.w1 || !f.w2 || !f.b1 || !f.b2 || !f.hres || !f.out_bf16)
         return cudaErrorInvalidValue;
+    if (fused ? (!f.wo || !f.bo) : !f.x) return cudaErrorInvalidValue;
     const cudaError_t attr_err = ffn_tc_init_device();
     if (attr_err != cudaSuccess) return attr_err;
 
@@ -485,6 +625,7 @@ cudaError_t ffn_tc_launch(const FfnProblem& f, int num_sms, cudaStream_t stream)
     p.num_tiles = f.M / kGemmBM;
     p.b1 = f.b1;
     p.b2 = f.b2;
+    p.bo = f.bo;
     p.ln = f.ln;
     p.row_seq = f.row_seq;
     p.hres = f.hres;
@@ -492,15 +633,22 @@ cudaError_t ffn_tc_launch(const FfnProblem& f, int num_sms, cudaStream_t stream)
     p.ln_eps = f.ln_eps;
     p.trace = f.trace;
 
-    CUtensorMap tX, tW1, tW2, tOut;
-    if (!encode_2d(&tX, f.x, kC, (uint64_t)f.M, kC, kGemmBM)) return cudaErrorInvalidValue;
+    CUtensorMap tX, tWo, tW1, tW2, tOut;
+    if (fused) {
+        if (!encode_2d(&tX, f.att, kOK, (uint64_t)f.M, kOK, kGemmBM)) return cudaErrorInvalidValue;
+        if (!encode_2d(&tWo, f.wo, kOK, kC, kOK, kC / kCluster)) return cudaErrorInvalidValue;
+    } else {
+        if (!encode_2d(&tX, f.x, kC, (uint64_t)f.M, kC, kGemmBM)) return cudaErrorInvalidValue;
+    }
     if (!encode_2d(&tW1, f.w1, kC, kHid, kC, kChunk)) return cudaErrorInvalidValue;
     if (!encode_2d(&tW2, f.w2, kHid, kC, kHid, kC / kCluster)) return cudaErrorInvalidValue;
     if (!encode_2d_ex(&tOut, f.out_bf16, kC, (uint64_t)f.M, (uint64_t)f.ldo, 32, 32, 1)) return cudaErrorInvalidValue;
+    if (!fused) tWo = tW1;
 
     int grid = (p.num_tiles + kCluster - 1) / kCluster * kCluster;
     if (grid > num_sms) grid = num_sms / kCluster * kCluster;
-    const cudaError_t le = launch_pdl(ffn_tc_kernel, dim3(grid), dim3(kThreads), kFfnSmem, stream, tX, tW1, tW2, tOut, p);
+    const cudaError_t le = fused ? launch_pdl(ffn_tc_kernel<true>, dim3(grid), dim3(kThreads), kFfnSmem, stream, tX, tWo, tW1, tW2, tOut, p)
+                                 : launch_pdl(ffn_tc_kernel<false>, dim3(grid), dim3(kThreads), kFfnSmem, stream, tX, tWo, tW1, tW2, tOut, p);
     if (le != cudaSuccess) return le;
     return cudaGetLastError();
 }

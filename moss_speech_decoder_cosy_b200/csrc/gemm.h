@@ -99,7 +99,12 @@ __host__ __device__ inline size_t tiled_f32_offset(int64_t row, int col) {
 
 // Fused transformer feed-forward (ffn_tc.cu): hres += W2 gelu(W1 x + b1) + b2 ; out = LN(hres) or bf16(hres).
 struct FfnProblem {
-    const __nv_bfloat16* x = nullptr;   // [M, 256] bf16 (normalised input)
+    const __nv_bfloat16* x = nullptr;   // [M, 256] bf16 (normalised input); unused in fused mode
+    // fused mode (att != nullptr): the attention out-projection + residual + LayerNorm run as a prologue of the same
+    // kernel -- hres += att . Wo^T + bo, x = LayerNorm(hres) never leaves the SM (matcha transformer.py:274-297)
+    const __nv_bfloat16* att = nullptr; // [M, 512] bf16 attention output
+    const __nv_bfloat16* wo = nullptr;  // [256, 512] K-major
+    const float* bo = nullptr;          // [256]
     int32_t M = 0;                      // multiple of 128
     const __nv_bfloat16* w1 = nullptr;  // [1024, 256] K-major
     const float* b1 = nullptr;
