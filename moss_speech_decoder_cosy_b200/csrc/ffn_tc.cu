@@ -292,7 +292,7 @@ ffn_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ C
             uint32_t pr_phase[2] = {0, 0};
             for (int tile = blockIdx.x; (tile & ~(kCluster - 1)) < p.num_tiles; tile += gridDim.x, ++it) {  // cluster-uniform trip count
                 if constexpr (kFused) {
-                    mbar_wait(acc2_init, (uint32_t)(it & 1));   // acc2 = hres + bo in tensor memory
+                    mbar_wait(acc2_init, (uint32_t)(it & 1));   // every epilogue warp has drained acc2 of the previous tile
                     tc_fence_after();
                     for (int kb = 0; kb < kOKB; ++kb) {
                         const int slot = kb & (kASlots - 1);
@@ -304,7 +304,7 @@ ffn_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ C
                             const uint64_t db = umma_desc_sw128(smem_u32(sRing + stage * kFStageBytes));
 #pragma unroll
                             for (int k = 0; k < kGemmBK / 16; ++k)
-                                umma_bf16(tmem_base + kAcc2Col, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc2, 1u);
+                                umma_bf16(tmem_base + kAcc2Col, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc2, (uint32_t)((kb | k) != 0));
                             umma_commit_mc(&empty[stage], kClusterMask);
                             if (kb < kASlots) umma_commit(&a_empty[slot]);
                             if (kb + 1 == kOKB) umma_commit(oproj_full);
@@ -359,6 +359,7 @@ ffn_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ C
             const bool live = tile < p.num_tiles;   // the last cluster may carry a padding tile: it only keeps the weight ring in step
             const bool valid = live && (p.row_seq == nullptr || __ldg(p.row_seq + row) >= 0);
 
+            if constexpr (!kFused)
             // ---- preload acc2 := hres + b2 (own row, own 64 columns): the MMAs then accumulate the residual stream
             // directly, and the L2 latency of these (coalesced, tiled-layout) loads hides behind G1(0) / G1(1).  This
             // warp drained the same TMEM lanes / columns in the previous tile; the p_ready[0] arrival of E1(0)
@@ -376,9 +377,7 @@ ffn_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ C
                     float r[16];
 #pragma unroll
                     for (int i = 0; i < 16; i += 4) {
-                        // legacy: + b2 (broadcast LDS).  fused: + bo here, b2 in the final drain
-                        const float4 bb = kFused ? ldg4(p.bo + part * 64 + q * 16 + i)
-                                                 : *reinterpret_cast<const float4*>(sB2 + part * 64 + q * 16 + i);
+                        const float4 bb = *reinterpret_cast<const float4*>(sB2 + part * 64 + q * 16 + i);   // broadcast LDS
                         const float4 tt = t[q * 4 + (i >> 2)];
                         r[i] = tt.x + bb.x; r[i + 1] = tt.y + bb.y; r[i + 2] = tt.z + bb.z; r[i + 3] = tt.w + bb.w;
                     }
@@ -388,10 +387,16 @@ ffn_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ C
             }
             FFN_STAMP(1);
             if constexpr (kFused) {
+                // acc2 is free (this warp drained it in the previous tile): the out-projection MMAs start from zero at once and
+                // overlap the residual loads below; h1 = acc2 + hres + bo is formed in registers and written back afterwards
                 tc_fence_before();
                 __syncwarp();
                 if (lane == 0) mbar_arrive(acc2_init);
-                // ---- out-projection done: h1 = acc2.  X = LayerNorm(h1) (affine folded into W1 / b1) -> bf16 -> shared memory
+                const float* hrow = p.hres + tiled_f32_offset(row, part * 64);  // float4 j of the row: + j * 512 floats
+                float4 hq[4], hn[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) hq[u] = live ? *reinterpret_cast<const float4*>(hrow + (size_t)u * 512) : make_float4(0.f, 0.f, 0.f, 0.f);
+                // ---- out-projection done.  X = LayerNorm(h1) (affine folded into W1 / b1) -> bf16 -> shared memory
                 mbar_wait(oproj_full, (uint32_t)(it & 1));
                 tc_fence_after();
                 float v[64];
@@ -401,7 +406,23 @@ ffn_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ C
 #pragma unroll
                     for (int q = 0; q < 4; ++q) {
                         tmem_ld_wait();
-                        if (q < 3) tmem_ld16(ta + (q + 1) * 16, v + (q + 1) * 16);
+                        if (q < 3) {
+                            tmem_ld16(ta + (q + 1) * 16, v + (q + 1) * 16);
+#pragma unroll
+                            for (int u = 0; u < 4; ++u)
+                                hn[u] = live ? *reinterpret_cast<const float4*>(hrow + (size_t)((q + 1) * 4 + u) * 512) : make_float4(0.f, 0.f, 0.f, 0.f);
+                        }
+                        float* w = v + q * 16;
+#pragma unroll
+                        for (int u = 0; u < 4; ++u) {
+                            const float4 bb = ldg4(p.bo + part * 64 + q * 16 + 4 * u);
+                            w[4 * u] = valid ? w[4 * u] + hq[u].x + bb.x : 0.f;
+                            w[4 * u + 1] = valid ? w[4 * u + 1] + hq[u].y + bb.y : 0.f;
+                            w[4 * u + 2] = valid ? w[4 * u + 2] + hq[u].z + bb.z : 0.f;
+                            w[4 * u + 3] = valid ? w[4 * u + 3] + hq[u].w + bb.w : 0.f;
+                        }
+#pragma unroll
+                        for (int u = 0; u < 4; ++u) hq[u] = hn[u];
                     }
                 }
                 if (lane == 0) tma_store_wait_read();   // the exchange slot is the head of the staging tile the last store read
@@ -443,6 +464,11 @@ ffn_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ C
                 tc_fence_before();
                 __syncwarp();
                 if (lane == 0) mbar_arrive(x_ready);
+                // h1 back into acc2 (own lanes / columns): the feed-forward MMAs accumulate onto it.  Off the critical path of
+                // G1; the p_ready[0] arrival of E1(0) publishes the stores to the MMA thread.
+#pragma unroll
+                for (int q = 0; q < 4; ++q) tmem_st16(tlane + kAcc2Col + (uint32_t)(part * 64 + q * 16), v + q * 16);
+                tmem_st_wait();
             }
 
             // ---- E1: hidden chunks -> GELU -> P[b].  TMEM -> register reads run at ~64 B/clk/SM (a 128 x 128 fp32 chunk
