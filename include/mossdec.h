@@ -114,6 +114,28 @@ int mossdec_token2mel(mossdec_handle* h, int32_t B, const int32_t* n_tok, const 
                       const float* prompt_feat, const float* embedding, int32_t ctx_len, int32_t chunk_tokens,
                       int32_t est_chunk_frames, int32_t n_steps, float cfg_rate, float* mel_out, void* stream);
 
+/* ---- Frozen-prefix cache for streaming chunk calls.
+ * The reference recomputes the flow over prompt + token window for every streamed chunk (flow_inference.py:188-218).  With
+ * `stream=True` the estimator's attention is block-causal (chunks of est_chunk_frames) and its convolutions are causal,
+ * so the first whole chunks that lie inside the prompt -- the frozen prefix -- are identical in every chunk call of a
+ * stream.  mossdec_token2mel_prefix with mode 1 (record) runs the full solve and stores, per Euler step and CFG branch, the
+ * K | V rows of the prefix for every transformer block and the two-row left context of every causal conv in cache slot
+ * slots[b]; with mode 2 (reuse) only the live frames behind the prefix are computed (the frozen keys come from the cache
+ * inside the attention kernel, with the same key tiling as in the recording call: the live frames are bit-identical to
+ * a recording call on the same inputs).  Exact, also for sliding `max_token_len` windows.  mode 0 = mossdec_token2mel.
+ *   mossdec_prefix_reserve: allocate the cache (n_slots streams x prefix_frames frames x n_steps; drops its contents).
+ *     prefix_frames must be a multiple of est_chunk_frames and of 4 * chunk_tokens.
+ *   slots / tags: HOST arrays [B]; tags[b] != 0 identifies the frozen inputs of the stream (prompt tokens, prompt mel,
+ *     speaker embedding); a reuse call whose tag differs from the recorded one fails with an error instead of drifting.
+ *   Requirements (checked): streaming call (chunk_tokens > 0, est_chunk_frames > 0), prompt_frames[b] >= prefix_frames and
+ *     prompt tokens >= prefix_frames / 4 + 3, every utterance longer than the prefix, same n_steps / cfg_rate / chunk
+ *     as recorded.  In reuse mode the first prefix_frames frames of every mel_out block are not written. */
+int mossdec_prefix_reserve(mossdec_handle* h, int32_t n_slots, int32_t prefix_frames, int32_t n_steps);
+int mossdec_token2mel_prefix(mossdec_handle* h, int32_t B, const int32_t* n_tok, const int64_t* tokens,
+                             const int32_t* prompt_frames, const float* prompt_feat, const float* embedding, int32_t ctx_len,
+                             int32_t chunk_tokens, int32_t est_chunk_frames, int32_t n_steps, float cfg_rate, int32_t mode,
+                             const int32_t* slots, const uint64_t* tags, float* mel_out, void* stream);
+
 /* Streaming glue (flow_inference.py:35-43,151-156): speech[:n] = speech[:n]*w[:n] + prev_tail[:n]*w[n:], fp32, device. */
 int mossdec_fade_in_out(mossdec_handle* h, float* speech, const float* prev_tail, const float* window2n, int32_t n,
                         void* stream);

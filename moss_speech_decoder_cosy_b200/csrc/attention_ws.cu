@@ -120,11 +120,17 @@ __device__ __forceinline__ void softmax_tile(uint32_t t_s, uint32_t t_o, int kba
     tmem_st_wait();
 }
 
-template <bool kBias>
+// kPrefix: every sequence has `prefix_len` FROZEN keys in front of its live rows (streaming with block-causal masks: the
+// first complete blocks of a stream are identical in every chunk, engine_solve.cu).  Their K | V rows come from a cache
+// tensor (tmP: [rows, 2 * H * 64] = [k | v], sequence s at row prefix_row[s]); the live keys follow at absolute position
+// prefix_len.  Key tiles never straddle the boundary: ceil(prefix_len / 32) prefix tiles (tail masked), then the live ones.
+template <bool kBias, bool kPrefix>
 __global__ void __launch_bounds__(kThreadsWs, 4)
-attention_ws_kernel(const __grid_constant__ CUtensorMap tm, __nv_bfloat16* __restrict__ out,
-                    const int32_t* __restrict__ seq_start, const int32_t* __restrict__ seq_len, int heads, int chunk,
-                    const __nv_bfloat16* __restrict__ bias, int64_t bias_head_stride, int bias_ld, int bias_tmax) {
+attention_ws_kernel(const __grid_constant__ CUtensorMap tm, const __grid_constant__ CUtensorMap tmP,
+                    __nv_bfloat16* __restrict__ out, const int32_t* __restrict__ seq_start,
+                    const int32_t* __restrict__ seq_len, int heads, int chunk, const __nv_bfloat16* __restrict__ bias,
+                    int64_t bias_head_stride, int bias_ld, int bias_tmax, int prefix_len,
+                    const int32_t* __restrict__ prefix_row) {
     const int s = blockIdx.z, h = blockIdx.y;
     const int len = __shfl_sync(0xffffffffu, seq_len[s], 0);
     const int q0 = blockIdx.x * kBQ;
@@ -170,11 +176,14 @@ attention_ws_kernel(const __grid_constant__ CUtensorMap tm, __nv_bfloat16* __res
     tc_fence_after();
     const uint32_t tmem = __shfl_sync(0xffffffffu, *tmem_slot, 0);
 
-    // keys visible to this query tile
+    // keys visible to this query tile (LIVE key index; absolute position = P + index)
+    const int P = kPrefix ? prefix_len : 0;
     int kv_end = len;
-    if (chunk > 0) kv_end = min(len, ((min(q0 + kBQ, len) - 1) / chunk + 1) * chunk);
-    const int nkt = (kv_end + kBK - 1) / kBK;
-    const int nk_last = ((kv_end - (nkt - 1) * kBK) + 15) & ~15;   // 16 or 32: the last tile only computes its 16-key groups
+    if (chunk > 0) kv_end = min(len, ((P + min(q0 + kBQ, len) - 1) / chunk + 1) * chunk - P);
+    const int npt = (P + kBK - 1) / kBK;                 // prefix key tiles (the last one may be partly masked)
+    const int nkt = npt + (kv_end + kBK - 1) / kBK;
+    const int nk_last = ((kv_end - (nkt - npt - 1) * kBK) + 15) & ~15;   // 16 or 32: the last tile only computes its 16-key groups
+    const int prow = kPrefix ? __shfl_sync(0xffffffffu, prefix_row[s], 0) : 0;
 
     if (warp == 4) {
         // ------------------------------------------------------------ TMA + MMA issue (whole warp, one elected lane issues)
@@ -186,8 +195,13 @@ attention_ws_kernel(const __grid_constant__ CUtensorMap tm, __nv_bfloat16* __res
         auto load_kv = [&](int t) {   // tile t -> stage t % kNS
             uint8_t* st = sKV + (t % kNS) * kStageBytes;
             mbar_expect_tx(&kv_full[t % kNS], kStageBytes);
-            tma_load_2d(st, &tm, kcol, start + t * kBK, &kv_full[t % kNS]);
-            tma_load_2d(st + kTileBytes, &tm, vcol, start + t * kBK, &kv_full[t % kNS]);
+            if (kPrefix && t < npt) {   // frozen keys: cache rows, k at column h * 64, v at (H + h) * 64
+                tma_load_2d(st, &tmP, h * kD, prow + t * kBK, &kv_full[t % kNS]);
+                tma_load_2d(st + kTileBytes, &tmP, (heads + h) * kD, prow + t * kBK, &kv_full[t % kNS]);
+            } else {
+                tma_load_2d(st, &tm, kcol, start + (t - npt) * kBK, &kv_full[t % kNS]);
+                tma_load_2d(st + kTileBytes, &tm, vcol, start + (t - npt) * kBK, &kv_full[t % kNS]);
+            }
         };
         auto issue_qk = [&](int t) {   // S[t & 1] = Q K_t^T
             const uint64_t dk = umma_desc_sw128(smem_u32(sKV + (t % kNS) * kStageBytes));
@@ -237,8 +251,8 @@ attention_ws_kernel(const __grid_constant__ CUtensorMap tm, __nv_bfloat16* __res
     } else if (warp < n_active) {
         // ------------------------------------------------------------ softmax warps, thread == query row
         const int qi = q0 + tid;
-        int lim = len;
-        if (chunk > 0) lim = min(len, (min(qi, len - 1) / chunk + 1) * chunk);
+        int lim = len;   // live key index limit of this query row
+        if (chunk > 0) lim = min(len, ((P + min(qi, len - 1)) / chunk + 1) * chunk - P);
         const uint32_t t_lane = tmem + ((uint32_t)(warp * 32) << 16);
         const uint32_t t_o = t_lane + 64;
         float m2 = -INFINITY, l = 0.f;
@@ -255,8 +269,11 @@ attention_ws_kernel(const __grid_constant__ CUtensorMap tm, __nv_bfloat16* __res
             tc_fence_after();
             uint64_t* o_stable = &kv_empty[(j + kNS - 1) % kNS];                      // completes with PV(j - 1)
             const uint32_t o_phase = (uint32_t)((((j > 0 ? j - 1 : 0)) / kNS) & 1);
-            if (j + 1 == nkt && nk_last == 16) softmax_tile<16, kBias>(t_lane + (uint32_t)(b * kBK), t_o, j * kBK, lim, j, m2, l, o_stable, o_phase, brow);
-            else softmax_tile<32, kBias>(t_lane + (uint32_t)(b * kBK), t_o, j * kBK, lim, j, m2, l, o_stable, o_phase, brow);
+            // prefix tiles: key index inside the prefix, valid below P; live tiles: live key index, valid below lim
+            const int kb0 = (kPrefix && j < npt) ? j * kBK : (j - npt) * kBK;
+            const int lm = (kPrefix && j < npt) ? P : lim;
+            if (j + 1 == nkt && nk_last == 16) softmax_tile<16, kBias>(t_lane + (uint32_t)(b * kBK), t_o, kb0, lm, j, m2, l, o_stable, o_phase, brow);
+            else softmax_tile<32, kBias>(t_lane + (uint32_t)(b * kBK), t_o, kb0, lm, j, m2, l, o_stable, o_phase, brow);
             tc_fence_before();
             __syncwarp();
             if ((tid & 31) == 0) mbar_arrive(&p_ready[b]);
@@ -294,8 +311,9 @@ cudaError_t attention_ws_init_device() {
     static std::atomic<uint64_t> done{0};
     static std::mutex mu;
     return once_per_device(done, mu, [] {
-        cudaError_t e = cudaFuncSetAttribute(attention_ws_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem);
-        if (e == cudaSuccess) e = cudaFuncSetAttribute(attention_ws_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem);
+        cudaError_t e = cudaFuncSetAttribute(attention_ws_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(attention_ws_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(attention_ws_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem);
         return e;
     });
 }
@@ -316,10 +334,28 @@ cudaError_t launch_attention_ws_ex(const __nv_bfloat16* qkv, int64_t rows, int q
     if (!encode_2d(&tm, qkv, (uint64_t)qkv_ld, (uint64_t)rows, (uint64_t)qkv_ld, kBK)) return cudaErrorInvalidValue;
     dim3 grid((max_len + kBQ - 1) / kBQ, heads, nseq);
     if (bias != nullptr)
-        attention_ws_kernel<true><<<grid, kThreadsWs, kSmem, st>>>(tm, out, seq_start, seq_len, heads, chunk, bias,
-                                                                   bias_head_stride, bias_ld, bias_tmax);
+        attention_ws_kernel<true, false><<<grid, kThreadsWs, kSmem, st>>>(tm, tm, out, seq_start, seq_len, heads, chunk, bias,
+                                                                          bias_head_stride, bias_ld, bias_tmax, 0, nullptr);
     else
-        attention_ws_kernel<false><<<grid, kThreadsWs, kSmem, st>>>(tm, out, seq_start, seq_len, heads, chunk, nullptr, 0, 0, 0);
+        attention_ws_kernel<false, false><<<grid, kThreadsWs, kSmem, st>>>(tm, tm, out, seq_start, seq_len, heads, chunk, nullptr,
+                                                                           0, 0, 0, 0, nullptr);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_attention_ws_prefix(const __nv_bfloat16* qkv, int64_t rows, __nv_bfloat16* out, const int32_t* seq_start,
+                                       const int32_t* seq_len, int nseq, int max_len, int heads, int chunk,
+                                       const __nv_bfloat16* prefix_kv, int64_t prefix_rows, int prefix_len,
+                                       const int32_t* prefix_row, cudaStream_t st) {
+    const cudaError_t ie = attention_ws_init_device();
+    if (ie != cudaSuccess) return ie;
+    if (prefix_len <= 0 || (chunk > 0 && (prefix_len % chunk) != 0)) return cudaErrorInvalidValue;
+    CUtensorMap tm, tmP;
+    if (!encode_2d(&tm, qkv, (uint64_t)3 * heads * kD, (uint64_t)rows, (uint64_t)3 * heads * kD, kBK)) return cudaErrorInvalidValue;
+    if (!encode_2d(&tmP, prefix_kv, (uint64_t)2 * heads * kD, (uint64_t)prefix_rows, (uint64_t)2 * heads * kD, kBK))
+        return cudaErrorInvalidValue;
+    dim3 grid((max_len + kBQ - 1) / kBQ, heads, nseq);
+    attention_ws_kernel<false, true><<<grid, kThreadsWs, kSmem, st>>>(tm, tmP, out, seq_start, seq_len, heads, chunk, nullptr, 0, 0,
+                                                                      0, prefix_len, prefix_row);
     return cudaGetLastError();
 }
 

@@ -83,6 +83,22 @@ int mossdec_token2mel(mossdec_handle* h, int32_t B, const int32_t* n_tok, const 
                              n_steps, cfg_rate, mel_out, (cudaStream_t)stream);
 }
 
+int mossdec_prefix_reserve(mossdec_handle* h, int32_t n_slots, int32_t prefix_frames, int32_t n_steps) {
+    return h->eng->prefix_reserve(n_slots, prefix_frames, n_steps);
+}
+
+int mossdec_token2mel_prefix(mossdec_handle* h, int32_t B, const int32_t* n_tok, const int64_t* tokens,
+                             const int32_t* prompt_frames, const float* prompt_feat, const float* embedding, int32_t ctx_len,
+                             int32_t chunk_tokens, int32_t est_chunk_frames, int32_t n_steps, float cfg_rate, int32_t mode,
+                             const int32_t* slots, const uint64_t* tags, float* mel_out, void* stream) {
+    Engine::PrefixArgs px;
+    px.mode = mode;
+    px.slots = slots;
+    px.tags = tags;
+    return h->eng->token2mel(B, n_tok, tokens, prompt_frames, prompt_feat, embedding, ctx_len, chunk_tokens, est_chunk_frames,
+                             n_steps, cfg_rate, mel_out, (cudaStream_t)stream, &px);
+}
+
 int mossdec_fade_in_out(mossdec_handle* h, float* speech, const float* prev_tail, const float* window2n, int32_t n,
                         void* stream) {
     return h->eng->fade_in_out(speech, prev_tail, window2n, n, (cudaStream_t)stream);

@@ -93,6 +93,16 @@ class Engine {
     explicit Engine(const EngineConfig& cfg);
     ~Engine();
 
+    // Frozen-prefix cache for streaming solves (engine_solve.cu).  With block-causal masks the
+    // first `prefix_frames` frames of a stream (whole estimator chunks inside the prompt) are identical in every chunk of
+    // that stream: their per-layer K | V and the two-row left context of every causal conv are recorded once
+    // (mode 1) and later chunks only compute the live frames behind them (mode 2).
+    int prefix_reserve(int n_slots, int prefix_frames, int n_steps);
+    struct PrefixArgs {
+        int mode = 0;                    // 0 = plain, 1 = record (full solve that also fills the cache), 2 = reuse
+        const int32_t* slots = nullptr;  // HOST [B] cache slot of every utterance
+        const uint64_t* tags = nullptr;  // HOST [B] caller's identity of the frozen inputs (checked on reuse)
+    };
     int set_tensor(const char* name, const void* host, int dtype, int ndim, const int64_t* shape);
     int finalize();
 
@@ -103,7 +113,7 @@ class Engine {
     // to back).  noise == nullptr -> built-in bank uploaded as tensor "flow.rand_noise".
     int flow_solve(int B, const int32_t* lens, const float* mu, const float* spks, const float* cond,
                    const float* noise, int noise_len_arg, int n_steps, float cfg_rate, float temperature, int chunk, float* mel_out,
-                   int flags, cudaStream_t st);
+                   int flags, cudaStream_t st, const PrefixArgs* px = nullptr);
     // HiFT vocoder for B ragged mel segments ([80, T_b] back to back) -> wav [480 T_b] back to back.
     int hift(int B, const int32_t* lens, const float* mel, const float* cache_source, int cache_stride,
              const int32_t* cache_len, const float* nsf_noise, float* wav_out, float* source_out, uint64_t seed,
@@ -121,7 +131,7 @@ class Engine {
     // ragged device [F_b, 80], embedding device [B, 192] -> mel_out ragged time-major [4 (n_tok[b] - ctx), 80].
     int token2mel(int B, const int32_t* n_tok, const int64_t* tokens, const int32_t* prompt_frames, const float* prompt_feat,
                   const float* embedding, int ctx, int chunk_tokens, int est_chunk_frames, int n_steps, float cfg_rate,
-                  float* mel_out, cudaStream_t st);
+                  float* mel_out, cudaStream_t st, const PrefixArgs* px = nullptr);
     // matcha mel_spectrogram (n_fft 1920, hop 480, 80 mels, 24 kHz, fmax 8000, center False; mel_kernels.cu):
     // wav device [L] -> mel_out device [80, T], T = (L - 480) / 480 + 1.  Returns T, negative on error.
     int mel_spectrogram(const float* wav, int64_t L, float* mel_out, cudaStream_t st);
@@ -165,13 +175,18 @@ class Engine {
 
     // flow internals
     struct FlowPlan;
-    int build_flow_layout(int nseq_half, const int32_t* lens, bool cfg_double, cudaStream_t st, int dense_T = 0);
+    int build_flow_layout(int nseq_half, const int32_t* lens, bool cfg_double, cudaStream_t st, int dense_T = 0, int frame0 = 0);
     int reserve_flow(size_t M, int nseq);
     int reserve_hift(int64_t rows_f, int nseq);
-    int run_euler_steps(int n_steps, int chunk, float cfg_rate, const float* dtv, cudaStream_t st);
+    int run_euler_steps(int n_steps, int chunk, float cfg_rate, const float* dtv, cudaStream_t st, int px_mode = 0);
     // row0 > 0: run on the rows [row0, row0 + M) of every workspace matrix (the second CFG half on its own stream)
+    // per-call view of the prefix cache for one (Euler step, CFG branch); nullptr = plain
+    struct PrefixCtx {
+        int mode, prefix, step, branch;
+    };
     int estimator_forward(int M, int nseq, int max_len, const float* tbias, int tbias_ld, int chunk, cudaStream_t st,
-                          int row0 = 0);
+                          int row0 = 0, const PrefixCtx* pc = nullptr);
+    int prefix_halo(const PrefixCtx* pc, int conv_id, __nv_bfloat16* buf, int64_t ld, int width, int nseq, cudaStream_t st);
     int time_bias(const float* t_dev, int nt, float* temb, float* tbias, cudaStream_t st);
     int finalize_hift();
     int finalize_encoder();
@@ -203,7 +218,7 @@ class Engine {
     struct GraphKey {
         int rows_half, nseq_half, max_len, chunk, n_steps, dual;
         uint32_t cfg_bits;
-        const void *ws, *lay, *tb;
+        const void *ws, *lay, *tb, *px, *pxi;
         bool operator<(const GraphKey& o) const;
     };
     struct GraphEntry {
@@ -217,6 +232,17 @@ class Engine {
     uint64_t graph_clock_ = 0;
     long graph_replays_ = 0;
     void drop_graphs();
+    // ---- frozen-prefix cache (engine_solve.cu)
+    DeviceBuffer ws_prefix_, ws_prefix_idx_;
+    int px_slots_ = 0, px_frames_ = 0, px_steps_ = 0;
+    int px_chunk_ = 0;
+    uint32_t px_cfg_bits_ = 0;
+    std::vector<uint64_t> px_tags_;          // host: what every slot holds (0 = empty)
+    int32_t *px_d_slot_ = nullptr, *px_d_prow_ = nullptr, *px_d_len_pref_ = nullptr, *px_d_start_live_ = nullptr,
+            *px_d_len_live_ = nullptr;      // device index arrays of the current call ([nseq_half] each)
+    __nv_bfloat16* px_kv(int step, int branch, int block) const;
+    __nv_bfloat16* px_halo(int step, int branch, int conv) const;
+    size_t px_kv_slab_elems() const { return ((size_t)px_slots_ * px_frames_ + 64) * 2 * cfg_.heads * cfg_.head_dim; }
     int solve_tbias_steps_ = 0;        // ws_time_solve_ holds the time-embedding biases of an n-step cosine schedule
     std::unordered_map<std::string, DevTensor> tensors_;
     std::string err_;

@@ -361,7 +361,7 @@ int Engine::encode_group(int b0, int b1, const int32_t* n_tok, const int64_t* to
 
 int Engine::token2mel(int B, const int32_t* n_tok, const int64_t* tokens, const int32_t* prompt_frames,
                       const float* prompt_feat, const float* embedding, int ctx, int chunk_tokens, int est_chunk_frames,
-                      int n_steps, float cfg_rate, float* mel_out, cudaStream_t st) {
+                      int n_steps, float cfg_rate, float* mel_out, cudaStream_t st, const PrefixArgs* px) {
     DeviceGuard g(device_);
     if (!finalized_) return fail("weights not finalized");
     if (!has_encoder_) return fail("encoder tensors missing: " + enc_missing_);
@@ -410,8 +410,17 @@ int Engine::token2mel(int B, const int32_t* n_tok, const int64_t* tokens, const 
     taps_["enc.mu"] = {mu, n_mel * 4};       // test hooks (mossdec_debug_read): ragged time-major [sum T_b, 80]
     taps_["enc.cond"] = {cond, n_mel * 4};
     taps_["enc.spks"] = {spks, (size_t)B * cfg_.n_feats * 4};
+    if (px != nullptr && px->mode != 0) {
+        // the frozen prefix must lie inside what is identical in every chunk of a stream: prompt mel frames, and prompt
+        // tokens up to the encoder's 3-token look-ahead (upsample_encoder.py:81-98); whole encoder chunks
+        if (chunk_tokens <= 0 || (px_frames_ % (4 * chunk_tokens)) != 0)
+            return fail("token2mel: the frozen prefix must be a whole number of encoder chunks (streaming only)");
+        for (int b = 0; b < B; ++b)
+            if (prompt_frames[b] < px_frames_ || prompt_frames[b] / 4 < px_frames_ / 4 + 3)
+                return fail("token2mel: the prompt of an utterance does not cover the frozen prefix (+ 3 look-ahead tokens)");
+    }
     return flow_solve(B, lens.data(), mu, spks, cond, nullptr, 0, n_steps, cfg_rate, 1.0f, est_chunk_frames, mel_out,
-                      /*time_major*/ 1, st);
+                      /*time_major*/ 1, st, px);
 }
 
 }  // namespace mossdec

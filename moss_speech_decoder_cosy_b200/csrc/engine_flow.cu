@@ -291,7 +291,7 @@ int Engine::reserve_flow(size_t M, int nseq) {
     return 0;
 }
 
-int Engine::build_flow_layout(int nseq_half, const int32_t* lens, bool cfg_double, cudaStream_t st, int dense_T) {
+int Engine::build_flow_layout(int nseq_half, const int32_t* lens, bool cfg_double, cudaStream_t st, int dense_T, int frame0) {
     int rows = 0, max_len = 0;
     const int nseq = cfg_double ? 2 * nseq_half : nseq_half;
     for (int s = 0; s < nseq_half; ++s) {
@@ -321,7 +321,7 @@ int Engine::build_flow_layout(int nseq_half, const int32_t* lens, bool cfg_doubl
         h_start[s] = r;
         h_len[s] = lens[s];
         h_off[s] = dense_T > 0 ? (int64_t)s * cfg_.n_feats * dense_T : off;
-        off += (int64_t)lens[s] * cfg_.n_feats;
+        off += (int64_t)(lens[s] + frame0) * cfg_.n_feats;   // the ragged block also holds the frame0 frames that have no rows
         for (int t = 0; t < lens[s]; ++t) h_rowseq[r + t] = s;
         r += lens[s];
     }
@@ -347,6 +347,7 @@ int Engine::build_flow_layout(int nseq_half, const int32_t* lens, bool cfg_doubl
     layout_.noise_cstride = cfg_.noise_len;
     layout_.time_major = 0;
     layout_.dense_T = dense_T;
+    layout_.frame0 = frame0;
     layout_.row_seq = d_rowseq;
     layout_.seq_start = d_rowseq + M;
     layout_.seq_len = d_rowseq + M + nseq;
@@ -392,10 +393,24 @@ int Engine::time_bias(const float* t_dev, int nt, float* temb, float* tbias, cud
 
 // ------------------------------------------------------------------------------------------------ estimator
 // Input: xin_ [M, 320] bf16 (guard rows zero).  Output: dout_ [M, 80] fp32 (guard rows zero).
+// Frozen-prefix cache hooks (pc != nullptr; engine_solve.cu explains the scheme).  Causal convs look two rows back:
+//   record (mode 1): the rows of frames prefix - 2, prefix - 1 of every conv input are saved;
+//   reuse  (mode 2): the sequences hold live frames only and the two guard rows in front of each are filled from the cache
+//                    right before the conv reads them (every producing epilogue zeroes guard rows again).
+int Engine::prefix_halo(const PrefixCtx* pc, int conv_id, __nv_bfloat16* buf, int64_t ld, int width, int nseq, cudaStream_t st) {
+    if (pc == nullptr || pc->mode == 0) return 0;
+    __nv_bfloat16* cache = px_halo(pc->step, pc->branch, conv_id);
+    if (pc->mode == 1) launch_prefix_halo(1, buf, ld, width, layout_.seq_start, pc->prefix - 2, px_d_slot_, nseq, cache, st);
+    else launch_prefix_halo(0, buf, ld, width, layout_.seq_start, -2, px_d_slot_, nseq, cache, st);
+    ++launches_;
+    return 0;
+}
+
 int Engine::estimator_forward(int M, int nseq, int max_len, const float* tbias, int tbias_ld, int chunk,
-                              cudaStream_t st, int row0) {
+                              cudaStream_t st, int row0, const PrefixCtx* pc) {
     const int C = cfg_.channels, H = cfg_.heads * cfg_.head_dim;
     const int ngroups = cfg_.n_mid + 2;
+    const int nb = cfg_.n_blocks;
     const int32_t* row_seq = layout_.row_seq + row0;
     // workspace views of the rows [row0, row0 + M) (these locals shadow the members on purpose; row0 is a multiple of
     // 128, so the tiled fp32 matrices are offset by whole tiles).  Sequence starts stay relative to the view: the
@@ -437,6 +452,7 @@ int Engine::estimator_forward(int M, int nseq, int max_len, const float* tbias, 
             gin = cat_;
             gin_c = 2 * C;
         }
+        if (prefix_halo(pc, 2 * g, const_cast<__nv_bfloat16*>(gin), gin_c, gin_c, nseq, st)) return -1;
         {   // block1: causal conv -> LN -> Mish -> mask -> + time bias            (decoder.py:65-78, matcha decoder.py:56-57)
             GemmProblem p;
             causal3(p, gin, gin_c);
@@ -459,6 +475,7 @@ int Engine::estimator_forward(int M, int nseq, int max_len, const float* tbias, 
             p.epi.out_f32 = rres_; p.epi.ldf = C; p.epi.f32_tiled = 1;
             if (gemm(p, st)) return -1;
         }
+        if (prefix_halo(pc, 2 * g + 1, h1_, C, C, nseq, st)) return -1;
         {   // block2 + residual; also emits norm1 of the first transformer block
             GemmProblem p;
             causal3(p, h1_, C);
@@ -486,10 +503,29 @@ int Engine::estimator_forward(int M, int nseq, int max_len, const float* tbias, 
                 if (gemm(p, st)) return -1;
             }
             if (profile_) prof_begin(1, 0.0, st);
-            {
+            if (pc == nullptr || pc->mode == 0) {
                 cudaError_t ae = launch_attention_ws(qkv_, M, att_, layout_.seq_start, layout_.seq_len, nseq, max_len,
                                                      cfg_.heads, chunk, st);
                 if (ae != cudaSuccess) return fail(std::string("launch_attention_ws: ") + cudaGetErrorString(ae));
+            } else {
+                __nv_bfloat16* slab = px_kv(pc->step, pc->branch, g * nb + j);
+                const int64_t slab_rows = (int64_t)px_slots_ * px_frames_ + 64;
+                cudaError_t ae = cudaSuccess;
+                if (pc->mode == 1) {
+                    // record: k | v of the frozen frames -> cache; their queries see only frozen keys (chunk divides the
+                    // prefix); the live queries run exactly as in reuse mode (frozen keys from the cache, same key tiling)
+                    launch_prefix_kv_save(qkv_, H, layout_.seq_start, px_d_slot_, nseq, pc->prefix, slab, st);
+                    ++launches_;
+                    ae = launch_attention_ws(qkv_, M, att_, layout_.seq_start, px_d_len_pref_, nseq, pc->prefix, cfg_.heads, chunk, st);
+                    ++launches_;
+                    if (ae == cudaSuccess)
+                        ae = launch_attention_ws_prefix(qkv_, M, att_, px_d_start_live_, px_d_len_live_, nseq, max_len - pc->prefix,
+                                                        cfg_.heads, chunk, slab, slab_rows, pc->prefix, px_d_prow_, st);
+                } else {
+                    ae = launch_attention_ws_prefix(qkv_, M, att_, layout_.seq_start, layout_.seq_len, nseq, max_len, cfg_.heads,
+                                                    chunk, slab, slab_rows, pc->prefix, px_d_prow_, st);
+                }
+                if (ae != cudaSuccess) return fail(std::string("launch_attention_ws (prefix): ") + cudaGetErrorString(ae));
             }
             if (profile_) prof_end(st);
             ++launches_;
@@ -534,6 +570,7 @@ int Engine::estimator_forward(int M, int nseq, int max_len, const float* tbias, 
             }
         }
         if (g == 0) {  // "downsample" slot = plain causal conv when channels == [256]   (decoder.py:348-350)
+            if (prefix_halo(pc, 2 * ngroups, cat_ + C, 2 * C, C, nseq, st)) return -1;
             GemmProblem p;
             p.a[0].ptr = cat_ + C; p.a[0].rows = M; p.a[0].cols = C; p.a[0].ld = 2 * C;
             p.num_segs = 3;
@@ -552,6 +589,7 @@ int Engine::estimator_forward(int M, int nseq, int max_len, const float* tbias, 
             gin_c = C;
         }
     }
+    if (prefix_halo(pc, 2 * ngroups + 1, xn_, C, C, nseq, st)) return -1;
     {   // "upsample" slot = causal conv                                                (decoder.py:395-399)
         GemmProblem p;
         causal3(p, xn_, C);
@@ -562,6 +600,7 @@ int Engine::estimator_forward(int M, int nseq, int max_len, const float* tbias, 
         p.epi.out_bf16 = h1_; p.epi.ldo = C;
         if (gemm(p, st)) return -1;
     }
+    if (prefix_halo(pc, 2 * ngroups + 2, h1_, C, C, nseq, st)) return -1;
     {   // final_block: conv -> LN -> Mish -> mask                                       (decoder.py:401, 492)
         GemmProblem p;
         causal3(p, h1_, C);

@@ -88,8 +88,8 @@ __global__ void flow_prepare_kernel(FlowLayout L, const float* __restrict__ mu, 
         xstate[(size_t)row * C + c] = 0.f;
         return;
     }
-    const int t = row - L.seq_start[s];
-    const int T = L.seq_len[s];
+    const int t = row - L.seq_start[s] + L.frame0;   // frame inside the utterance's ragged block
+    const int T = L.seq_len[s] + L.frame0;
     const size_t off = L.in_offset[s] + (L.time_major ? (size_t)t * C + c : (size_t)c * T + t);  // ragged [C, T] or [T, C]
     xc[C + c] = __float2bfloat16(mu[off]);
     xc[2 * C + c] = __float2bfloat16(spks[(size_t)s * C + c]);
@@ -134,8 +134,8 @@ __global__ void rows_to_bct_kernel(FlowLayout L, const float* __restrict__ rows,
     const int row = idx / C, c = idx % C;
     const int s = L.row_seq[row];
     if (s < 0) return;
-    const int t = row - L.seq_start[s];
-    const int cs = L.dense_T > 0 ? L.dense_T : L.seq_len[s];   // channel stride of the channel-first form
+    const int t = row - L.seq_start[s] + L.frame0;
+    const int cs = L.dense_T > 0 ? L.dense_T : L.seq_len[s] + L.frame0;   // channel stride of the channel-first form
     out[L.in_offset[s] + (L.time_major ? (size_t)t * C + c : (size_t)c * cs + t)] = rows[(size_t)(row + row_offset) * C + c];
 }
 
@@ -183,7 +183,40 @@ __global__ void mask_lens_kernel(const float* __restrict__ mask, int T, int32_t*
     }
 }
 
+__global__ void prefix_kv_save_kernel(const __nv_bfloat16* __restrict__ qkv, int hd, const int32_t* __restrict__ seq_start,
+                                      const int32_t* __restrict__ slot, int prefix, __nv_bfloat16* __restrict__ slab) {
+    const int s = blockIdx.y, per_row = 2 * hd / 8;   // uint4 per cached row
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= prefix * per_row) return;
+    const int r = idx / per_row, j = idx % per_row;
+    const uint4 v = *reinterpret_cast<const uint4*>(qkv + (size_t)(seq_start[s] + r) * 3 * hd + hd + j * 8);
+    *reinterpret_cast<uint4*>(slab + ((size_t)slot[s] * prefix + r) * 2 * hd + j * 8) = v;
+}
+
+__global__ void prefix_halo_kernel(int save, __nv_bfloat16* __restrict__ buf, int64_t ld, int width,
+                                   const int32_t* __restrict__ seq_start, int row_delta, const int32_t* __restrict__ slot,
+                                   __nv_bfloat16* __restrict__ cache) {
+    const int s = blockIdx.x, per_row = width / 8;
+    for (int idx = threadIdx.x; idx < 2 * per_row; idx += blockDim.x) {
+        const int r = idx / per_row, j = idx % per_row;
+        uint4* m = reinterpret_cast<uint4*>(buf + (size_t)(seq_start[s] + row_delta + r) * ld + j * 8);
+        uint4* c = reinterpret_cast<uint4*>(cache + ((size_t)slot[s] * 2 + r) * 512 + j * 8);
+        if (save) *c = *m;
+        else *m = *c;
+    }
+}
+
 }  // namespace
+
+void launch_prefix_kv_save(const __nv_bfloat16* qkv, int hd, const int32_t* seq_start, const int32_t* slot, int nseq, int prefix,
+                           __nv_bfloat16* slab, cudaStream_t st) {
+    dim3 grid((prefix * (2 * hd / 8) + 255) / 256, nseq);
+    prefix_kv_save_kernel<<<grid, 256, 0, st>>>(qkv, hd, seq_start, slot, prefix, slab);
+}
+void launch_prefix_halo(int save, __nv_bfloat16* buf, int64_t ld, int width, const int32_t* seq_start, int row_delta,
+                        const int32_t* slot, int nseq, __nv_bfloat16* cache, cudaStream_t st) {
+    prefix_halo_kernel<<<nseq, 128, 0, st>>>(save, buf, ld, width, seq_start, row_delta, slot, cache);
+}
 
 void launch_mask_lens(const float* mask, int B, int T, int32_t* lens, int32_t* bad, cudaStream_t st) {
     mask_lens_kernel<<<B, 256, 0, st>>>(mask, T, lens, bad);

@@ -14,6 +14,8 @@ struct FlowLayout {
     int32_t noise_cstride;    // channel stride of the noise bank
     int32_t time_major;       // ragged tensors are [T_b, C] (1) instead of the reference's [C, T_b] (0)
     int32_t dense_T;          // > 0: tensors are dense [nseq, C, dense_T] (channel stride dense_T); 0: ragged
+    int32_t frame0;           // packed row t of a sequence is frame frame0 + t of its ragged block (frozen-prefix reuse: the
+                              // first frame0 frames of every utterance have no rows); the block holds frame0 + seq_len frames
     const int32_t* row_seq;   // [2 * rows_half] sequence id or -1
     const int32_t* seq_start; // [nseq] first row
     const int32_t* seq_len;   // [nseq] frames
@@ -30,6 +32,14 @@ void launch_flow_prepare(const FlowLayout& L, const float* mu, const float* spks
 void launch_euler_cfg(const FlowLayout& L, const float* d, float dt, float cfg_rate, float* xstate,
                       __nv_bfloat16* xin, cudaStream_t st);
 void launch_rows_to_bct(const FlowLayout& L, const float* rows, int row_offset, float* out, cudaStream_t st);
+// Frozen-prefix cache of a streaming solve (engine_solve.cu): copies between the packed activation matrices and the cache.
+//   kv:   rows [seq_start[s], + prefix) of qkv [*, 3 * HD] (columns HD .. 3 HD = k | v)  ->  slab rows [slot[s] * prefix, + prefix)
+//   halo: the two rows in front of row seq_start[s] + row_delta + 2 of a conv input (width channels, row stride ld)
+//         <-> cache[slot[s]][2][512]; save = 1 copies matrix -> cache, 0 cache -> matrix
+void launch_prefix_kv_save(const __nv_bfloat16* qkv, int hd, const int32_t* seq_start, const int32_t* slot, int nseq, int prefix,
+                           __nv_bfloat16* slab, cudaStream_t st);
+void launch_prefix_halo(int save, __nv_bfloat16* buf, int64_t ld, int width, const int32_t* seq_start, int row_delta,
+                        const int32_t* slot, int nseq, __nv_bfloat16* cache, cudaStream_t st);
 void launch_mask_lens(const float* mask, int B, int T, int32_t* lens, int32_t* bad, cudaStream_t st);
 void launch_est_pack(const FlowLayout& L, int nrows, const float* x, const float* mu, const float* spks,
                      const float* cond, const float* mask, __nv_bfloat16* xin, cudaStream_t st);
@@ -48,6 +58,14 @@ cudaError_t launch_attention_ws_ex(const __nv_bfloat16* qkv, int64_t rows, int q
                                    const int32_t* seq_start, const int32_t* seq_len, int nseq, int max_len, int heads, int chunk,
                                    const __nv_bfloat16* bias, int64_t bias_head_stride, int bias_ld, int bias_tmax,
                                    cudaStream_t st);
+
+// Attention over live rows whose sequences each have `prefix_len` frozen keys in front (absolute key positions
+// 0 .. prefix_len - 1; the live rows start at position prefix_len).  prefix_kv: bf16 [prefix_rows, 2 * H * 64] = [k | v];
+// sequence s's prefix starts at row prefix_row[s] (device array).  chunk must divide prefix_len.
+cudaError_t launch_attention_ws_prefix(const __nv_bfloat16* qkv, int64_t rows, __nv_bfloat16* out, const int32_t* seq_start,
+                                       const int32_t* seq_len, int nseq, int max_len, int heads, int chunk,
+                                       const __nv_bfloat16* prefix_kv, int64_t prefix_rows, int prefix_len,
+                                       const int32_t* prefix_row, cudaStream_t st);
 
 // ------------------------------------------------------------------------------------------------ encoder front end
 // Packed token-rate layout of a group of utterances (device pointers): sequence b owns token rows

@@ -212,13 +212,14 @@ class AudioDecoder(torch.nn.Module):
 
     # ------------------------------------------------------------------------------------------ batched core
     @torch.inference_mode()
-    def flow_batch(self, tokens, prompt_tokens, prompt_feats, embeddings, streaming, finalize):
+    def flow_batch(self, tokens, prompt_tokens, prompt_feats, embeddings, streaming, finalize, prefix=None):
         """CausalMaskedDiffWithXvec.inference (flow.py:237-283) for a list of utterances.
 
         tokens[b]: int [1, N_b]; prompt_tokens[b]: int [1, P_b]; prompt_feats[b]: float [1, F_b, 80];
         embeddings: float [B, 192].  Returns ragged time-major mel [sum T_b, 80] (prompt frames included), the
         per-utterance frame counts T_b and prompt frame counts F_b.  Host work: one concatenation per input kind into
-        pinned memory; everything else is mossdec_token2mel."""
+        pinned memory; everything else is mossdec_token2mel.  prefix: frozen-prefix cache arguments of a streaming chunk
+        call ({"mode", "slots", "tags"}, lib.Engine.token2mel); in reuse mode the frozen frames of "mel" are not written."""
         dev = self.device
         B = len(tokens)
         rows = [t.reshape(-1) for b in range(B) for t in (prompt_tokens[b], tokens[b])]
@@ -230,10 +231,10 @@ class AudioDecoder(torch.nn.Module):
         embeddings = embeddings.float().contiguous()
         self.last_h2d_bytes = tok.nbytes + feat_cat.nbytes + embeddings.nbytes   # what this call copies host -> device
         return self.flow_device(tok.to(dev, non_blocking=True), n_tok, feat_cat.to(dev, non_blocking=True), F_,
-                                embeddings.to(dev, non_blocking=True), streaming, finalize)
+                                embeddings.to(dev, non_blocking=True), streaming, finalize, prefix)
 
     @torch.inference_mode()
-    def flow_device(self, tok, n_tok, prompt_feat_cat, prompt_frames, embeddings, streaming, finalize):
+    def flow_device(self, tok, n_tok, prompt_feat_cat, prompt_frames, embeddings, streaming, finalize, prefix=None):
         """Device-resident core of flow_batch: tok int64 [sum n_tok] (prompt + new tokens of every utterance back to back),
         n_tok host list, prompt_feat_cat fp32 [sum F_b, 80] (prompt mels back to back), prompt_frames host list F_b,
         embeddings fp32 [B, 192] -- all tensors already on the device."""
@@ -247,7 +248,7 @@ class AudioDecoder(torch.nn.Module):
         mel = self.engine.token2mel(n_tok, tok, F_, prompt_feat_cat, embeddings, ctx,
                                     self.static_chunk_size if streaming else 0,
                                     self.estimator_chunk_frames if streaming else 0,
-                                    n_steps=self.n_timesteps, cfg_rate=self.inference_cfg_rate)
+                                    n_steps=self.n_timesteps, cfg_rate=self.inference_cfg_rate, prefix=prefix)
         return {"mel": mel, "frames": T, "prompt_frames": F_}
 
     @torch.inference_mode()

@@ -55,6 +55,11 @@ def load_library():
     lib.mossdec_hift_skip.restype = i32
     lib.mossdec_token2mel.argtypes = [vp, i32, ctypes.POINTER(i32), vp, ctypes.POINTER(i32), vp, vp, i32, i32, i32, i32, f32, vp, vp]
     lib.mossdec_token2mel.restype = i32
+    lib.mossdec_prefix_reserve.argtypes = [vp, i32, i32, i32]
+    lib.mossdec_prefix_reserve.restype = i32
+    lib.mossdec_token2mel_prefix.argtypes = [vp, i32, ctypes.POINTER(i32), vp, ctypes.POINTER(i32), vp, vp, i32, i32, i32, i32, f32,
+                                             i32, ctypes.POINTER(i32), ctypes.POINTER(ctypes.c_uint64), vp, vp]
+    lib.mossdec_token2mel_prefix.restype = i32
     lib.mossdec_fade_in_out.argtypes = [vp, vp, vp, vp, i32, vp]
     lib.mossdec_fade_in_out.restype = i32
     lib.mossdec_mel_spectrogram.argtypes = [vp, vp, i64, vp, vp]
@@ -99,7 +104,7 @@ EXPORTED_SYMBOLS = [
     "mossdec_launch_count", "mossdec_reset_launch_count", "mossdec_debug_read", "mossdec_profile",
     "mossdec_profile_read", "mossdec_set_hift_group_frames", "mossdec_cv1_resnet_block", "mossdec_cv1_downsample",
     "mossdec_cv1_upsample", "mossdec_cv1_block1d", "mossdec_reserve", "mossdec_set_graph_mode", "mossdec_graph_replays",
-    "mossdec_device", "mossdec_profile_named", "mossdec_mel_spectrogram", "mossdec_hift_skip", "mossdec_token2mel",
+    "mossdec_device", "mossdec_profile_named", "mossdec_mel_spectrogram", "mossdec_hift_skip", "mossdec_token2mel", "mossdec_prefix_reserve", "mossdec_token2mel_prefix",
 ]
 
 
@@ -221,13 +226,25 @@ class Engine:
                                                _ptr(wav), _ptr(src), int(seed), self._stream()), "hift_skip")
         return wav, src
 
+    def prefix_reserve(self, n_slots, prefix_frames, n_steps=10):
+        """Allocate the frozen-prefix cache of streaming solves (mossdec_prefix_reserve)."""
+        self._check(self.lib.mossdec_prefix_reserve(self.h, int(n_slots), int(prefix_frames), int(n_steps)), "prefix_reserve")
+
     def token2mel(self, n_tok, tokens, prompt_frames, prompt_feat, embedding, ctx_len, chunk_tokens, est_chunk_frames,
-                  n_steps=10, cfg_rate=0.7):
+                  n_steps=10, cfg_rate=0.7, prefix=None):
         """CausalMaskedDiffWithXvec.inference for a ragged batch (mossdec_token2mel): tokens int64 CUDA (ragged),
         prompt_feat fp32 CUDA ragged [F_b, 80], embedding fp32 CUDA [B, 192] -> mel fp32 ragged time-major [sum T_b, 80]."""
         B = len(n_tok)
         frames = sum(4 * (int(n) - ctx_len) for n in n_tok)
         out = torch.empty(frames, 80, dtype=torch.float32, device=tokens.device)
+        if prefix is not None and prefix["mode"] != 0:
+            # prefix = {"mode": 1 record | 2 reuse, "slots": [B], "tags": [B]}; in reuse mode the frozen frames of `out` stay unwritten
+            tags = (ctypes.c_uint64 * B)(*[int(t) & 0xFFFFFFFFFFFFFFFF for t in prefix["tags"]])
+            self._check(self.lib.mossdec_token2mel_prefix(
+                self.h, B, _i32_array(n_tok), _ptr(tokens), _i32_array(prompt_frames), _ptr(prompt_feat), _ptr(embedding),
+                int(ctx_len), int(chunk_tokens), int(est_chunk_frames), int(n_steps), float(cfg_rate), int(prefix["mode"]),
+                _i32_array(prefix["slots"]), tags, _ptr(out), self._stream()), "token2mel_prefix")
+            return out
         self._check(self.lib.mossdec_token2mel(self.h, B, _i32_array(n_tok), _ptr(tokens), _i32_array(prompt_frames),
                                                _ptr(prompt_feat), _ptr(embedding), int(ctx_len), int(chunk_tokens),
                                                int(est_chunk_frames), int(n_steps), float(cfg_rate), _ptr(out), self._stream()),

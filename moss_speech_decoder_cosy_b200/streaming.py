@@ -144,6 +144,7 @@ def stream_inference(dec, token, prompt_token, prompt_feat, embedding, block_siz
 
 class Stream:
     """One concurrent session of the batched scheduler."""
+    _next_tag = 1
 
     def __init__(self, tokens, prompt_token, prompt_feat, embedding, block_size, max_token_len):
         self.tokens = [int(t) for t in tokens]
@@ -152,6 +153,9 @@ class Stream:
         self.step = 0
         self.cache = None
         self.out = []
+        self.slot, self.recorded = None, False            # frozen-prefix cache slot of this stream
+        self.tag = Stream._next_tag                        # identity of its frozen inputs (prompt, speaker)
+        Stream._next_tag += 1
 
     @property
     def done(self):
@@ -161,45 +165,96 @@ class Stream:
 class StreamScheduler:
     """Steps many streams together: every `step()` takes the next chunk of each unfinished stream, runs ONE batched
     flow solve (block-causal for non-final chunks, full attention for final ones, like the reference's per-call flags)
-    and ONE batched vocoder pass, and returns {stream index: speech chunk [1, n]} on the device."""
+    and ONE batched vocoder pass, and returns {stream index: speech chunk [1, n]} on the device.
 
-    def __init__(self, dec, block_size=5, max_token_len=40):
+    prefix_cache: the reference recomputes the flow over prompt + window for every chunk
+    (flow_inference.py:188-218).  The first whole attention chunks inside the prompt are identical in every chunk call of
+    a stream, so their K | V and conv context are recorded by the stream's first chunk and reused afterwards
+    (include/mossdec.h, mossdec_token2mel_prefix): exact, ~1/3 less work per chunk at a 37-token prompt + 40-token window."""
+
+    def __init__(self, dec, block_size=5, max_token_len=40, prefix_cache=True):
         self.dec, self.block_size, self.max_token_len = dec, block_size, max_token_len
         self.streams = []
+        self.prefix_cache = bool(prefix_cache)
+        self._cap, self._prefix_frames = 0, 0
 
     def add(self, tokens, prompt_token, prompt_feat, embedding):
         self.streams.append(Stream(tokens, prompt_token, prompt_feat, embedding, self.block_size, self.max_token_len))
         return len(self.streams) - 1
 
+    def _prefix_frames_for(self, s):
+        """Frames of the frozen prefix a stream supports: whole estimator chunks (== whole encoder chunks) that lie inside the
+        prompt mel AND whose tokens (+ the encoder's 3 look-ahead tokens) are prompt tokens."""
+        dec = self.dec
+        chunk = dec.estimator_chunk_frames
+        if chunk <= 0 or chunk != dec.static_chunk_size * TOKEN_MEL_RATIO:
+            return 0
+        usable = min(int(s.prompt_feat.shape[1]), TOKEN_MEL_RATIO * (int(s.prompt_token.shape[1]) - PRE_LOOKAHEAD))
+        return max(0, usable // chunk) * chunk
+
+    def _ensure_cache(self):
+        """One cache geometry per scheduler: the smallest prefix any eligible stream supports (>= one chunk)."""
+        if not self.prefix_cache:
+            return
+        frames = [f for f in (self._prefix_frames_for(s) for s in self.streams) if f > 0]
+        if not frames:
+            return
+        want = min(frames)
+        n = len(self.streams)
+        if want != self._prefix_frames or n > self._cap:
+            self._cap = max(n, 2 * self._cap, 4)
+            self._prefix_frames = want
+            self.dec.engine.prefix_reserve(self._cap, want, self.dec.n_timesteps)
+            for i, s in enumerate(self.streams):               # (re)allocation drops the contents
+                s.slot, s.recorded = None, False
+        for i, s in enumerate(self.streams):
+            if s.slot is None and self._prefix_frames_for(s) >= self._prefix_frames:
+                s.slot = i
+
     @torch.inference_mode()
     def step(self):
         dec = self.dec
         emitted = {}
+        self._ensure_cache()
         for fin in (False, True):
-            ids = [i for i, s in enumerate(self.streams) if not s.done and s.plan[s.step][3] == fin]
-            if not ids:
-                continue
-            toks, offs = [], []
-            for i in ids:
+            live = [i for i, s in enumerate(self.streams) if not s.done and s.plan[s.step][3] == fin]
+            # non-final chunks: streams with a recorded prefix reuse it (mode 2), eligible new ones record it (mode 1)
+            groups = {0: [], 1: [], 2: []}
+            for i in live:
                 s = self.streams[i]
-                start, end, actual, _ = s.plan[s.step]
-                toks.append(torch.tensor(s.tokens[start:end]).unsqueeze(0))
-                offs.append(actual)
-            emb = torch.cat([self.streams[i].embedding.reshape(1, -1) for i in ids], 0)
-            r = dec.flow_batch(toks, [self.streams[i].prompt_token for i in ids],
-                               [self.streams[i].prompt_feat for i in ids], emb, streaming=not fin, finalize=fin)
-            mels, off = [], 0
-            for k in range(len(ids)):
-                T, F_ = r["frames"][k], r["prompt_frames"][k]
-                mels.append(r["mel"][off + F_ + offs[k] * TOKEN_MEL_RATIO: off + T])
-                off += T
-            out, caches = _hift_chunks(dec, mels, [self.streams[i].cache for i in ids], fin)
-            for k, i in enumerate(ids):
-                s = self.streams[i]
-                s.cache = caches[k]
-                s.step += 1
-                s.out.append(out[k])
-                emitted[i] = out[k]
+                mode = 0 if (fin or s.slot is None) else (2 if s.recorded else 1)
+                groups[mode].append(i)
+            for mode, ids in groups.items():
+                if not ids:
+                    continue
+                toks, offs = [], []
+                for i in ids:
+                    s = self.streams[i]
+                    start, end, actual, _ = s.plan[s.step]
+                    toks.append(torch.tensor(s.tokens[start:end]).unsqueeze(0))
+                    offs.append(actual)
+                emb = torch.cat([self.streams[i].embedding.reshape(1, -1) for i in ids], 0)
+                prefix = None
+                if mode:
+                    prefix = {"mode": mode, "slots": [self.streams[i].slot for i in ids],
+                              "tags": [self.streams[i].tag for i in ids]}
+                r = dec.flow_batch(toks, [self.streams[i].prompt_token for i in ids],
+                                   [self.streams[i].prompt_feat for i in ids], emb, streaming=not fin, finalize=fin,
+                                   prefix=prefix)
+                mels, off = [], 0
+                for k in range(len(ids)):
+                    T, F_ = r["frames"][k], r["prompt_frames"][k]
+                    mels.append(r["mel"][off + F_ + offs[k] * TOKEN_MEL_RATIO: off + T])
+                    off += T
+                out, caches = _hift_chunks(dec, mels, [self.streams[i].cache for i in ids], fin)
+                for k, i in enumerate(ids):
+                    s = self.streams[i]
+                    s.cache = caches[k]
+                    s.step += 1
+                    s.out.append(out[k])
+                    emitted[i] = out[k]
+                    if mode == 1:
+                        s.recorded = True
         return emitted
 
     def run(self):
