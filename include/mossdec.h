@@ -171,6 +171,16 @@ int mossdec_cv1_downsample(mossdec_handle* h, const char* prefix, int32_t B, int
 int mossdec_cv1_upsample(mossdec_handle* h, const char* prefix, int32_t B, int32_t T, int32_t C, const float* x, float* out,
                          void* stream);
 
+/* The assembled non-causal decoder of the secondary configuration: ConditionalDecoder.forward(x, mask, mu, t, spks, cond)
+ * (GLM_modules/cosyvoice/flow/decoder.py:206-291; cosyvoice1/flow/decoder.py:151-222 is the same graph) with
+ * channels = [256, 256], n_blocks transformer blocks per level (8 heads x 64, GELU), n_mid mid blocks.  Same tensor
+ * contract as mossdec_estimator: x, mu, cond, out [B, 80, T] fp32, mask [B, 1, T] (prefix masks), t [B], spks [B, 80]
+ * (spks / cond may be NULL).  Weights: tensors "<prefix>.*" (weights.py pack_cv1_decoder).  Synchronises `stream` once
+ * (mask lengths).  Chained from the building blocks above, each on its own packed rows: correct, not tuned. */
+int mossdec_cv1_estimator(mossdec_handle* h, const char* prefix, int32_t n_blocks, int32_t n_mid, int32_t B, int32_t T, const float* x,
+                          const float* mask, const float* mu, const float* t, const float* spks, const float* cond, float* out,
+                          void* stream);
+
 /* Test hook: copy up to max_floats of a named fp32 intermediate of the last call ("hift.f0", "hift.p480",
  * "hift.post", "hift.x"; "enc.mu", "enc.cond", "enc.spks" after mossdec_token2mel) to HOST memory; synchronises the device.  Returns floats copied, negative on error. */
 int mossdec_debug_read(mossdec_handle* h, const char* name, float* host_dst, int64_t max_floats);

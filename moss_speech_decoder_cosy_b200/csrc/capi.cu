@@ -125,6 +125,12 @@ int mossdec_cv1_upsample(mossdec_handle* h, const char* prefix, int32_t B, int32
     return h->eng->cv1_upsample(prefix, B, T, C, x, out, (cudaStream_t)stream);
 }
 
+int mossdec_cv1_estimator(mossdec_handle* h, const char* prefix, int32_t n_blocks, int32_t n_mid, int32_t B, int32_t T, const float* x,
+                          const float* mask, const float* mu, const float* t, const float* spks, const float* cond, float* out,
+                          void* stream) {
+    return h->eng->cv1_estimator(prefix, n_blocks, n_mid, B, T, x, mask, mu, t, spks, cond, out, (cudaStream_t)stream);
+}
+
 int mossdec_debug_read(mossdec_handle* h, const char* name, float* host_dst, int64_t max_floats) {
     return h->eng->debug_read(name, host_dst, (size_t)max_floats * 4);
 }

@@ -237,6 +237,99 @@ __global__ void __launch_bounds__(kC) gn_apply_bct_kernel(const float* __restric
     }
 }
 
+// ---- glue of the assembled two-level decoder (cv1_estimator below), all on dense [B, C, T] fp32 tensors
+// xin [B, 4 * 80, T] = x | mu | spks (broadcast over t) | cond      (decoder.py:230-236 pack)
+__global__ void cv1_cat4_kernel(const float* __restrict__ x, const float* __restrict__ mu, const float* __restrict__ spks,
+                                const float* __restrict__ cond, float* __restrict__ out, int B, int F, int T) {
+    const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= (int64_t)B * 4 * F * T) return;
+    const int t = (int)(idx % T), c = (int)((idx / T) % (4 * F)), b = (int)(idx / ((int64_t)T * 4 * F));
+    const int part = c / F, cc = c % F;
+    const size_t o = ((size_t)b * F + cc) * T + t;
+    float v = 0.f;
+    if (part == 0) v = x[o];
+    else if (part == 1) v = mu[o];
+    else if (part == 2) v = spks ? spks[(size_t)b * F + cc] : 0.f;
+    else v = cond ? cond[o] : 0.f;
+    out[idx] = v;
+}
+// out [B, 2C, T] = a[:, :, :T] (a has Ta >= T frames) | skip [B, C, T]      (decoder.py:272 pack([x[:, :, :T], skip]))
+__global__ void cv1_cat2_kernel(const float* __restrict__ a, int Ta, const float* __restrict__ skip, float* __restrict__ out,
+                                int B, int C, int T) {
+    const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= (int64_t)B * 2 * C * T) return;
+    const int t = (int)(idx % T), c = (int)((idx / T) % (2 * C)), b = (int)(idx / ((int64_t)T * 2 * C));
+    out[idx] = c < C ? a[((size_t)b * C + c) * Ta + t] : skip[((size_t)b * C + (c - C)) * T + t];
+}
+// m1[b, t] = m0[b, 2 t]      (decoder.py:252 masks.append(mask_down[:, :, ::2]))
+__global__ void cv1_mask_stride2_kernel(const float* __restrict__ m0, float* __restrict__ m1, int B, int T, int T1) {
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= B * T1) return;
+    m1[idx] = m0[(size_t)(idx / T1) * T + 2 * (idx % T1)];
+}
+__global__ void cv1_mask_mul_kernel(float* __restrict__ x, const float* __restrict__ mask, int B, int C, int T) {
+    const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= (int64_t)B * C * T) return;
+    x[idx] *= mask[(size_t)(idx / ((int64_t)C * T)) * T + idx % T];
+}
+
+// Entry of a transformer group: dense [B, 256, T] fp32 -> the packed-row fp32 residual stream (lane-major tiled layout,
+// gemm.h) + plain LayerNorm -> bf16 operand of the first q|k|v GEMM (norm1's affine is folded into its weights).
+// grid (ceil(T / 32), B), 256 threads: 32-frame x 256-channel tile through shared memory, then one warp per row.
+__global__ void __launch_bounds__(256) cv1_tf_pack_kernel(const float* __restrict__ x, int T, const int32_t* __restrict__ seq_start,
+                                                           const int32_t* __restrict__ seq_len, float* __restrict__ hres,
+                                                           __nv_bfloat16* __restrict__ xn, float eps) {
+    __shared__ float tile[32][kC + 1];
+    const int b = blockIdx.y, t0 = blockIdx.x * 32, lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const int len = seq_len[b], start = seq_start[b];
+    for (int c = w; c < kC; c += 8) tile[lane][c] = (t0 + lane < T) ? x[((size_t)b * kC + c) * T + t0 + lane] : 0.f;
+    __syncthreads();
+    for (int j = w * 4; j < w * 4 + 4; ++j) {
+        const int t = t0 + j;
+        if (t >= len) continue;
+        float v[8], s = 0.f;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            v[k] = tile[j][lane + 32 * k];
+            s += v[k];
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+        const float mean = s * (1.f / kC);
+        float q = 0.f;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) q = fmaf(v[k] - mean, v[k] - mean, q);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) q += __shfl_xor_sync(0xffffffffu, q, o);
+        const float rstd = rsqrtf(q * (1.f / kC) + eps);
+        const int row = start + t;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            const int c = lane + 32 * k;
+            hres[tiled_f32_offset(row, c)] = v[k];
+            xn[(size_t)row * kC + c] = __float2bfloat16((v[k] - mean) * rstd);
+        }
+    }
+}
+// Exit of a transformer group: tiled fp32 stream -> dense [B, 256, T] fp32 (zeros on padded frames)
+__global__ void __launch_bounds__(256) cv1_tf_unpack_kernel(const float* __restrict__ hres, int T, const int32_t* __restrict__ seq_start,
+                                                             const int32_t* __restrict__ seq_len, float* __restrict__ out) {
+    __shared__ float tile[32][kC + 1];
+    const int b = blockIdx.y, t0 = blockIdx.x * 32, lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const int len = seq_len[b], start = seq_start[b];
+    for (int j = w * 4; j < w * 4 + 4; ++j) {
+        const int t = t0 + j;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            const int c = lane + 32 * k;
+            tile[j][c] = t < len ? hres[tiled_f32_offset(start + t, c)] : 0.f;
+        }
+    }
+    __syncthreads();
+    for (int c = w; c < kC; c += 8)
+        if (t0 + lane < T) out[((size_t)b * kC + c) * T + t0 + lane] = tile[lane][c];
+}
+
 inline size_t align256(size_t v) { return (v + 255) & ~(size_t)255; }
 
 }  // namespace
@@ -453,6 +546,197 @@ int Engine::cv1_upsample(const char* prefix, int B, int T, int C, const float* x
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return fail(std::string("cv1_upsample: ") + cudaGetErrorString(e));
     return 0;
+}
+
+// Plain Conv1d of the decoder with "same" padding (k = 3: the `downsample` / `upsample` slots of the last level,
+// decoder.py:137-139,182-186; k = 1: final_proj, :188): out [B, Cout, T] = conv(x * mask_in) (* mask_out)
+int Engine::cv1_conv(const char* prefix, int B, int T, int Cin, int Cout, int k, const float* x, const float* mask_in,
+                     const float* mask_out, float* out, cudaStream_t st) {
+    DeviceGuard guard_(device_);
+    if (B <= 0 || T <= 0 || (k != 1 && k != 3) || Cout > 256 || (Cout % 16) != 0) return fail("cv1_conv: bad shape");
+    const std::string P(prefix);
+    missing_.clear();
+    const __nv_bfloat16* w = W<__nv_bfloat16>(P + ".w");
+    const float* bias = W<float>(P + ".b");
+    if (!missing_.empty()) return fail("cv1_conv: missing tensors: " + missing_);
+    const int cin_pad = (Cin + kGemmBK - 1) / kGemmBK * kGemmBK;
+    const int S = T + 2, g = 1;
+    const int Mp = (int)(((int64_t)B * S + kGemmBM - 1) / kGemmBM * kGemmBM);
+    size_t off = 0;
+    auto take = [&](size_t bytes) { size_t o = off; off = align256(off + bytes); return o; };
+    const size_t o_xa = take((size_t)(Mp + 2) * cin_pad * 2), o_y = take((size_t)Mp * Cout * 4), o_rs = take((size_t)Mp * 4);
+    ws_cv1_.reserve(off);
+    char* base = ws_cv1_.as<char>();
+    if (!base) return fail("cv1_conv: workspace allocation failed");
+    auto* xa = reinterpret_cast<__nv_bfloat16*>(base + o_xa);
+    float* y = reinterpret_cast<float*>(base + o_y);
+    auto* row_seq = reinterpret_cast<int32_t*>(base + o_rs);
+    cudaMemsetAsync(xa, 0, (size_t)(Mp + 2) * cin_pad * 2, st);
+    cv1_rowseq_kernel<<<(Mp + 255) / 256, 256, 0, st>>>(row_seq, Mp, B, S, g, T);
+    cv1_pack_kernel<<<dim3((T + 31) / 32, cin_pad / 64, B), dim3(32, 8), 0, st>>>(x, mask_in, xa, Cin, cin_pad, T, S, g);
+    GemmProblem p;
+    p.a[0].ptr = xa; p.a[0].rows = Mp; p.a[0].cols = cin_pad; p.a[0].ld = cin_pad;
+    p.num_segs = k;
+    for (int j = 0; j < k; ++j) p.segs[j] = {0, j - k / 2, 0, cin_pad / kGemmBK};
+    p.M = Mp; p.N = Cout; p.BN = Cout; p.w = w;
+    p.epi.bias = bias; p.epi.row_seq = row_seq;
+    p.epi.out_f32 = y; p.epi.ldf = Cout;
+    if (gemm(p, st)) return -1;
+    cv1_unpack_kernel<<<dim3((T + 31) / 32, (Cout + 31) / 32, B), dim3(32, 8), 0, st>>>(y, out, Cout, Cout, T, 1, S, g, T);
+    launches_ += 3;
+    if (mask_out) {
+        const int64_t n = (int64_t)B * Cout * T;
+        cv1_mask_mul_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(out, mask_out, B, Cout, T);
+        ++launches_;
+    }
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return fail(std::string("cv1_conv: ") + cudaGetErrorString(e));
+    return 0;
+}
+
+// n_blocks BasicTransformerBlocks of one decoder level (decoder.py:238-249: rearrange, key-padding attention bias, blocks,
+// rearrange back) on the kernels of the live path: q|k|v GEMM, attention_ws_kernel with chunk = 0 (non-causal: the
+// key-padding predicate only), fused out-projection + feed-forward.  lens: HOST valid frames per utterance.
+int Engine::cv1_transformer_group(const char* prefix, int n_blocks, int B, int T, const float* x, const int32_t* lens, float* out,
+                                  cudaStream_t st) {
+    DeviceGuard guard_(device_);
+    const std::string P(prefix);
+    const int C = cfg_.channels, H = cfg_.heads * cfg_.head_dim;
+    if (build_flow_layout(B, lens, /*cfg_double=*/false, st, /*dense_T=*/T)) return -1;
+    const int M = flow_M_;
+    cv1_tf_pack_kernel<<<dim3((T + 31) / 32, B), 256, 0, st>>>(x, T, layout_.seq_start, layout_.seq_len, hres_, xn_, 1e-5f);
+    ++launches_;
+    missing_.clear();
+    for (int j = 0; j < n_blocks; ++j) {
+        char buf[32];
+        snprintf(buf, sizeof buf, ".%d.", j);
+        const std::string t = P + buf;
+        const __nv_bfloat16 *wqkv = W<__nv_bfloat16>(t + "qkv.w"), *wo = W<__nv_bfloat16>(t + "o.w"),
+                            *w1 = W<__nv_bfloat16>(t + "ff1.w"), *w2 = W<__nv_bfloat16>(t + "ff2.w");
+        const float *bqkv = W<float>(t + "qkv.b"), *bo = W<float>(t + "o.b"), *b1 = W<float>(t + "ff1.b"), *b2 = W<float>(t + "ff2.b");
+        if (!missing_.empty()) return fail("cv1_transformer_group: missing tensors: " + missing_);
+        {
+            GemmProblem p;
+            p.a[0].ptr = xn_; p.a[0].rows = M; p.a[0].cols = C; p.a[0].ld = C;
+            p.num_segs = 1;
+            p.segs[0] = {0, 0, 0, C / kGemmBK};
+            p.M = M; p.N = 3 * H; p.BN = 256; p.w = wqkv;
+            p.epi.bias = bqkv;
+            p.epi.row_seq = layout_.row_seq;
+            p.epi.out_bf16 = qkv_; p.epi.ldo = 3 * H;
+            if (gemm(p, st)) return -1;
+        }
+        cudaError_t ae = launch_attention_ws(qkv_, M, att_, layout_.seq_start, layout_.seq_len, B, flow_max_len_, cfg_.heads, 0, st);
+        if (ae != cudaSuccess) return fail(std::string("cv1 attention: ") + cudaGetErrorString(ae));
+        ++launches_;
+        FfnProblem f;
+        f.M = M;
+        f.att = att_; f.wo = wo; f.bo = bo;
+        f.w1 = w1; f.b1 = b1; f.w2 = w2; f.b2 = b2;
+        f.hres = hres_;
+        f.row_seq = layout_.row_seq;
+        f.ln = j + 1 < n_blocks;   // norm1 of the next block (affine folded into its q|k|v weights)
+        f.out_bf16 = xn_; f.ldo = C;
+        f.store_f32 = 1;
+        if (ffn(f, st)) return -1;
+    }
+    cv1_tf_unpack_kernel<<<dim3((T + 31) / 32, B), 256, 0, st>>>(hres_, T, layout_.seq_start, layout_.seq_len, out);
+    ++launches_;
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return fail(std::string("cv1_transformer_group: ") + cudaGetErrorString(e));
+    return 0;
+}
+
+// The assembled non-causal decoder: ConditionalDecoder.forward of cosyvoice (flow/decoder.py:206-291; cosyvoice1/flow/decoder.py
+// :151-222 is the same graph) with channels = [256, 256]: two resolutions (T and ceil(T / 2)), skip concatenation, GroupNorm
+// resnets, non-causal transformer groups, stride-2 down / ConvTranspose up.  Chained from the blocks above on dense
+// [B, C, T] fp32 tensors -- every op packs / unpacks its own rows (correct, not fast: see DESIGN.md section 7).
+// Tensors: "<p>.time.{w1,b1,w2,b2}", "<p>.{d0,d1,m<i>,u0,u1}.res.*" (pack_cv1_resnet), "<p>.<level>.tf.<j>.*" (q|k|v, o, ff1,
+// ff2 as in the live path), "<p>.d0.down.*", "<p>.d1.conv.*", "<p>.u0.up.*", "<p>.u1.conv.*", "<p>.final.*", "<p>.proj.*".
+int Engine::cv1_estimator(const char* prefix, int n_blocks, int n_mid, int B, int T, const float* x, const float* mask, const float* mu,
+                          const float* t, const float* spks, const float* cond, float* out, cudaStream_t st) {
+    DeviceGuard guard_(device_);
+    if (B <= 0 || T < 2 || n_blocks <= 0 || n_mid < 0) return fail("cv1_estimator: bad shape");
+    const std::string P(prefix);
+    const int F = cfg_.n_feats, C = kC, TD = cfg_.time_dim, T1 = (T - 1) / 2 + 1;
+    // valid lengths (prefix masks only), read back once: this entry point mirrors a synchronous module call
+    std::vector<int32_t> lens0(B), lens1(B);
+    {
+        if (mask_lens_cap_ < B + 1) {
+            if (h_mask_lens_) cudaFreeHost(h_mask_lens_);
+            if (d_mask_lens_) cudaFree(d_mask_lens_);
+            h_mask_lens_ = nullptr;
+            d_mask_lens_ = nullptr;
+            mask_lens_cap_ = 0;
+            if (cudaMallocHost(reinterpret_cast<void**>(&h_mask_lens_), (size_t)(B + 1) * 4) != cudaSuccess ||
+                cudaMalloc(reinterpret_cast<void**>(&d_mask_lens_), (size_t)(B + 1) * 4) != cudaSuccess)
+                return fail("cv1_estimator: allocation failed");
+            mask_lens_cap_ = B + 1;
+        }
+        cudaMemsetAsync(d_mask_lens_ + B, 0, 4, st);
+        launch_mask_lens(mask, B, T, d_mask_lens_, d_mask_lens_ + B, st);
+        cudaMemcpyAsync(h_mask_lens_, d_mask_lens_, (size_t)(B + 1) * 4, cudaMemcpyDeviceToHost, st);
+        if (cudaStreamSynchronize(st) != cudaSuccess) return fail("cv1_estimator: sync failed");
+        if (h_mask_lens_[B] != 0) return fail("cv1_estimator: mask must be a prefix (padding) mask");
+        for (int b = 0; b < B; ++b) {
+            lens0[b] = h_mask_lens_[b];
+            if (lens0[b] <= 0) return fail("cv1_estimator: a sequence is fully masked");
+            lens1[b] = (lens0[b] + 1) / 2;   // mask[:, :, ::2]
+        }
+        ++launches_;
+    }
+    // dense intermediates
+    size_t off = 0;
+    auto take = [&](size_t bytes) { size_t o = off; off = align256(off + bytes); return o; };
+    const size_t nT = (size_t)B * C * T, nT1 = (size_t)B * C * T1;
+    const size_t o_xin = take((size_t)B * 4 * F * T * 4), o_temb = take((size_t)B * TD * 4), o_m1 = take((size_t)B * T1 * 4),
+                 o_cat = take(2 * nT * 4), o_a = take(nT * 4), o_b = take(nT * 4), o_s0 = take(nT * 4), o_s1 = take(nT1 * 4),
+                 o_up = take((size_t)B * C * 2 * T1 * 4);
+    ws_cv1e_.reserve(off);
+    char* base = ws_cv1e_.as<char>();
+    if (!base) return fail("cv1_estimator: workspace allocation failed");
+    float *xin = (float*)(base + o_xin), *temb = (float*)(base + o_temb), *m1 = (float*)(base + o_m1), *cat = (float*)(base + o_cat),
+          *A = (float*)(base + o_a), *Bf = (float*)(base + o_b), *skip0 = (float*)(base + o_s0), *skip1 = (float*)(base + o_s1),
+          *up = (float*)(base + o_up);
+    missing_.clear();
+    const float *tw1 = W<float>(P + ".time.w1"), *tb1 = W<float>(P + ".time.b1"), *tw2 = W<float>(P + ".time.w2"), *tb2 = W<float>(P + ".time.b2");
+    if (!missing_.empty()) return fail("cv1_estimator: missing tensors: " + missing_);
+    launch_time_embed(t, B, 4 * F, TD, tw1, tb1, tw2, tb2, temb, st, /*apply_mish=*/0);   // raw: ResnetBlock1D.mlp applies Mish
+    {
+        const int64_t n = (int64_t)B * 4 * F * T;
+        cv1_cat4_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(x, mu, spks, cond, xin, B, F, T);
+        cv1_mask_stride2_kernel<<<(B * T1 + 255) / 256, 256, 0, st>>>(mask, m1, B, T, T1);
+    }
+    launches_ += 3;
+    auto level = [&](const std::string& name, int Cin, int Tl, const float* in, const float* m, const int32_t* lens, float* dst) -> int {
+        if (cv1_resnet_block((P + "." + name + ".res").c_str(), B, Tl, Cin, in, m, temb, TD, A, st)) return -1;
+        return cv1_transformer_group((P + "." + name + ".tf").c_str(), n_blocks, B, Tl, A, lens, dst, st);
+    };
+    auto cat2 = [&](const float* a, int Ta, const float* skip, int Tl) {
+        const int64_t n = (int64_t)B * 2 * C * Tl;
+        cv1_cat2_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(a, Ta, skip, cat, B, C, Tl);
+        ++launches_;
+    };
+    // down path
+    if (level("d0", 4 * F, T, xin, mask, lens0.data(), skip0)) return -1;
+    if (cv1_downsample((P + ".d0.down").c_str(), B, T, C, skip0, Bf, st)) return -1;             // x * mask: padded frames are already zero
+    if (level("d1", C, T1, Bf, m1, lens1.data(), skip1)) return -1;
+    if (cv1_conv((P + ".d1.conv").c_str(), B, T1, C, C, 3, skip1, m1, nullptr, Bf, st)) return -1;
+    // mid
+    for (int i = 0; i < n_mid; ++i) {
+        char nm[16];
+        snprintf(nm, sizeof nm, "m%d", i);
+        if (level(nm, C, T1, Bf, m1, lens1.data(), Bf)) return -1;
+    }
+    // up path
+    cat2(Bf, T1, skip1, T1);
+    if (level("u0", 2 * C, T1, cat, m1, lens1.data(), Bf)) return -1;
+    if (cv1_upsample((P + ".u0.up").c_str(), B, T1, C, Bf, up, st)) return -1;
+    cat2(up, 2 * T1, skip0, T);
+    if (level("u1", 2 * C, T, cat, mask, lens0.data(), Bf)) return -1;
+    if (cv1_conv((P + ".u1.conv").c_str(), B, T, C, C, 3, Bf, mask, nullptr, A, st)) return -1;
+    if (cv1_block1d((P + ".final").c_str(), B, T, C, A, mask, Bf, st)) return -1;
+    return cv1_conv((P + ".proj").c_str(), B, T, C, F, 1, Bf, mask, mask, out, st);
 }
 
 }  // namespace mossdec

@@ -142,6 +142,13 @@ class Engine {
     int cv1_block1d(const char* prefix, int B, int T, int Cin, const float* x, const float* mask, float* out, cudaStream_t st);
     int cv1_downsample(const char* prefix, int B, int T, int C, const float* x, float* out, cudaStream_t st);
     int cv1_upsample(const char* prefix, int B, int T, int C, const float* x, float* out, cudaStream_t st);
+    // the assembled two-level non-causal decoder (ConditionalDecoder.forward, flow/decoder.py:206-291) and its remaining parts
+    int cv1_conv(const char* prefix, int B, int T, int Cin, int Cout, int k, const float* x, const float* mask_in,
+                 const float* mask_out, float* out, cudaStream_t st);
+    int cv1_transformer_group(const char* prefix, int n_blocks, int B, int T, const float* x, const int32_t* lens, float* out,
+                              cudaStream_t st);
+    int cv1_estimator(const char* prefix, int n_blocks, int n_mid, int B, int T, const float* x, const float* mask, const float* mu,
+                      const float* t, const float* spks, const float* cond, float* out, cudaStream_t st);
 
     const char* last_error() const { return err_.c_str(); }
     long launches() const { return launches_; }
@@ -261,7 +268,7 @@ class Engine {
     float *temb_ = nullptr, *tbias_ = nullptr, *tvals_ = nullptr;
 
     // ---- cosyvoice1 building-block workspace (cv1_ops.cu)
-    DeviceBuffer ws_cv1_;
+    DeviceBuffer ws_cv1_, ws_cv1e_;
     DeviceBuffer ws_mel_;   // prompt mel front end (mel_kernels.cu)
 
     // ---- encoder front end (engine_encoder.cu)

@@ -19,7 +19,7 @@ __device__ __forceinline__ float warp_sum(float v) {
 // One block per distinct timestep value.  temb[s, :] = lin2(silu(lin1(sinusoid(1000 t_s)))).
 __global__ void time_embed_kernel(const float* __restrict__ t, int dim_in, int dim_h, const float* __restrict__ w1,
                                   const float* __restrict__ b1, const float* __restrict__ w2,
-                                  const float* __restrict__ b2, float* __restrict__ temb_mish) {
+                                  const float* __restrict__ b2, float* __restrict__ temb_mish, int apply_mish) {
     extern __shared__ float sm[];
     float* pe = sm;           // [dim_in]
     float* h1 = sm + dim_in;  // [dim_h]
@@ -49,7 +49,8 @@ __global__ void time_embed_kernel(const float* __restrict__ t, int dim_in, int d
         for (int i = lane; i < dim_h; i += 32) acc += w[i] * h1[i];
         acc = warp_sum(acc);
         // every consumer applies Mish first (ResnetBlock1D.mlp = Sequential(Mish, Linear)), so store mish(temb)
-        if (lane == 0) temb_mish[(size_t)s * dim_h + o] = mish_f(acc + b2[o]);
+        // (apply_mish == 0: the raw embedding, for consumers that apply their own activation -- cv1_ops.cu)
+        if (lane == 0) temb_mish[(size_t)s * dim_h + o] = apply_mish ? mish_f(acc + b2[o]) : acc + b2[o];
     }
 }
 
@@ -223,8 +224,8 @@ void launch_mask_lens(const float* mask, int B, int T, int32_t* lens, int32_t* b
 }
 
 void launch_time_embed(const float* t, int nseq, int dim_in, int dim_h, const float* w1, const float* b1,
-                       const float* w2, const float* b2, float* temb_mish, cudaStream_t st) {
-    time_embed_kernel<<<nseq, 512, (dim_in + dim_h) * sizeof(float), st>>>(t, dim_in, dim_h, w1, b1, w2, b2, temb_mish);
+                       const float* w2, const float* b2, float* temb_mish, cudaStream_t st, int apply_mish) {
+    time_embed_kernel<<<nseq, 512, (dim_in + dim_h) * sizeof(float), st>>>(t, dim_in, dim_h, w1, b1, w2, b2, temb_mish, apply_mish);
 }
 void launch_time_bias(const float* temb_mish, int nseq, int dim_h, const float* w, const float* b, int n_out,
                       float* tbias, cudaStream_t st) {

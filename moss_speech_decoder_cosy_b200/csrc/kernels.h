@@ -23,7 +23,7 @@ struct FlowLayout {
 };
 
 void launch_time_embed(const float* t, int nseq, int dim_in, int dim_h, const float* w1, const float* b1,
-                       const float* w2, const float* b2, float* temb_mish, cudaStream_t st);
+                       const float* w2, const float* b2, float* temb_mish, cudaStream_t st, int apply_mish = 1);
 void launch_time_bias(const float* temb_mish, int nseq, int dim_h, const float* w, const float* b, int n_out,
                       float* tbias, cudaStream_t st);
 void launch_flow_prepare(const FlowLayout& L, const float* mu, const float* spks, const float* cond,

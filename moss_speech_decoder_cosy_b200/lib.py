@@ -72,6 +72,8 @@ def load_library():
     lib.mossdec_cv1_downsample.restype = i32
     lib.mossdec_cv1_upsample.argtypes = [vp, ctypes.c_char_p, i32, i32, i32, vp, vp, vp]
     lib.mossdec_cv1_upsample.restype = i32
+    lib.mossdec_cv1_estimator.argtypes = [vp, ctypes.c_char_p, i32, i32, i32, i32, vp, vp, vp, vp, vp, vp, vp, vp]
+    lib.mossdec_cv1_estimator.restype = i32
     lib.mossdec_debug_read.argtypes = [vp, ctypes.c_char_p, vp, i64]
     lib.mossdec_debug_read.restype = i32
     lib.mossdec_profile.argtypes = [vp, i32]
@@ -104,7 +106,7 @@ EXPORTED_SYMBOLS = [
     "mossdec_launch_count", "mossdec_reset_launch_count", "mossdec_debug_read", "mossdec_profile",
     "mossdec_profile_read", "mossdec_set_hift_group_frames", "mossdec_cv1_resnet_block", "mossdec_cv1_downsample",
     "mossdec_cv1_upsample", "mossdec_cv1_block1d", "mossdec_reserve", "mossdec_set_graph_mode", "mossdec_graph_replays",
-    "mossdec_device", "mossdec_profile_named", "mossdec_mel_spectrogram", "mossdec_hift_skip", "mossdec_token2mel", "mossdec_prefix_reserve", "mossdec_token2mel_prefix",
+    "mossdec_device", "mossdec_profile_named", "mossdec_mel_spectrogram", "mossdec_hift_skip", "mossdec_token2mel", "mossdec_prefix_reserve", "mossdec_token2mel_prefix", "mossdec_cv1_estimator",
 ]
 
 
@@ -304,6 +306,17 @@ class Engine:
         out = torch.empty(B, C, 2 * T, device=x.device, dtype=torch.float32)
         self._check(self.lib.mossdec_cv1_upsample(self.h, prefix.encode(), B, T, C, _ptr(x), _ptr(out), self._stream()),
                     "cv1_upsample")
+        return out
+
+    def cv1_estimator(self, prefix, n_blocks, n_mid, x, mask, mu, t, spks=None, cond=None):
+        """ConditionalDecoder.forward of the non-causal cosyvoice / cosyvoice1 decoder (flow/decoder.py:206-291), channels [256, 256]."""
+        B, _, T = x.shape
+        f = lambda a: None if a is None else a.float().contiguous()
+        x, mask, mu, t, spks, cond = f(x), f(mask), f(mu), f(t), f(spks), f(cond)
+        out = torch.empty_like(x)
+        self._check(self.lib.mossdec_cv1_estimator(self.h, prefix.encode(), int(n_blocks), int(n_mid), B, T, _ptr(x), _ptr(mask),
+                                                   _ptr(mu), _ptr(t), _ptr(spks), _ptr(cond), _ptr(out), self._stream()),
+                    "cv1_estimator")
         return out
 
     def debug_read(self, name, max_floats):

@@ -135,3 +135,59 @@ def synth_cv1_blocks_state_dict(seed: int = 0, cin: int = 320, time_dim: int = 1
         else:
             sd[key] = _normal(seed, k, shape, 0.05)
     return sd
+
+
+def cv1_decoder_shapes(n_blocks: int = 4, n_mid: int = 12, in_channels: int = 320, out_channels: int = 80, C: int = 256,
+                       heads: int = 8, head_dim: int = 64):
+    """state_dict keys / shapes of the non-causal ConditionalDecoder (cosyvoice/flow/decoder.py:88-204, cosyvoice1/flow/decoder.py)
+    with channels = [C, C] (oracle/make_golden_r2.py loads them with strict=True into the reference class)."""
+    td, inner = 4 * C, heads * head_dim
+    sh = {"time_mlp.linear_1.weight": (td, in_channels), "time_mlp.linear_1.bias": (td,),
+          "time_mlp.linear_2.weight": (td, td), "time_mlp.linear_2.bias": (td,)}
+
+    def resnet(p, cin):
+        sh.update({f"{p}.block1.block.0.weight": (C, cin, 3), f"{p}.block1.block.0.bias": (C,),
+                   f"{p}.block1.block.1.weight": (C,), f"{p}.block1.block.1.bias": (C,),
+                   f"{p}.block2.block.0.weight": (C, C, 3), f"{p}.block2.block.0.bias": (C,),
+                   f"{p}.block2.block.1.weight": (C,), f"{p}.block2.block.1.bias": (C,),
+                   f"{p}.mlp.1.weight": (C, td), f"{p}.mlp.1.bias": (C,),
+                   f"{p}.res_conv.weight": (C, cin, 1), f"{p}.res_conv.bias": (C,)})
+
+    def tf(p):
+        for j in range(n_blocks):
+            q = f"{p}.{j}"
+            sh.update({f"{q}.norm1.weight": (C,), f"{q}.norm1.bias": (C,), f"{q}.norm3.weight": (C,), f"{q}.norm3.bias": (C,),
+                       f"{q}.attn1.to_q.weight": (inner, C), f"{q}.attn1.to_k.weight": (inner, C), f"{q}.attn1.to_v.weight": (inner, C),
+                       f"{q}.attn1.to_out.0.weight": (C, inner), f"{q}.attn1.to_out.0.bias": (C,),
+                       f"{q}.ff.net.0.proj.weight": (4 * C, C), f"{q}.ff.net.0.proj.bias": (4 * C,),
+                       f"{q}.ff.net.2.weight": (C, 4 * C), f"{q}.ff.net.2.bias": (C,)})
+    resnet("down_blocks.0.0", in_channels); tf("down_blocks.0.1")
+    sh.update({"down_blocks.0.2.conv.weight": (C, C, 3), "down_blocks.0.2.conv.bias": (C,)})          # Downsample1D
+    resnet("down_blocks.1.0", C); tf("down_blocks.1.1")
+    sh.update({"down_blocks.1.2.weight": (C, C, 3), "down_blocks.1.2.bias": (C,)})                    # Conv1d k3 p1
+    for i in range(n_mid):
+        resnet(f"mid_blocks.{i}.0", C); tf(f"mid_blocks.{i}.1")
+    resnet("up_blocks.0.0", 2 * C); tf("up_blocks.0.1")
+    sh.update({"up_blocks.0.2.conv.weight": (C, C, 4), "up_blocks.0.2.conv.bias": (C,)})              # Upsample1D ConvTranspose
+    resnet("up_blocks.1.0", 2 * C); tf("up_blocks.1.1")
+    sh.update({"up_blocks.1.2.weight": (C, C, 3), "up_blocks.1.2.bias": (C,)})
+    sh.update({"final_block.block.0.weight": (C, C, 3), "final_block.block.0.bias": (C,),
+               "final_block.block.1.weight": (C,), "final_block.block.1.bias": (C,),
+               "final_proj.weight": (out_channels, C, 1), "final_proj.bias": (out_channels,)})
+    return sh
+
+
+def synth_cv1_decoder_state_dict(seed: int = 0, n_blocks: int = 4, n_mid: int = 12):
+    """Random-init weights of the assembled non-causal decoder, same scale rules as the flow checkpoint."""
+    sd = {}
+    for key, shape in cv1_decoder_shapes(n_blocks, n_mid).items():
+        k = "cv1dec." + key
+        if len(shape) >= 2:
+            fan_in = int(np.prod(shape[1:]))
+            gain = 2.0 if (".ff.net.0.proj." in key or "block.0.weight" in key) else 1.0
+            sd[key] = _normal(seed, k, shape, math.sqrt(gain / fan_in))
+        elif key.endswith("weight"):      # GroupNorm / LayerNorm gammas
+            sd[key] = _normal(seed, k, shape, 0.1, 1.0)
+        else:
+            sd[key] = _normal(seed, k, shape, 0.05)
+    return sd

@@ -68,6 +68,28 @@ def _f32(t):
     return t.float().contiguous()
 
 
+def pack_transformer_block(g, t, o, head_dim=64):
+    """BasicTransformerBlock (matcha transformer.py:243-316 + diffusers Attention / GELU) keys under `t` (read through the
+    getter g) -> engine tensors under `o`.  The affine part of norm1 / norm3 is folded into the Linear that consumes the
+    normalised activation (W . (g * n + b) = (W diag g) . n + W . b), so the kernels' LayerNorm epilogues only normalise;
+    1 / sqrt(head_dim) is folded into the q rows."""
+    out = {}
+    n1g, n1b = g(t + "norm1.weight"), g(t + "norm1.bias")
+    n3g, n3b = g(t + "norm3.weight"), g(t + "norm3.bias")
+    q = g(t + "attn1.to_q.weight") * (1.0 / math.sqrt(head_dim))
+    wqkv = torch.cat([q, g(t + "attn1.to_k.weight"), g(t + "attn1.to_v.weight")], 0)
+    out[o + "qkv.w"] = _bf16(wqkv * n1g[None, :])
+    out[o + "qkv.b"] = _f32(wqkv @ n1b)
+    out[o + "o.w"] = _bf16(g(t + "attn1.to_out.0.weight"))
+    out[o + "o.b"] = _f32(g(t + "attn1.to_out.0.bias"))
+    w1 = g(t + "ff.net.0.proj.weight")
+    out[o + "ff1.w"] = _bf16(w1 * n3g[None, :])
+    out[o + "ff1.b"] = _f32(g(t + "ff.net.0.proj.bias") + w1 @ n3b)
+    out[o + "ff2.w"] = _bf16(g(t + "ff.net.2.weight"))
+    out[o + "ff2.b"] = _f32(g(t + "ff.net.2.bias"))
+    return out
+
+
 def pack_estimator(sd, prefix="decoder.estimator.", n_mid=12, n_blocks=4, head_dim=64):
     """CausalConditionalDecoder (cosyvoice/flow/decoder.py:294-403) with channels=[256]."""
     out = {}
@@ -96,21 +118,7 @@ def pack_estimator(sd, prefix="decoder.estimator.", n_mid=12, n_blocks=4, head_d
         for j in range(n_blocks):
             t = f"{gp}.1.{j}."
             o = f"est.tf{gi}.{j}."
-            # The affine part of norm1 / norm3 is folded into the Linear that consumes the normalised activation
-            # (W . (g * n + b) = (W diag g) . n + W . b), so the kernels' LayerNorm epilogues only normalise.
-            n1g, n1b = g(t + "norm1.weight"), g(t + "norm1.bias")
-            n3g, n3b = g(t + "norm3.weight"), g(t + "norm3.bias")
-            q = g(t + "attn1.to_q.weight") * (1.0 / math.sqrt(head_dim))
-            wqkv = torch.cat([q, g(t + "attn1.to_k.weight"), g(t + "attn1.to_v.weight")], 0)
-            out[o + "qkv.w"] = _bf16(wqkv * n1g[None, :])
-            out[o + "qkv.b"] = _f32(wqkv @ n1b)
-            out[o + "o.w"] = _bf16(g(t + "attn1.to_out.0.weight"))
-            out[o + "o.b"] = _f32(g(t + "attn1.to_out.0.bias"))
-            w1 = g(t + "ff.net.0.proj.weight")
-            out[o + "ff1.w"] = _bf16(w1 * n3g[None, :])
-            out[o + "ff1.b"] = _f32(g(t + "ff.net.0.proj.bias") + w1 @ n3b)
-            out[o + "ff2.w"] = _bf16(g(t + "ff.net.2.weight"))
-            out[o + "ff2.b"] = _f32(g(t + "ff.net.2.bias"))
+            out.update(pack_transformer_block(g, t, o, head_dim))
     out["est.tbias.w"] = _f32(torch.cat(tb_w, 0))
     out["est.tbias.b"] = _f32(torch.cat(tb_b, 0))
     out["est.down.conv.w"] = _bf16(conv_weight_taps(g("down_blocks.0.2.weight")))     # decoder.py:348-350
@@ -285,4 +293,28 @@ def pack_encoder(sd, heads=8):
     out["enc.up.w"] = _bf16(wp.reshape(s_ * w.shape[0], 3 * w.shape[1]))
     out["enc.up.b"] = _f32(g(e + "up_layer.conv.bias").repeat(s_))
     out["enc.after.g"], out["enc.after.b"] = _f32(g(e + "after_norm.weight")), _f32(g(e + "after_norm.bias"))
+    return out
+
+
+def pack_cv1_decoder(sd, dst="cv1d", n_blocks=4, n_mid=12, head_dim=64):
+    """The assembled non-causal ConditionalDecoder (cosyvoice/flow/decoder.py:88-204, channels = [256, 256]) -> engine tensors
+    under `dst` for mossdec_cv1_estimator (csrc/cv1_ops.cu)."""
+    out = {}
+    g = lambda k: sd[k].float()
+    for a, b in (("w1", "linear_1.weight"), ("b1", "linear_1.bias"), ("w2", "linear_2.weight"), ("b2", "linear_2.bias")):
+        out[f"{dst}.time.{a}"] = _f32(g("time_mlp." + b))
+    levels = [("d0", "down_blocks.0"), ("d1", "down_blocks.1")] + [(f"m{i}", f"mid_blocks.{i}") for i in range(n_mid)] + \
+             [("u0", "up_blocks.0"), ("u1", "up_blocks.1")]
+    for name, src in levels:
+        out.update(pack_cv1_resnet(sd, f"{src}.0", f"{dst}.{name}.res"))
+        for j in range(n_blocks):
+            out.update(pack_transformer_block(g, f"{src}.1.{j}.", f"{dst}.{name}.tf.{j}.", head_dim))
+    out.update(pack_cv1_downsample(sd, "down_blocks.0.2", f"{dst}.d0.down"))
+    out.update(pack_cv1_upsample(sd, "up_blocks.0.2", f"{dst}.u0.up"))
+    for name, src in (("d1", "down_blocks.1.2"), ("u1", "up_blocks.1.2")):                       # plain Conv1d(k3, p1) slots
+        out[f"{dst}.{name}.conv.w"] = _bf16(conv_weight_taps(g(src + ".weight")))
+        out[f"{dst}.{name}.conv.b"] = _f32(g(src + ".bias"))
+    out.update(pack_cv1_block1d(sd, "final_block", f"{dst}.final"))
+    out[f"{dst}.proj.w"] = _bf16(conv_weight_taps(g("final_proj.weight")))
+    out[f"{dst}.proj.b"] = _f32(g("final_proj.bias"))
     return out

@@ -53,5 +53,31 @@ def main():
     _save("cv1_blocks.npz", **out)
 
 
+def decoder_golden(n_blocks=2, n_mid=2):
+    """The assembled non-causal ConditionalDecoder (cosyvoice/flow/decoder.py:88-291, UNMODIFIED) with channels = [256, 256],
+    8 heads x 64, GELU, `n_blocks` transformer blocks per level and `n_mid` mid blocks, random-init weights of
+    synth.synth_cv1_decoder_state_dict; ragged masks, odd and even lengths.  -> tests/golden/cv1_decoder.npz"""
+    import numpy as np
+    ref_shims.install()
+    from cosyvoice.flow.decoder import ConditionalDecoder
+    from moss_speech_decoder_cosy_b200 import synth
+    dec = ConditionalDecoder(in_channels=320, out_channels=80, channels=[256, 256], dropout=0.0, attention_head_dim=64,
+                             n_blocks=n_blocks, num_mid_blocks=n_mid, num_heads=8, act_fn="gelu").eval()
+    dec.load_state_dict(synth.synth_cv1_decoder_state_dict(0, n_blocks, n_mid), strict=True)
+    from . import cases
+    out = {"n_blocks": np.int64(n_blocks), "n_mid": np.int64(n_mid)}
+    for tag, T, lens in (("a", 77, (77, 61)), ("b", 130, (130, 97))):
+        c = cases.estimator_inputs(T, 8800 + T, lens=list(lens))
+        with torch.inference_mode():
+            y = dec(c["x"], c["mask"], c["mu"], c["t"], c["spks"], c["cond"])
+        out.update({f"{tag}_T": np.int64(T), f"{tag}_lens": np.asarray(lens), f"{tag}_out": y,
+                    f"{tag}_fp": cases.fingerprint(c["x"], c["cond"], c["spks"])})
+    _save("cv1_decoder.npz", **out)
+
+
 if __name__ == "__main__":
-    main()
+    import sys
+    if "decoder" in sys.argv[1:]:
+        decoder_golden()
+    else:
+        main()

@@ -424,3 +424,37 @@ def cv1_downsample(sd, p, x):
 def cv1_upsample(sd, p, x):
     """Upsample1D (use_conv_transpose), matcha decoder.py:120-158: ConvTranspose1d(C, C, 4, stride 2, padding 1)."""
     return F.conv_transpose1d(x, sd[p + "conv.weight"], sd[p + "conv.bias"], stride=2, padding=1)
+
+
+def cv1_decoder(sd, x, mask, mu, t, spks, cond, n_blocks=4, n_mid=12):
+    """ConditionalDecoder.forward of the NON-causal decoder, cosyvoice/flow/decoder.py:206-291 (cosyvoice1/flow/decoder.py:151-222
+    is the same graph), channels = [256, 256]: two resolutions, skip concatenation, GroupNorm resnets, key-padding attention."""
+    temb = _sinusoidal(t)
+    temb = F.linear(F.silu(F.linear(temb, sd["time_mlp.linear_1.weight"], sd["time_mlp.linear_1.bias"])),
+                    sd["time_mlp.linear_2.weight"], sd["time_mlp.linear_2.bias"])
+    x = torch.cat([x, mu, spks.unsqueeze(-1).expand(-1, -1, x.shape[-1]), cond], dim=1)
+
+    def level(x, m, p):
+        x = cv1_resnet_block(sd, p + ".0.", x, m, temb)
+        bias = _attn_bias(m, 0)                                       # add_optional_chunk_mask(..., 0, 0, -1) + mask_to_bias
+        x = x.transpose(1, 2)
+        for j in range(n_blocks):
+            x = _transformer(x, bias, sd, p + f".1.{j}.")
+        return x.transpose(1, 2)
+
+    m0 = mask
+    x = level(x, m0, "down_blocks.0")
+    skip0 = x
+    x = cv1_downsample(sd, "down_blocks.0.2.", x * m0)
+    m1 = m0[:, :, ::2]
+    x = level(x, m1, "down_blocks.1")
+    skip1 = x
+    x = F.conv1d(x * m1, sd["down_blocks.1.2.weight"], sd["down_blocks.1.2.bias"], padding=1)
+    for i in range(n_mid):
+        x = level(x, m1, f"mid_blocks.{i}")
+    x = level(torch.cat([x[:, :, :skip1.shape[-1]], skip1], dim=1), m1, "up_blocks.0")
+    x = cv1_upsample(sd, "up_blocks.0.2.", x * m1)
+    x = level(torch.cat([x[:, :, :skip0.shape[-1]], skip0], dim=1), m0, "up_blocks.1")
+    x = F.conv1d(x * m0, sd["up_blocks.1.2.weight"], sd["up_blocks.1.2.bias"], padding=1)
+    x = cv1_block1d(x, m0, sd, "final_block.")
+    return F.conv1d(x * m0, sd["final_proj.weight"], sd["final_proj.bias"]) * m0

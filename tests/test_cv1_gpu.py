@@ -121,3 +121,61 @@ def test_cv1_edge_lengths_match_oracle(cv1, B, T):
         err = rel_l2(o.cpu(), ref)
         print(f"cv1 edge B={B} T={T} {name}: rel_l2={err:.3e}")
         assert err < tol, name
+
+
+# ------------------------------------------------------------------ the assembled two-level decoder (mossdec_cv1_estimator)
+def _cv1_decoder_engine(n_blocks, n_mid):
+    from moss_speech_decoder_cosy_b200 import lib, synth, weights
+    eng = lib.Engine()
+    t = weights.pack_estimator(synth.synth_flow_state_dict(0))         # the engine needs the live estimator to finalize
+    t.update(weights.pack_cv1_decoder(synth.synth_cv1_decoder_state_dict(0, n_blocks, n_mid), "cv1d", n_blocks, n_mid))
+    eng.load_tensors(t)
+    eng.finalize()
+    return eng
+
+
+@pytest.mark.parametrize("tag", ["a", "b"])
+def test_cv1_decoder_matches_reference(tag):
+    """ConditionalDecoder.forward (non-causal, channels [256, 256], cosyvoice/flow/decoder.py:206-291): two resolutions, skip
+    concatenation, GroupNorm resnets, key-padding attention, stride-2 down / ConvTranspose up -- vs the golden of the
+    unmodified reference class; ragged masks, odd (77) and even (130) lengths."""
+    import os
+    import numpy as np
+    from conftest import GOLDEN
+    from oracle import cases
+    z = np.load(os.path.join(GOLDEN, "cv1_decoder.npz"))
+    nb, nm = int(z["n_blocks"]), int(z["n_mid"])
+    T, lens = int(z[f"{tag}_T"]), [int(v) for v in z[f"{tag}_lens"]]
+    c = cases.estimator_inputs(T, 8800 + T, lens=lens)
+    if not np.allclose(cases.fingerprint(c["x"], c["cond"], c["spks"]), z[f"{tag}_fp"], rtol=1e-6, atol=1e-6):
+        pytest.skip("torch CPU generator differs from the build that produced the fixture")
+    eng = _cv1_decoder_engine(nb, nm)
+    d = {k: v.cuda() for k, v in c.items()}
+    out = eng.cv1_estimator("cv1d", nb, nm, d["x"], d["mask"], d["mu"], d["t"], d["spks"], d["cond"])
+    torch.cuda.synchronize()
+    ref = torch.from_numpy(z[f"{tag}_out"]).cuda()
+    e = float(torch.linalg.norm(out.double() - ref.double()) / torch.linalg.norm(ref.double()))
+    print(f"cv1 decoder {tag} (T={T}, lens {lens}, {nb} blocks x {nm + 4} levels): rel_l2 {e:.3e}")
+    assert torch.isfinite(out).all()
+    assert float(out[1, :, lens[1]:].abs().max()) == 0.0
+    assert e < 1.6e-2
+
+
+def test_cv1_decoder_full_depth_vs_oracle():
+    """The CosyVoice-300M depth (4 blocks per level, 12 mid blocks) at T = 500 against the oracle on the host cores."""
+    import os
+    from moss_speech_decoder_cosy_b200 import synth
+    from oracle import cases, port
+    torch.set_num_threads(os.cpu_count() or 1)
+    nb, nm, T, lens = 4, 12, 500, [500, 333]
+    c = cases.estimator_inputs(T, 8899, lens=lens)
+    eng = _cv1_decoder_engine(nb, nm)
+    d = {k: v.cuda() for k, v in c.items()}
+    out = eng.cv1_estimator("cv1d", nb, nm, d["x"], d["mask"], d["mu"], d["t"], d["spks"], d["cond"])
+    torch.cuda.synchronize()
+    with torch.inference_mode():
+        ref = port.cv1_decoder(synth.synth_cv1_decoder_state_dict(0, nb, nm), c["x"], c["mask"], c["mu"], c["t"], c["spks"],
+                               c["cond"], nb, nm)
+    e = float(torch.linalg.norm(out.double().cpu() - ref.double()) / torch.linalg.norm(ref.double()))
+    print(f"cv1 decoder full depth T={T}: rel_l2 {e:.3e}")
+    assert e < 1.6e-2

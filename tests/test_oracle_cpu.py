@@ -172,3 +172,21 @@ def test_mel_spectrogram_restatement(tag):
     assert mel.shape == ref.shape == (80, n // 480)
     assert float(ref.min()) < -8.5 and float(ref.max()) > 1.0       # the fixture spans 10 nepers: near-silence to loud frames
     torch.testing.assert_close(mel, ref, rtol=1e-5, atol=1e-5)
+
+
+@pytest.mark.parametrize("tag", ["a", "b"])
+def test_cv1_decoder_restatement(tag):
+    """Row A9: oracle/port.py:cv1_decoder against the UNMODIFIED non-causal ConditionalDecoder (channels [256, 256])."""
+    from oracle import cases
+    z = np.load(os.path.join(GOLDEN, "cv1_decoder.npz"))
+    nb, nm = int(z["n_blocks"]), int(z["n_mid"])
+    T, lens = int(z[f"{tag}_T"]), [int(v) for v in z[f"{tag}_lens"]]
+    c = cases.estimator_inputs(T, 8800 + T, lens=lens)
+    if not np.allclose(cases.fingerprint(c["x"], c["cond"], c["spks"]), z[f"{tag}_fp"], rtol=1e-6, atol=1e-6):
+        pytest.skip("torch CPU generator differs from the build that produced the fixture")
+    sd = synth.synth_cv1_decoder_state_dict(0, nb, nm)
+    with torch.inference_mode():
+        out = port.cv1_decoder(sd, c["x"], c["mask"], c["mu"], c["t"], c["spks"], c["cond"], nb, nm)
+    ref = torch.from_numpy(z[f"{tag}_out"])
+    assert out.shape == ref.shape and float(ref[1, :, lens[1]:].abs().max()) == 0.0
+    assert _rel(out, ref) < 1e-5
