@@ -143,13 +143,19 @@ def stream_inference(dec, token, prompt_token, prompt_feat, embedding, block_siz
 
 
 class Stream:
-    """One concurrent session of the batched scheduler."""
+    """One concurrent session of the batched scheduler.  Tokens may be given up front (`ended=True`, the offline
+    `stream_inference` case) or pushed while the stream runs (`push` / `finish`: the server case, where the language model
+    produces them); the chunk schedule is that of stream_inference (flow_inference.py:186-232) evaluated lazily --
+    `next_chunk()` yields exactly the entries of `chunk_plan` for the tokens seen so far."""
     _next_tag = 1
 
-    def __init__(self, tokens, prompt_token, prompt_feat, embedding, block_size, max_token_len):
+    def __init__(self, tokens, prompt_token, prompt_feat, embedding, block_size, max_token_len, ended=True):
         self.tokens = [int(t) for t in tokens]
         self.prompt_token, self.prompt_feat, self.embedding = prompt_token, prompt_feat, embedding
-        self.plan = chunk_plan(len(self.tokens), prompt_token.shape[1], block_size, max_token_len)
+        self.block_size, self.max_token_len = block_size, max_token_len
+        self.ended = bool(ended)
+        self.token_offset, self.finalized = 0, False
+        self.pad = int(np.ceil(prompt_token.shape[1] / block_size) * block_size - prompt_token.shape[1])
         self.step = 0
         self.cache = None
         self.out = []
@@ -157,9 +163,50 @@ class Stream:
         self.tag = Stream._next_tag                        # identity of its frozen inputs (prompt, speaker)
         Stream._next_tag += 1
 
+    def push(self, tokens):
+        if self.ended:
+            raise ValueError("stream already finished")
+        self.tokens.extend(int(t) for t in tokens)
+
+    def finish(self):
+        self.ended = True
+
+    def cancel(self):
+        """Drop the stream (client went away): nothing more is decoded for it."""
+        self.ended = self.finalized = True
+
+    def next_chunk(self):
+        """(start, end, actual_token_offset, finalize) of the chunk that can be decoded now, or None (waiting for tokens)."""
+        if self.finalized:
+            return None
+        n = len(self.tokens)
+        this_hop = self.block_size + self.pad if self.token_offset == 0 else self.block_size
+        if n - self.token_offset >= this_hop + PRE_LOOKAHEAD:
+            end = self.token_offset + this_hop + PRE_LOOKAHEAD
+            if self.max_token_len is not None:
+                start = max(0, end - self.max_token_len)
+                actual = self.token_offset - start if start > 0 else self.token_offset
+            else:
+                start, actual = 0, self.token_offset
+            return (start, end, actual, False)
+        if not self.ended:
+            return None
+        if self.max_token_len is not None:
+            start = max(0, n - self.max_token_len)
+            return (start, n, self.token_offset - start, True)
+        return (0, n, self.token_offset, True)
+
+    def advance(self, chunk):
+        """Bookkeeping after `chunk` (a value of next_chunk) has been decoded."""
+        if chunk[3]:
+            self.finalized = True
+        else:
+            self.token_offset += self.block_size + self.pad if self.token_offset == 0 else self.block_size
+        self.step += 1
+
     @property
     def done(self):
-        return self.step >= len(self.plan)
+        return self.finalized
 
 
 class StreamScheduler:
@@ -177,10 +224,24 @@ class StreamScheduler:
         self.streams = []
         self.prefix_cache = bool(prefix_cache)
         self._cap, self._prefix_frames = 0, 0
+        self._free = []                                    # indices of released streams, reused by add()
 
-    def add(self, tokens, prompt_token, prompt_feat, embedding):
-        self.streams.append(Stream(tokens, prompt_token, prompt_feat, embedding, self.block_size, self.max_token_len))
+    def add(self, tokens, prompt_token, prompt_feat, embedding, ended=True):
+        """New stream; with ended=False more tokens follow through streams[i].push(...) / .finish()."""
+        s = Stream(tokens, prompt_token, prompt_feat, embedding, self.block_size, self.max_token_len, ended)
+        if self._free:                                     # a released position: its prefix-cache slot is re-recorded (new tag)
+            i = self._free.pop()
+            self.streams[i] = s
+            return i
+        self.streams.append(s)
         return len(self.streams) - 1
+
+    def release(self, i):
+        """Give position i (and its prefix-cache slot) back; a long-running server calls this when a connection ends."""
+        self.streams[i].cancel()
+        self.streams[i].out = []
+        if i not in self._free:
+            self._free.append(i)
 
     def _prefix_frames_for(self, s):
         """Frames of the frozen prefix a stream supports: whole estimator chunks (== whole encoder chunks) that lie inside the
@@ -216,8 +277,10 @@ class StreamScheduler:
         dec = self.dec
         emitted = {}
         self._ensure_cache()
+        ready = {i: s.next_chunk() for i, s in enumerate(self.streams) if not s.done}
+        ready = {i: c for i, c in ready.items() if c is not None}
         for fin in (False, True):
-            live = [i for i, s in enumerate(self.streams) if not s.done and s.plan[s.step][3] == fin]
+            live = [i for i, c in ready.items() if c[3] == fin]
             # non-final chunks: streams with a recorded prefix reuse it (mode 2), eligible new ones record it (mode 1)
             groups = {0: [], 1: [], 2: []}
             for i in live:
@@ -230,7 +293,7 @@ class StreamScheduler:
                 toks, offs = [], []
                 for i in ids:
                     s = self.streams[i]
-                    start, end, actual, _ = s.plan[s.step]
+                    start, end, actual, _ = ready[i]
                     toks.append(torch.tensor(s.tokens[start:end]).unsqueeze(0))
                     offs.append(actual)
                 emb = torch.cat([self.streams[i].embedding.reshape(1, -1) for i in ids], 0)
@@ -250,7 +313,7 @@ class StreamScheduler:
                 for k, i in enumerate(ids):
                     s = self.streams[i]
                     s.cache = caches[k]
-                    s.step += 1
+                    s.advance(ready[i])
                     s.out.append(out[k])
                     emitted[i] = out[k]
                     if mode == 1:
