@@ -148,6 +148,27 @@ int mossdec_fade_in_out(mossdec_handle* h, float* speech, const float* prev_tail
  * negative on error. */
 int32_t mossdec_mel_spectrogram(mossdec_handle* h, const float* wav, int64_t n_samples, float* mel_out, void* stream);
 
+/* Allocation-free variant of mossdec_mel_spectrogram.  It has NO counterpart in the reference: it was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  Same arguments, same kernels and the same result as mossdec_mel_spectrogram, but the workspace
+ * (padded signal, spectrum, magnitude, mel energies) is a file-scope `static __device__` array inside libmossdec.so instead
+ * of a growable cudaMalloc buffer, so no call -- the first one included -- calls cudaMalloc, cudaFree or an allocating
+ * library routine.
+ *   limit : T = n_samples / 480 <= MOSSDEC_MEL_STATIC_MAX_FRAMES (512 frames = 10.24 s at 24 kHz, n_samples <= 246239); longer
+ *           inputs are rejected with an error (negative return, text via mossdec_last_error) and must use
+ *           mossdec_mel_spectrogram.
+ *   cost  : MOSSDEC_MEL_STATIC_SCRATCH_BYTES (7.2 MiB) of device memory on every GPU that loads the library, held until the
+ *           process exits, whether or not this entry point is ever called.
+ *   races : every call on a device shares the one array (calls through different handles too).  Calls that overlap on the
+ *           GPU (different streams without an ordering between them) race; calls on one stream are ordered by the stream.
+ *           The array keeps the previous call's contents: the entry point rewrites or clears everything it later reads.
+ *   set-up: the first call on a device resolves the array's device address (cudaGetSymbolAddress, with the handle's device
+ *           current); like any first launch it loads the module, so make one warm-up call before starting a capture.
+ * wav, mel_out: device pointers owned by the caller as above (mel_out: 80 * (n_samples / 480) floats).  Returns T. */
+#define MOSSDEC_MEL_STATIC_MAX_FRAMES 512
+#define MOSSDEC_MEL_STATIC_SCRATCH_BYTES 7544832
+int32_t mossdec_mel_spectrogram_static(mossdec_handle* h, const float* wav, int64_t n_samples, float* mel_out, void* stream);
+
 /* ---- Secondary configuration: building blocks of the NON-causal cosyvoice1 / Matcha
  * estimator (GLM_modules/cosyvoice1 uses third_party/Matcha-TTS/matcha/models/components/decoder.py).  Dense
  * [B, C, T] fp32 tensors exactly as the reference modules take them; block width 256, GroupNorm(8).  Weights are the

@@ -108,6 +108,10 @@ int32_t mossdec_mel_spectrogram(mossdec_handle* h, const float* wav, int64_t n_s
     return h->eng->mel_spectrogram(wav, n_samples, mel_out, (cudaStream_t)stream);
 }
 
+int32_t mossdec_mel_spectrogram_static(mossdec_handle* h, const float* wav, int64_t n_samples, float* mel_out, void* stream) {
+    return h->eng->mel_spectrogram_static(wav, n_samples, mel_out, (cudaStream_t)stream);
+}
+
 int mossdec_cv1_resnet_block(mossdec_handle* h, const char* prefix, int32_t B, int32_t T, int32_t Cin, const float* x,
                              const float* mask, const float* time_emb, int32_t time_dim, float* out, void* stream) {
     return h->eng->cv1_resnet_block(prefix, B, T, Cin, x, mask, time_emb, time_dim, out, (cudaStream_t)stream);

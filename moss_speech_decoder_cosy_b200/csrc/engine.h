@@ -135,6 +135,8 @@ class Engine {
     // matcha mel_spectrogram (n_fft 1920, hop 480, 80 mels, 24 kHz, fmax 8000, center False; mel_kernels.cu):
     // wav device [L] -> mel_out device [80, T], T = (L - 480) / 480 + 1.  Returns T, negative on error.
     int mel_spectrogram(const float* wav, int64_t L, float* mel_out, cudaStream_t st);
+    // the same on a file-scope static device scratch (<= 512 frames): no cudaMalloc / cudaFree on any call (mel_kernels.cu)
+    int mel_spectrogram_static(const float* wav, int64_t L, float* mel_out, cudaStream_t st);
     // Building blocks of the non-causal cosyvoice1 / Matcha estimator (cv1_ops.cu): dense
     // [B, C, T] fp32 in / out like the reference modules, weights looked up as "<prefix>.*" (weights.py pack_cv1_*).
     int cv1_resnet_block(const char* prefix, int B, int T, int Cin, const float* x, const float* mask, const float* temb,

@@ -64,6 +64,8 @@ def load_library():
     lib.mossdec_fade_in_out.restype = i32
     lib.mossdec_mel_spectrogram.argtypes = [vp, vp, i64, vp, vp]
     lib.mossdec_mel_spectrogram.restype = i32
+    lib.mossdec_mel_spectrogram_static.argtypes = [vp, vp, i64, vp, vp]
+    lib.mossdec_mel_spectrogram_static.restype = i32
     lib.mossdec_cv1_resnet_block.argtypes = [vp, ctypes.c_char_p, i32, i32, i32, vp, vp, vp, i32, vp, vp]
     lib.mossdec_cv1_resnet_block.restype = i32
     lib.mossdec_cv1_block1d.argtypes = [vp, ctypes.c_char_p, i32, i32, i32, vp, vp, vp, vp]
@@ -106,7 +108,7 @@ EXPORTED_SYMBOLS = [
     "mossdec_launch_count", "mossdec_reset_launch_count", "mossdec_debug_read", "mossdec_profile",
     "mossdec_profile_read", "mossdec_set_hift_group_frames", "mossdec_cv1_resnet_block", "mossdec_cv1_downsample",
     "mossdec_cv1_upsample", "mossdec_cv1_block1d", "mossdec_reserve", "mossdec_set_graph_mode", "mossdec_graph_replays",
-    "mossdec_device", "mossdec_profile_named", "mossdec_mel_spectrogram", "mossdec_hift_skip", "mossdec_token2mel", "mossdec_prefix_reserve", "mossdec_token2mel_prefix", "mossdec_cv1_estimator",
+    "mossdec_device", "mossdec_profile_named", "mossdec_mel_spectrogram", "mossdec_mel_spectrogram_static", "mossdec_hift_skip", "mossdec_token2mel", "mossdec_prefix_reserve", "mossdec_token2mel_prefix", "mossdec_cv1_estimator",
 ]
 
 
@@ -267,6 +269,21 @@ class Engine:
         if T < 0:
             raise RuntimeError(f"mel_spectrogram failed: {self.lib.mossdec_last_error(self.h).decode()}")
         assert T == out.shape[1], (T, out.shape)
+        return out
+
+    MEL_STATIC_MAX_FRAMES = 512
+
+    def mel_spectrogram_static(self, wav, out):
+        """mossdec_mel_spectrogram_static: the same result on the library's static device scratch -- the native call allocates
+        nothing, so `out` ([80, L // 480] fp32 CUDA) comes from the caller; L // 480 <= MEL_STATIC_MAX_FRAMES."""
+        L = wav.numel()
+        if wav.dtype != torch.float32 or not wav.is_contiguous() or out.dtype != torch.float32 or not out.is_contiguous():
+            raise ValueError("mel_spectrogram_static takes contiguous fp32 tensors (it does not copy or allocate)")
+        if out.numel() != 80 * (L // 480):
+            raise ValueError(f"out must hold 80 x {L // 480} floats")
+        T = self.lib.mossdec_mel_spectrogram_static(self.h, _ptr(wav), L, _ptr(out), self._stream())
+        if T < 0:
+            raise RuntimeError(f"mel_spectrogram_static failed: {self.lib.mossdec_last_error(self.h).decode()}")
         return out
 
     # ---- cosyvoice1 / Matcha non-causal building blocks (SURVEY 8 row A9); same call shapes as the reference modules
