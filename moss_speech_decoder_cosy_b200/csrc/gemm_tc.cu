@@ -896,6 +896,13 @@ cudaError_t gemm_tc_launch(const GemmProblem& g, int num_sms, cudaStream_t strea
     }
     kp.num_units = (kp.num_tiles + kp.group - 1) / kp.group;
     const int grid = kp.num_units < num_sms ? kp.num_units : num_sms;
+    static const bool trace = getenv("MOSSDEC_GEMM_TRACE") != nullptr;   // developer aid: the first launches' geometry on stderr
+    static int traced = 0;
+    if (trace && traced < 40) {
+        ++traced;
+        fprintf(stderr, "[mossdec] gemm M=%d N=%d BN=%d K=%d segs=%d group=%d a_stationary=%d grid=%d\n", g.M, g.N, g.BN, (int)K,
+                g.num_segs, kp.group, kp.a_stationary, grid);
+    }
     cudaError_t le;
     if (lnact_a) le = launch_pdl(gemm_tc_kernel<3>, dim3(grid), dim3(kThreads), kSmemBytes + 1024, stream, tA0, tA1, tB, tOut, kp);
     else if (lnact_b) le = launch_pdl(gemm_tc_kernel<4>, dim3(grid), dim3(kThreads), kSmemBytes + 1024, stream, tA0, tA1, tB, tOut, kp);
