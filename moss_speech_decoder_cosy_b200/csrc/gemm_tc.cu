@@ -173,9 +173,44 @@ __device__ __forceinline__ void epi_fast_half(const EpiCtx& c, const CUtensorMap
 // returns after the last TMEM read of the tile; the caller hands the accumulator back to the MMA warp
 __device__ __forceinline__ void epi_fast(const EpiCtx& c, const CUtensorMap* tmOut, int part, uint64_t* tempty_bar) {
     const KParams& p = *c.p;
-    const int wcols = p.BN >> 2;            // 64 or 32 columns per warp
+    const int wcols = p.BN >> 2;            // 64, 32 or 16 columns per warp
     const int col0 = part * wcols;          // inside the tile
     const int n = c.n0 + col0;
+    if (wcols == 16) {   // BN = 64 (vocoder C = 64 stage): one 16-column chunk, 32 rows x 32 B staging tile without swizzle
+        const GemmEpilogue& e = p.epi;
+        float v[16];
+        tmem_ld16(c.taddr + (uint32_t)col0, v);
+        tmem_ld_wait();
+        tc_fence_before();
+        __syncwarp();
+        if (c.lane == 0) mbar_arrive(tempty_bar);
+        if (e.bias) {
+#pragma unroll
+            for (int i = 0; i < 16; i += 4) {
+                const float4 b = ldg4(e.bias + n + i);
+                v[i] += b.x; v[i + 1] += b.y; v[i + 2] += b.z; v[i + 3] += b.w;
+            }
+        }
+        apply_act_vec<16>(v, e.act1, e.act1_p, e.act1_alpha ? e.act1_alpha + n : nullptr);
+        if (!c.valid) {
+#pragma unroll
+            for (int i = 0; i < 16; ++i) v[i] = 0.f;
+        }
+        if (c.lane == 0) tma_store_wait_read();
+        __syncwarp();
+        uint4 t0, t1;
+        t0.x = pack_bf16x2(v[0], v[1]); t0.y = pack_bf16x2(v[2], v[3]); t0.z = pack_bf16x2(v[4], v[5]); t0.w = pack_bf16x2(v[6], v[7]);
+        t1.x = pack_bf16x2(v[8], v[9]); t1.y = pack_bf16x2(v[10], v[11]); t1.z = pack_bf16x2(v[12], v[13]); t1.w = pack_bf16x2(v[14], v[15]);
+        *reinterpret_cast<uint4*>(c.stg + c.lane * 32) = t0;
+        *reinterpret_cast<uint4*>(c.stg + c.lane * 32 + 16) = t1;
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        __syncwarp();
+        if (c.lane == 0) {
+            tma_store_2d(tmOut, c.stg, n, c.row0);
+            tma_store_commit();
+        }
+        return;
+    }
     float va[32], vb[32];
     tmem_ld16(c.taddr + (uint32_t)col0, va);
     tmem_ld16(c.taddr + (uint32_t)(col0 + 16), va + 16);
@@ -498,12 +533,100 @@ __device__ __forceinline__ void epi_lnact(const EpiCtx& c, const CUtensorMap* tm
     }
 }
 
+// ---- "bias + fp32 residual (+ running sum) -> fp32 stream, Snake / leaky-ReLU of it -> bf16" tiles: the second conv of the
+// vocoder ResBlocks (cosyvoice/hifigan/generator.py:94-101) at C = 64 / 128, N == BN.  In the general epilogue these tiles
+// cost ~570 instructions per warp for 16 elements per thread (index arithmetic, predicates, staged row I/O): the kernel
+// ran at 4 % of the tensor pipe whatever K was.  Here a warp owns 32 rows x 16 (BN = 64) or 2 x 16 (BN = 128) columns;
+// per 16-column sub-tile the residual (and, when accumulating, the running sum) arrives by TMA in a 64B-swizzled 2 KB
+// tile -- requested BEFORE the wait for the accumulator -- the result overwrites it in place and leaves by a TMA store,
+// the bf16 side by a second one.  No per-element predicates: TMA clips the M tail, masked rows are zeroed by multiplication.
+// The fp32 tiles live in the part of the B stage slots that a BN <= 128 problem does not use (r1), the bf16 tile in the
+// warp's staging tile.
+__device__ __forceinline__ void epi_vocres(const EpiCtx& c, const CUtensorMap* tmRes, const CUtensorMap* tmF32,
+                                           const CUtensorMap* tmOut, int part, uint64_t* tfull_bar, uint32_t accphase,
+                                           uint64_t* tempty_bar, uint64_t* rbar, uint32_t& rphase, uint8_t* r1) {
+    const KParams& p = *c.p;
+    const GemmEpilogue& e = p.epi;
+    const int wcols = p.BN >> 2;   // 16 or 32 columns per warp
+    const int nsub = wcols >> 4;
+    const uint32_t swz = (uint32_t)((c.lane >> 1) & 3);   // 64B swizzle: 16-byte unit index XOR bits [7, 9) of the byte offset
+    const float keep = c.valid ? e.out_scale : 0.f;
+    for (int sub = 0; sub < nsub; ++sub) {
+        const int col = part * wcols + sub * 16;   // column inside the tile == global column (N == BN)
+        if (c.lane == 0) {
+            tma_store_wait_read();   // the previous stores of this warp have finished reading the staging tiles
+            mbar_expect_tx(rbar, e.accum_f32 ? 4096u : 2048u);
+            tma_load_2d(r1, tmRes, col, c.row0, rbar);
+            if (e.accum_f32) tma_load_2d(r1 + 2048, tmF32, col, c.row0, rbar);
+        }
+        if (sub == 0) {
+            mbar_wait(tfull_bar, accphase);
+            tc_fence_after();
+        }
+        float v[16];
+        tmem_ld16(c.taddr + (uint32_t)col, v);
+        tmem_ld_wait();
+        if (sub + 1 == nsub) {   // last TMEM read of the tile: the accumulator goes back to the MMA warp
+            tc_fence_before();
+            __syncwarp();
+            if (c.lane == 0) mbar_arrive(tempty_bar);
+        }
+        if (e.bias) {
+#pragma unroll
+            for (int i = 0; i < 16; i += 4) {
+                const float4 b = ldg4(e.bias + col + i);
+                v[i] += b.x; v[i + 1] += b.y; v[i + 2] += b.z; v[i + 3] += b.w;
+            }
+        }
+        mbar_wait(rbar, rphase);
+        rphase ^= 1;
+        uint8_t* rrow = r1 + c.lane * 64;
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            float4* q = reinterpret_cast<float4*>(rrow + ((u ^ swz) << 4));
+            float4 t = *q;
+            if (e.accum_f32) {
+                const float4 o = *reinterpret_cast<const float4*>(rrow + 2048 + ((u ^ swz) << 4));
+                t.x += o.x; t.y += o.y; t.z += o.z; t.w += o.w;
+            }
+            v[4 * u] = (v[4 * u] + t.x) * keep;
+            v[4 * u + 1] = (v[4 * u + 1] + t.y) * keep;
+            v[4 * u + 2] = (v[4 * u + 2] + t.z) * keep;
+            v[4 * u + 3] = (v[4 * u + 3] + t.w) * keep;
+            *q = make_float4(v[4 * u], v[4 * u + 1], v[4 * u + 2], v[4 * u + 3]);   // in place: the thread's own row
+        }
+        if (e.out_bf16) {
+            if (e.act2 != ACT_NONE) {
+                apply_act_vec<16>(v, e.act2, e.act2_p, e.act2_alpha ? e.act2_alpha + col : nullptr);
+                if (!c.valid) {
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) v[i] = 0.f;
+                }
+            }
+            uint4 t0, t1;
+            t0.x = pack_bf16x2(v[0], v[1]); t0.y = pack_bf16x2(v[2], v[3]); t0.z = pack_bf16x2(v[4], v[5]); t0.w = pack_bf16x2(v[6], v[7]);
+            t1.x = pack_bf16x2(v[8], v[9]); t1.y = pack_bf16x2(v[10], v[11]); t1.z = pack_bf16x2(v[12], v[13]); t1.w = pack_bf16x2(v[14], v[15]);
+            *reinterpret_cast<uint4*>(c.stg + c.lane * 32) = t0;   // 32 rows x 32 B, no swizzle
+            *reinterpret_cast<uint4*>(c.stg + c.lane * 32 + 16) = t1;
+        }
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        __syncwarp();
+        if (c.lane == 0) {
+            tma_store_2d(tmF32, r1, col, c.row0);
+            if (e.out_bf16) tma_store_2d(tmOut, c.stg, col, c.row0);
+            tma_store_commit();
+        }
+    }
+}
+
 // kMode: 0 = general epilogue, 1 = epi_fast (bias + act -> bf16), 2 = epi_resln (residual + LayerNorm),
-//        3 / 4 = epi_lnact (LayerNorm + Mish resnet blocks without / with residual + second LayerNorm)
+//        3 / 4 = epi_lnact (LayerNorm + Mish resnet blocks without / with residual + second LayerNorm),
+//        5 = epi_vocres (fp32 residual / running sum through TMA: vocoder ResBlock convs at C = 64 / 128)
 template <int kMode>
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__ CUtensorMap tmA1,
                const __grid_constant__ CUtensorMap tmB, const __grid_constant__ CUtensorMap tmOut,
+               const __grid_constant__ CUtensorMap tmRes, const __grid_constant__ CUtensorMap tmF32,
                const __grid_constant__ KParams p) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);  // stays in the shared address space (STS / LDS)
@@ -536,9 +659,14 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
             mbar_init(&tfull[i], 1);
             mbar_init(&tempty[i], kEpiWarps);
         }
+        if (kMode == 5) {
+            tma_prefetch_desc(&tmRes);
+            tma_prefetch_desc(&tmF32);
+            for (int i = 0; i < kEpiWarps; ++i) mbar_init(&bars[16 + i], 1);   // one transaction barrier per epilogue warp
+        }
         mbar_fence_init();
     }
-    if (kMode >= 3 && threadIdx.x >= 64 && threadIdx.x < 64 + 256) sBias[threadIdx.x - 64] = __ldg(p.epi.bias + threadIdx.x - 64);
+    if ((kMode == 3 || kMode == 4) && threadIdx.x >= 64 && threadIdx.x < 64 + 256) sBias[threadIdx.x - 64] = __ldg(p.epi.bias + threadIdx.x - 64);
     if (warp == 1) {
         tmem_alloc(tmem_slot, kTmemCols);
         tmem_relinquish();
@@ -639,6 +767,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
         const int cend = cbeg + cbase + (part < crem ? 1 : 0);
         int acc = 0;
         uint32_t accphase = 0;
+        [[maybe_unused]] uint32_t vr_phase = 0;
         for (int unit = blockIdx.x; unit < p.num_units; unit += gridDim.x)
         for (int ju = 0; ju < p.group; ++ju) {
             const int tile = unit * p.group + ju;
@@ -653,13 +782,21 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
             c.valid = inb && c.seq >= 0;
 
             c.taddr = tmem_base + ((uint32_t)(c.quarter * 32) << 16) + (uint32_t)acc * 256u;
+            if constexpr (kMode == 5) {
+                // fp32 staging of this warp: 4 KB behind the B tile of stage slot (ew & 3) (BN <= 128 leaves >= 16 KB of each slot free)
+                epi_vocres(c, &tmRes, &tmF32, &tmOut, part, &tfull[acc], accphase, &tempty[acc], &bars[16 + ew], vr_phase,
+                           sB + (ew & 3) * kBBytesMax + p.BN * (kGemmBK * 2) + (ew >> 2) * 4096);
+                acc ^= 1;
+                if (acc == 0) accphase ^= 1;
+                continue;
+            }
             if constexpr (kMode == 2) {
                 epi_resln(c, &tmOut, part, c.taddr, &tfull[acc], accphase, &tempty[acc]);
                 acc ^= 1;
                 if (acc == 0) accphase ^= 1;
                 continue;
             }
-            if constexpr (kMode >= 3) {
+            if constexpr (kMode == 3 || kMode == 4) {
                 if constexpr (kMode == 3) epi_lnact_single<false>(c, &tmOut, part, c.taddr, &tfull[acc], accphase, &tempty[acc], sBias);
                 else epi_lnact<true>(c, &tmOut, part, c.taddr, &tfull[acc], accphase, &tempty[acc], sBias);
                 acc ^= 1;
@@ -806,6 +943,28 @@ bool encode_2d_ex(CUtensorMap* m, const void* ptr, uint64_t cols, uint64_t rows,
     return true;
 }
 
+// any element type: dtype 0 = bf16, 1 = fp32; swizzle 0 = none, 1 = 64B, 2 = 128B (the inner box must fit the swizzle span)
+bool encode_2d_any(CUtensorMap* m, const void* ptr, int dtype, uint64_t cols, uint64_t rows, uint64_t ld, uint32_t box_cols,
+                   uint32_t box_rows, int swizzle) {
+    EncodeTiledFn fn = get_encode_fn();
+    if (!fn) return false;
+    const uint64_t esz = dtype ? 4 : 2;
+    cuuint64_t dims[2] = {cols, rows};
+    cuuint64_t strides[1] = {ld * esz};
+    cuuint32_t box[2] = {box_cols, box_rows};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = fn(m, dtype ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims,
+                    strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                    swizzle == 2 ? CU_TENSOR_MAP_SWIZZLE_128B : (swizzle == 1 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_NONE),
+                    CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        fprintf(stderr, "[mossdec] cuTensorMapEncodeTiled (%s map) failed: %d (ptr=%p cols=%llu rows=%llu ld=%llu)\n",
+                dtype ? "fp32" : "bf16", (int)r, ptr, (unsigned long long)cols, (unsigned long long)rows, (unsigned long long)ld);
+        return false;
+    }
+    return true;
+}
+
 cudaError_t gemm_tc_init_device() {
     static std::atomic<uint64_t> done{0};
     static std::mutex mu;
@@ -816,6 +975,7 @@ cudaError_t gemm_tc_init_device() {
         if (e == cudaSuccess) e = cudaFuncSetAttribute(gemm_tc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
         if (e == cudaSuccess) e = cudaFuncSetAttribute(gemm_tc_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes + 1024);
         if (e == cudaSuccess) e = cudaFuncSetAttribute(gemm_tc_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes + 1024);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(gemm_tc_kernel<5>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
         return e;
     });
 }
@@ -867,7 +1027,7 @@ cudaError_t gemm_tc_launch(const GemmProblem& g, int num_sms, cudaStream_t strea
     const GemmEpilogue& e = g.epi;
     kp.fast_bf16 = e.out_bf16 != nullptr && !e.out_f32 && !e.resid && !e.ln1_g && !e.ln2_g && !e.ln2_plain && !e.tbias &&
                    !e.out_bf16_lo && !e.accum_f32 && e.act2 == ACT_NONE && e.out_scale == 1.f &&
-                   (g.BN == 256 || g.BN == 128) && (g.N % g.BN) == 0 && (e.ldo % 8) == 0 &&
+                   (g.BN == 256 || g.BN == 128 || g.BN == 64) && (g.N % g.BN) == 0 && (e.ldo % 8) == 0 &&
                    (reinterpret_cast<uintptr_t>(e.out_bf16) & 15) == 0;
     // residual + LayerNorm epilogue of the attention out-projection (epi_resln)
     const bool resln = e.out_bf16 != nullptr && e.out_f32 != nullptr && e.resid != nullptr && e.f32_tiled && e.ln2_plain &&
@@ -883,8 +1043,29 @@ cudaError_t gemm_tc_launch(const GemmProblem& g, int num_sms, cudaStream_t strea
     const bool lnact_a = !force_general && ln_common && !e.out_f32 && !e.resid && !e.ln2_plain && (!e.tbias || (e.tbias_ld % 4) == 0);
     const bool lnact_b = !force_general && ln_common && e.out_f32 != nullptr && e.resid != nullptr && e.f32_tiled && e.ln2_plain && !e.tbias;
     CUtensorMap tOut = tB;
-    if ((kp.fast_bf16 || resln || lnact_a || lnact_b) && !encode_2d_ex(&tOut, e.out_bf16, (uint64_t)g.N, (uint64_t)g.M, (uint64_t)e.ldo, 32, 32, 1))
+    if (kp.fast_bf16 && g.BN == 64) {   // 16 columns per warp: 32-byte rows, no swizzle
+        if (!encode_2d_any(&tOut, e.out_bf16, 0, (uint64_t)g.N, (uint64_t)g.M, (uint64_t)e.ldo, 16, 32, 0)) return cudaErrorInvalidValue;
+    } else if ((kp.fast_bf16 || resln || lnact_a || lnact_b) &&
+               !encode_2d_ex(&tOut, e.out_bf16, (uint64_t)g.N, (uint64_t)g.M, (uint64_t)e.ldo, 32, 32, 1)) {
         return cudaErrorInvalidValue;
+    }
+    // fp32 residual (+ running sum) convs of the vocoder ResBlocks at C = 64 / 128 (epi_vocres); MOSSDEC_GEMM_VOCRES=0: general epilogue
+    static const bool vocres_on = [] {
+        const char* v = getenv("MOSSDEC_GEMM_VOCRES");
+        return !(v && v[0] == '0');
+    }();
+    const bool vocres = vocres_on && !force_general && e.resid != nullptr && e.out_f32 != nullptr && !e.f32_tiled && !e.ln1_g && !e.ln2_g &&
+                        !e.ln2_plain && !e.tbias && !e.out_bf16_lo && e.act1 == ACT_NONE && g.N == g.BN && (g.BN == 64 || g.BN == 128) &&
+                        e.ldr == g.N && e.ldf == g.N && (!e.out_bf16 || e.ldo == g.N) &&
+                        (reinterpret_cast<uintptr_t>(e.resid) & 15) == 0 && (reinterpret_cast<uintptr_t>(e.out_f32) & 15) == 0 &&
+                        (!e.out_bf16 || (reinterpret_cast<uintptr_t>(e.out_bf16) & 15) == 0);
+    CUtensorMap tRes = tB, tF32 = tB;
+    if (vocres) {
+        if (!encode_2d_any(&tRes, e.resid, 1, (uint64_t)g.N, (uint64_t)g.M, (uint64_t)e.ldr, 16, 32, 1) ||
+            !encode_2d_any(&tF32, e.out_f32, 1, (uint64_t)g.N, (uint64_t)g.M, (uint64_t)e.ldf, 16, 32, 1) ||
+            (e.out_bf16 && !encode_2d_any(&tOut, e.out_bf16, 0, (uint64_t)g.N, (uint64_t)g.M, (uint64_t)e.ldo, 16, 32, 0)))
+            return cudaErrorInvalidValue;
+    }
 
     // A-stationary units (see the producer): K fits the ring exactly, several N tiles per M tile, enough units to fill the GPU
     if (kp.total_kb == kGemmStages && g.num_segs == 1 && kp.tiles_n > 1) {
@@ -904,11 +1085,12 @@ cudaError_t gemm_tc_launch(const GemmProblem& g, int num_sms, cudaStream_t strea
                 g.num_segs, kp.group, kp.a_stationary, grid);
     }
     cudaError_t le;
-    if (lnact_a) le = launch_pdl(gemm_tc_kernel<3>, dim3(grid), dim3(kThreads), kSmemBytes + 1024, stream, tA0, tA1, tB, tOut, kp);
-    else if (lnact_b) le = launch_pdl(gemm_tc_kernel<4>, dim3(grid), dim3(kThreads), kSmemBytes + 1024, stream, tA0, tA1, tB, tOut, kp);
-    else if (resln) le = launch_pdl(gemm_tc_kernel<2>, dim3(grid), dim3(kThreads), kSmemBytes, stream, tA0, tA1, tB, tOut, kp);
-    else if (kp.fast_bf16) le = launch_pdl(gemm_tc_kernel<1>, dim3(grid), dim3(kThreads), kSmemBytes, stream, tA0, tA1, tB, tOut, kp);
-    else le = launch_pdl(gemm_tc_kernel<0>, dim3(grid), dim3(kThreads), kSmemBytes, stream, tA0, tA1, tB, tOut, kp);
+    if (lnact_a) le = launch_pdl(gemm_tc_kernel<3>, dim3(grid), dim3(kThreads), kSmemBytes + 1024, stream, tA0, tA1, tB, tOut, tRes, tF32, kp);
+    else if (lnact_b) le = launch_pdl(gemm_tc_kernel<4>, dim3(grid), dim3(kThreads), kSmemBytes + 1024, stream, tA0, tA1, tB, tOut, tRes, tF32, kp);
+    else if (resln) le = launch_pdl(gemm_tc_kernel<2>, dim3(grid), dim3(kThreads), kSmemBytes, stream, tA0, tA1, tB, tOut, tRes, tF32, kp);
+    else if (kp.fast_bf16) le = launch_pdl(gemm_tc_kernel<1>, dim3(grid), dim3(kThreads), kSmemBytes, stream, tA0, tA1, tB, tOut, tRes, tF32, kp);
+    else if (vocres) le = launch_pdl(gemm_tc_kernel<5>, dim3(grid), dim3(kThreads), kSmemBytes, stream, tA0, tA1, tB, tOut, tRes, tF32, kp);
+    else le = launch_pdl(gemm_tc_kernel<0>, dim3(grid), dim3(kThreads), kSmemBytes, stream, tA0, tA1, tB, tOut, tRes, tF32, kp);
     return le != cudaSuccess ? le : cudaGetLastError();
 }
 

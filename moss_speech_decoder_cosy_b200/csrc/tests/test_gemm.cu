@@ -53,6 +53,9 @@ struct Case {
 };
 
 static int run_case(const Case& c, int num_sms) {
+    if (const char* only = getenv("GEMM_ONLY")) {   // developer aid: run the cases whose name contains this string
+        if (!strstr(c.name, only)) return 0;
+    }
     int total_kb = 0;
     for (int s = 0; s < c.num_segs; ++s) total_kb += c.segs[s].nkb;
     const int K = total_kb * 64;
@@ -339,6 +342,28 @@ int main() {
             Case c = base("bench_qkv", 83712, 1536, 256, 256);
             fails += run_case(c, sms);
         }
+        // vocoder C = 64 stage (16 utterances x 61 440 rows): convs1 with the Snake epilogue, convs2 with the fp32 residual
+        for (int k : {3, 11}) {
+            Case c = base(k == 3 ? "bench_voc64_k3_snake" : "bench_voc64_k11_snake", 983040, 64, 64, 64);
+            c.num_segs = k;
+            for (int j = 0; j < k; ++j) c.segs[j] = {0, (j - (k - 1) / 2) * 3, 0, 1};
+            c.act1 = ACT_SNAKE; c.rowseq = true;
+            fails += run_case(c, sms);
+        }
+        {
+            Case c = base("bench_voc128_k7_resid", 327680, 128, 128, 128);
+            c.num_segs = 7;
+            for (int j = 0; j < 7; ++j) c.segs[j] = {0, j - 3, 0, 2};
+            c.rowseq = true; c.resid = true; c.outf32 = true; c.act2 = ACT_SNAKE;
+            fails += run_case(c, sms);
+        }
+        for (int k : {3, 11}) {
+            Case c = base(k == 3 ? "bench_voc64_k3_resid" : "bench_voc64_k11_resid", 983040, 64, 64, 64);
+            c.num_segs = k;
+            for (int j = 0; j < k; ++j) c.segs[j] = {0, j - (k - 1) / 2, 0, 1};
+            c.rowseq = true; c.resid = true; c.outf32 = true;
+            fails += run_case(c, sms);
+        }
     }
     {   // 8. N=80 projection
         Case c = base("proj_n80", 1500, 80, 80, 256); c.outf32 = true; c.outbf16 = false; c.rowseq = true;
@@ -368,6 +393,36 @@ int main() {
     }
     {   // 13. TMA-store epilogue with two warps per 64 columns (BN = 128), snake, masked rows, ragged M
         Case c = base("n128_snake_tma_store", 3001, 256, 128, 192); c.act1 = ACT_SNAKE; c.rowseq = true;
+        fails += run_case(c, sms);
+    }
+    {   // 14. vocoder ResBlock second conv, C = 64: fp32 residual -> fp32 stream + Snake bf16, masked rows, ragged M (epi_vocres)
+        Case c = base("vocres_n64_snake", 3001, 64, 64, 64);
+        c.num_segs = 3;
+        for (int j = 0; j < 3; ++j) c.segs[j] = {0, j - 1, 0, 1};
+        c.rowseq = true; c.resid = true; c.outf32 = true; c.act2 = ACT_SNAKE;
+        fails += run_case(c, sms);
+    }
+    {   // 15. same at C = 128 (two 16-column sub-tiles per warp), accumulating into the running sum with the 1/3 scale, leaky ReLU out
+        Case c = base("vocres_n128_accum", 2500, 128, 128, 128);
+        c.num_segs = 7;
+        for (int j = 0; j < 7; ++j) c.segs[j] = {0, j - 3, 0, 2};
+        c.rowseq = true; c.resid = true; c.outf32 = true; c.accum = true; c.scale = 1.f / 3.f; c.act2 = ACT_LRELU;
+        fails += run_case(c, sms);
+    }
+    {   // 16. fp32 only (no bf16 side), no bias
+        Case c = base("vocres_n64_f32only", 1000, 64, 64, 64);
+        c.num_segs = 3;
+        for (int j = 0; j < 3; ++j) c.segs[j] = {0, (j - 1) * 5, 0, 1};
+        c.bias = false; c.outbf16 = false; c.resid = true; c.outf32 = true;
+        fails += run_case(c, sms);
+    }
+    {   // 17. TMA-store epilogue at BN = 64 (16 columns per warp), Snake, masked rows, ragged M, no bias variant below
+        Case c = base("n64_snake_tma_store", 3001, 64, 64, 64);
+        c.num_segs = 3;
+        for (int j = 0; j < 3; ++j) c.segs[j] = {0, (j - 1) * 3, 0, 1};
+        c.act1 = ACT_SNAKE; c.rowseq = true;
+        fails += run_case(c, sms);
+        c.name = "n64_plain_tma_store_nobias"; c.bias = false; c.act1 = ACT_NONE; c.rowseq = false;
         fails += run_case(c, sms);
     }
     printf("%s (%d failing)\n", fails ? "SOME TESTS FAILED" : "ALL TESTS PASSED", fails);
