@@ -25,3 +25,18 @@ def test_gemm_kernel_matches_host_reference():
     assert n_pass >= 18 and "FAIL" not in r.stdout, r.stdout[-3000:]
     for case in ("vocres_n64_snake", "vocres_n128_accum", "vocres_n64_f32only", "n64_snake_tma_store", "conv3_ln_mish_res_ln2_lnact"):
         assert f"[{case}]" in r.stdout, case
+
+
+FFN_BINARY = os.path.join(os.path.dirname(BINARY), "test_ffn")
+
+
+def test_fused_transformer_tail_matches_host_reference():
+    """csrc/tests/test_ffn.cu: ffn_tc_kernel (LayerNorm + FF1 + exact-erf GELU + FF2 + residual, 2-CTA multicast clusters) against
+    a host fp64 reference, single tiles, ragged tile counts and the config-2 size."""
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    assert os.path.exists(FFN_BINARY), "lib/test_ffn is missing: run __graft_entry__.build()"
+    r = subprocess.run([FFN_BINARY], capture_output=True, text=True, timeout=600)
+    tail = "\n".join(r.stdout.strip().splitlines()[-8:])
+    print(tail)
+    assert r.returncode == 0 and "ALL OK" in r.stdout and "FAILED" not in r.stdout, tail + r.stderr[-2000:]
