@@ -68,3 +68,62 @@ def test_server_streams_match_offline_scheduler():
         print(f"connection {k}: {len(toks[k])} tokens, {n} samples, band distance vs offline scheduler {d:.2f} dB")
         assert d < 3.0
     assert sorted(sch._free) == [0, 1, 2]
+
+
+def test_http_frontdoor_batches_requests_through_the_decoder():
+    """The Gradio REST front door (http_frontdoor.py) with the real decoder: three concurrent client_streaming.sh-style requests
+    share one decode_batch call; each gets 1920 samples per token, the band-energy distance to a direct decode_batch of the same
+    inputs is at the NSF-noise floor.  The reference `.npz` carries the 24 kHz prompt waveform: its mel comes from feat_extractor."""
+    import base64
+    import io
+    import json
+    import re
+    import wave
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    from aiohttp import FormData
+    from moss_speech_decoder_cosy_b200 import http_frontdoor as fd
+    from moss_speech_decoder_cosy_b200.flow_inference import AudioDecoder
+    from oracle import cases
+    dec = AudioDecoder(seed=0)
+    g = torch.Generator().manual_seed(9)
+    P = 20
+    prompt_wav = cases.prompt_waveform(4242, P * 4 * 480 + 700).reshape(-1).numpy()
+    ref = io.BytesIO()
+    np.savez(ref, prompt_token=torch.randint(0, 16384, (P,), generator=g).numpy(), embedding=torch.randn(192, generator=g).numpy(),
+             prompt_wav=prompt_wav)
+    toks = [torch.randint(0, 16384, (n,), generator=g).numpy() for n in (30, 52, 41)]
+    door = fd.FrontDoor(dec, window_s=0.05)
+
+    async def one(tc, t):
+        form = FormData()
+        b = io.BytesIO()
+        np.save(b, t)
+        form.add_field("files", b.getvalue(), filename="tokens.npy")
+        form.add_field("files", ref.getvalue(), filename="ref.npz")
+        paths = await (await tc.post("/gradio_api/upload", data=form)).json()
+        r = await tc.post(f"/gradio_api/call/{fd.API}", json={"data": [{"path": paths[0]}, {"path": paths[1]}, 0.8]})
+        ev = (await r.json())["event_id"]
+        return (await (await tc.get(f"/gradio_api/call/{fd.API}/{ev}")).read()).decode()
+
+    async def main():
+        async with TestClient(TestServer(fd.make_app(door))) as tc:
+            return await asyncio.gather(*[one(tc, t) for t in toks])
+    texts = asyncio.run(main())
+    assert sum(door.batches) == 3 and max(door.batches) > 1, door.batches
+    # the same inputs straight through the public API
+    voice = door.reference(next(p for p in [__import__("os").path.join(door.upload_dir, f) for f in __import__("os").listdir(door.upload_dir)]
+                                if p.endswith("ref.npz")))
+    direct = dec.decode_batch([torch.from_numpy(t).reshape(1, -1) for t in toks], [voice[0]] * 3, [voice[1]] * 3, voice[2].repeat(3, 1))
+    dw, off = direct["wav"].float().cpu(), 0
+    for t, text in zip(toks, texts):
+        line = [l for l in text.splitlines() if re.match(r"^data: \[.+\]$", l)][0]
+        html = json.loads(line[6:])[0]
+        with wave.open(io.BytesIO(base64.b64decode(re.search(r"data:audio/wav;base64,([A-Za-z0-9+/=]+)", html).group(1)))) as w:
+            pcm = np.frombuffer(w.readframes(w.getnframes()), "<i2").astype(np.float32) / 32767.0
+        n = len(t) * 1920
+        assert pcm.shape == (n,) and np.isfinite(pcm).all() and np.abs(pcm).max() > 1e-3
+        d = band_db(torch.from_numpy(pcm).reshape(1, -1), dw[off:off + n].clamp(-1, 1).reshape(1, -1))
+        print(f"front door, {len(t)} tokens: band distance vs direct decode_batch {d:.2f} dB")
+        assert d < 3.0
+        off += n
