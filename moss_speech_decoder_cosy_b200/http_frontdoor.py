@@ -4,6 +4,7 @@
 
     POST /gradio_api/upload                                     multipart `files=@input  files=@reference`  -> ["<path>", "<path>"]
     POST /gradio_api/call/process_audio_nonstreaming            {"data": [{"path": ...}, {"path": ...}, 0.8]}  -> {"event_id": "..."}
+    (`process_audio_streaming` likewise, data = [input, reference, block_size, max_token_len]: chunked decode as stream_inference)
     GET  /gradio_api/call/process_audio_nonstreaming/<event_id> server-sent events: `event: heartbeat` while working, then
                                                                 `event: complete` + `data: [html, info, file]` where html embeds
                                                                 `data:audio/wav;base64,...` (the client's regex), or `event: error`
@@ -37,6 +38,7 @@ import wave
 import numpy as np
 
 API = "process_audio_nonstreaming"
+API_STREAMING = "process_audio_streaming"     # same calls, data = [input, reference, block_size, max_token_len]
 SAMPLE_RATE = 24000
 
 
@@ -96,8 +98,9 @@ def make_default_reference(decoder):
 
 
 class _Job:
-    def __init__(self, tokens, voice):
+    def __init__(self, tokens, voice, stream_params=None):
         self.tokens, self.voice = tokens, voice
+        self.stream_params = stream_params      # None: one-shot decode; (block_size, max_token_len): chunked like stream_inference
         self.done = asyncio.Event()
         self.result = None      # (html, info, file dict)
         self.error = None
@@ -136,6 +139,11 @@ class FrontDoor:
                     break
             while len(batch) < self.max_batch and not self.queue.empty():
                 batch.append(self.queue.get_nowait())
+            # one decode per kind: one-shot requests together, streaming requests of equal (block_size, max_token_len) together
+            rest = [j for j in batch if j.stream_params != first.stream_params]
+            batch = [j for j in batch if j.stream_params == first.stream_params]
+            for j in rest:
+                self.queue.put_nowait(j)
             self.batches.append(len(batch))
             try:
                 wavs = await loop.run_in_executor(None, self._decode, batch)
@@ -157,6 +165,15 @@ class FrontDoor:
 
     def _decode(self, batch):
         import torch
+        if batch[0].stream_params is not None:
+            # process_audio_streaming (gradio_voice_converter_unstreaming_streaming.py:299-401 -> decode_streaming ->
+            # stream_inference): chunked decode of every request of the batch through ONE batched stream scheduler
+            from .streaming import StreamScheduler
+            block, mtl = batch[0].stream_params
+            sched = StreamScheduler(self.decoder, block, mtl)
+            for j in batch:
+                sched.add(j.tokens.reshape(-1).tolist(), *j.voice)
+            return [w.detach().float().cpu().reshape(-1).numpy() for w in sched.run()]
         toks = [j.tokens.reshape(1, -1) for j in batch]
         ptoks = [j.voice[0] for j in batch]
         pfeats = [j.voice[1] for j in batch]
@@ -212,10 +229,17 @@ class FrontDoor:
             data = body["data"]
             tokens = self.tokenize(self._path_of(data[0]))
             voice = self.reference(self._path_of(data[1]))
+            stream_params = None
+            if request.match_info.get("api") == API_STREAMING:
+                block = int(data[2])
+                mtl = None if len(data) < 4 or data[3] in (None, 0, "") else int(data[3])
+                if block < 1 or (mtl is not None and mtl < block + 3):
+                    raise ValueError("block_size must be >= 1 and max_token_len >= block_size + 3 (the look-ahead)")
+                stream_params = (block, mtl)
         except Exception as e:   # noqa: BLE001 - the client prints the body of a failed request
             return web.json_response({"error": f"{type(e).__name__}: {e}"}, status=422)
         self._ensure_loop()
-        job = _Job(tokens, voice)
+        job = _Job(tokens, voice, stream_params)
         event_id = uuid.uuid4().hex
         self.jobs[event_id] = job
         self.queue.put_nowait(job)
@@ -247,8 +271,8 @@ def make_app(door):
     from aiohttp import web
     app = web.Application(client_max_size=256 << 20)
     app.router.add_post("/gradio_api/upload", door.upload)
-    app.router.add_post(f"/gradio_api/call/{API}", door.call)
-    app.router.add_get(f"/gradio_api/call/{API}/{{event_id}}", door.events)
+    app.router.add_post(f"/gradio_api/call/{{api:{API}|{API_STREAMING}}}", door.call)
+    app.router.add_get(f"/gradio_api/call/{{api:{API}|{API_STREAMING}}}/{{event_id}}", door.events)
     return app
 
 

@@ -144,3 +144,49 @@ def test_frontdoor_hooks_replace_the_default_parsers():
         return text
     wav = _wav_from_events(asyncio.run(main()))
     assert wav.shape == (12 * 1920,)
+
+
+def test_frontdoor_streaming_api_goes_through_the_stream_scheduler(monkeypatch):
+    """process_audio_streaming: same three calls with [input, reference, block_size, max_token_len]; requests of equal
+    parameters share one batched stream scheduler, one-shot requests queued at the same time are decoded separately."""
+    from moss_speech_decoder_cosy_b200 import streaming
+    made = []
+
+    class FakeSched:
+        def __init__(self, dec, block, mtl):
+            self.args, self.items = (block, mtl), []
+            made.append(self)
+
+        def add(self, tokens, ptok, pfeat, emb):
+            self.items.append(tokens)
+
+        def run(self):
+            return [torch.repeat_interleave(torch.tensor(t).float() / 8192.0, 1920).reshape(1, -1) for t in self.items]
+    monkeypatch.setattr(streaming, "StreamScheduler", FakeSched)
+
+    async def call(tc, api, tokens, extra):
+        form = FormData()
+        form.add_field("files", _npy(tokens), filename="tokens.npy")
+        form.add_field("files", _ref(), filename="ref.npz")
+        paths = await (await tc.post("/gradio_api/upload", data=form)).json()
+        r = await tc.post(f"/gradio_api/call/{api}", json={"data": [{"path": paths[0]}, {"path": paths[1]}] + extra})
+        body = await r.json()
+        if r.status != 200:
+            return r.status, body
+        return 200, (await (await tc.get(f"/gradio_api/call/{api}/{body['event_id']}")).read()).decode()
+
+    async def main():
+        dec = FakeDecoder()
+        door = fd.FrontDoor(dec, window_s=0.05)
+        async with TestClient(TestServer(fd.make_app(door))) as tc:
+            a, b = np.arange(40), np.arange(100, 170)
+            res = await asyncio.gather(call(tc, fd.API_STREAMING, a, [5, 40]), call(tc, fd.API_STREAMING, b, [5, 40]),
+                                       call(tc, fd.API, a, [0.8]), call(tc, fd.API_STREAMING, a, [0, 40]))
+        return dec, door, res, (a, b)
+    dec, door, res, (a, b) = asyncio.run(main())
+    assert [r[0] for r in res] == [200, 200, 200, 422] and "block_size" in res[3][1]["error"]
+    for (status, text), t in zip(res[:3], (a, b, a)):
+        wav = _wav_from_events(text)
+        assert np.abs(wav - np.repeat(t.astype(np.float32) / 8192.0, 1920)).max() < 1e-4
+    assert len(made) == 1 and made[0].args == (5, 40) and len(made[0].items) == 2      # both streaming requests in one scheduler
+    assert dec.calls == [1]                                                             # the one-shot request on its own
