@@ -150,7 +150,7 @@ static int run_case(const Case& c, int num_sms) {
     e.act2 = c.act2; e.act2_p = 0.1f; e.act2_alpha = dalpha;
 
     cudaError_t err = gemm_tc_launch(g, num_sms, 0);
-    if (getenv("GEMM_BENCH") && c.M > 20000) {
+    if (getenv("GEMM_BENCH") && c.M > 10000) {
         cudaEvent_t e0, e1;
         cudaEventCreate(&e0); cudaEventCreate(&e1);
         for (int i = 0; i < 3; ++i) gemm_tc_launch(g, num_sms, 0);
@@ -340,6 +340,10 @@ int main() {
         }
         {
             Case c = base("bench_qkv", 83712, 1536, 256, 256);
+            fails += run_case(c, sms);
+        }
+        for (int m : {41856, 20928, 10496}) {   // the same projection on a half / quarter / eighth batch: output 128 / 64 / 32 MB (L2 is 126 MB)
+            Case c = base(m == 41856 ? "bench_qkv_half" : (m == 20928 ? "bench_qkv_quarter" : "bench_qkv_eighth"), m, 1536, 256, 256);
             fails += run_case(c, sms);
         }
         // vocoder C = 64 stage (16 utterances x 61 440 rows): convs1 with the Snake epilogue, convs2 with the fp32 residual
