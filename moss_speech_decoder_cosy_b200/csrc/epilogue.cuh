@@ -24,6 +24,7 @@ struct KParams {
     int32_t M, N, BN;
     int32_t tiles_n, num_tiles, total_kb, num_segs;
     int32_t group, num_units, a_stationary;   // work unit = `group` N tiles of one M tile; A fetched once per unit (gemm_tc.cu producer)
+    int32_t b_stationary, tiles_m;            // 1: every CTA owns ONE N tile, its B tile is fetched once and stays in the ring; M tiles stream (gemm_tc.cu)
     int32_t fast_bf16;   // epilogue = bias + act1 + mask -> bf16 through TMA stores (gemm_tc.cu epi_fast)
     GemmSeg segs[kGemmMaxSegs];
     GemmEpilogue epi;

@@ -619,6 +619,50 @@ __device__ __forceinline__ void epi_vocres(const EpiCtx& c, const CUtensorMap* t
     }
 }
 
+// The it-th tile of this CTA.  Two schedules:
+//   units (default): work unit = `group` consecutive N tiles of one M tile, units strided over the CTAs; with a_stationary
+//     the A tile of a unit is fetched once (keep_a for its following N tiles);
+//   b_stationary: K fits the ring exactly and there are few N tiles -- CTA b owns N tile b % tiles_n for the whole launch,
+//     fetches its B tile ONCE (it stays in the B halves of the ring's stages) and streams the M tiles
+//     b / tiles_n, + gridDim.x / tiles_n, ...: what an SM takes in per tile drops from A / group + B to A alone
+//     (q | k | v projection: 149 KB -> 64 KB per 128 x 256 tile, against ~42 B/clk that an SM can take in).
+struct TileIter {   // incremental: no division beyond the one the unit schedule always had
+    int m0, n0;
+    bool keep_a, keep_b;
+    int unit, ju, m_tile, per_n;
+    __device__ __forceinline__ void init(const KParams& p) {
+        unit = (int)blockIdx.x;
+        ju = -1;
+        keep_a = keep_b = false;
+        if (p.b_stationary) {
+            per_n = (int)gridDim.x / p.tiles_n;            // CTAs per N tile (the grid is a multiple of tiles_n)
+            const int owner = (int)blockIdx.x / p.tiles_n;
+            n0 = ((int)blockIdx.x - owner * p.tiles_n) * p.BN;
+            m_tile = owner - per_n;
+        }
+    }
+    __device__ __forceinline__ bool next(const KParams& p) {
+        if (p.b_stationary) {
+            keep_b = ju >= 0;
+            ju = 0;
+            m_tile += per_n;
+            m0 = m_tile * kGemmBM;
+            return m_tile < p.tiles_m;
+        }
+        if (++ju == p.group) {
+            ju = 0;
+            unit += (int)gridDim.x;
+        }
+        const int tile = unit * p.group + ju;
+        if (unit >= p.num_units || tile >= p.num_tiles) return false;
+        const int mt = tile / p.tiles_n;
+        m0 = mt * kGemmBM;
+        n0 = (tile - mt * p.tiles_n) * p.BN;
+        keep_a = p.a_stationary && ju > 0;
+        return true;
+    }
+};
+
 // kMode: 0 = general epilogue, 1 = epi_fast (bias + act -> bf16), 2 = epi_resln (residual + LayerNorm),
 //        3 / 4 = epi_lnact (LayerNorm + Mish resnet blocks without / with residual + second LayerNorm),
 //        5 = epi_vocres (fp32 residual / running sum through TMA: vocoder ResBlock convs at C = 64 / 128)
@@ -688,13 +732,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
             // Work unit = `group` consecutive N tiles of one M tile.  When the whole K extent fits the ring (total_kb ==
             // stages, one segment) the A tile of a unit is fetched once and stays in its stages; only B is refilled for
             // the following N tiles (these GEMMs are bound by the bytes delivered into the SM, ~42 B/clk/SM chip-wide).
-            for (int unit = blockIdx.x; unit < p.num_units; unit += gridDim.x)
-            for (int ju = 0; ju < p.group; ++ju) {
-                const int tile = unit * p.group + ju;
-                if (tile >= p.num_tiles) break;
-                const bool keep_a = p.a_stationary && ju > 0;
-                const int m0 = (tile / p.tiles_n) * kGemmBM;
-                const int n0 = (tile % p.tiles_n) * p.BN;
+            TileIter tr;
+            for (tr.init(p); tr.next(p);) {
+                const bool keep_a = tr.keep_a, keep_b = tr.keep_b;
+                const int m0 = tr.m0, n0 = tr.n0;
                 int kb = 0;
                 for (int s = 0; s < p.num_segs; ++s) {
                     const GemmSeg sg = p.segs[s];
@@ -702,9 +743,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
                     for (int j = 0; j < sg.nkb; ++j, ++kb) {
                         mbar_wait(&empty[stage], phase ^ 1);
                         if (elect_one()) {
-                            mbar_expect_tx(&full[stage], (keep_a ? 0u : (uint32_t)kABytes) + b_bytes);
+                            mbar_expect_tx(&full[stage], (keep_a ? 0u : (uint32_t)kABytes) + (keep_b ? 0u : b_bytes));
                             if (!keep_a) tma_load_2d(sA + stage * kABytes, tmA, sg.col0 + j * kGemmBK, m0 + sg.row_shift, &full[stage]);
-                            tma_load_2d(sB + stage * kBBytesMax, &tmB, kb * kGemmBK, n0, &full[stage]);
+                            if (!keep_b) tma_load_2d(sB + stage * kBBytesMax, &tmB, kb * kGemmBK, n0, &full[stage]);
                         }
                         if (++stage == kGemmStages) {
                             stage = 0;
@@ -722,9 +763,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
             uint32_t phase = 0;
             int acc = 0;
             uint32_t accphase = 0;
-            for (int unit = blockIdx.x; unit < p.num_units; unit += gridDim.x)
-            for (int ju = 0; ju < p.group; ++ju) {
-                if (unit * p.group + ju >= p.num_tiles) break;
+            TileIter tr;
+            for (tr.init(p); tr.next(p);) {
                 mbar_wait(&tempty[acc], accphase ^ 1);
                 tc_fence_after();
                 const uint32_t d_tmem = tmem_base + (uint32_t)acc * 256u;
@@ -768,12 +808,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
         int acc = 0;
         uint32_t accphase = 0;
         [[maybe_unused]] uint32_t vr_phase = 0;
-        for (int unit = blockIdx.x; unit < p.num_units; unit += gridDim.x)
-        for (int ju = 0; ju < p.group; ++ju) {
-            const int tile = unit * p.group + ju;
-            if (tile >= p.num_tiles) break;
-            const int m0 = (tile / p.tiles_n) * kGemmBM;
-            c.n0 = (tile % p.tiles_n) * p.BN;
+        TileIter tr;
+        for (tr.init(p); tr.next(p);) {
+            const int m0 = tr.m0;
+            c.n0 = tr.n0;
             c.row0 = m0 + c.quarter * 32;
             const int row = c.row0 + lane;
             const bool inb = row < p.M;
@@ -1003,6 +1041,8 @@ cudaError_t gemm_tc_launch(const GemmProblem& g, int num_sms, cudaStream_t strea
     kp.num_tiles = tiles_m * kp.tiles_n;
     kp.group = 1;
     kp.a_stationary = 0;
+    kp.b_stationary = 0;
+    kp.tiles_m = tiles_m;
     kp.num_segs = g.num_segs;
     kp.total_kb = 0;
     for (int s = 0; s < g.num_segs; ++s) {
@@ -1076,13 +1116,26 @@ cudaError_t gemm_tc_launch(const GemmProblem& g, int num_sms, cudaStream_t strea
         }
     }
     kp.num_units = (kp.num_tiles + kp.group - 1) / kp.group;
-    const int grid = kp.num_units < num_sms ? kp.num_units : num_sms;
+    int grid = kp.num_units < num_sms ? kp.num_units : num_sms;
+    // B-stationary schedule (see TileIter): same condition on K, few N tiles, several M tiles per CTA.  MOSSDEC_GEMM_BSTAT=0: off
+    static const bool bstat_on = [] {
+        const char* v = getenv("MOSSDEC_GEMM_BSTAT");
+        return !(v && v[0] == '0');
+    }();
+    if (bstat_on && kp.total_kb == kGemmStages && g.num_segs == 1 && kp.tiles_n > 1 && kp.tiles_n <= 8 &&
+        tiles_m >= 2 * (num_sms / kp.tiles_n)) {
+        kp.b_stationary = 1;
+        kp.a_stationary = 0;
+        kp.group = 1;
+        kp.num_units = kp.num_tiles;
+        grid = (num_sms / kp.tiles_n) * kp.tiles_n;
+    }
     static const bool trace = getenv("MOSSDEC_GEMM_TRACE") != nullptr;   // developer aid: the first launches' geometry on stderr
     static int traced = 0;
     if (trace && traced < 40) {
         ++traced;
-        fprintf(stderr, "[mossdec] gemm M=%d N=%d BN=%d K=%d segs=%d group=%d a_stationary=%d grid=%d\n", g.M, g.N, g.BN, (int)K,
-                g.num_segs, kp.group, kp.a_stationary, grid);
+        fprintf(stderr, "[mossdec] gemm M=%d N=%d BN=%d K=%d segs=%d group=%d a_stationary=%d b_stationary=%d grid=%d\n", g.M, g.N, g.BN, (int)K,
+                g.num_segs, kp.group, kp.a_stationary, kp.b_stationary, grid);
     }
     cudaError_t le;
     if (lnact_a) le = launch_pdl(gemm_tc_kernel<3>, dim3(grid), dim3(kThreads), kSmemBytes + 1024, stream, tA0, tA1, tB, tOut, tRes, tF32, kp);
