@@ -272,6 +272,10 @@ int main() {
         Case c = base("qkv_n1536", 1000, 1536, 256, 256);
         fails += run_case(c, sms);
     }
+    {   // 3b. the same projection at a size that takes the B-stationary schedule (6 N tiles, 157 M tiles, ragged last tile)
+        Case c = base("qkv_bstat_raggedM", 20011, 1536, 256, 256);
+        fails += run_case(c, sms);
+    }
     {   // 4. FF1 + GELU, long persistent loop
         Case c = base("ff1_gelu_bigM", 40000, 1024, 256, 256); c.act1 = ACT_GELU;
         fails += run_case(c, sms);
