@@ -387,11 +387,15 @@ ffn_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ C
             }
             FFN_STAMP(1);
             if constexpr (kFused) {
-                // acc2 is free (this warp drained it in the previous tile): the out-projection MMAs start from zero at once and
-                // overlap the residual loads below; h1 = acc2 + hres + bo is formed in registers and written back afterwards
-                tc_fence_before();
-                __syncwarp();
-                if (lane == 0) mbar_arrive(acc2_init);
+                // acc2 is free: the out-projection MMAs start from zero at once and overlap the residual loads below; h1 = acc2 +
+                // hres + bo is formed in registers and written back afterwards.  For every tile but the CTA's first the hand-over
+                // was already made at the end of the previous tile's accumulator drain (below), so that this tile's
+                // out-projection runs under the previous tile's LayerNorm and stores.
+                if (it == 0) {
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(acc2_init);
+                }
                 const float* hrow = p.hres + tiled_f32_offset(row, part * 64);  // float4 j of the row: + j * 512 floats
                 float4 hq[4], hn[4];
 #pragma unroll
@@ -559,6 +563,15 @@ ffn_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ C
                         for (int u = 0; u < 4; ++u)
                             *reinterpret_cast<float4*>(dst + (size_t)u * 512) = make_float4(w[4 * u], w[4 * u + 1], w[4 * u + 2], w[4 * u + 3]);
                     }
+                }
+            }
+            if constexpr (kFused) {
+                // acc2 is drained into registers: hand it to the MMA thread now if this CTA has another tile (cluster-uniform
+                // trip count as in the loop header), its out-projection GEMM then overlaps the LayerNorm + stores below
+                if (((tile + (int)gridDim.x) & ~(kCluster - 1)) < p.num_tiles) {
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(acc2_init);
                 }
             }
             if (lane == 0) tma_store_wait_read();   // the previous tile's last store has long finished reading this staging tile
